@@ -1,0 +1,721 @@
+// C ABI of pgq_b200 (include/pgq_b200.h): context, CSR lifecycle, queries, helpers.
+// Thread-safety: every entry point takes the context mutex (DuckDB may enter a scalar function
+// from several worker threads at once: /root/reference/src/parallel/pipeline.cpp:79-123).
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace pgq {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_err, sizeof(g_err), fmt, ap);
+	va_end(ap);
+}
+
+static Csr *find_csr(Ctx *c, int32_t id) {
+	auto it = c->csrs.find(id);
+	if (it == c->csrs.end()) {
+		set_error("unknown csr id %d", id);
+		return nullptr;
+	}
+	return it->second;
+}
+
+static constexpr int64_t STAGE_ROWS = 4 << 20; // rows per pinned staging block (32 MiB per column)
+
+static int flush_staged(Ctx *c, Csr *g) {
+	if (g->staged == 0) return PGQ_OK;
+	size_t bytes = (size_t)g->staged * sizeof(int64_t);
+	PGQ_CUDA(cudaMemcpyAsync(g->d_src64.as<int64_t>() + g->uploaded, g->h_src, bytes, cudaMemcpyHostToDevice,
+	                         c->stream));
+	PGQ_CUDA(cudaMemcpyAsync(g->d_dst64.as<int64_t>() + g->uploaded, g->h_dst, bytes, cudaMemcpyHostToDevice,
+	                         c->stream));
+	c->stats.h2d_bytes += 2 * bytes;
+	if (g->have_eid) {
+		PGQ_CUDA(cudaMemcpyAsync(g->d_eid64.as<int64_t>() + g->uploaded, g->h_eid, bytes, cudaMemcpyHostToDevice,
+		                         c->stream));
+		c->stats.h2d_bytes += bytes;
+	}
+	PGQ_CUDA(cudaStreamSynchronize(c->stream)); // staging block is reused
+	g->uploaded += g->staged;
+	g->staged = 0;
+	return PGQ_OK;
+}
+
+static int begin_edges(Ctx *c, Csr *g, int64_t E, bool with_eid) {
+	if (g->state != Csr::CREATED) {
+		set_error("create_csr_edge: csr already has its edge array");
+		return PGQ_ERR_STATE;
+	}
+	if (E < 0) {
+		set_error("negative edge count");
+		return PGQ_ERR_INVALID;
+	}
+	g->E = E;
+	g->have_eid = with_eid;
+	if (with_eid) g->keep_rows = true;
+	size_t bytes = (size_t)(E > 0 ? E : 1) * sizeof(int64_t);
+	PGQ_TRY(g->d_src64.reserve(bytes));
+	PGQ_TRY(g->d_dst64.reserve(bytes));
+	if (with_eid) PGQ_TRY(g->d_eid64.reserve(bytes));
+	g->uploaded = 0;
+	g->staged = 0;
+	g->state = Csr::EDGES_OPEN;
+	return PGQ_OK;
+}
+
+static int finalize(Ctx *c, Csr *g) {
+	if (g->state != Csr::EDGES_OPEN) {
+		set_error("csr finalize: no open edge array");
+		return PGQ_ERR_STATE;
+	}
+	PGQ_TRY(flush_staged(c, g));
+	if (g->uploaded != g->E) {
+		set_error("create_csr_edge: got %lld rows, num_edges said %lld", (long long)g->uploaded, (long long)g->E);
+		return PGQ_ERR_MISMATCH;
+	}
+	PGQ_TRY(csr_device_build(c, g));
+	g->d_src64.release();
+	g->d_dst64.release();
+	g->d_eid64.release();
+	if (g->h_src) cudaFreeHost(g->h_src);
+	if (g->h_dst) cudaFreeHost(g->h_dst);
+	if (g->h_eid) cudaFreeHost(g->h_eid);
+	g->h_src = g->h_dst = g->h_eid = nullptr;
+	g->staged_cap = 0;
+	g->state = Csr::READY;
+	return PGQ_OK;
+}
+
+} // namespace pgq
+
+using namespace pgq;
+
+#define LOCK(ctx)                                   \
+	if (!(ctx)) {                                   \
+		pgq::set_error("null context");             \
+		return PGQ_ERR_INVALID;                     \
+	}                                               \
+	Ctx *c = &(ctx)->c;                             \
+	std::lock_guard<std::mutex> _guard(c->mu);      \
+	if (cudaSetDevice(c->device) != cudaSuccess) {  \
+		pgq::set_error("cudaSetDevice failed");     \
+		return PGQ_ERR_CUDA;                        \
+	}
+
+extern "C" {
+
+const char *pgq_last_error(void) {
+	return g_err;
+}
+
+int pgq_init(int device, pgq_ctx_t **out_ctx) {
+	if (!out_ctx) return PGQ_ERR_INVALID;
+	*out_ctx = nullptr;
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0) {
+		set_error("no CUDA device: %s (pgq_b200 has no CPU fallback)", cudaGetErrorString(e));
+		(void)cudaGetLastError();
+		return PGQ_ERR_CUDA;
+	}
+	if (device < 0 || device >= ndev) {
+		set_error("device %d out of range (%d devices)", device, ndev);
+		return PGQ_ERR_INVALID;
+	}
+	PGQ_CUDA(cudaSetDevice(device));
+	cudaDeviceProp prop;
+	PGQ_CUDA(cudaGetDeviceProperties(&prop, device));
+	if (prop.major < 10) {
+		set_error("device %d is sm_%d%d; pgq_b200 is built for sm_100a only", device, prop.major, prop.minor);
+		return PGQ_ERR_CUDA;
+	}
+	pgq_ctx_t *ctx = new pgq_ctx_t();
+	Ctx *c = &ctx->c;
+	c->device = device;
+	c->sm_count = prop.multiProcessorCount;
+	PGQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+	PGQ_CUDA(cudaEventCreate(&c->ev_a));
+	PGQ_CUDA(cudaEventCreate(&c->ev_b));
+	PGQ_CUDA(cudaEventCreate(&c->ev_timer));
+	PGQ_CUDA(cudaEventCreate(&c->ev_timer2));
+	PGQ_CUDA(cudaHostAlloc(&c->h_ctrl, 4096, cudaHostAllocDefault));
+	*out_ctx = ctx;
+	return PGQ_OK;
+}
+
+int pgq_shutdown(pgq_ctx_t *ctx) {
+	if (!ctx) return PGQ_OK;
+	Ctx *c = &ctx->c;
+	cudaSetDevice(c->device);
+	cudaStreamSynchronize(c->stream);
+	for (auto &kv : c->csrs) {
+		kv.second->free_all();
+		delete kv.second;
+	}
+	c->csrs.clear();
+	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
+	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->bfs_seen, &c->bfs_visit[0],
+	                  &c->bfs_visit[1], &c->bfs_parent, &c->bfs_hubacc, &c->bfs_lane, &c->bfs_ctrl, &c->l2_flush};
+	for (DevBuf *b : bufs) b->release();
+	if (c->h_ctrl) cudaFreeHost(c->h_ctrl);
+	cudaEventDestroy(c->ev_a);
+	cudaEventDestroy(c->ev_b);
+	cudaEventDestroy(c->ev_timer);
+	cudaEventDestroy(c->ev_timer2);
+	cudaStreamDestroy(c->stream);
+	delete ctx;
+	return PGQ_OK;
+}
+
+int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
+	LOCK(ctx);
+	if (!key) return PGQ_ERR_INVALID;
+	if (!strcmp(key, "lanes")) {
+		if (value != 0 && value != 64 && value != 128 && value != 256 && value != 512) {
+			set_error("lanes must be 0 (auto), 64, 128, 256 or 512");
+			return PGQ_ERR_INVALID;
+		}
+		c->opt.lanes = value;
+	} else if (!strcmp(key, "stats")) c->opt.stats = value;
+	else if (!strcmp(key, "timing")) c->opt.timing = value;
+	else if (!strcmp(key, "small_max")) c->opt.small_max = value < 0 ? 0 : value;
+	else if (!strcmp(key, "hub_min")) c->opt.hub_min = value < 1 ? 1 : value;
+	else if (!strcmp(key, "hub_chunk")) c->opt.hub_chunk = value < 256 ? 256 : value;
+	else if (!strcmp(key, "direction")) c->opt.direction = value;
+	else {
+		set_error("unknown option '%s'", key);
+		return PGQ_ERR_INVALID;
+	}
+	return PGQ_OK;
+}
+
+int pgq_get_stats(pgq_ctx_t *ctx, pgq_stats_t *out) {
+	LOCK(ctx);
+	if (!out) return PGQ_ERR_INVALID;
+	*out = c->stats;
+	return PGQ_OK;
+}
+
+int pgq_reset_stats(pgq_ctx_t *ctx) {
+	LOCK(ctx);
+	double b = c->stats.csr_build_ms, t = c->stats.transpose_ms;
+	memset(&c->stats, 0, sizeof(c->stats));
+	c->stats.csr_build_ms = b;
+	c->stats.transpose_ms = t;
+	return PGQ_OK;
+}
+
+// ---- CSR lifecycle ------------------------------------------------------------------------
+
+int pgq_csr_create(pgq_ctx_t *ctx, int32_t id, int64_t v_size) {
+	LOCK(ctx);
+	if (v_size < 0) {
+		set_error("negative v_size");
+		return PGQ_ERR_INVALID;
+	}
+	auto it = c->csrs.find(id);
+	if (it != c->csrs.end()) { // re-creating an id replaces it (the reference deletes after the query)
+		it->second->free_all();
+		delete it->second;
+		c->csrs.erase(it);
+	}
+	Csr *g = new Csr();
+	g->V = v_size;
+	c->csrs[id] = g;
+	return PGQ_OK;
+}
+
+int pgq_csr_set_degrees(pgq_ctx_t *ctx, int32_t id, const int64_t *vid, const int64_t *cnt, int64_t n,
+                        int64_t *out_sum) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (g->state != Csr::CREATED) {
+		set_error("create_csr_vertex after create_csr_edge started");
+		return PGQ_ERR_STATE;
+	}
+	if (!g->have_cnt) {
+		g->cnt_host.assign((size_t)g->V, 0);
+		g->have_cnt = true;
+	}
+	int64_t sum = 0;
+	for (int64_t i = 0; i < n; i++) {
+		if (vid[i] < 0 || vid[i] >= g->V) {
+			set_error("create_csr_vertex: vertex id %lld outside [0,%lld)", (long long)vid[i], (long long)g->V);
+			return PGQ_ERR_INVALID;
+		}
+		g->cnt_host[(size_t)vid[i]] = cnt[i];
+		sum += cnt[i];
+	}
+	if (out_sum) *out_sum += sum;
+	return PGQ_OK;
+}
+
+int pgq_csr_begin_edges(pgq_ctx_t *ctx, int32_t id, int64_t e_size) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	g->E = e_size;
+	g->state = Csr::CREATED;
+	g->pending_begin = true;
+	return PGQ_OK;
+}
+
+int pgq_csr_add_edges(pgq_ctx_t *ctx, int32_t id, const int64_t *src, const int64_t *dst, const int64_t *eid,
+                      int64_t n) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (g->pending_begin) { // whether edge ids exist is only known at the first row batch
+		g->pending_begin = false;
+		PGQ_TRY(begin_edges(c, g, g->E, eid != nullptr));
+	}
+	if (g->state != Csr::EDGES_OPEN) {
+		set_error("create_csr_edge before CsrInitializeEdge (pgq_csr_begin_edges)");
+		return PGQ_ERR_STATE;
+	}
+	if ((eid != nullptr) != g->have_eid) {
+		set_error("create_csr_edge: edge ids given for some rows only");
+		return PGQ_ERR_INVALID;
+	}
+	if (g->uploaded + g->staged + n > g->E) {
+		set_error("create_csr_edge: more rows than num_edges=%lld", (long long)g->E);
+		return PGQ_ERR_MISMATCH;
+	}
+	if (!g->h_src) {
+		g->staged_cap = g->E < STAGE_ROWS ? (g->E > 0 ? g->E : 1) : STAGE_ROWS;
+		size_t bytes = (size_t)g->staged_cap * sizeof(int64_t);
+		PGQ_CUDA(cudaHostAlloc((void **)&g->h_src, bytes, cudaHostAllocDefault));
+		PGQ_CUDA(cudaHostAlloc((void **)&g->h_dst, bytes, cudaHostAllocDefault));
+		if (g->have_eid) PGQ_CUDA(cudaHostAlloc((void **)&g->h_eid, bytes, cudaHostAllocDefault));
+	}
+	int64_t done = 0;
+	while (done < n) {
+		int64_t room = g->staged_cap - g->staged;
+		int64_t k = n - done < room ? n - done : room;
+		memcpy(g->h_src + g->staged, src + done, (size_t)k * sizeof(int64_t));
+		memcpy(g->h_dst + g->staged, dst + done, (size_t)k * sizeof(int64_t));
+		if (g->have_eid) memcpy(g->h_eid + g->staged, eid + done, (size_t)k * sizeof(int64_t));
+		g->staged += k;
+		done += k;
+		if (g->staged == g->staged_cap) PGQ_TRY(flush_staged(c, g));
+	}
+	return PGQ_OK;
+}
+
+int pgq_csr_finalize(pgq_ctx_t *ctx, int32_t id) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (g->pending_begin) { // zero edge rows arrived
+		g->pending_begin = false;
+		PGQ_TRY(begin_edges(c, g, g->E, false));
+	}
+	return finalize(c, g);
+}
+
+static int build_common(Ctx *c, int32_t id, int64_t v_size, int64_t e_size, const int64_t *src, const int64_t *dst,
+                        const int64_t *eid, int flags, bool device_ptrs) {
+	if (v_size < 0 || e_size < 0) {
+		set_error("negative size");
+		return PGQ_ERR_INVALID;
+	}
+	auto it = c->csrs.find(id);
+	if (it != c->csrs.end()) {
+		it->second->free_all();
+		delete it->second;
+		c->csrs.erase(it);
+	}
+	Csr *g = new Csr();
+	g->V = v_size;
+	c->csrs[id] = g;
+	g->keep_rows = (flags & PGQ_CSR_ROWIDS) != 0;
+	if (device_ptrs) { // inputs already resident: no staging copy of the edge table
+		g->E = e_size;
+		g->have_eid = eid != nullptr;
+		if (g->have_eid) g->keep_rows = true;
+		g->state = Csr::EDGES_OPEN;
+	} else {
+		PGQ_TRY(begin_edges(c, g, e_size, eid != nullptr));
+	}
+	size_t bytes = (size_t)e_size * sizeof(int64_t);
+	cudaMemcpyKind kind = device_ptrs ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+	if (e_size > 0) {
+		if (device_ptrs) {
+			// inputs already resident: build straight from the caller's arrays, no copy
+			g->d_src64.p = const_cast<int64_t *>(src);
+			g->d_dst64.p = const_cast<int64_t *>(dst);
+			g->borrowed_edges = true;
+			if (eid) g->d_eid64.p = const_cast<int64_t *>(eid);
+		} else {
+			PGQ_CUDA(cudaMemcpyAsync(g->d_src64.p, src, bytes, kind, c->stream));
+			PGQ_CUDA(cudaMemcpyAsync(g->d_dst64.p, dst, bytes, kind, c->stream));
+			c->stats.h2d_bytes += 2 * bytes;
+			if (eid) {
+				PGQ_CUDA(cudaMemcpyAsync(g->d_eid64.p, eid, bytes, kind, c->stream));
+				c->stats.h2d_bytes += bytes;
+			}
+		}
+	}
+	g->uploaded = e_size;
+	int rc = csr_device_build(c, g);
+	if (g->borrowed_edges) { // never free the caller's arrays
+		g->d_src64.p = nullptr; g->d_src64.cap = 0;
+		g->d_dst64.p = nullptr; g->d_dst64.cap = 0;
+		g->d_eid64.p = nullptr; g->d_eid64.cap = 0;
+		g->borrowed_edges = false;
+	}
+	g->d_src64.release();
+	g->d_dst64.release();
+	g->d_eid64.release();
+	if (rc != PGQ_OK) return rc;
+	g->state = Csr::READY;
+	return PGQ_OK;
+}
+
+int pgq_csr_build(pgq_ctx_t *ctx, int32_t id, int64_t v_size, int64_t e_size, const int64_t *src,
+                  const int64_t *dst, const int64_t *eid, int flags) {
+	LOCK(ctx);
+	return build_common(c, id, v_size, e_size, src, dst, eid, flags, false);
+}
+
+int pgq_csr_build_device(pgq_ctx_t *ctx, int32_t id, int64_t v_size, int64_t e_size, const int64_t *d_src,
+                         const int64_t *d_dst, const int64_t *d_eid, int flags) {
+	LOCK(ctx);
+	return build_common(c, id, v_size, e_size, d_src, d_dst, d_eid, flags, true);
+}
+
+__global__ void __launch_bounds__(256) widen_u32_kernel(const uint32_t *__restrict__ in, uint32_t n,
+                                                        int64_t *__restrict__ out) {
+	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) out[i] = (int64_t)in[i];
+}
+
+int pgq_csr_download(pgq_ctx_t *ctx, int32_t id, int64_t *v, int64_t *e, int64_t *eid) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (g->state != Csr::READY) {
+		set_error("csr %d not finalized", id);
+		return PGQ_ERR_STATE;
+	}
+	cudaStream_t st = c->stream;
+	if (v) {
+		PGQ_CUDA(cudaMemcpyAsync(v, g->d_off.p, (size_t)(g->V + 2) * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+		c->stats.d2h_bytes += (uint64_t)(g->V + 2) * 8;
+	}
+	TmpBuf wide;
+	if ((e || (eid && !g->have_eid)) && g->E > 0) PGQ_TRY(wide.reserve((size_t)g->E * sizeof(int64_t)));
+	if (e && g->E > 0) {
+		widen_u32_kernel<<<div_up(g->E, 256), 256, 0, st>>>(g->d_tgt.as<uint32_t>(), (uint32_t)g->E,
+		                                                    wide.as<int64_t>());
+		count_launch(c);
+		PGQ_CUDA(cudaMemcpyAsync(e, wide.p, (size_t)g->E * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+		PGQ_CUDA(cudaStreamSynchronize(st));
+		c->stats.d2h_bytes += (uint64_t)g->E * 8;
+	}
+	if (eid && g->E > 0) {
+		if (g->have_eid) {
+			PGQ_CUDA(cudaMemcpyAsync(eid, g->d_eid.p, (size_t)g->E * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+		} else if (g->keep_rows) {
+			widen_u32_kernel<<<div_up(g->E, 256), 256, 0, st>>>(g->d_row.as<uint32_t>(), (uint32_t)g->E,
+			                                                    wide.as<int64_t>());
+			count_launch(c);
+			PGQ_CUDA(cudaMemcpyAsync(eid, wide.p, (size_t)g->E * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+		} else {
+			set_error("csr %d was built without edge ids", id);
+			return PGQ_ERR_STATE;
+		}
+		c->stats.d2h_bytes += (uint64_t)g->E * 8;
+	}
+	PGQ_CUDA(cudaStreamSynchronize(st));
+	return PGQ_OK;
+}
+
+int pgq_csr_info(pgq_ctx_t *ctx, int32_t id, int64_t *v_size, int64_t *e_size) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (v_size) *v_size = g->V;
+	if (e_size) *e_size = g->E;
+	return PGQ_OK;
+}
+
+int pgq_csr_delete(pgq_ctx_t *ctx, int32_t id) {
+	LOCK(ctx);
+	auto it = c->csrs.find(id);
+	if (it == c->csrs.end()) return PGQ_OK;
+	cudaStreamSynchronize(c->stream);
+	it->second->free_all();
+	delete it->second;
+	c->csrs.erase(it);
+	return PGQ_OK;
+}
+
+int pgq_csr_prepare(pgq_ctx_t *ctx, int32_t id) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (g->state != Csr::READY) {
+		set_error("csr %d not finalized", id);
+		return PGQ_ERR_STATE;
+	}
+	return csr_prepare(c, g);
+}
+
+// ---- queries ---------------------------------------------------------------------------------
+
+// Lane filling exactly like the reference's loop: rows are consumed in order;
+// NULL rows and src==dst rows are answered without a lane; every other row takes the next lane.
+static int build_lane_table(Ctx *c, Csr *g, int64_t n, const int64_t *src, const int64_t *dst,
+                            const uint8_t *sv, const uint8_t *dv, LaneTable *lt) {
+	lt->kind.assign((size_t)n, 0);
+	int64_t need = 0;
+	for (int64_t i = 0; i < n; i++) {
+		if ((sv && !sv[i]) || (dv && !dv[i])) continue;
+		if (src[i] < 0 || src[i] >= g->V || dst[i] < 0 || dst[i] >= g->V) {
+			set_error("vertex id outside [0, v_size) in row %lld", (long long)i);
+			return PGQ_ERR_INVALID;
+		}
+		if (src[i] == dst[i]) lt->kind[i] = 1;
+		else {
+			lt->kind[i] = 2;
+			need++;
+		}
+	}
+	const int W = c->opt.lanes ? (int)c->opt.lanes : pick_lane_width(need);
+	lt->W = W;
+	int64_t started = 0;
+	while (started < n) {
+		const int64_t b = lt->nbatch;
+		lt->src.resize((size_t)(b + 1) * W, 0xFFFFFFFFu);
+		lt->dst.resize((size_t)(b + 1) * W, 0u);
+		lt->row.resize((size_t)(b + 1) * W, -1);
+		lt->batch_row_begin.push_back(started);
+		for (int lane = 0; lane < W; lane++) {
+			while (started < n) {
+				int64_t r = started++;
+				if (lt->kind[r] == 2) {
+					lt->src[(size_t)b * W + lane] = (uint32_t)src[r];
+					lt->dst[(size_t)b * W + lane] = (uint32_t)dst[r];
+					lt->row[(size_t)b * W + lane] = r;
+					break;
+				}
+			}
+		}
+		lt->batch_row_end.push_back(started);
+		lt->nbatch++;
+	}
+	return PGQ_OK;
+}
+
+static int query_lengths(Ctx *c, int32_t id, int64_t n, const int64_t *src, const int64_t *dst, const uint8_t *sv,
+                         const uint8_t *dv, int64_t *out_len, uint8_t *out_bool, uint8_t *out_valid) {
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (g->state != Csr::READY) {
+		set_error("csr %d not finalized", id);
+		return PGQ_ERR_STATE;
+	}
+	if (n <= 0) return PGQ_OK;
+	LaneTable lt;
+	PGQ_TRY(build_lane_table(c, g, n, src, dst, sv, dv, &lt));
+	std::vector<int32_t> found((size_t)lt.nbatch * lt.W, -1);
+	PGQ_TRY(msbfs_run(c, g, lt, found.data(), nullptr, src, n));
+	for (int64_t i = 0; i < n; i++) {
+		if (lt.kind[i] == 0) {
+			out_valid[i] = 0;
+			if (out_len) out_len[i] = -1;
+			if (out_bool) out_bool[i] = 0;
+		} else if (lt.kind[i] == 1) {
+			out_valid[i] = 1;
+			if (out_len) out_len[i] = 0;
+			if (out_bool) out_bool[i] = 1;
+		}
+	}
+	for (size_t s = 0; s < found.size(); s++) {
+		int64_t r = lt.row[s];
+		if (r < 0) continue;
+		if (out_len) { // iterativelength: NULL when no path
+			out_valid[r] = found[s] >= 0;
+			out_len[r] = found[s] >= 0 ? found[s] : -1;
+		} else { // reachability: false, not NULL (R6)
+			out_valid[r] = 1;
+			out_bool[r] = found[s] >= 0;
+		}
+	}
+	return PGQ_OK;
+}
+
+int pgq_iterativelength(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                        const uint8_t *src_valid, const uint8_t *dst_valid, int64_t *out, uint8_t *out_valid) {
+	LOCK(ctx);
+	return query_lengths(c, id, n, src, dst, src_valid, dst_valid, out, nullptr, out_valid);
+}
+
+int pgq_reachability(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                     const uint8_t *src_valid, const uint8_t *dst_valid, uint8_t *out, uint8_t *out_valid) {
+	LOCK(ctx);
+	return query_lengths(c, id, n, src, dst, src_valid, dst_valid, nullptr, out, out_valid);
+}
+
+int pgq_shortestpath(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                     const uint8_t *src_valid, const uint8_t *dst_valid, int mode, pgq_list_entry_t *entries,
+                     uint8_t *out_valid, int64_t **out_vals, uint64_t *out_total) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (g->state != Csr::READY) {
+		set_error("csr %d not finalized", id);
+		return PGQ_ERR_STATE;
+	}
+	if (mode != 0 && mode != 1) {
+		set_error("shortestpath mode must be 0 or 1");
+		return PGQ_ERR_INVALID;
+	}
+	if (mode == 1 && !g->have_eid && !g->keep_rows) {
+		set_error("shortestpath mode 1 needs a csr built with edge ids");
+		return PGQ_ERR_STATE;
+	}
+	*out_vals = nullptr;
+	*out_total = 0;
+	if (n <= 0) return PGQ_OK;
+	LaneTable lt;
+	PGQ_TRY(build_lane_table(c, g, n, src, dst, src_valid, dst_valid, &lt));
+	std::vector<int32_t> found((size_t)lt.nbatch * lt.W, -1);
+	PathOut po;
+	po.mode = mode;
+	po.entries = entries;
+	po.valid = out_valid;
+	PGQ_TRY(msbfs_run(c, g, lt, found.data(), &po, src, n));
+	int64_t *vals = (int64_t *)malloc((po.vals.size() ? po.vals.size() : 1) * sizeof(int64_t));
+	if (!vals) {
+		set_error("host allocation failed");
+		return PGQ_ERR_OOM;
+	}
+	if (!po.vals.empty()) memcpy(vals, po.vals.data(), po.vals.size() * sizeof(int64_t));
+	*out_vals = vals;
+	*out_total = po.vals.size();
+	return PGQ_OK;
+}
+
+void pgq_free(void *p) {
+	free(p);
+}
+
+int pgq_iterativelength_device(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *d_src, const int64_t *d_dst,
+                               int64_t *d_out, uint8_t *d_out_valid) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (g->state != Csr::READY) {
+		set_error("csr %d not finalized", id);
+		return PGQ_ERR_STATE;
+	}
+	return msbfs_run_device(c, g, n, d_src, d_dst, d_out, d_out_valid);
+}
+
+// ---- bench / test helpers -----------------------------------------------------------------------
+
+int pgq_dev_alloc(pgq_ctx_t *ctx, uint64_t bytes, void **out_dptr) {
+	LOCK(ctx);
+	if (!out_dptr) return PGQ_ERR_INVALID;
+	*out_dptr = nullptr;
+	cudaError_t e = cudaMalloc(out_dptr, bytes ? bytes : 16);
+	if (e != cudaSuccess) {
+		set_error("cudaMalloc(%llu) -> %s", (unsigned long long)bytes, cudaGetErrorString(e));
+		(void)cudaGetLastError();
+		return PGQ_ERR_OOM;
+	}
+	return PGQ_OK;
+}
+
+int pgq_dev_free(pgq_ctx_t *ctx, void *dptr) {
+	LOCK(ctx);
+	if (dptr) PGQ_CUDA(cudaFree(dptr));
+	return PGQ_OK;
+}
+
+int pgq_dev_h2d(pgq_ctx_t *ctx, void *dptr, const void *hptr, uint64_t bytes) {
+	LOCK(ctx);
+	PGQ_CUDA(cudaMemcpyAsync(dptr, hptr, bytes, cudaMemcpyHostToDevice, c->stream));
+	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	return PGQ_OK;
+}
+
+int pgq_dev_d2h(pgq_ctx_t *ctx, void *hptr, const void *dptr, uint64_t bytes) {
+	LOCK(ctx);
+	PGQ_CUDA(cudaMemcpyAsync(hptr, dptr, bytes, cudaMemcpyDeviceToHost, c->stream));
+	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	return PGQ_OK;
+}
+
+int pgq_host_alloc_pinned(uint64_t bytes, void **out_hptr) {
+	if (!out_hptr) return PGQ_ERR_INVALID;
+	*out_hptr = nullptr;
+	cudaError_t e = cudaHostAlloc(out_hptr, bytes ? bytes : 16, cudaHostAllocDefault);
+	if (e != cudaSuccess) {
+		set_error("cudaHostAlloc(%llu) -> %s", (unsigned long long)bytes, cudaGetErrorString(e));
+		(void)cudaGetLastError();
+		return PGQ_ERR_OOM;
+	}
+	return PGQ_OK;
+}
+
+int pgq_host_free_pinned(void *hptr) {
+	if (hptr) cudaFreeHost(hptr);
+	return PGQ_OK;
+}
+
+int pgq_sync(pgq_ctx_t *ctx) {
+	LOCK(ctx);
+	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	return PGQ_OK;
+}
+
+int pgq_gen_rmat_device(pgq_ctx_t *ctx, uint64_t seed, int scale, int64_t e_size, int64_t *d_src, int64_t *d_dst) {
+	LOCK(ctx);
+	PGQ_TRY(gen_rmat_device(c, seed, scale, e_size, d_src, d_dst));
+	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	return PGQ_OK;
+}
+
+int pgq_gen_knows_device(pgq_ctx_t *ctx, uint64_t seed, int64_t v_size, int64_t e_size, uint64_t mult, uint64_t add,
+                         int64_t *d_src, int64_t *d_dst) {
+	LOCK(ctx);
+	PGQ_TRY(gen_knows_device(c, seed, v_size, e_size, mult, add, d_src, d_dst));
+	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	return PGQ_OK;
+}
+
+int pgq_flush_l2(pgq_ctx_t *ctx) {
+	LOCK(ctx);
+	const size_t bytes = (size_t)256 << 20; // > 126 MB L2
+	PGQ_TRY(c->l2_flush.reserve(bytes));
+	PGQ_CUDA(cudaMemsetAsync(c->l2_flush.p, 0x5a, bytes, c->stream));
+	return PGQ_OK;
+}
+
+int pgq_timer_start(pgq_ctx_t *ctx) {
+	LOCK(ctx);
+	PGQ_CUDA(cudaEventRecord(c->ev_timer, c->stream));
+	return PGQ_OK;
+}
+
+int pgq_timer_stop_ms(pgq_ctx_t *ctx, double *out_ms) {
+	LOCK(ctx);
+	PGQ_CUDA(cudaEventRecord(c->ev_timer2, c->stream));
+	PGQ_CUDA(cudaEventSynchronize(c->ev_timer2));
+	float ms = 0;
+	PGQ_CUDA(cudaEventElapsedTime(&ms, c->ev_timer, c->ev_timer2));
+	if (out_ms) *out_ms = ms;
+	return PGQ_OK;
+}
+
+} // extern "C"

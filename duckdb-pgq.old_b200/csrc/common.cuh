@@ -1,0 +1,209 @@
+// Shared declarations of the pgq_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/pgq_b200.h"
+
+namespace pgq {
+
+void set_error(const char *fmt, ...);
+
+#define PGQ_CUDA(call)                                                                              \
+	do {                                                                                            \
+		cudaError_t _e = (call);                                                                    \
+		if (_e != cudaSuccess) {                                                                    \
+			pgq::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e));    \
+			return (_e == cudaErrorMemoryAllocation) ? PGQ_ERR_OOM : PGQ_ERR_CUDA;                   \
+		}                                                                                           \
+	} while (0)
+
+#define PGQ_TRY(call)                 \
+	do {                              \
+		int _rc = (call);             \
+		if (_rc != PGQ_OK) return _rc; \
+	} while (0)
+
+// Owning device buffer (grows, never shrinks unless released).
+struct DevBuf {
+	void *p = nullptr;
+	size_t cap = 0;
+	int reserve(size_t bytes) {
+		if (bytes <= cap) return PGQ_OK;
+		if (p) cudaFree(p);
+		p = nullptr;
+		cap = 0;
+		cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+		if (e != cudaSuccess) {
+			set_error("cudaMalloc(%zu) -> %s", bytes, cudaGetErrorString(e));
+			(void)cudaGetLastError();
+			return PGQ_ERR_OOM;
+		}
+		cap = bytes;
+		return PGQ_OK;
+	}
+	void release() {
+		if (p) cudaFree(p);
+		p = nullptr;
+		cap = 0;
+	}
+	template <class T>
+	T *as() const {
+		return reinterpret_cast<T *>(p);
+	}
+};
+
+// Scoped temporary device buffer.
+struct TmpBuf : DevBuf {
+	~TmpBuf() {
+		release();
+	}
+};
+
+// Hub chunk descriptor: in-edges [begin,end) of hub `hub` (index into hub_list).
+struct HubChunk {
+	uint32_t hub;
+	uint32_t begin;
+	uint32_t end;
+};
+
+// One CSR (R1): forward arrays in the reference layout plus the reverse CSR used by the
+// pull-direction MS-BFS.  Vertex ids and edge positions are 32-bit on the device
+// (V < 2^32, E < 2^32 per GPU); download widens to the reference's int64.
+struct Csr {
+	int64_t V = 0, E = 0;
+	enum State { CREATED, EDGES_OPEN, READY } state = CREATED;
+	// create_csr_vertex rows (host staging, validated against the device histogram)
+	std::vector<int64_t> cnt_host; // size V when any row was given
+	bool have_cnt = false;
+	// create_csr_edge rows staged in pinned host memory until finalize
+	int64_t *h_src = nullptr, *h_dst = nullptr, *h_eid = nullptr;
+	int64_t staged = 0, staged_cap = 0;
+	bool have_eid = false;
+	bool pending_begin = false; // begin_edges deferred until the first row batch tells whether eids exist
+	// device edge table (int64, input order) while EDGES_OPEN
+	DevBuf d_src64, d_dst64, d_eid64;
+	int64_t uploaded = 0;
+	bool borrowed_edges = false; // d_src64/d_dst64 point at caller-owned device arrays
+	// forward CSR
+	DevBuf d_off;  // int64[V+2], reference `v`
+	DevBuf d_tgt;  // uint32[E], reference `e` narrowed
+	DevBuf d_row;  // uint32[E] input row of each CSR slot (only when edge ids are kept)
+	DevBuf d_eid;  // int64[E] edge ids in CSR order (only when caller gave eids)
+	bool keep_rows = false;
+	// reverse CSR (lazy)
+	bool prepared = false;
+	DevBuf d_ioff;  // uint32[V+1]
+	DevBuf d_isrc;  // uint32[E] source of each in-edge, ascending (src, fwd pos) per target
+	DevBuf d_ipos;  // uint32[E] forward CSR position of each in-edge
+	DevBuf d_mid;   // uint32[] vertices with small_max < indeg <= hub_min
+	DevBuf d_hub;   // uint32[] vertices with indeg > hub_min
+	DevBuf d_hubchunks; // HubChunk[]
+	uint32_t n_mid = 0, n_hub = 0, n_hubchunks = 0;
+	int64_t bins_small_max = -1, bins_hub_min = -1;
+	void free_all();
+};
+
+struct Options {
+	int64_t lanes = 0;
+	int64_t stats = 0;
+	int64_t timing = 0;
+	int64_t small_max = 32;
+	int64_t hub_min = 4096;
+	int64_t hub_chunk = 4096;
+	int64_t direction = 0;
+};
+
+struct Ctx {
+	int device = 0;
+	int sm_count = 148;
+	cudaStream_t stream = nullptr;
+	std::mutex mu;
+	std::map<int32_t, Csr *> csrs;
+	Options opt;
+	pgq_stats_t stats{};
+	// scratch reused across calls
+	DevBuf scan_tmp;
+	DevBuf sort_keys[2], sort_p0[2], sort_p1[2], sort_hist;
+	DevBuf bfs_seen, bfs_visit[2], bfs_parent, bfs_hubacc;
+	DevBuf bfs_lane; // per-call lane tables
+	DevBuf bfs_ctrl; // device control block
+	DevBuf l2_flush;
+	void *h_ctrl = nullptr; // pinned host mirror of the control block
+	cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_timer = nullptr, ev_timer2 = nullptr;
+	std::vector<cudaEvent_t> ev_pool; // level-kernel timing events
+	size_t ev_used = 0;
+};
+
+inline void count_launch(Ctx *c, uint64_t n = 1) {
+	c->stats.kernel_launches += n;
+}
+
+static inline uint32_t div_up(uint64_t a, uint64_t b) {
+	return (uint32_t)((a + b - 1) / b);
+}
+
+// ---- scan.cu ----
+// exclusive scan of n uint32 values into uint32 (out may alias in); total written to *d_total (u64) if non-null
+int exclusive_scan_u32(Ctx *c, const uint32_t *d_in, uint32_t *d_out, uint64_t n, uint64_t *d_total);
+// exclusive scan of n uint32 values into int64 out with a +0 base
+int exclusive_scan_u32_to_i64(Ctx *c, const uint32_t *d_in, int64_t *d_out, uint64_t n);
+
+// ---- radix_sort.cu ----
+// Sort description (host).
+struct SortIO {
+	const int64_t *k64 = nullptr, *p64 = nullptr; // 64-bit first-pass inputs, or
+	const uint32_t *k32 = nullptr, *p32 = nullptr; // 32-bit first-pass inputs
+	uint32_t n = 0;
+	int key_bits = 1;
+	uint32_t *out_p0 = nullptr; // payload0 in sorted order
+	uint32_t *out_p1 = nullptr; // original index in sorted order (nullptr = not wanted)
+};
+
+int radix_sort_stable(Ctx *c, const SortIO &io);
+
+// ---- csr_build.cu ----
+int csr_device_build(Ctx *c, Csr *g);   // K1-K3 from d_src64/d_dst64/d_eid64
+int csr_prepare(Ctx *c, Csr *g);        // reverse CSR + degree bins
+
+// ---- msbfs.cu ----
+struct LaneTable {
+	// host-side compact description of the lanes of all batches of one call
+	std::vector<uint32_t> src, dst;   // per lane slot (batch*W + lane); 0xFFFFFFFF = unused
+	std::vector<int64_t> row;         // row index of the lane slot, -1 unused
+	std::vector<int64_t> batch_row_begin, batch_row_end; // rows consumed by each batch [begin,end)
+	std::vector<uint8_t> kind;        // per row: 0 NULL, 1 trivial (src==dst), 2 searched in a lane
+	int W = 0;
+	int64_t nbatch = 0;
+};
+static inline int pick_lane_width(int64_t lanes_needed) {
+	return lanes_needed <= 64 ? 64 : lanes_needed <= 128 ? 128 : lanes_needed <= 256 ? 256 : 512;
+}
+// Runs all batches; found[slot] = level at which dst was seen (or -1).  If want_paths, path values
+// are produced per batch through the callback-free interface in paths.cu (see msbfs.cu).
+struct PathOut {
+	int mode = 0;
+	pgq_list_entry_t *entries = nullptr; // per row
+	uint8_t *valid = nullptr;            // per row
+	std::vector<int64_t> vals;
+};
+int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *paths,
+              const int64_t *row_src /*host, for trivial rows in path mode*/, int64_t nrows);
+int msbfs_run_device(Ctx *c, Csr *g, int64_t n, const int64_t *d_src, const int64_t *d_dst, int64_t *d_out,
+                     uint8_t *d_out_valid);
+
+// ---- gen.cu ----
+int gen_rmat_device(Ctx *c, uint64_t seed, int scale, int64_t E, int64_t *d_src, int64_t *d_dst);
+int gen_knows_device(Ctx *c, uint64_t seed, int64_t V, int64_t E, uint64_t mult, uint64_t add, int64_t *d_src,
+                     int64_t *d_dst);
+
+} // namespace pgq
+
+struct pgq_ctx {
+	pgq::Ctx c;
+};

@@ -1,0 +1,325 @@
+// Host driver of the bitset MS-BFS (iterativelength / reachability / shortestpath batches).
+// Mirrors the reference's batch loop: clear seen/visit, seed the lanes,
+// run level steps while a lane is active and something changed, check destinations after each
+// level, retire found lanes.  One stream, one host sync per level (reads 16 bytes of control).
+#include "msbfs_kernels.cuh"
+
+namespace pgq {
+
+namespace {
+
+struct BatchBufs {
+	uint32_t *seen, *visit[2], *parent, *hubacc;
+	BfsCtrl *ctrl;
+};
+
+template <int W>
+int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents) {
+	using C = LaneCfg<W>;
+	cudaStream_t st = c->stream;
+	PullArgs a{};
+	a.ioff = g->d_ioff.as<uint32_t>();
+	a.isrc = g->d_isrc.as<uint32_t>();
+	a.visit = b.visit[cur];
+	a.next = b.visit[cur ^ 1];
+	a.seen = b.seen;
+	a.parent = b.parent;
+	a.ctrl = b.ctrl;
+	a.V = (uint32_t)g->V;
+	a.small_max = (uint32_t)c->opt.small_max;
+	a.hubacc = b.hubacc;
+	const uint64_t small_threads = (uint64_t)g->V * C::TPV;
+	if (small_threads) {
+		uint32_t grid = div_up(small_threads, 256);
+		if (parents) pull_small_kernel<W, true><<<grid, 256, 0, st>>>(a);
+		else pull_small_kernel<W, false><<<grid, 256, 0, st>>>(a);
+		count_launch(c);
+	}
+	if (g->n_mid) {
+		a.list = g->d_mid.as<uint32_t>();
+		a.nlist = g->n_mid;
+		uint32_t grid = div_up((uint64_t)g->n_mid * 32, 256);
+		if (parents) pull_warp_parents_kernel<W><<<grid, 256, 0, st>>>(a);
+		else pull_warp_kernel<W><<<grid, 256, 0, st>>>(a);
+		count_launch(c);
+	}
+	if (g->n_hub) {
+		a.list = g->d_hub.as<uint32_t>();
+		a.nlist = g->n_hub;
+		if (parents) {
+			// ordered first-match needs a single consumer per vertex: one warp per hub
+			uint32_t grid = div_up((uint64_t)g->n_hub * 32, 256);
+			pull_warp_parents_kernel<W><<<grid, 256, 0, st>>>(a);
+			count_launch(c);
+		} else {
+			a.chunks = g->d_hubchunks.as<HubChunk>();
+			a.nchunks = g->n_hubchunks;
+			pull_hub_kernel<W><<<g->n_hubchunks, 256, 0, st>>>(a);
+			hub_finalize_kernel<W><<<div_up((uint64_t)g->n_hub * C::TPV, 256), 256, 0, st>>>(a);
+			count_launch(c, 2);
+		}
+	}
+	return PGQ_OK;
+}
+
+int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, bool parents) {
+	switch (W) {
+	case 64: return launch_level<64>(c, g, b, cur, parents);
+	case 128: return launch_level<128>(c, g, b, cur, parents);
+	case 256: return launch_level<256>(c, g, b, cur, parents);
+	case 512: return launch_level<512>(c, g, b, cur, parents);
+	}
+	set_error("unsupported lane width %d", W);
+	return PGQ_ERR_INVALID;
+}
+
+void launch_count(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur) {
+	uint32_t grid = div_up(g->V, 256);
+	if (!grid) return;
+	const int64_t *off = g->d_off.as<int64_t>();
+	switch (W) {
+	case 64: bfs_count_kernel<64><<<grid, 256, 0, c->stream>>>(b.visit[cur], off, (uint32_t)g->V, b.ctrl); break;
+	case 128: bfs_count_kernel<128><<<grid, 256, 0, c->stream>>>(b.visit[cur], off, (uint32_t)g->V, b.ctrl); break;
+	case 256: bfs_count_kernel<256><<<grid, 256, 0, c->stream>>>(b.visit[cur], off, (uint32_t)g->V, b.ctrl); break;
+	case 512: bfs_count_kernel<512><<<grid, 256, 0, c->stream>>>(b.visit[cur], off, (uint32_t)g->V, b.ctrl); break;
+	}
+	count_launch(c);
+}
+
+int read_ctrl(Ctx *c, const BatchBufs &b, BfsCtrl *h) {
+	PGQ_CUDA(cudaMemcpyAsync(c->h_ctrl, b.ctrl, sizeof(BfsCtrl), cudaMemcpyDeviceToHost, c->stream));
+	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	*h = *reinterpret_cast<BfsCtrl *>(c->h_ctrl);
+	return PGQ_OK;
+}
+
+int alloc_bufs(Ctx *c, Csr *g, int W, bool parents, BatchBufs *b) {
+	const size_t bm = (size_t)(g->V > 0 ? g->V : 1) * (W / 8);
+	PGQ_TRY(c->bfs_seen.reserve(bm));
+	PGQ_TRY(c->bfs_visit[0].reserve(bm));
+	PGQ_TRY(c->bfs_visit[1].reserve(bm));
+	PGQ_TRY(c->bfs_ctrl.reserve(sizeof(BfsCtrl)));
+	if (parents) PGQ_TRY(c->bfs_parent.reserve((size_t)(g->V > 0 ? g->V : 1) * W * sizeof(uint32_t)));
+	const size_t hb = (size_t)(g->n_hub > 0 ? g->n_hub : 1) * (W / 8);
+	if (hb > c->bfs_hubacc.cap) {
+		PGQ_TRY(c->bfs_hubacc.reserve(hb));
+	}
+	// hubacc must be zero on entry of every level (finalize re-zeroes it)
+	PGQ_CUDA(cudaMemsetAsync(c->bfs_hubacc.p, 0, c->bfs_hubacc.cap, c->stream));
+	b->seen = c->bfs_seen.as<uint32_t>();
+	b->visit[0] = c->bfs_visit[0].as<uint32_t>();
+	b->visit[1] = c->bfs_visit[1].as<uint32_t>();
+	b->parent = parents ? c->bfs_parent.as<uint32_t>() : nullptr;
+	b->hubacc = c->bfs_hubacc.as<uint32_t>();
+	b->ctrl = c->bfs_ctrl.as<BfsCtrl>();
+	return PGQ_OK;
+}
+
+// One batch of W lanes.  d_lane_src/dst/found point at this batch's W slots.
+int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uint32_t *d_lane_src,
+              const uint32_t *d_lane_dst, int32_t *d_found) {
+	cudaStream_t st = c->stream;
+	const size_t bm = (size_t)g->V * (W / 8);
+	if (bm) {
+		PGQ_CUDA(cudaMemsetAsync(b.seen, 0, bm, st));
+		PGQ_CUDA(cudaMemsetAsync(b.visit[0], 0, bm, st));
+	}
+	bfs_init_kernel<<<1, W, 0, st>>>(d_lane_src, W, b.visit[0], d_found, b.ctrl);
+	count_launch(c);
+	BfsCtrl h;
+	PGQ_TRY(read_ctrl(c, b, &h));
+	c->stats.batches++;
+	uint32_t active = h.n_active;
+	int cur = 0;
+	for (int iter = 1; active; iter++) {
+		if (c->opt.stats) launch_count(c, g, b, W, cur);
+		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
+		uint64_t before = c->stats.kernel_launches;
+		PGQ_TRY(launch_level_w(c, g, b, W, cur, parents));
+		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
+		bfs_check_kernel<<<1, W, 0, st>>>(b.seen, d_lane_dst, W, d_found, b.ctrl, iter);
+		count_launch(c);
+		PGQ_TRY(read_ctrl(c, b, &h));
+		c->stats.levels++;
+		if (c->opt.timing) {
+			float ms = 0;
+			PGQ_CUDA(cudaEventElapsedTime(&ms, c->ev_a, c->ev_b));
+			c->stats.level_kernel_ms += ms;
+			c->stats.level_kernel_launches += c->stats.kernel_launches - 1 - before;
+		}
+		if (!h.change_out) break;
+		active = h.n_active;
+		cur ^= 1;
+	}
+	if (c->opt.stats) {
+		// counters accumulate in the control block over the batch (reset by the init kernel)
+		PGQ_TRY(read_ctrl(c, b, &h));
+		c->stats.edges_lane += h.edges_lane;
+		c->stats.edges_unique += h.edges_unique;
+		// 4*V*(W/8) per level + E_act*(4 + W/8) + 8*V_act
+		c->stats.algo_bytes += h.edges_unique * (uint64_t)(4 + W / 8) + 8ull * h.verts_active;
+	}
+	PGQ_CUDA(cudaGetLastError());
+	return PGQ_OK;
+}
+
+} // namespace
+
+// found[slot] for all lane slots of all batches (host).  Path output per batch when `paths`.
+int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *paths, const int64_t *row_src,
+              int64_t nrows) {
+	(void)nrows;
+	const int W = lt.W;
+	const int64_t nslots = lt.nbatch * W;
+	if (nslots == 0) return PGQ_OK;
+	PGQ_TRY(csr_prepare(c, g));
+	const bool want_paths = paths != nullptr;
+	BatchBufs b{};
+	PGQ_TRY(alloc_bufs(c, g, W, want_paths, &b));
+	cudaStream_t st = c->stream;
+	// lane tables: src | dst | found | lane_off(u64, paths only)
+	size_t lane_bytes = (size_t)nslots * (2 * sizeof(uint32_t) + sizeof(int32_t)) + (size_t)W * sizeof(uint64_t) + 64;
+	PGQ_TRY(c->bfs_lane.reserve(lane_bytes));
+	uint64_t *d_lane_off = c->bfs_lane.as<uint64_t>(); // first, 8 B aligned
+	uint32_t *d_src = reinterpret_cast<uint32_t *>(d_lane_off + W);
+	uint32_t *d_dst = d_src + nslots;
+	int32_t *d_found = reinterpret_cast<int32_t *>(d_dst + nslots);
+	PGQ_CUDA(cudaMemcpyAsync(d_src, lt.src.data(), (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
+	PGQ_CUDA(cudaMemcpyAsync(d_dst, lt.dst.data(), (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
+	c->stats.h2d_bytes += (uint64_t)nslots * 8;
+	const uint64_t levels_before = c->stats.levels;
+	TmpBuf d_out;
+	std::vector<uint64_t> lane_off((size_t)W);
+	uint64_t total = 0; // running list offset over all rows (paths)
+	for (int64_t bi = 0; bi < lt.nbatch; bi++) {
+		PGQ_TRY(run_batch(c, g, b, W, want_paths, d_src + bi * W, d_dst + bi * W, d_found + bi * W));
+		if (!want_paths) continue;
+		// ---- K8: reconstruct this batch's paths in ROW order (R9) ----
+		int32_t *hf = h_found + bi * W;
+		PGQ_CUDA(cudaMemcpyAsync(hf, d_found + bi * W, (size_t)W * 4, cudaMemcpyDeviceToHost, st));
+		PGQ_CUDA(cudaStreamSynchronize(st));
+		c->stats.d2h_bytes += (uint64_t)W * 4;
+		const int64_t r0 = lt.batch_row_begin[bi], r1 = lt.batch_row_end[bi];
+		const uint64_t base = total;
+		int lane = 0;
+		for (int64_t r = r0; r < r1; r++) {
+			const uint8_t kind = lt.kind[r];
+			uint64_t len = 0;
+			if (kind == 1) {
+				len = 1;
+			} else if (kind == 2) {
+				while (lane < W && lt.row[bi * W + lane] != r) lane++;
+				if (lane < W && hf[lane] >= 0) {
+					len = paths->mode == 0 ? (uint64_t)hf[lane] + 1 : 2ull * (uint64_t)hf[lane] + 1;
+					lane_off[lane] = total - base;
+				}
+			}
+			paths->entries[r].offset = total;
+			paths->entries[r].length = len;
+			paths->valid[r] = len ? 1 : 0;
+			total += len;
+		}
+		const uint64_t bt = total - base;
+		paths->vals.resize(total);
+		if (bt) {
+			PGQ_TRY(d_out.reserve(bt * sizeof(int64_t)));
+			PGQ_CUDA(cudaMemcpyAsync(d_lane_off, lane_off.data(), (size_t)W * 8, cudaMemcpyHostToDevice, st));
+			bfs_paths_kernel<<<div_up(W, 128), 128, 0, st>>>(
+			    b.parent, g->d_isrc.as<uint32_t>(), g->d_ipos.as<uint32_t>(),
+			    g->have_eid ? g->d_eid.as<int64_t>() : nullptr, g->keep_rows ? g->d_row.as<uint32_t>() : nullptr,
+			    d_dst + bi * W, d_found + bi * W, (const unsigned long long *)d_lane_off, W, paths->mode,
+			    d_out.as<int64_t>());
+			count_launch(c);
+			PGQ_CUDA(cudaMemcpyAsync(paths->vals.data() + base, d_out.p, bt * sizeof(int64_t),
+			                         cudaMemcpyDeviceToHost, st));
+			PGQ_CUDA(cudaStreamSynchronize(st));
+			c->stats.d2h_bytes += bt * 8;
+			// trivial rows: [src]
+			for (int64_t r = r0; r < r1; r++)
+				if (lt.kind[r] == 1) paths->vals[paths->entries[r].offset] = row_src[r];
+		}
+	}
+	if (!want_paths) {
+		PGQ_CUDA(cudaMemcpyAsync(h_found, d_found, (size_t)nslots * 4, cudaMemcpyDeviceToHost, st));
+		PGQ_CUDA(cudaStreamSynchronize(st));
+		c->stats.d2h_bytes += (uint64_t)nslots * 4;
+	}
+	if (c->opt.stats)
+		c->stats.algo_bytes += (c->stats.levels - levels_before) * 4ull * (uint64_t)g->V * (uint64_t)(W / 8);
+	return PGQ_OK;
+}
+
+// ---- device-resident variant: slot i <-> row i -------------------------------------------------
+
+__global__ void __launch_bounds__(256) lanes_from_rows_kernel(const int64_t *__restrict__ src,
+                                                              const int64_t *__restrict__ dst, int64_t n,
+                                                              int64_t nslots, uint64_t V,
+                                                              uint32_t *__restrict__ lane_src,
+                                                              uint32_t *__restrict__ lane_dst, uint32_t *err) {
+	int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= nslots) return;
+	uint32_t s = 0xFFFFFFFFu, d = 0;
+	if (i < n) {
+		uint64_t a = (uint64_t)src[i], b = (uint64_t)dst[i];
+		if (a >= V || b >= V) atomicOr(err, 1u);
+		else if (a != b) {
+			s = (uint32_t)a;
+			d = (uint32_t)b;
+		}
+	}
+	lane_src[i] = s;
+	lane_dst[i] = d;
+}
+
+__global__ void __launch_bounds__(256) rows_from_lanes_kernel(const int64_t *__restrict__ src,
+                                                              const int64_t *__restrict__ dst, int64_t n,
+                                                              const int32_t *__restrict__ found,
+                                                              int64_t *__restrict__ out, uint8_t *__restrict__ valid) {
+	int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	if (src[i] == dst[i]) {
+		out[i] = 0;
+		valid[i] = 1;
+	} else {
+		int32_t f = found[i];
+		out[i] = f >= 0 ? (int64_t)f : -1;
+		valid[i] = f >= 0;
+	}
+}
+
+int msbfs_run_device(Ctx *c, Csr *g, int64_t n, const int64_t *d_srcs, const int64_t *d_dsts, int64_t *d_out,
+                     uint8_t *d_out_valid) {
+	if (n == 0) return PGQ_OK;
+	const int W = c->opt.lanes ? (int)c->opt.lanes : pick_lane_width(n);
+	const int64_t nbatch = (n + W - 1) / W, nslots = nbatch * W;
+	PGQ_TRY(csr_prepare(c, g));
+	BatchBufs b{};
+	PGQ_TRY(alloc_bufs(c, g, W, false, &b));
+	cudaStream_t st = c->stream;
+	PGQ_TRY(c->bfs_lane.reserve((size_t)nslots * 12 + 64));
+	uint32_t *d_src = c->bfs_lane.as<uint32_t>() + 4; // [0] = error flag
+	uint32_t *d_err = c->bfs_lane.as<uint32_t>();
+	uint32_t *d_dst = d_src + nslots;
+	int32_t *d_found = reinterpret_cast<int32_t *>(d_dst + nslots);
+	PGQ_CUDA(cudaMemsetAsync(d_err, 0, 16, st));
+	lanes_from_rows_kernel<<<div_up(nslots, 256), 256, 0, st>>>(d_srcs, d_dsts, n, nslots, (uint64_t)g->V, d_src,
+	                                                            d_dst, d_err);
+	count_launch(c);
+	const uint64_t levels_before = c->stats.levels;
+	for (int64_t bi = 0; bi < nbatch; bi++)
+		PGQ_TRY(run_batch(c, g, b, W, false, d_src + bi * W, d_dst + bi * W, d_found + bi * W));
+	rows_from_lanes_kernel<<<div_up(n, 256), 256, 0, st>>>(d_srcs, d_dsts, n, d_found, d_out, d_out_valid);
+	count_launch(c);
+	uint32_t h_err = 0;
+	PGQ_CUDA(cudaMemcpyAsync(&h_err, d_err, 4, cudaMemcpyDeviceToHost, st));
+	PGQ_CUDA(cudaStreamSynchronize(st));
+	if (c->opt.stats)
+		c->stats.algo_bytes += (c->stats.levels - levels_before) * 4ull * (uint64_t)g->V * (uint64_t)(W / 8);
+	if (h_err) {
+		set_error("iterativelength: src/dst id outside [0, v_size)");
+		return PGQ_ERR_INVALID;
+	}
+	return PGQ_OK;
+}
+
+} // namespace pgq

@@ -1,0 +1,552 @@
+// MS-BFS level kernels (K4-K7), pull direction over the reverse CSR.
+//
+// Semantics restated from SURVEY.md §8(a) R4/R5/R7: one level computes, for every vertex n,
+//   next[n] = (OR over in-neighbours v of visit[v]) & ~seen[n];  seen[n] |= next[n]
+// which is exactly the reference's push loop (next[e[off]] |= visit[v]; next &= ~seen;
+// seen |= next) evaluated from the target side — no atomics, deterministic.  Lanes retired by
+// the destination check are masked out through `active` (per-lane early exit).
+//
+// Parent rule R7 falls out of the reverse CSR's order: the in-list of n is sorted by
+// (source id ascending, forward CSR offset ascending), so the FIRST in-edge whose source has
+// lane l in the frontier, at the level n is first reached by l, is the reference's parent.
+//
+// Layout: bitmaps are uint32[V][W/32]; a thread owns a 128-bit slice (64-bit when W=64) of one
+// vertex word and moves it with one vector load/store.  HBM-bound: per level
+//   4*V*(W/8) + E_act*(4 + W/8) bytes.
+#pragma once
+#include "common.cuh"
+
+namespace pgq {
+
+struct BfsCtrl {
+	uint32_t active[32]; // lane mask, W/32 words used (W <= 1024); first so slices are 16 B aligned
+	uint32_t change;     // set by level kernels when any new bit appeared
+	uint32_t change_out; // snapshot taken by the check kernel
+	uint32_t n_active;   // lanes still searching
+	uint32_t pad;
+	unsigned long long edges_lane;
+	unsigned long long edges_unique;
+	unsigned long long verts_active;
+	unsigned long long pad2;
+};
+
+struct PullArgs {
+	const uint32_t *ioff;
+	const uint32_t *isrc;
+	const uint32_t *visit;
+	uint32_t *next;
+	uint32_t *seen;
+	uint32_t *parent; // [V][W] in-edge index, PARENTS only
+	BfsCtrl *ctrl;
+	uint32_t V;
+	uint32_t small_max;
+	const uint32_t *list; // mid or hub vertex list
+	uint32_t nlist;
+	const HubChunk *chunks;
+	uint32_t nchunks;
+	uint32_t *hubacc;
+};
+
+template <int W>
+struct LaneCfg {
+	static constexpr int SW = (W >= 128) ? 4 : 2;         // uint32 words per thread slice
+	static constexpr int TPV = (W >= 128) ? (W / 128) : 1; // threads per vertex word
+	static constexpr int WPV = W / 32;                     // uint32 words per vertex
+	static constexpr int G = 32 / TPV;                     // vertex-slices (edge groups) per warp
+};
+
+template <int SW>
+struct Slice {
+	uint32_t w[SW];
+};
+
+template <int SW>
+__device__ __forceinline__ Slice<SW> slice_zero() {
+	Slice<SW> s;
+#pragma unroll
+	for (int i = 0; i < SW; i++) s.w[i] = 0;
+	return s;
+}
+
+template <int SW>
+__device__ __forceinline__ Slice<SW> ld_slice(const uint32_t *p) {
+	Slice<SW> s;
+	if (SW == 4) {
+		uint4 v = *reinterpret_cast<const uint4 *>(p);
+		s.w[0] = v.x; s.w[1] = v.y; s.w[2] = v.z; s.w[3] = v.w;
+	} else {
+		uint2 v = *reinterpret_cast<const uint2 *>(p);
+		s.w[0] = v.x; s.w[1] = v.y;
+	}
+	return s;
+}
+
+// read-only (non-coherent) gather of a frontier slice written by the previous launch
+template <int SW>
+__device__ __forceinline__ Slice<SW> ldg_slice(const uint32_t *p) {
+	Slice<SW> s;
+	if (SW == 4) {
+		uint4 v = __ldg(reinterpret_cast<const uint4 *>(p));
+		s.w[0] = v.x; s.w[1] = v.y; s.w[2] = v.z; s.w[3] = v.w;
+	} else {
+		uint2 v = __ldg(reinterpret_cast<const uint2 *>(p));
+		s.w[0] = v.x; s.w[1] = v.y;
+	}
+	return s;
+}
+
+template <int SW>
+__device__ __forceinline__ void st_slice(uint32_t *p, const Slice<SW> &s) {
+	if (SW == 4) *reinterpret_cast<uint4 *>(p) = make_uint4(s.w[0], s.w[1], s.w[2], s.w[3]);
+	else *reinterpret_cast<uint2 *>(p) = make_uint2(s.w[0], s.w[1]);
+}
+
+template <int SW>
+__device__ __forceinline__ bool slice_any(const Slice<SW> &s) {
+	uint32_t o = 0;
+#pragma unroll
+	for (int i = 0; i < SW; i++) o |= s.w[i];
+	return o != 0;
+}
+
+template <int SW>
+__device__ __forceinline__ bool slice_covers(const Slice<SW> &acc, const Slice<SW> &need) {
+	uint32_t miss = 0;
+#pragma unroll
+	for (int i = 0; i < SW; i++) miss |= need.w[i] & ~acc.w[i];
+	return miss == 0;
+}
+
+// OR-reduce across the G groups of a warp (lanes with equal lane % TPV); result in every lane.
+template <int SW, int TPV>
+__device__ __forceinline__ Slice<SW> warp_or_groups(Slice<SW> s) {
+#pragma unroll
+	for (int d = TPV; d < 32; d <<= 1) {
+#pragma unroll
+		for (int i = 0; i < SW; i++) s.w[i] |= __shfl_xor_sync(0xffffffffu, s.w[i], d);
+	}
+	return s;
+}
+
+// record parent = in-edge index j for every set bit of `bits` (lanes base..base+SW*32)
+template <int SW>
+__device__ __forceinline__ void store_parents(uint32_t *prow, const Slice<SW> &bits, uint32_t j) {
+#pragma unroll
+	for (int i = 0; i < SW; i++) {
+		uint32_t b = bits.w[i];
+		while (b) {
+			int k = __ffs(b) - 1;
+			b &= b - 1;
+			prow[i * 32 + k] = j;
+		}
+	}
+}
+
+__device__ __forceinline__ void flag_change(BfsCtrl *ctrl, bool anynew) {
+	if (__any_sync(0xffffffffu, anynew)) {
+		if ((threadIdx.x & 31) == 0) ctrl->change = 1u;
+	}
+}
+
+// ---- K4/K7 small: one TPV-thread group per vertex, in-degree <= small_max ---------------------
+template <int W, bool PARENTS>
+__global__ void __launch_bounds__(256) pull_small_kernel(PullArgs a) {
+	using C = LaneCfg<W>;
+	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
+	const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	const uint64_t n64 = gid / TPV;
+	const uint32_t t = (uint32_t)(gid % TPV);
+	const bool inrange = n64 < a.V;
+	const uint32_t n = (uint32_t)n64;
+	uint32_t lo = 0, hi = 0;
+	if (inrange) {
+		lo = a.ioff[n];
+		hi = a.ioff[n + 1];
+	}
+	const bool mine = inrange && (hi - lo) <= a.small_max;
+	Slice<SW> news = slice_zero<SW>();
+	if (mine) {
+		const size_t wo = (size_t)n * WPV + (size_t)t * SW;
+		Slice<SW> s = ld_slice<SW>(a.seen + wo);
+		Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
+		Slice<SW> unseen;
+#pragma unroll
+		for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
+		Slice<SW> acc = slice_zero<SW>();
+		if (slice_any<SW>(unseen)) {
+			uint32_t *prow = PARENTS ? a.parent + (size_t)n * W + (size_t)t * (SW * 32) : nullptr;
+			uint32_t j = lo;
+			for (; j + 4 <= hi; j += 4) {
+				uint32_t v0 = a.isrc[j], v1 = a.isrc[j + 1], v2 = a.isrc[j + 2], v3 = a.isrc[j + 3];
+				Slice<SW> w0 = ldg_slice<SW>(a.visit + (size_t)v0 * WPV + t * SW);
+				Slice<SW> w1 = ldg_slice<SW>(a.visit + (size_t)v1 * WPV + t * SW);
+				Slice<SW> w2 = ldg_slice<SW>(a.visit + (size_t)v2 * WPV + t * SW);
+				Slice<SW> w3 = ldg_slice<SW>(a.visit + (size_t)v3 * WPV + t * SW);
+				Slice<SW> ws[4] = {w0, w1, w2, w3};
+#pragma unroll
+				for (int u = 0; u < 4; u++) {
+					if (PARENTS) {
+						Slice<SW> nb;
+#pragma unroll
+						for (int i = 0; i < SW; i++) nb.w[i] = ws[u].w[i] & unseen.w[i] & ~acc.w[i];
+						store_parents<SW>(prow, nb, j + u);
+					}
+#pragma unroll
+					for (int i = 0; i < SW; i++) acc.w[i] |= ws[u].w[i];
+				}
+				if (slice_covers<SW>(acc, unseen)) {
+					j = hi;
+					break;
+				}
+			}
+			for (; j < hi; j++) {
+				uint32_t v0 = a.isrc[j];
+				Slice<SW> w0 = ldg_slice<SW>(a.visit + (size_t)v0 * WPV + t * SW);
+				if (PARENTS) {
+					Slice<SW> nb;
+#pragma unroll
+					for (int i = 0; i < SW; i++) nb.w[i] = w0.w[i] & unseen.w[i] & ~acc.w[i];
+					store_parents<SW>(prow, nb, j);
+				}
+#pragma unroll
+				for (int i = 0; i < SW; i++) acc.w[i] |= w0.w[i];
+			}
+		}
+#pragma unroll
+		for (int i = 0; i < SW; i++) news.w[i] = acc.w[i] & unseen.w[i];
+		st_slice<SW>(a.next + wo, news);
+		if (slice_any<SW>(news)) {
+#pragma unroll
+			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
+			st_slice<SW>(a.seen + wo, s);
+		}
+	}
+	flag_change(a.ctrl, slice_any<SW>(news));
+}
+
+// ---- K4 mid: one warp per vertex (small_max < in-degree), lengths only -------------------------
+// G groups x TPV slice-threads; each group strides the in-list, 4 edges in flight per thread.
+template <int W>
+__global__ void __launch_bounds__(256) pull_warp_kernel(PullArgs a) {
+	using C = LaneCfg<W>;
+	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
+	const uint32_t wid = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+	if (wid >= a.nlist) return; // warp-uniform
+	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
+	const uint32_t n = a.list[wid];
+	const uint32_t lo = a.ioff[n], hi = a.ioff[n + 1];
+	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
+	Slice<SW> s = ld_slice<SW>(a.seen + wo);
+	Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
+	Slice<SW> unseen;
+#pragma unroll
+	for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
+	Slice<SW> tot = slice_zero<SW>();
+	if (__any_sync(0xffffffffu, slice_any<SW>(unseen))) {
+		Slice<SW> acc = slice_zero<SW>();
+		for (uint32_t j0 = lo; j0 < hi; j0 += G * U) {
+			uint32_t vs[U];
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				uint32_t j = j0 + u * G + g;
+				vs[u] = j < hi ? a.isrc[j] : 0xFFFFFFFFu;
+			}
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				if (vs[u] != 0xFFFFFFFFu) {
+					Slice<SW> w = ldg_slice<SW>(a.visit + (size_t)vs[u] * WPV + t * SW);
+#pragma unroll
+					for (int i = 0; i < SW; i++) acc.w[i] |= w.w[i];
+				}
+			}
+			tot = warp_or_groups<SW, TPV>(acc);
+			if (__all_sync(0xffffffffu, slice_covers<SW>(tot, unseen))) break; // every unseen lane reached
+		}
+		tot = warp_or_groups<SW, TPV>(acc);
+	}
+	Slice<SW> news;
+#pragma unroll
+	for (int i = 0; i < SW; i++) news.w[i] = tot.w[i] & unseen.w[i];
+	if (g == 0) {
+		st_slice<SW>(a.next + wo, news);
+		if (slice_any<SW>(news)) {
+#pragma unroll
+			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
+			st_slice<SW>(a.seen + wo, s);
+		}
+	}
+	flag_change(a.ctrl, slice_any<SW>(news));
+}
+
+// ---- K7 mid/hub with parents: one warp per vertex, in-edges consumed in ORDER -------------------
+// Round = G consecutive in-edges (group g takes edge j0+g).  A lane bit claimed by several groups
+// in one round goes to the lowest group (exclusive prefix-OR over groups) = lowest in-edge index.
+template <int W>
+__global__ void __launch_bounds__(256) pull_warp_parents_kernel(PullArgs a) {
+	using C = LaneCfg<W>;
+	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G;
+	const uint32_t wid = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+	if (wid >= a.nlist) return;
+	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
+	const uint32_t n = a.list[wid];
+	const uint32_t lo = a.ioff[n], hi = a.ioff[n + 1];
+	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
+	Slice<SW> s = ld_slice<SW>(a.seen + wo);
+	Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
+	Slice<SW> unseen;
+#pragma unroll
+	for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
+	Slice<SW> acc = slice_zero<SW>(); // lane bits already claimed (identical in all groups)
+	if (__any_sync(0xffffffffu, slice_any<SW>(unseen))) {
+		uint32_t *prow = a.parent + (size_t)n * W + (size_t)t * (SW * 32);
+		for (uint32_t j0 = lo; j0 < hi; j0 += 2 * G) {
+			// two rounds of loads in flight, consumed in order
+			uint32_t ja = j0 + g, jb = j0 + G + g;
+			uint32_t va = ja < hi ? a.isrc[ja] : 0xFFFFFFFFu;
+			uint32_t vb = jb < hi ? a.isrc[jb] : 0xFFFFFFFFu;
+			Slice<SW> wr[2];
+			wr[0] = va != 0xFFFFFFFFu ? ldg_slice<SW>(a.visit + (size_t)va * WPV + t * SW) : slice_zero<SW>();
+			wr[1] = vb != 0xFFFFFFFFu ? ldg_slice<SW>(a.visit + (size_t)vb * WPV + t * SW) : slice_zero<SW>();
+#pragma unroll
+			for (int r = 0; r < 2; r++) {
+				const uint32_t j = r == 0 ? ja : jb;
+				Slice<SW> cand;
+#pragma unroll
+				for (int i = 0; i < SW; i++) cand.w[i] = wr[r].w[i] & unseen.w[i] & ~acc.w[i];
+				if (__any_sync(0xffffffffu, slice_any<SW>(cand))) {
+					Slice<SW> incl = cand;
+#pragma unroll
+					for (int d = TPV; d < 32; d <<= 1) {
+#pragma unroll
+						for (int i = 0; i < SW; i++) {
+							uint32_t y = __shfl_up_sync(0xffffffffu, incl.w[i], d);
+							if (lane >= (uint32_t)d) incl.w[i] |= y;
+						}
+					}
+					Slice<SW> excl, all;
+#pragma unroll
+					for (int i = 0; i < SW; i++) {
+						uint32_t y = __shfl_up_sync(0xffffffffu, incl.w[i], TPV);
+						excl.w[i] = g == 0 ? 0u : y;
+						all.w[i] = __shfl_sync(0xffffffffu, incl.w[i], 32 - TPV + t);
+					}
+					Slice<SW> take;
+#pragma unroll
+					for (int i = 0; i < SW; i++) take.w[i] = cand.w[i] & ~excl.w[i];
+					store_parents<SW>(prow, take, j);
+#pragma unroll
+					for (int i = 0; i < SW; i++) acc.w[i] |= all.w[i];
+				}
+			}
+			if (__all_sync(0xffffffffu, slice_covers<SW>(acc, unseen))) break;
+		}
+	}
+	Slice<SW> news;
+#pragma unroll
+	for (int i = 0; i < SW; i++) news.w[i] = acc.w[i] & unseen.w[i];
+	if (g == 0) {
+		st_slice<SW>(a.next + wo, news);
+		if (slice_any<SW>(news)) {
+#pragma unroll
+			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
+			st_slice<SW>(a.seen + wo, s);
+		}
+	}
+	flag_change(a.ctrl, slice_any<SW>(news));
+}
+
+// ---- K4 hubs: one block per chunk of a hub's in-list, partial ORs merged with atomicOr ---------
+template <int W>
+__global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
+	using C = LaneCfg<W>;
+	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
+	const HubChunk hc = a.chunks[blockIdx.x];
+	const uint32_t n = a.list[hc.hub];
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+	const uint32_t g = lane / TPV, t = lane % TPV;
+	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
+	Slice<SW> s = ld_slice<SW>(a.seen + wo);
+	Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
+	Slice<SW> unseen;
+#pragma unroll
+	for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
+	if (!__any_sync(0xffffffffu, slice_any<SW>(unseen))) return; // same decision in every warp
+	Slice<SW> acc = slice_zero<SW>();
+	Slice<SW> tot = slice_zero<SW>();
+	for (uint32_t j0 = hc.begin + warp * (G * U); j0 < hc.end; j0 += nwarps * G * U) {
+		uint32_t vs[U];
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			uint32_t j = j0 + u * G + g;
+			vs[u] = j < hc.end ? a.isrc[j] : 0xFFFFFFFFu;
+		}
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			if (vs[u] != 0xFFFFFFFFu) {
+				Slice<SW> w = ldg_slice<SW>(a.visit + (size_t)vs[u] * WPV + t * SW);
+#pragma unroll
+				for (int i = 0; i < SW; i++) acc.w[i] |= w.w[i];
+			}
+		}
+		tot = warp_or_groups<SW, TPV>(acc);
+		if (__all_sync(0xffffffffu, slice_covers<SW>(tot, unseen))) break;
+	}
+	tot = warp_or_groups<SW, TPV>(acc);
+	if (g == 0) {
+		uint32_t *dst = a.hubacc + (size_t)hc.hub * WPV + (size_t)t * SW;
+#pragma unroll
+		for (int i = 0; i < SW; i++) {
+			uint32_t x = tot.w[i] & unseen.w[i];
+			if (x) atomicOr(dst + i, x);
+		}
+	}
+}
+
+// one TPV-thread group per hub: next = hubacc & ~seen & active; seen |= next; hubacc = 0
+template <int W>
+__global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
+	using C = LaneCfg<W>;
+	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
+	const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t h = gid / TPV, t = gid % TPV;
+	Slice<SW> news = slice_zero<SW>();
+	if (h < a.nlist) {
+		const uint32_t n = a.list[h];
+		const size_t wo = (size_t)n * WPV + (size_t)t * SW;
+		uint32_t *ha = a.hubacc + (size_t)h * WPV + (size_t)t * SW;
+		Slice<SW> acc = ld_slice<SW>(ha);
+		st_slice<SW>(ha, slice_zero<SW>());
+		Slice<SW> s = ld_slice<SW>(a.seen + wo);
+		Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
+#pragma unroll
+		for (int i = 0; i < SW; i++) news.w[i] = acc.w[i] & ~s.w[i] & act.w[i];
+		st_slice<SW>(a.next + wo, news);
+		if (slice_any<SW>(news)) {
+#pragma unroll
+			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
+			st_slice<SW>(a.seen + wo, s);
+		}
+	}
+	flag_change(a.ctrl, slice_any<SW>(news));
+}
+
+// ---- batch init / K6 destination check / stats / K8 path reconstruction -----------------------
+
+// One block of W threads.  Sets the source bits (R4: visit only, seen untouched), the active mask,
+// found = -1.  lane_src == 0xFFFFFFFF marks an unused lane slot.
+__global__ void bfs_init_kernel(const uint32_t *__restrict__ lane_src, int W, uint32_t *__restrict__ visit,
+                                int32_t *__restrict__ found, BfsCtrl *ctrl) {
+	__shared__ uint32_t cnt;
+	const int lane = threadIdx.x;
+	if (lane == 0) {
+		cnt = 0;
+		ctrl->change = 0; ctrl->change_out = 0;
+		ctrl->edges_lane = 0; ctrl->edges_unique = 0; ctrl->verts_active = 0;
+	}
+	__syncthreads();
+	const uint32_t s = lane_src[lane];
+	const bool used = s != 0xFFFFFFFFu;
+	found[lane] = -1;
+	if (used) atomicOr(&visit[(size_t)s * (W / 32) + (lane >> 5)], 1u << (lane & 31));
+	const unsigned m = __ballot_sync(0xffffffffu, used);
+	if ((lane & 31) == 0) {
+		ctrl->active[lane >> 5] = m;
+		atomicAdd(&cnt, (uint32_t)__popc(m));
+	}
+	__syncthreads();
+	if (lane == 0) ctrl->n_active = cnt;
+}
+
+// After a level: lanes whose destination has been seen get found=iter and leave the active mask.
+__global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, const uint32_t *__restrict__ lane_dst, int W,
+                                 int32_t *__restrict__ found, BfsCtrl *ctrl, int iter) {
+	__shared__ uint32_t cnt;
+	const int lane = threadIdx.x;
+	if (lane == 0) cnt = 0;
+	__syncthreads();
+	const uint32_t word = ctrl->active[lane >> 5];
+	const bool act = (word >> (lane & 31)) & 1u;
+	bool hit = false;
+	if (act) {
+		const uint32_t d = lane_dst[lane];
+		hit = (seen[(size_t)d * (W / 32) + (lane >> 5)] >> (lane & 31)) & 1u;
+		if (hit) found[lane] = iter;
+	}
+	const unsigned hm = __ballot_sync(0xffffffffu, hit);
+	__syncthreads(); // all reads of active[] done before any warp rewrites its word
+	if ((lane & 31) == 0) {
+		const uint32_t nw = word & ~hm;
+		ctrl->active[lane >> 5] = nw;
+		atomicAdd(&cnt, (uint32_t)__popc(nw));
+	}
+	__syncthreads();
+	if (lane == 0) {
+		ctrl->n_active = cnt;
+		ctrl->change_out = ctrl->change;
+		ctrl->change = 0;
+	}
+}
+
+// TEPS numerator of the level about to run (stats mode only; not part of the timed path).
+template <int W>
+__global__ void __launch_bounds__(256) bfs_count_kernel(const uint32_t *__restrict__ visit,
+                                                        const int64_t *__restrict__ off, uint32_t V,
+                                                        BfsCtrl *ctrl) {
+	constexpr int WPV = W / 32;
+	const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned long long el = 0, eu = 0, va = 0;
+	if (n < V) {
+		uint32_t pc = 0;
+#pragma unroll
+		for (int i = 0; i < WPV; i++) pc += __popc(visit[(size_t)n * WPV + i] & ctrl->active[i]);
+		if (pc) {
+			unsigned long long deg = (unsigned long long)(off[n + 1] - off[n]);
+			el = deg * pc; eu = deg; va = 1;
+		}
+	}
+#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) {
+		el += __shfl_xor_sync(0xffffffffu, el, d);
+		eu += __shfl_xor_sync(0xffffffffu, eu, d);
+		va += __shfl_xor_sync(0xffffffffu, va, d);
+	}
+	if ((threadIdx.x & 31) == 0 && va) {
+		atomicAdd(&ctrl->edges_lane, el);
+		atomicAdd(&ctrl->edges_unique, eu);
+		atomicAdd(&ctrl->verts_active, va);
+	}
+}
+
+// K8: one thread per lane walks dst -> parent in-edges -> src and writes the list back to front.
+// mode 0: [src,..,dst] (len L+1); mode 1: [src,e0,v1,..,dst] (len 2L+1).  R7/R8.
+__global__ void bfs_paths_kernel(const uint32_t *__restrict__ parent, const uint32_t *__restrict__ isrc,
+                                 const uint32_t *__restrict__ ipos, const int64_t *__restrict__ eid,
+                                 const uint32_t *__restrict__ row, const uint32_t *__restrict__ lane_dst,
+                                 const int32_t *__restrict__ found, const unsigned long long *__restrict__ lane_off,
+                                 int W, int mode, int64_t *__restrict__ out) {
+	const int lane = blockIdx.x * blockDim.x + threadIdx.x;
+	if (lane >= W) return;
+	const int L = found[lane];
+	if (L < 0) return;
+	uint32_t cur = lane_dst[lane];
+	int64_t *o = out + lane_off[lane];
+	if (mode == 0) {
+		o[L] = (int64_t)cur;
+		for (int k = L - 1; k >= 0; k--) {
+			uint32_t q = parent[(size_t)cur * W + lane];
+			cur = isrc[q];
+			o[k] = (int64_t)cur;
+		}
+	} else {
+		o[2 * L] = (int64_t)cur;
+		for (int k = L - 1; k >= 0; k--) {
+			uint32_t q = parent[(size_t)cur * W + lane];
+			uint32_t p = ipos[q];
+			o[2 * k + 1] = eid ? eid[p] : (int64_t)row[p];
+			cur = isrc[q];
+			o[2 * k] = (int64_t)cur;
+		}
+	}
+}
+
+} // namespace pgq

@@ -1,0 +1,140 @@
+/*
+ * pgq_b200 — C ABI of the B200-native DuckPGQ graph hot path.
+ *
+ * This is the drop-in boundary: plain C types, caller-owned buffers, int return codes
+ * (0 = ok, <0 = error; text via pgq_last_error()).  No torch / C++ types cross it.
+ * The DuckDB extension (duckdb-pgq.old_b200/ext/pgq_b200_extension.cpp) and the Python
+ * host (duckdb-pgq.old_b200/__init__.py, ctypes) are both thin callers of these entry
+ * points.  There is NO CPU fallback: every compute entry point fails with PGQ_ERR_CUDA
+ * when no sm_100 device / driver is present.
+ *
+ * What each entry point replaces.  The PGQ scalar functions themselves are not in the
+ * mounted reference; their semantics are rules R1-R9 of SURVEY.md §8(a).
+ * The DuckDB-side contracts they plug into ARE in the tree and are cited per function:
+ *   scalar_function_t     /root/reference/src/include/duckdb/function/scalar_function.hpp:24
+ *   one call = one chunk  /root/reference/src/execution/expression_executor/execute_function.cpp:19-40
+ *   <=1024 rows per call  /root/reference/src/include/duckdb/common/vector_size.hpp:16-18
+ *   list_entry_t layout   /root/reference/src/include/duckdb/common/types.hpp:188-195
+ *   validity = 1 bit/row  /root/reference/src/include/duckdb/common/types/validity_mask.hpp:151-156,190-196
+ *                         (the shim expands/packs bits to the one-byte-per-row arrays used here)
+ */
+#ifndef PGQ_B200_H
+#define PGQ_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PGQ_OK 0
+#define PGQ_ERR_INVALID (-1)  /* bad argument / unknown csr id / id out of range */
+#define PGQ_ERR_CUDA (-2)     /* CUDA runtime error or no device */
+#define PGQ_ERR_OOM (-3)      /* device or host allocation failed */
+#define PGQ_ERR_STATE (-4)    /* call order violated (e.g. query before finalize) */
+#define PGQ_ERR_MISMATCH (-5) /* create_csr_vertex counts disagree with the edge rows */
+
+typedef struct pgq_ctx pgq_ctx_t;
+
+/* list_entry_t {uint64 offset; uint64 length} — types.hpp:188-195 */
+typedef struct {
+	uint64_t offset;
+	uint64_t length;
+} pgq_list_entry_t;
+
+typedef struct {
+	uint64_t kernel_launches; /* kernels of this library launched since the last reset */
+	uint64_t batches;         /* MS-BFS batches */
+	uint64_t levels;          /* level steps */
+	uint64_t edges_lane;      /* TEPS numerator (only when option "stats"=1), SURVEY.md §8(d) */
+	uint64_t edges_unique;    /* unique edge visits (only when option "stats"=1) */
+	uint64_t algo_bytes;      /* algorithmic bytes of the level kernels, §8(d) formula ("stats"=1) */
+	double level_kernel_ms;   /* CUDA-event time of the level (pull/push) kernels ("timing"=1) */
+	uint64_t level_kernel_launches;
+	double csr_build_ms;      /* CUDA-event time of the last device CSR build (K1-K3) */
+	double transpose_ms;      /* CUDA-event time of the last reverse-CSR build */
+	uint64_t h2d_bytes;       /* bytes copied host->device by this library since reset */
+	uint64_t d2h_bytes;
+} pgq_stats_t;
+
+/* ---- context ------------------------------------------------------------------------- */
+int pgq_init(int device, pgq_ctx_t **out_ctx);
+int pgq_shutdown(pgq_ctx_t *ctx);
+const char *pgq_last_error(void); /* thread-local message of the last failing call */
+
+/* options: "lanes" (0=auto, 64,128,256,512), "stats" (0/1), "timing" (0/1),
+ *          "small_max", "hub_min" (in-degree bin thresholds), "direction" (0 auto,1 pull only) */
+int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value);
+int pgq_get_stats(pgq_ctx_t *ctx, pgq_stats_t *out);
+int pgq_reset_stats(pgq_ctx_t *ctx);
+
+/* ---- CSR lifecycle: mirrors create_csr_vertex / create_csr_edge (R1-R3) ------------------ */
+/* CsrInitializeVertex: allocate v[V+2] zero-filled for csr `id` (first create_csr_vertex call). */
+int pgq_csr_create(pgq_ctx_t *ctx, int32_t id, int64_t v_size);
+/* create_csr_vertex rows: v[vid+2] = cnt; *out_sum += sum(cnt) (what the SQL caller SUMs). */
+int pgq_csr_set_degrees(pgq_ctx_t *ctx, int32_t id, const int64_t *vid, const int64_t *cnt, int64_t n,
+                        int64_t *out_sum);
+/* CsrInitializeEdge: e.resize(E) + prefix sum (first create_csr_edge call). */
+int pgq_csr_begin_edges(pgq_ctx_t *ctx, int32_t id, int64_t e_size);
+/* create_csr_edge rows, appended in ARRIVAL order (= the stable key; R3).  eid may be NULL. */
+int pgq_csr_add_edges(pgq_ctx_t *ctx, int32_t id, const int64_t *src, const int64_t *dst,
+                      const int64_t *eid, int64_t n);
+/* Runs K1 (degree histogram) + K2 (exclusive scan) + K3 (stable scatter) on the device. */
+int pgq_csr_finalize(pgq_ctx_t *ctx, int32_t id);
+
+#define PGQ_CSR_ROWIDS 1 /* eid==NULL: edge ids = input row numbers (kept for mode-1 paths/download) */
+/* One-shot build from HOST arrays (create + begin + add + finalize). */
+int pgq_csr_build(pgq_ctx_t *ctx, int32_t id, int64_t v_size, int64_t e_size, const int64_t *src,
+                  const int64_t *dst, const int64_t *eid, int flags);
+/* One-shot build from DEVICE int64 arrays (inputs already resident in HBM). */
+int pgq_csr_build_device(pgq_ctx_t *ctx, int32_t id, int64_t v_size, int64_t e_size, const int64_t *d_src,
+                         const int64_t *d_dst, const int64_t *d_eid, int flags);
+/* Reference-layout arrays: v[V+2], e[E], eid[E] (any pointer may be NULL to skip). */
+int pgq_csr_download(pgq_ctx_t *ctx, int32_t id, int64_t *v, int64_t *e, int64_t *eid);
+int pgq_csr_info(pgq_ctx_t *ctx, int32_t id, int64_t *v_size, int64_t *e_size);
+int pgq_csr_delete(pgq_ctx_t *ctx, int32_t id);
+/* Build the reverse CSR + degree bins now (otherwise done lazily by the first query). */
+int pgq_csr_prepare(pgq_ctx_t *ctx, int32_t id);
+
+/* ---- queries: iterativelength / reachability / shortestpath (R4-R9) ------------------------ */
+/* HOST buffers, one byte per row validity (NULL = all valid).  out_valid[i]==0 -> SQL NULL. */
+int pgq_iterativelength(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                        const uint8_t *src_valid, const uint8_t *dst_valid, int64_t *out,
+                        uint8_t *out_valid);
+int pgq_reachability(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                     const uint8_t *src_valid, const uint8_t *dst_valid, uint8_t *out, uint8_t *out_valid);
+/* mode 0: [src,...,dst]; mode 1: [src,e0,v1,e1,...,dst].  *out_vals is allocated by the
+ * library (pgq_free), *out_total = number of int64 values; entries[i] = list_entry_t. */
+int pgq_shortestpath(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                     const uint8_t *src_valid, const uint8_t *dst_valid, int mode,
+                     pgq_list_entry_t *entries, uint8_t *out_valid, int64_t **out_vals,
+                     uint64_t *out_total);
+void pgq_free(void *p);
+
+/* DEVICE-resident variant (all rows valid): d_out int64[n] (-1 = no path), d_out_valid uint8[n]. */
+int pgq_iterativelength_device(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *d_src,
+                               const int64_t *d_dst, int64_t *d_out, uint8_t *d_out_valid);
+
+/* ---- bench / test helpers (not part of the reference surface) ------------------------------ */
+int pgq_dev_alloc(pgq_ctx_t *ctx, uint64_t bytes, void **out_dptr);
+int pgq_dev_free(pgq_ctx_t *ctx, void *dptr);
+int pgq_dev_h2d(pgq_ctx_t *ctx, void *dptr, const void *hptr, uint64_t bytes);
+int pgq_dev_d2h(pgq_ctx_t *ctx, void *hptr, const void *dptr, uint64_t bytes);
+int pgq_host_alloc_pinned(uint64_t bytes, void **out_hptr);
+int pgq_host_free_pinned(void *hptr);
+int pgq_sync(pgq_ctx_t *ctx);
+/* synthetic edge tables written straight into HBM (same streams as oracle/pgq_gen.h) */
+int pgq_gen_rmat_device(pgq_ctx_t *ctx, uint64_t seed, int scale, int64_t e_size, int64_t *d_src,
+                        int64_t *d_dst);
+int pgq_gen_knows_device(pgq_ctx_t *ctx, uint64_t seed, int64_t v_size, int64_t e_size, uint64_t mult,
+                         uint64_t add, int64_t *d_src, int64_t *d_dst);
+/* write >L2-sized scratch so the next timed step starts with a cold L2 */
+int pgq_flush_l2(pgq_ctx_t *ctx);
+/* CUDA-event stopwatch on the library's stream */
+int pgq_timer_start(pgq_ctx_t *ctx);
+int pgq_timer_stop_ms(pgq_ctx_t *ctx, double *out_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,8 +1,8 @@
 /*
- * TEST / BENCH INFRASTRUCTURE ONLY — synthetic input generators.
+ * Synthetic input generators (bench / test inputs only; no query algorithm lives here).
  *
  * Counter-based (stateless) generators so that the CPU side here and the CUDA
- * side (duckdb-pgq.old_b200/csrc/gen.cu) produce bit-identical edge tables from
+ * side (duckdb-pgq.old_b200/csrc/gen.cu) and the CPU oracle (oracle/) produce bit-identical edge tables from
  * (seed, row index) alone.  All arithmetic is integer: no float thresholds, so
  * host and device cannot disagree on rounding.
  *

@@ -4,7 +4,7 @@
  */
 #define _GNU_SOURCE
 #include "pgq_oracle.h"
-#include "pgq_gen.h"
+#include "../include/pgq_gen.h"
 
 #include <pthread.h>
 #include <stdlib.h>
