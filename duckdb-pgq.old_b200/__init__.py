@@ -151,10 +151,15 @@ class Context:
         self._chk(self.lib.pgq_csr_add_edges(self._ctx, C.c_int32(csr_id), ps, pd, pe, C.c_int64(src.shape[0])))
         return int(src.shape[0])
 
-    def csr_finalize(self, csr_id):
-        self._chk(self.lib.pgq_csr_finalize(self._ctx, C.c_int32(csr_id)))
+    def _forget(self, csr_id):
         self.__dict__.get("_vertex_started", {}).pop(csr_id, None)
         self.__dict__.get("_edge_started", {}).pop(csr_id, None)
+
+    def csr_finalize(self, csr_id):
+        try:
+            self._chk(self.lib.pgq_csr_finalize(self._ctx, C.c_int32(csr_id)))
+        finally:
+            self._forget(csr_id)
 
     def csr_build(self, csr_id, v_size, src, dst, eid=None, rowids=False):
         src, ps = _i64(src)
@@ -188,6 +193,7 @@ class Context:
         return v, e[:E], (eid[:E] if want_eid else None)
 
     def csr_delete(self, csr_id):
+        self._forget(csr_id)
         self._chk(self.lib.pgq_csr_delete(self._ctx, C.c_int32(csr_id)))
 
     def csr_prepare(self, csr_id):

@@ -1,0 +1,304 @@
+"""GPU parity suite (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle on
+the same seeded inputs — bit-exact CSR arrays, lengths, reachability and paths."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import orc
+from golden_cases import CASES, CSR_EXPECT
+from helpers import lengths_list, unpack_paths, assert_paths_equal, check_path_valid
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _build_both(ctx, V, src, dst, eid=None, csr_id=1):
+    v, e, eids = orc.csr_build(V, src, dst, eid)
+    ctx.csr_build(csr_id, V, src, dst, eid=eid, rowids=True)
+    return v, e, eids
+
+
+def _cmp_arr(name, a, b):
+    a, b = np.asarray(a), np.asarray(b)
+    if a.shape != b.shape or not np.array_equal(a, b):
+        n = min(len(a), len(b))
+        bad = np.nonzero(a[:n] != b[:n])[0]
+        raise AssertionError("%s mismatch: shapes %s/%s first bad %s gpu=%s orc=%s" %
+                             (name, a.shape, b.shape, bad[:8], a[bad[:8]], b[bad[:8]]))
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_golden_cases(ctx, name):
+    c = CASES[name]
+    src = [a for a, _ in c["edges"]]
+    dst = [b for _, b in c["edges"]]
+    ctx.csr_build(7, c["V"], src, dst, rowids=True)
+    v, e, eid = ctx.csr_download(7, want_eid=True)
+    if name in CSR_EXPECT:
+        assert v.tolist() == CSR_EXPECT[name]["v"]
+        assert e.tolist() == CSR_EXPECT[name]["e"]
+        assert eid.tolist() == CSR_EXPECT[name]["eid"]
+    qs = [a for a, _ in c["q"]]
+    qd = [b for _, b in c["q"]]
+    out, ov = ctx.iterativelength(7, qs, qd)
+    assert lengths_list(out, ov) == c["lengths"]
+    r, rv = ctx.reachability(7, qs, qd)
+    assert rv.tolist() == [1] * len(qs) and r.tolist() == c["reach"]
+    assert unpack_paths(*ctx.shortestpath(7, qs, qd, mode=0)) == c["paths"]
+    assert unpack_paths(*ctx.shortestpath(7, qs, qd, mode=1)) == c["paths_e"]
+    ctx.csr_delete(7)
+
+
+def test_cte_golden(ctx):
+    g = json.load(open(os.path.join(GOLD, "cte_lengths.json")))
+    ctx.csr_build(8, g["V"], g["src"], g["dst"])
+    out, ov = ctx.iterativelength(8, g["q_src"], g["q_dst"])
+    assert lengths_list(out, ov) == g["expected"]
+    ctx.csr_delete(8)
+
+
+@pytest.mark.parametrize("scale,ef", [(8, 4), (12, 16), (16, 16), (18, 16)])
+def test_csr_bit_identical_rmat(ctx, scale, ef):
+    V = 1 << scale
+    src, dst = orc.gen_rmat(0x5eed0000 + scale, scale, E=ef << scale)
+    v, e, eids = _build_both(ctx, V, src, dst)
+    gv, ge, geid = ctx.csr_download(1, want_eid=True)
+    _cmp_arr("v", gv, v)
+    _cmp_arr("e", ge, e)
+    _cmp_arr("eid", geid, eids)
+    ctx.csr_delete(1)
+
+
+def test_csr_with_explicit_edge_ids_and_chunked_rows(ctx):
+    """create_csr_vertex + create_csr_edge fed in 1024-row chunks like DuckDB does (R2/R3)."""
+    V, E = 5000, 60000
+    src, dst = orc.gen_knows(21, V, E)
+    eid = (np.arange(E, dtype=np.int64) * 7 + 13)
+    v, e, eids = orc.csr_build(V, src, dst, eid)
+    cnt = np.bincount(src, minlength=V).astype(np.int64)
+    total = 0
+    for lo in range(0, V, 1024):
+        total += ctx.create_csr_vertex(3, V, np.arange(lo, min(V, lo + 1024)), cnt[lo:lo + 1024])
+    assert total == E
+    for lo in range(0, E, 1024):
+        ctx.create_csr_edge(3, V, E, src[lo:lo + 1024], dst[lo:lo + 1024], eid[lo:lo + 1024])
+    ctx.csr_finalize(3)
+    gv, ge, geid = ctx.csr_download(3, want_eid=True)
+    _cmp_arr("v", gv, v)
+    _cmp_arr("e", ge, e)
+    _cmp_arr("eid", geid, eids)
+    ctx.csr_delete(3)
+
+
+def test_csr_count_mismatch_is_an_error(ctx):
+    import pgq_b200
+    ctx.create_csr_vertex(4, 4, [0, 1, 2, 3], [1, 0, 0, 0])
+    ctx.create_csr_edge(4, 4, 2, [0, 1], [1, 2])
+    with pytest.raises(pgq_b200.PgqError):
+        ctx.csr_finalize(4)
+    ctx.csr_delete(4)
+    with pytest.raises(pgq_b200.PgqError):
+        ctx.csr_build(4, 4, [0, 9], [1, 2])  # id out of range
+    ctx.csr_delete(4)
+
+
+def test_empty_graphs(ctx):
+    ctx.csr_build(5, 3, [], [])
+    v, e, _ = ctx.csr_download(5)
+    assert v.tolist() == [0, 0, 0, 0, 0] and len(e) == 0
+    out, ov = ctx.iterativelength(5, [0, 1], [1, 1])
+    assert lengths_list(out, ov) == [None, 0]
+    out, ov = ctx.iterativelength(5, [], [])
+    assert len(out) == 0
+    ctx.csr_delete(5)
+
+
+@pytest.mark.parametrize("lanes", [0, 64, 128, 256, 512])
+def test_lengths_rmat_all_lane_widths(ctx, lanes):
+    scale = 14
+    V = 1 << scale
+    src, dst = orc.gen_rmat(0x5eed0000 + scale, scale)
+    v, e, _ = _build_both(ctx, V, src, dst)
+    n = 1500
+    ps, pd = orc.gen_pairs(5, V, v, n)
+    rng = np.random.default_rng(1)
+    sv = (rng.random(n) > 0.01).astype(np.uint8)
+    dv = (rng.random(n) > 0.01).astype(np.uint8)
+    ps[::97] = pd[::97]  # ~1% trivial rows
+    ctx.set_option("lanes", lanes)
+    ctx.set_option("stats", 1)
+    ctx.reset_stats()
+    try:
+        out, ov = ctx.iterativelength(1, ps, pd, sv, dv)
+        st = ctx.stats()
+    finally:
+        ctx.set_option("lanes", 0)
+        ctx.set_option("stats", 0)
+    eo, ev, est = orc.iterativelength(V, v, e, ps, pd, sv, dv, stats=True)
+    _cmp_arr("valid", ov, ev)
+    _cmp_arr("length", out, eo)
+    if lanes in (0, 512):
+        # TEPS numerator and batch/level structure agree with the reference-shaped oracle
+        assert st["edges_lane"] == est["edges_lane"]
+        assert st["batches"] == est["batches"] and st["levels"] <= est["levels"]
+        assert st["edges_unique"] == est["edges_unique"]
+    r, rv = ctx.reachability(1, ps, pd, sv, dv)
+    er, erv = orc.reachability(V, v, e, ps, pd, sv, dv)
+    _cmp_arr("reach valid", rv, erv)
+    _cmp_arr("reach", r, er)
+    ctx.csr_delete(1)
+
+
+@pytest.mark.parametrize("bins", [(0, 1), (2, 8), (32, 4096), (1 << 30, 1 << 30)])
+def test_lengths_all_degree_bins(ctx, bins):
+    """Force every vertex through each of the small / warp / hub kernels."""
+    V, E = 3000, 90000
+    src, dst = orc.gen_knows(33, V, E)
+    v, e, _ = _build_both(ctx, V, src, dst)
+    ps, pd = orc.gen_pairs(6, V, v, 700)
+    ctx.set_option("small_max", bins[0])
+    ctx.set_option("hub_min", bins[1])
+    ctx.set_option("hub_chunk", 256)
+    try:
+        out, ov = ctx.iterativelength(1, ps, pd)
+        p = ctx.shortestpath(1, ps, pd, mode=1)
+    finally:
+        ctx.set_option("small_max", 32)
+        ctx.set_option("hub_min", 4096)
+        ctx.set_option("hub_chunk", 4096)
+    eo, ev = orc.iterativelength(V, v, e, ps, pd)
+    _cmp_arr("valid", ov, ev)
+    _cmp_arr("length", out, eo)
+    _, _, eids = orc.csr_build(V, src, dst)
+    assert_paths_equal(p, orc.shortestpath(V, v, e, eids, ps, pd, mode=1), "paths bins=%s" % (bins,))
+    ctx.csr_delete(1)
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("graph", ["rmat12", "knows"])
+def test_shortestpath_bit_identical(ctx, graph, mode):
+    if graph == "rmat12":
+        V = 1 << 12
+        src, dst = orc.gen_rmat(0x5eed0000 + 12, 12)
+    else:
+        V = 10000
+        src, dst = orc.gen_knows(0x1dbc, V, 180000)
+    v, e, eids = _build_both(ctx, V, src, dst)
+    n = 1300
+    ps, pd = orc.gen_pairs(8, V, v, n)
+    rng = np.random.default_rng(2)
+    sv = (rng.random(n) > 0.02).astype(np.uint8)
+    ps[::53] = pd[::53]
+    got = ctx.shortestpath(1, ps, pd, sv, None, mode=mode)
+    exp = orc.shortestpath(V, v, e, eids, ps, pd, sv, None, mode=mode)
+    assert_paths_equal(got, exp, "%s mode %d" % (graph, mode))
+    paths = unpack_paths(*got)
+    if mode == 0:
+        for i in range(0, n, 17):
+            if paths[i] is not None and len(paths[i]) > 1:
+                check_path_valid(V, v, e, int(ps[i]), int(pd[i]), paths[i])
+    ctx.csr_delete(1)
+
+
+def test_config1_ldbc_sf1_shape(ctx):
+    """BASELINE config 1: LDBC-SF1-shaped knows graph, CSR build + iterativelength for 2048 pairs."""
+    V, E = 10000, 180000
+    src, dst = orc.gen_knows(0x1dbc0001, V, E)
+    v, e, _ = _build_both(ctx, V, src, dst)
+    gv, ge, _ = ctx.csr_download(1)
+    _cmp_arr("v", gv, v)
+    _cmp_arr("e", ge, e)
+    ps, pd = orc.gen_pairs(1, V, v, 2048)
+    out, ov = ctx.iterativelength(1, ps, pd)
+    _, eo, ev = orc.run_chunks_mt(0, 4, V, v, e, ps, pd)
+    _cmp_arr("valid", ov, ev)
+    _cmp_arr("length", out, eo)
+    ctx.csr_delete(1)
+
+
+def test_device_resident_variant_and_generators(ctx):
+    scale = 13
+    V, E = 1 << scale, 16 << scale
+    seed = 0x5eed0000 + scale
+    d_src = ctx.dev_alloc(E * 8)
+    d_dst = ctx.dev_alloc(E * 8)
+    ctx.gen_rmat_device(seed, scale, E, d_src, d_dst)
+    hs = np.empty(E, dtype=np.int64)
+    hd = np.empty(E, dtype=np.int64)
+    ctx.d2h(hs, d_src)
+    ctx.d2h(hd, d_dst)
+    es, ed = orc.gen_rmat(seed, scale)
+    _cmp_arr("gen src", hs, es)
+    _cmp_arr("gen dst", hd, ed)
+    ctx.csr_build_device(2, V, E, d_src, d_dst)
+    v, e, _ = orc.csr_build(V, es, ed)
+    gv, ge, _ = ctx.csr_download(2)
+    _cmp_arr("v", gv, v)
+    _cmp_arr("e", ge, e)
+    n = 2000
+    ps, pd = orc.gen_pairs(4, V, v, n)
+    ps[::41] = pd[::41]
+    d_ps, d_pd = ctx.dev_alloc(n * 8), ctx.dev_alloc(n * 8)
+    d_out, d_ov = ctx.dev_alloc(n * 8), ctx.dev_alloc(n)
+    ctx.h2d(d_ps, ps)
+    ctx.h2d(d_pd, pd)
+    ctx.iterativelength_device(2, n, d_ps, d_pd, d_out, d_ov)
+    out = np.empty(n, dtype=np.int64)
+    ov = np.empty(n, dtype=np.uint8)
+    ctx.d2h(out, d_out)
+    ctx.d2h(ov, d_ov)
+    eo, ev = orc.iterativelength(V, v, e, ps, pd)
+    _cmp_arr("valid", ov, ev)
+    _cmp_arr("length", out, eo)
+    # knows generator parity
+    KV, KE = 7000, 50000
+    mult, add = orc.knows_params(KV)
+    ctx.gen_knows_device(9, KV, KE, mult, add, d_src, d_dst)
+    ks = np.empty(KE, dtype=np.int64)
+    kd = np.empty(KE, dtype=np.int64)
+    ctx.d2h(ks, d_src)
+    ctx.d2h(kd, d_dst)
+    oks, okd = orc.gen_knows(9, KV, KE)
+    _cmp_arr("knows src", ks, oks)
+    _cmp_arr("knows dst", kd, okd)
+    for p in (d_src, d_dst, d_ps, d_pd, d_out, d_ov):
+        ctx.dev_free(p)
+    ctx.csr_delete(2)
+
+
+def test_large_scale_properties(ctx):
+    """R-MAT scale 20 (1M vertices, 16M edges): sizes where the oracle is slow.  Checks
+    size-independent properties: CSR checksums vs a numpy stable sort, lane-width independence,
+    path validity and |path| == iterativelength + 1, sampled textbook BFS."""
+    scale = 20
+    V, E = 1 << scale, 16 << scale
+    src, dst = orc.gen_rmat(0x5eed0000 + scale, scale)
+    ctx.csr_build(9, V, src, dst)
+    gv, ge, _ = ctx.csr_download(9)
+    order = np.argsort(src, kind="stable")
+    _cmp_arr("e (stable sort)", ge, dst[order])
+    cnt = np.bincount(src, minlength=V)
+    _cmp_arr("v", gv, np.concatenate([[0], np.cumsum(cnt), [E]]))
+    n = 1024
+    ps, pd = orc.gen_pairs(2, V, gv, n)
+    out512, ov512 = ctx.iterativelength(9, ps, pd)
+    ctx.set_option("lanes", 64)
+    try:
+        out64, ov64 = ctx.iterativelength(9, ps[:256], pd[:256])
+    finally:
+        ctx.set_option("lanes", 0)
+    _cmp_arr("lane-width independence", out64, out512[:256])
+    for i in range(0, n, 128):
+        dist = orc.bfs_simple(V, gv, ge, int(ps[i]))
+        assert (int(out512[i]) if ov512[i] else -1) == int(dist[pd[i]])
+    paths = unpack_paths(*ctx.shortestpath(9, ps[:512], pd[:512]))
+    for i in range(512):
+        if ov512[i]:
+            assert paths[i] is not None and len(paths[i]) == out512[i] + 1
+            if i % 16 == 0:
+                check_path_valid(V, gv, ge, int(ps[i]), int(pd[i]), paths[i])
+        else:
+            assert paths[i] is None
+    ctx.csr_delete(9)
