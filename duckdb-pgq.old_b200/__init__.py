@@ -28,7 +28,7 @@ class PgqError(RuntimeError):
 
 
 class Stats(C.Structure):
-    _fields_ = [("kernel_launches", C.c_uint64), ("batches", C.c_uint64), ("levels", C.c_uint64),
+    _fields_ = [("kernel_launches", C.c_uint64), ("batches", C.c_uint64), ("levels", C.c_uint64), ("push_levels", C.c_uint64),
                 ("edges_lane", C.c_uint64), ("edges_unique", C.c_uint64), ("algo_bytes", C.c_uint64),
                 ("level_kernel_ms", C.c_double), ("level_kernel_launches", C.c_uint64),
                 ("csr_build_ms", C.c_double), ("transpose_ms", C.c_double),

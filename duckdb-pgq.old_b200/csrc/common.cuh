@@ -116,7 +116,9 @@ struct Options {
 	int64_t small_max = 32;
 	int64_t hub_min = 4096;
 	int64_t hub_chunk = 4096;
-	int64_t direction = 0;
+	int64_t direction = 0; // 0 auto (push when the frontier is sparse), 1 pull only
+	int64_t trace = 0;     // with timing=1: per-level line on stderr
+	int64_t push_beta = 4; // push when frontier out-edges * push_beta <= E
 };
 
 struct Ctx {
@@ -131,6 +133,7 @@ struct Ctx {
 	DevBuf scan_tmp;
 	DevBuf sort_keys[2], sort_p0[2], sort_p1[2], sort_hist;
 	DevBuf bfs_seen, bfs_visit[2], bfs_parent, bfs_hubacc;
+	DevBuf bfs_queue[2], bfs_inq[2]; // push work queues + dedupe bitmaps
 	DevBuf bfs_lane; // per-call lane tables
 	DevBuf bfs_ctrl; // device control block
 	DevBuf l2_flush;

@@ -10,6 +10,9 @@ namespace {
 
 struct BatchBufs {
 	uint32_t *seen, *visit[2], *parent, *hubacc;
+	uint2 *queue[2];
+	uint32_t *inq[2];
+	size_t inq_bytes;
 	BfsCtrl *ctrl;
 };
 
@@ -28,6 +31,7 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents) {
 	a.V = (uint32_t)g->V;
 	a.small_max = (uint32_t)c->opt.small_max;
 	a.hubacc = b.hubacc;
+	a.off = g->d_off.as<int64_t>();
 	const uint64_t small_threads = (uint64_t)g->V * C::TPV;
 	if (small_threads) {
 		uint32_t grid = div_up(small_threads, 256);
@@ -73,6 +77,59 @@ int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, bool pare
 	return PGQ_ERR_INVALID;
 }
 
+// One top-down level over queue[q] (frontier in visit[cur]); builds queue[q^1].
+template <int W>
+int launch_push(Ctx *c, Csr *g, const BatchBufs &b, int cur, int q) {
+	PushArgs a{};
+	a.off = g->d_off.as<int64_t>();
+	a.tgt = g->d_tgt.as<uint32_t>();
+	a.visit = b.visit[cur];
+	a.visit_rw = b.visit[cur];
+	a.next = b.visit[cur ^ 1];
+	a.seen = b.seen;
+	a.ctrl = b.ctrl;
+	a.queue = b.queue[q];
+	a.queue_next = b.queue[q ^ 1];
+	a.inq_next = b.inq[q ^ 1];
+	a.inq_cur = b.inq[q];
+	const uint32_t grid = (uint32_t)c->sm_count * 8;
+	push_kernel<W><<<grid, 256, 0, c->stream>>>(a);
+	push_cleanup_kernel<W><<<grid, 256, 0, c->stream>>>(a);
+	count_launch(c, 2);
+	return PGQ_OK;
+}
+
+int launch_push_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, int q) {
+	switch (W) {
+	case 64: return launch_push<64>(c, g, b, cur, q);
+	case 128: return launch_push<128>(c, g, b, cur, q);
+	case 256: return launch_push<256>(c, g, b, cur, q);
+	case 512: return launch_push<512>(c, g, b, cur, q);
+	}
+	return PGQ_ERR_INVALID;
+}
+
+// pull -> push transition: queue[q] from the dense frontier visit[cur]; visit[cur^1] and the
+// dedupe bitmaps start clean.
+int launch_compact(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, int q) {
+	cudaStream_t st = c->stream;
+	const size_t bm = (size_t)g->V * (W / 8);
+	PGQ_CUDA(cudaMemsetAsync(b.visit[cur ^ 1], 0, bm, st));
+	PGQ_CUDA(cudaMemsetAsync(b.inq[0], 0, b.inq_bytes, st));
+	PGQ_CUDA(cudaMemsetAsync(b.inq[1], 0, b.inq_bytes, st));
+	const int64_t *off = g->d_off.as<int64_t>();
+	const uint32_t V = (uint32_t)g->V;
+	switch (W) {
+	case 64: compact_frontier_kernel<64><<<div_up((uint64_t)V * LaneCfg<64>::TPV, 256), 256, 0, st>>>(b.visit[cur], V, off, b.queue[q], b.ctrl); break;
+	case 128: compact_frontier_kernel<128><<<div_up((uint64_t)V * LaneCfg<128>::TPV, 256), 256, 0, st>>>(b.visit[cur], V, off, b.queue[q], b.ctrl); break;
+	case 256: compact_frontier_kernel<256><<<div_up((uint64_t)V * LaneCfg<256>::TPV, 256), 256, 0, st>>>(b.visit[cur], V, off, b.queue[q], b.ctrl); break;
+	case 512: compact_frontier_kernel<512><<<div_up((uint64_t)V * LaneCfg<512>::TPV, 256), 256, 0, st>>>(b.visit[cur], V, off, b.queue[q], b.ctrl); break;
+	}
+	bfs_snapshot_kernel<<<1, 1, 0, st>>>(b.ctrl);
+	count_launch(c, 2);
+	return PGQ_OK;
+}
+
 void launch_count(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur) {
 	uint32_t grid = div_up(g->V, 256);
 	if (!grid) return;
@@ -112,6 +169,14 @@ int alloc_bufs(Ctx *c, Csr *g, int W, bool parents, BatchBufs *b) {
 	b->parent = parents ? c->bfs_parent.as<uint32_t>() : nullptr;
 	b->hubacc = c->bfs_hubacc.as<uint32_t>();
 	b->ctrl = c->bfs_ctrl.as<BfsCtrl>();
+	const size_t qcap = (size_t)g->V + (size_t)(g->E / PUSH_CHUNK) + 2;
+	b->inq_bytes = ((size_t)g->V / 32 + 1) * sizeof(uint32_t);
+	for (int i = 0; i < 2; i++) {
+		PGQ_TRY(c->bfs_queue[i].reserve(qcap * sizeof(uint2)));
+		PGQ_TRY(c->bfs_inq[i].reserve(b->inq_bytes));
+		b->queue[i] = c->bfs_queue[i].as<uint2>();
+		b->inq[i] = c->bfs_inq[i].as<uint32_t>();
+	}
 	return PGQ_OK;
 }
 
@@ -123,19 +188,37 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 	if (bm) {
 		PGQ_CUDA(cudaMemsetAsync(b.seen, 0, bm, st));
 		PGQ_CUDA(cudaMemsetAsync(b.visit[0], 0, bm, st));
+		PGQ_CUDA(cudaMemsetAsync(b.visit[1], 0, bm, st)); // a top-down level 1 ORs into it
 	}
-	bfs_init_kernel<<<1, W, 0, st>>>(d_lane_src, W, b.visit[0], d_found, b.ctrl);
+	PGQ_CUDA(cudaMemsetAsync(b.inq[0], 0, b.inq_bytes, st));
+	PGQ_CUDA(cudaMemsetAsync(b.inq[1], 0, b.inq_bytes, st));
+	bfs_init_kernel<<<1, W, 0, st>>>(d_lane_src, W, b.visit[0], d_found, b.ctrl, g->d_off.as<int64_t>(), b.queue[0],
+	                                 b.inq[0]);
 	count_launch(c);
 	BfsCtrl h;
 	PGQ_TRY(read_ctrl(c, b, &h));
 	c->stats.batches++;
 	uint32_t active = h.n_active;
-	int cur = 0;
+	int cur = 0, q = 0;
+	bool have_queue = true; // queue[q] describes visit[cur] and visit[cur^1] is all-zero
 	for (int iter = 1; active; iter++) {
+		// direction switch on frontier density: top-down while the frontier's out-edges are few
+		const bool push = !parents && c->opt.direction == 0 &&
+		                  (unsigned long long)h.out_edges * (unsigned long long)c->opt.push_beta <=
+		                      (unsigned long long)g->E;
 		if (c->opt.stats) launch_count(c, g, b, W, cur);
 		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
 		uint64_t before = c->stats.kernel_launches;
-		PGQ_TRY(launch_level_w(c, g, b, W, cur, parents));
+		if (push) {
+			if (!have_queue) PGQ_TRY(launch_compact(c, g, b, W, cur, q));
+			PGQ_TRY(launch_push_w(c, g, b, W, cur, q));
+			have_queue = true;
+			q ^= 1;
+			c->stats.push_levels++;
+		} else {
+			PGQ_TRY(launch_level_w(c, g, b, W, cur, parents));
+			have_queue = false;
+		}
 		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
 		bfs_check_kernel<<<1, W, 0, st>>>(b.seen, d_lane_dst, W, d_found, b.ctrl, iter);
 		count_launch(c);
@@ -146,6 +229,10 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 			PGQ_CUDA(cudaEventElapsedTime(&ms, c->ev_a, c->ev_b));
 			c->stats.level_kernel_ms += ms;
 			c->stats.level_kernel_launches += c->stats.kernel_launches - 1 - before;
+			if (c->opt.trace)
+				fprintf(stderr, "[pgq] iter %d %s %.3f ms  next: verts %u edges %llu items %u  active %u change %u\n",
+				        iter, push ? "push" : "pull", ms, h.out_verts, (unsigned long long)h.out_edges, h.out_items,
+				        h.n_active, h.change_out);
 		}
 		if (!h.change_out) break;
 		active = h.n_active;

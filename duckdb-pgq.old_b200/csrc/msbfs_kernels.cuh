@@ -28,7 +28,17 @@ struct BfsCtrl {
 	unsigned long long edges_unique;
 	unsigned long long verts_active;
 	unsigned long long pad2;
+	// frontier being produced by the running level (accumulated), and its snapshot
+	unsigned long long next_edges; // sum of out-degrees of vertices with a non-empty next word
+	uint32_t next_verts;
+	uint32_t next_items;           // work items written to the next push queue
+	unsigned long long out_edges;
+	uint32_t out_verts;
+	uint32_t out_items;
 };
+
+// Push work item: out-edges [off[v] + chunk*PUSH_CHUNK, +PUSH_CHUNK) of frontier vertex v.
+static constexpr uint32_t PUSH_CHUNK = 1024;
 
 struct PullArgs {
 	const uint32_t *ioff;
@@ -40,6 +50,7 @@ struct PullArgs {
 	BfsCtrl *ctrl;
 	uint32_t V;
 	uint32_t small_max;
+	const int64_t *off;   // forward offsets (out-degree of new frontier vertices, direction heuristic)
 	const uint32_t *list; // mid or hub vertex list
 	uint32_t nlist;
 	const HubChunk *chunks;
@@ -148,6 +159,38 @@ __device__ __forceinline__ void flag_change(BfsCtrl *ctrl, bool anynew) {
 	}
 }
 
+__device__ __forceinline__ void snapshot_frontier(BfsCtrl *ctrl) {
+	ctrl->out_edges = ctrl->next_edges;
+	ctrl->out_verts = ctrl->next_verts;
+	ctrl->out_items = ctrl->next_items;
+	ctrl->next_edges = 0;
+	ctrl->next_verts = 0;
+	ctrl->next_items = 0;
+}
+
+// Frontier statistics for the direction switch: vertices with a non-empty `next` word and the sum
+// of their out-degrees.  `leader_new` is true in exactly one thread per such vertex.
+__device__ __forceinline__ void count_frontier(BfsCtrl *ctrl, const int64_t *off, uint32_t n, bool leader_new) {
+	unsigned long long deg = 0;
+	if (leader_new) deg = (unsigned long long)(off[n + 1] - off[n]);
+	const unsigned m = __ballot_sync(0xffffffffu, leader_new);
+	if (m == 0) return;
+#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) deg += __shfl_xor_sync(0xffffffffu, deg, d);
+	if ((threadIdx.x & 31) == 0) {
+		atomicAdd(&ctrl->next_edges, deg);
+		atomicAdd(&ctrl->next_verts, (uint32_t)__popc(m));
+	}
+}
+
+template <int TPV>
+__device__ __forceinline__ bool group_any(bool x) {
+	unsigned b = x ? 1u : 0u;
+#pragma unroll
+	for (int d = 1; d < TPV; d <<= 1) b |= __shfl_xor_sync(0xffffffffu, b, d);
+	return b != 0;
+}
+
 // ---- K4/K7 small: one TPV-thread group per vertex, in-degree <= small_max ---------------------
 template <int W, bool PARENTS>
 __global__ void __launch_bounds__(256) pull_small_kernel(PullArgs a) {
@@ -221,7 +264,10 @@ __global__ void __launch_bounds__(256) pull_small_kernel(PullArgs a) {
 			st_slice<SW>(a.seen + wo, s);
 		}
 	}
-	flag_change(a.ctrl, slice_any<SW>(news));
+	const bool anyn = slice_any<SW>(news);
+	flag_change(a.ctrl, anyn);
+	const bool gnew = group_any<TPV>(anyn);
+	count_frontier(a.ctrl, a.off, n, gnew && t == 0 && mine);
 }
 
 // ---- K4 mid: one warp per vertex (small_max < in-degree), lengths only -------------------------
@@ -275,7 +321,12 @@ __global__ void __launch_bounds__(256) pull_warp_kernel(PullArgs a) {
 			st_slice<SW>(a.seen + wo, s);
 		}
 	}
-	flag_change(a.ctrl, slice_any<SW>(news));
+	const bool wany = __any_sync(0xffffffffu, slice_any<SW>(news));
+	if (wany && lane == 0) {
+		a.ctrl->change = 1u;
+		atomicAdd(&a.ctrl->next_edges, (unsigned long long)(a.off[n + 1] - a.off[n]));
+		atomicAdd(&a.ctrl->next_verts, 1u);
+	}
 }
 
 // ---- K7 mid/hub with parents: one warp per vertex, in-edges consumed in ORDER -------------------
@@ -352,7 +403,12 @@ __global__ void __launch_bounds__(256) pull_warp_parents_kernel(PullArgs a) {
 			st_slice<SW>(a.seen + wo, s);
 		}
 	}
-	flag_change(a.ctrl, slice_any<SW>(news));
+	const bool wany = __any_sync(0xffffffffu, slice_any<SW>(news));
+	if (wany && lane == 0) {
+		a.ctrl->change = 1u;
+		atomicAdd(&a.ctrl->next_edges, (unsigned long long)(a.off[n + 1] - a.off[n]));
+		atomicAdd(&a.ctrl->next_verts, 1u);
+	}
 }
 
 // ---- K4 hubs: one block per chunk of a hub's in-list, partial ORs merged with atomicOr ---------
@@ -427,37 +483,64 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 			st_slice<SW>(a.seen + wo, s);
 		}
 	}
-	flag_change(a.ctrl, slice_any<SW>(news));
+	const bool anyn = slice_any<SW>(news);
+	flag_change(a.ctrl, anyn);
+	const bool gnew = group_any<TPV>(anyn);
+	count_frontier(a.ctrl, a.off, h < a.nlist ? a.list[h] : 0u, gnew && t == 0 && h < a.nlist);
 }
 
 // ---- batch init / K6 destination check / stats / K8 path reconstruction -----------------------
 
+// Appends vertex n to the push queue being built: one work item per PUSH_CHUNK out-edges (at
+// least one, so zero-out-degree vertices still get their frontier word cleaned up).
+__device__ __forceinline__ void enqueue_vertex(uint32_t n, const int64_t *off, uint2 *q, BfsCtrl *ctrl) {
+	const unsigned long long deg = (unsigned long long)(off[n + 1] - off[n]);
+	uint32_t k = (uint32_t)((deg + PUSH_CHUNK - 1) / PUSH_CHUNK);
+	if (k == 0) k = 1;
+	const uint32_t base = atomicAdd(&ctrl->next_items, k);
+	for (uint32_t c = 0; c < k; c++) q[base + c] = make_uint2(n, c);
+	atomicAdd(&ctrl->next_edges, deg);
+	atomicAdd(&ctrl->next_verts, 1u);
+}
+
 // One block of W threads.  Sets the source bits (R4: visit only, seen untouched), the active mask,
-// found = -1.  lane_src == 0xFFFFFFFF marks an unused lane slot.
+// found = -1, and the level-1 push queue (the distinct sources).  lane_src == 0xFFFFFFFF marks an
+// unused lane slot.  inq must be zero on entry.
 __global__ void bfs_init_kernel(const uint32_t *__restrict__ lane_src, int W, uint32_t *__restrict__ visit,
-                                int32_t *__restrict__ found, BfsCtrl *ctrl) {
+                                int32_t *__restrict__ found, BfsCtrl *ctrl, const int64_t *__restrict__ off,
+                                uint2 *__restrict__ queue, uint32_t *__restrict__ inq) {
 	__shared__ uint32_t cnt;
 	const int lane = threadIdx.x;
 	if (lane == 0) {
 		cnt = 0;
 		ctrl->change = 0; ctrl->change_out = 0;
 		ctrl->edges_lane = 0; ctrl->edges_unique = 0; ctrl->verts_active = 0;
+		ctrl->next_edges = 0; ctrl->next_verts = 0; ctrl->next_items = 0;
 	}
 	__syncthreads();
 	const uint32_t s = lane_src[lane];
 	const bool used = s != 0xFFFFFFFFu;
 	found[lane] = -1;
-	if (used) atomicOr(&visit[(size_t)s * (W / 32) + (lane >> 5)], 1u << (lane & 31));
+	if (used) {
+		atomicOr(&visit[(size_t)s * (W / 32) + (lane >> 5)], 1u << (lane & 31));
+		const uint32_t bit = 1u << (s & 31);
+		if (!(atomicOr(&inq[s >> 5], bit) & bit)) enqueue_vertex(s, off, queue, ctrl);
+	}
 	const unsigned m = __ballot_sync(0xffffffffu, used);
 	if ((lane & 31) == 0) {
 		ctrl->active[lane >> 5] = m;
 		atomicAdd(&cnt, (uint32_t)__popc(m));
 	}
 	__syncthreads();
-	if (lane == 0) ctrl->n_active = cnt;
+	if (lane == 0) {
+		ctrl->n_active = cnt;
+		__threadfence();
+		snapshot_frontier(ctrl);
+	}
 }
 
-// After a level: lanes whose destination has been seen get found=iter and leave the active mask.
+// After a level: lanes whose destination has been seen get found=iter and leave the active mask;
+// the frontier statistics of the level are snapshotted for the host's direction decision.
 __global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, const uint32_t *__restrict__ lane_dst, int W,
                                  int32_t *__restrict__ found, BfsCtrl *ctrl, int iter) {
 	__shared__ uint32_t cnt;
@@ -484,7 +567,116 @@ __global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, const uint32
 		ctrl->n_active = cnt;
 		ctrl->change_out = ctrl->change;
 		ctrl->change = 0;
+		snapshot_frontier(ctrl);
 	}
+}
+
+__global__ void bfs_snapshot_kernel(BfsCtrl *ctrl) {
+	snapshot_frontier(ctrl);
+}
+
+// ---- K4 top-down (push) for sparse frontiers ---------------------------------------------------
+// One warp per work item (frontier vertex v, chunk of its out-edges).  For every out-edge v->n and
+// every non-empty 32-lane word of visit[v]:  old = atomicOr(seen[n].w, bits); the bits that were
+// not in `old` are exactly next[n] = visit[v] & ~seen[n] of the reference (R4/R5), so they are
+// ORed into next[n] and n joins the next queue the first time that happens this level.
+struct PushArgs {
+	const int64_t *off;
+	const uint32_t *tgt;
+	const uint32_t *visit;
+	uint32_t *next;
+	uint32_t *seen;
+	BfsCtrl *ctrl;
+	const uint2 *queue;  // items of this level (count = ctrl->out_items)
+	uint2 *queue_next;   // items for the next level
+	uint32_t *inq_next;  // dedupe bitmap of queue_next
+	uint32_t *inq_cur;   // dedupe bitmap that built `queue` (cleared by the cleanup kernel)
+	uint32_t *visit_rw;  // same buffer as visit, for the cleanup kernel
+};
+
+template <int W>
+__global__ void __launch_bounds__(256) push_kernel(PushArgs a) {
+	constexpr int WPV = W / 32;
+	const uint32_t nitems = a.ctrl->out_items;
+	const uint32_t lane = threadIdx.x & 31;
+	const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+	bool anynew = false;
+	for (uint32_t it = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; it < nitems; it += nwarps) {
+		const uint2 item = a.queue[it];
+		const uint32_t v = item.x;
+		uint32_t word = 0;
+		if (lane < WPV) word = a.visit[(size_t)v * WPV + lane] & a.ctrl->active[lane];
+		const unsigned nz = __ballot_sync(0xffffffffu, word != 0);
+		if (nz == 0) continue;
+		const int64_t e0 = a.off[v] + (int64_t)item.y * PUSH_CHUNK;
+		int64_t e1 = a.off[v + 1];
+		if (e1 > e0 + PUSH_CHUNK) e1 = e0 + PUSH_CHUNK;
+		for (int64_t j0 = e0; j0 < e1; j0 += 32) {
+			const int64_t j = j0 + lane;
+			const bool have = j < e1;
+			const uint32_t n = have ? a.tgt[j] : 0u;
+			bool mynew = false;
+			unsigned rem = nz;
+			while (rem) { // warp-uniform loop over the non-empty words of visit[v]
+				const int w = __ffs(rem) - 1;
+				rem &= rem - 1;
+				const uint32_t bits = __shfl_sync(0xffffffffu, word, w);
+				if (have) {
+					const uint32_t old = atomicOr(&a.seen[(size_t)n * WPV + w], bits);
+					const uint32_t nb = bits & ~old;
+					if (nb) {
+						atomicOr(&a.next[(size_t)n * WPV + w], nb);
+						mynew = true;
+					}
+				}
+			}
+			if (mynew) {
+				anynew = true;
+				const uint32_t bit = 1u << (n & 31);
+				if (!(atomicOr(&a.inq_next[n >> 5], bit) & bit)) enqueue_vertex(n, a.off, a.queue_next, a.ctrl);
+			}
+		}
+	}
+	if (__any_sync(0xffffffffu, anynew) && lane == 0) a.ctrl->change = 1u;
+}
+
+// After a push level: consumed frontier words go back to zero (so the buffer can serve as `next`
+// two levels later) and the dedupe bits of the consumed queue are cleared.
+template <int W>
+__global__ void __launch_bounds__(256) push_cleanup_kernel(PushArgs a) {
+	constexpr int WPV = W / 32;
+	const uint32_t nitems = a.ctrl->out_items;
+	const uint32_t stride = gridDim.x * blockDim.x;
+	for (uint32_t it = blockIdx.x * blockDim.x + threadIdx.x; it < nitems; it += stride) {
+		const uint2 item = a.queue[it];
+		if (item.y != 0) continue;
+		const uint32_t v = item.x;
+		uint32_t *p = a.visit_rw + (size_t)v * WPV;
+		if (WPV >= 4) {
+#pragma unroll
+			for (int i = 0; i < WPV; i += 4) *reinterpret_cast<uint4 *>(p + i) = make_uint4(0, 0, 0, 0);
+		} else {
+#pragma unroll
+			for (int i = 0; i < WPV; i++) p[i] = 0;
+		}
+		atomicAnd(&a.inq_cur[v >> 5], ~(1u << (v & 31)));
+	}
+}
+
+// pull -> push transition: rebuild the queue from a dense frontier buffer.
+template <int W>
+__global__ void __launch_bounds__(256) compact_frontier_kernel(const uint32_t *__restrict__ visit, uint32_t V,
+                                                               const int64_t *__restrict__ off,
+                                                               uint2 *__restrict__ queue, BfsCtrl *ctrl) {
+	using C = LaneCfg<W>;
+	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
+	const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	const uint64_t n64 = gid / TPV;
+	const uint32_t t = (uint32_t)(gid % TPV);
+	bool any = false;
+	if (n64 < V) any = slice_any<SW>(ld_slice<SW>(visit + (size_t)n64 * WPV + (size_t)t * SW));
+	const bool gany = group_any<TPV>(any);
+	if (gany && t == 0 && n64 < V) enqueue_vertex((uint32_t)n64, off, queue, ctrl);
 }
 
 // TEPS numerator of the level about to run (stats mode only; not part of the timed path).

@@ -46,6 +46,7 @@ typedef struct {
 	uint64_t kernel_launches; /* kernels of this library launched since the last reset */
 	uint64_t batches;         /* MS-BFS batches */
 	uint64_t levels;          /* level steps */
+	uint64_t push_levels;     /* of which top-down (sparse frontier) */
 	uint64_t edges_lane;      /* TEPS numerator (only when option "stats"=1), SURVEY.md §8(d) */
 	uint64_t edges_unique;    /* unique edge visits (only when option "stats"=1) */
 	uint64_t algo_bytes;      /* algorithmic bytes of the level kernels, §8(d) formula ("stats"=1) */
@@ -63,7 +64,8 @@ int pgq_shutdown(pgq_ctx_t *ctx);
 const char *pgq_last_error(void); /* thread-local message of the last failing call */
 
 /* options: "lanes" (0=auto, 64,128,256,512), "stats" (0/1), "timing" (0/1),
- *          "small_max", "hub_min" (in-degree bin thresholds), "direction" (0 auto,1 pull only) */
+ *          "small_max", "hub_min" (in-degree bin thresholds), "direction" (0 auto, 1 pull only),
+ *          "push_beta" (top-down when frontier out-edges * beta <= E) */
 int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value);
 int pgq_get_stats(pgq_ctx_t *ctx, pgq_stats_t *out);
 int pgq_reset_stats(pgq_ctx_t *ctx);

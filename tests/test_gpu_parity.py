@@ -176,6 +176,42 @@ def test_lengths_all_degree_bins(ctx, bins):
     ctx.csr_delete(1)
 
 
+@pytest.mark.parametrize("direction,beta", [(1, 4), (0, 1), (0, 4), (0, 64)])
+@pytest.mark.parametrize("lanes", [64, 512])
+def test_direction_switch(ctx, direction, beta, lanes):
+    """pull-only, push-only, and mixed schedules (incl. pull->push transitions) give identical answers."""
+    scale = 15
+    V = 1 << scale
+    src, dst = orc.gen_rmat(0x5eed0000 + scale, scale)
+    v, e, _ = _build_both(ctx, V, src, dst)
+    ps, pd = orc.gen_pairs(12, V, v, 1100)
+    ctx.set_option("direction", direction)
+    ctx.set_option("push_beta", beta)
+    ctx.set_option("lanes", lanes)
+    ctx.set_option("stats", 1)
+    ctx.reset_stats()
+    try:
+        out, ov = ctx.iterativelength(1, ps, pd)
+        st = ctx.stats()
+    finally:
+        ctx.set_option("direction", 0)
+        ctx.set_option("push_beta", 4)
+        ctx.set_option("lanes", 0)
+        ctx.set_option("stats", 0)
+    eo, ev, est = orc.iterativelength(V, v, e, ps, pd, stats=True)
+    _cmp_arr("valid", ov, ev)
+    _cmp_arr("length", out, eo)
+    if lanes == 512:
+        assert st["edges_lane"] == est["edges_lane"] and st["edges_unique"] == est["edges_unique"]
+    if direction == 1:
+        assert st["push_levels"] == 0
+    elif beta == 1:
+        assert st["push_levels"] >= st["levels"] - 1
+    elif beta == 4:
+        assert 0 < st["push_levels"] < st["levels"]
+    ctx.csr_delete(1)
+
+
 @pytest.mark.parametrize("mode", [0, 1])
 @pytest.mark.parametrize("graph", ["rmat12", "knows"])
 def test_shortestpath_bit_identical(ctx, graph, mode):
