@@ -101,11 +101,14 @@ struct Csr {
 	DevBuf d_ioff;  // uint32[V+1]
 	DevBuf d_isrc;  // uint32[E] source of each in-edge, ascending (src, fwd pos) per target
 	DevBuf d_ipos;  // uint32[E] forward CSR position of each in-edge
-	DevBuf d_mid;   // uint32[] vertices with small_max < indeg <= hub_min
-	DevBuf d_hub;   // uint32[] vertices with indeg > hub_min
+	// in-degree classes, each an ascending vertex list (in-degree 0 is in no list: never a target)
+	DevBuf d_tiny;  // 1 <= indeg <= tiny_max          one thread group per vertex, one round
+	DevBuf d_small; // tiny_max < indeg <= small_max   two thread groups per vertex
+	DevBuf d_mid;   // small_max < indeg <= hub_min    one warp per vertex
+	DevBuf d_hub;   // indeg > hub_min                 one block per chunk of the in-list
 	DevBuf d_hubchunks; // HubChunk[]
-	uint32_t n_mid = 0, n_hub = 0, n_hubchunks = 0;
-	int64_t bins_small_max = -1, bins_hub_min = -1;
+	uint32_t n_tiny = 0, n_small = 0, n_mid = 0, n_hub = 0, n_hubchunks = 0;
+	int64_t bins_tiny_max = -1, bins_small_max = -1, bins_hub_min = -1;
 	void free_all();
 };
 
@@ -113,12 +116,14 @@ struct Options {
 	int64_t lanes = 0;
 	int64_t stats = 0;
 	int64_t timing = 0;
+	int64_t tiny_max = 4;
 	int64_t small_max = 32;
 	int64_t hub_min = 4096;
 	int64_t hub_chunk = 4096;
 	int64_t direction = 0; // 0 auto (push when the frontier is sparse), 1 pull only
 	int64_t trace = 0;     // with timing=1: per-level line on stderr
-	int64_t push_beta = 4; // push when frontier out-edges * push_beta <= E
+	int64_t push_beta = 32; // push when frontier out-edges * push_beta <= E
+	int64_t filter_gamma = 2; // pull tests the frontier bitmap while frontier out-edges * gamma <= E
 };
 
 struct Ctx {

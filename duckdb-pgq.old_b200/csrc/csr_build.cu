@@ -144,40 +144,74 @@ int csr_device_build(Ctx *c, Csr *g) {
 
 // ---- reverse CSR + in-degree bins ------------------------------------------------------------
 
-struct BinCounters {
-	uint32_t n_mid, n_hub, n_chunks, pad;
-};
-
-__global__ void __launch_bounds__(256) bin_kernel(const uint32_t *__restrict__ ioff, uint32_t V,
-                                                  uint32_t small_max, uint32_t hub_min, uint32_t chunk,
-                                                  uint32_t *__restrict__ mid, uint32_t *__restrict__ hub,
-                                                  HubChunk *__restrict__ chunks, BinCounters *__restrict__ cnt) {
+// In-degree classes of the pull kernels: each class is a vertex list in ascending id order
+// (flag -> exclusive scan -> scatter), so neighbouring list entries touch neighbouring words.
+__global__ void __launch_bounds__(256) class_flag_kernel(const uint32_t *__restrict__ ioff, uint32_t V, uint32_t dlo,
+                                                         uint32_t dhi, uint32_t *__restrict__ flag) {
 	uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
 	if (v >= V) return;
-	uint32_t lo = ioff[v], hi = ioff[v + 1], deg = hi - lo;
-	if (deg > hub_min) {
-		uint32_t h = atomicAdd(&cnt->n_hub, 1u);
-		hub[h] = v;
-		uint32_t k = (deg + chunk - 1) / chunk;
-		uint32_t c0 = atomicAdd(&cnt->n_chunks, k);
-		for (uint32_t j = 0; j < k; j++) {
-			HubChunk hc;
-			hc.hub = h;
-			hc.begin = lo + j * chunk;
-			hc.end = min(hi, lo + (j + 1) * chunk);
-			chunks[c0 + j] = hc;
-		}
-	} else if (deg > small_max) {
-		uint32_t m = atomicAdd(&cnt->n_mid, 1u);
-		mid[m] = v;
+	uint32_t deg = ioff[v + 1] - ioff[v];
+	flag[v] = (deg >= dlo && deg <= dhi) ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(256) class_scatter_kernel(const uint32_t *__restrict__ ioff, uint32_t V,
+                                                            uint32_t dlo, uint32_t dhi,
+                                                            const uint32_t *__restrict__ pos,
+                                                            uint32_t *__restrict__ out) {
+	uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+	if (v >= V) return;
+	uint32_t deg = ioff[v + 1] - ioff[v];
+	if (deg >= dlo && deg <= dhi) out[pos[v]] = v;
+}
+
+// chunk descriptors of the hub class: in-edges [begin,end) of hub list entry h
+__global__ void __launch_bounds__(256) hub_chunk_kernel(const uint32_t *__restrict__ ioff,
+                                                        const uint32_t *__restrict__ hub, uint32_t nhub,
+                                                        uint32_t chunk, HubChunk *__restrict__ chunks,
+                                                        uint32_t *__restrict__ nchunks) {
+	uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
+	if (h >= nhub) return;
+	uint32_t v = hub[h];
+	uint32_t lo = ioff[v], hi = ioff[v + 1];
+	uint32_t k = (hi - lo + chunk - 1) / chunk;
+	uint32_t c0 = atomicAdd(nchunks, k);
+	for (uint32_t j = 0; j < k; j++) {
+		HubChunk hc;
+		hc.hub = h;
+		hc.begin = lo + j * chunk;
+		hc.end = min(hi, lo + (j + 1) * chunk);
+		chunks[c0 + j] = hc;
 	}
+}
+
+static int build_class(Ctx *c, Csr *g, uint32_t dlo, uint32_t dhi, uint32_t *flag, uint64_t *d_total, DevBuf *out,
+                       uint32_t *n_out) {
+	const uint32_t V = (uint32_t)g->V;
+	cudaStream_t st = c->stream;
+	*n_out = 0;
+	if (V == 0 || dlo > dhi) return PGQ_OK;
+	class_flag_kernel<<<div_up(V, 256), 256, 0, st>>>(g->d_ioff.as<uint32_t>(), V, dlo, dhi, flag);
+	count_launch(c);
+	PGQ_TRY(exclusive_scan_u32(c, flag, flag, V, d_total));
+	uint64_t total = 0;
+	PGQ_CUDA(cudaMemcpyAsync(&total, d_total, sizeof(total), cudaMemcpyDeviceToHost, st));
+	PGQ_CUDA(cudaStreamSynchronize(st));
+	PGQ_TRY(out->reserve((size_t)(total ? total : 1) * sizeof(uint32_t)));
+	if (total) {
+		class_scatter_kernel<<<div_up(V, 256), 256, 0, st>>>(g->d_ioff.as<uint32_t>(), V, dlo, dhi, flag,
+		                                                    out->as<uint32_t>());
+		count_launch(c);
+	}
+	*n_out = (uint32_t)total;
+	return PGQ_OK;
 }
 
 int csr_prepare(Ctx *c, Csr *g) {
 	const int64_t V = g->V, E = g->E;
 	cudaStream_t st = c->stream;
 	const bool need_rev = !g->prepared;
-	const bool need_bins = need_rev || g->bins_small_max != c->opt.small_max || g->bins_hub_min != c->opt.hub_min;
+	const bool need_bins = need_rev || g->bins_tiny_max != c->opt.tiny_max || g->bins_small_max != c->opt.small_max ||
+	                       g->bins_hub_min != c->opt.hub_min;
 	if (!need_bins) return PGQ_OK;
 	PGQ_CUDA(cudaEventRecord(c->ev_a, st));
 	if (need_rev) {
@@ -214,34 +248,35 @@ int csr_prepare(Ctx *c, Csr *g) {
 		srcof.release();
 		g->prepared = true;
 	}
-	// bins
+	// in-degree classes
 	{
-		uint32_t small_max = (uint32_t)c->opt.small_max, hub_min = (uint32_t)c->opt.hub_min;
-		uint32_t chunk = (uint32_t)c->opt.hub_chunk;
+		uint32_t tiny_max = (uint32_t)c->opt.tiny_max, small_max = (uint32_t)c->opt.small_max;
+		uint32_t hub_min = (uint32_t)c->opt.hub_min, chunk = (uint32_t)c->opt.hub_chunk;
+		if (small_max < tiny_max) tiny_max = small_max;
 		if (hub_min < small_max) hub_min = small_max;
-		size_t max_mid = (size_t)(E / ((int64_t)small_max + 1)) + 1;
-		size_t max_hub = (size_t)(E / ((int64_t)hub_min + 1)) + 1;
-		size_t max_chunks = (size_t)(E / chunk) + max_hub + 1;
-		PGQ_TRY(g->d_mid.reserve(max_mid * sizeof(uint32_t)));
-		PGQ_TRY(g->d_hub.reserve(max_hub * sizeof(uint32_t)));
-		PGQ_TRY(g->d_hubchunks.reserve(max_chunks * sizeof(HubChunk)));
-		TmpBuf cnt;
-		PGQ_TRY(cnt.reserve(sizeof(BinCounters)));
-		PGQ_CUDA(cudaMemsetAsync(cnt.p, 0, sizeof(BinCounters), st));
-		if (V > 0) {
-			bin_kernel<<<div_up(V, 256), 256, 0, st>>>(g->d_ioff.as<uint32_t>(), (uint32_t)V, small_max, hub_min,
-			                                           chunk, g->d_mid.as<uint32_t>(), g->d_hub.as<uint32_t>(),
-			                                           g->d_hubchunks.as<HubChunk>(), cnt.as<BinCounters>());
+		TmpBuf flag, tot;
+		PGQ_TRY(flag.reserve((size_t)(V + 1) * sizeof(uint32_t)));
+		PGQ_TRY(tot.reserve(16));
+		uint32_t *f = flag.as<uint32_t>();
+		uint64_t *dt = tot.as<uint64_t>();
+		PGQ_TRY(build_class(c, g, 1, tiny_max, f, dt, &g->d_tiny, &g->n_tiny));
+		PGQ_TRY(build_class(c, g, tiny_max + 1, small_max, f, dt, &g->d_small, &g->n_small));
+		PGQ_TRY(build_class(c, g, small_max + 1, hub_min, f, dt, &g->d_mid, &g->n_mid));
+		PGQ_TRY(build_class(c, g, hub_min + 1, 0xFFFFFFFFu, f, dt, &g->d_hub, &g->n_hub));
+		g->n_hubchunks = 0;
+		if (g->n_hub) {
+			size_t max_chunks = (size_t)(E / chunk) + g->n_hub + 1;
+			PGQ_TRY(g->d_hubchunks.reserve(max_chunks * sizeof(HubChunk)));
+			uint32_t *dn = reinterpret_cast<uint32_t *>(dt);
+			PGQ_CUDA(cudaMemsetAsync(dn, 0, sizeof(uint32_t), st));
+			hub_chunk_kernel<<<div_up(g->n_hub, 256), 256, 0, st>>>(g->d_ioff.as<uint32_t>(), g->d_hub.as<uint32_t>(),
+			                                                        g->n_hub, chunk, g->d_hubchunks.as<HubChunk>(), dn);
 			count_launch(c);
+			PGQ_CUDA(cudaMemcpyAsync(&g->n_hubchunks, dn, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 		}
-		BinCounters h{};
-		PGQ_CUDA(cudaMemcpyAsync(&h, cnt.p, sizeof(h), cudaMemcpyDeviceToHost, st));
 		PGQ_CUDA(cudaEventRecord(c->ev_b, st));
 		PGQ_CUDA(cudaStreamSynchronize(st));
-		cnt.release();
-		g->n_mid = h.n_mid;
-		g->n_hub = h.n_hub;
-		g->n_hubchunks = h.n_chunks;
+		g->bins_tiny_max = c->opt.tiny_max;
 		g->bins_small_max = c->opt.small_max;
 		g->bins_hub_min = c->opt.hub_min;
 	}
@@ -262,7 +297,7 @@ void Csr::free_all() {
 	d_src64.release(); d_dst64.release(); d_eid64.release();
 	d_off.release(); d_tgt.release(); d_row.release(); d_eid.release();
 	d_ioff.release(); d_isrc.release(); d_ipos.release();
-	d_mid.release(); d_hub.release(); d_hubchunks.release();
+	d_tiny.release(); d_small.release(); d_mid.release(); d_hub.release(); d_hubchunks.release();
 }
 
 } // namespace pgq

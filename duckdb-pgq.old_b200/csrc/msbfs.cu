@@ -11,15 +11,41 @@ namespace {
 struct BatchBufs {
 	uint32_t *seen, *visit[2], *parent, *hubacc;
 	uint2 *queue[2];
-	uint32_t *inq[2];
-	size_t inq_bytes;
+	uint32_t *fbit[2]; // frontier bitmap of visit[i] (1 bit per vertex, padded)
+	size_t fbit_bytes;
+	uint32_t fbit_words;
 	BfsCtrl *ctrl;
 };
 
+template <int W, int GPV>
+void launch_class(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool parents, bool filter) {
+	if (!nlist) return;
+	using C = LaneCfg<W>;
+	constexpr int VPW = C::G / GPV;
+	a.list = list.as<uint32_t>();
+	a.nlist = nlist;
+	const uint32_t warps = div_up(nlist, VPW);
+	const uint32_t grid = div_up((uint64_t)warps * 32, 128);
+	if (parents) pull_list_kernel<W, GPV, true, true><<<grid, 128, 0, c->stream>>>(a);
+	else if (filter) pull_list_kernel<W, GPV, false, true><<<grid, 128, 0, c->stream>>>(a);
+	else pull_list_kernel<W, GPV, false, false><<<grid, 128, 0, c->stream>>>(a);
+	count_launch(c);
+}
+
+// One bottom-up level: frontier visit[cur]/fbit[cur] -> next visit[cur^1]/fbit[cur^1].
 template <int W>
-int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents) {
+int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents, int iter, bool filter) {
 	using C = LaneCfg<W>;
 	cudaStream_t st = c->stream;
+	// fnext is built with atomicOr: start from zero.  At level 2 `next` still holds the source words
+	// (level-0 frontier), some at in-degree-0 vertices that no class rewrites: clear them by bitmap.
+	if (iter == 2) {
+		clear_by_bitmap_kernel<W><<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[cur ^ 1], b.fbit_words,
+		                                                                    b.visit[cur ^ 1]);
+		count_launch(c);
+	} else {
+		PGQ_CUDA(cudaMemsetAsync(b.fbit[cur ^ 1], 0, b.fbit_bytes, st));
+	}
 	PullArgs a{};
 	a.ioff = g->d_ioff.as<uint32_t>();
 	a.isrc = g->d_isrc.as<uint32_t>();
@@ -29,33 +55,20 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents) {
 	a.parent = b.parent;
 	a.ctrl = b.ctrl;
 	a.V = (uint32_t)g->V;
-	a.small_max = (uint32_t)c->opt.small_max;
 	a.hubacc = b.hubacc;
 	a.off = g->d_off.as<int64_t>();
-	const uint64_t small_threads = (uint64_t)g->V * C::TPV;
-	if (small_threads) {
-		uint32_t grid = div_up(small_threads, 256);
-		if (parents) pull_small_kernel<W, true><<<grid, 256, 0, st>>>(a);
-		else pull_small_kernel<W, false><<<grid, 256, 0, st>>>(a);
-		count_launch(c);
-	}
-	if (g->n_mid) {
-		a.list = g->d_mid.as<uint32_t>();
-		a.nlist = g->n_mid;
-		uint32_t grid = div_up((uint64_t)g->n_mid * 32, 256);
-		if (parents) pull_warp_parents_kernel<W><<<grid, 256, 0, st>>>(a);
-		else pull_warp_kernel<W><<<grid, 256, 0, st>>>(a);
-		count_launch(c);
-	}
+	a.fcur = b.fbit[cur];
+	a.fnext = b.fbit[cur ^ 1];
+	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, parents, filter);
+	launch_class<W, 2>(c, a, g->d_small, g->n_small, parents, filter);
+	launch_class<W, C::G>(c, a, g->d_mid, g->n_mid, parents, filter);
 	if (g->n_hub) {
-		a.list = g->d_hub.as<uint32_t>();
-		a.nlist = g->n_hub;
 		if (parents) {
 			// ordered first-match needs a single consumer per vertex: one warp per hub
-			uint32_t grid = div_up((uint64_t)g->n_hub * 32, 256);
-			pull_warp_parents_kernel<W><<<grid, 256, 0, st>>>(a);
-			count_launch(c);
+			launch_class<W, C::G>(c, a, g->d_hub, g->n_hub, true, true);
 		} else {
+			a.list = g->d_hub.as<uint32_t>();
+			a.nlist = g->n_hub;
 			a.chunks = g->d_hubchunks.as<HubChunk>();
 			a.nchunks = g->n_hubchunks;
 			pull_hub_kernel<W><<<g->n_hubchunks, 256, 0, st>>>(a);
@@ -66,35 +79,35 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents) {
 	return PGQ_OK;
 }
 
-int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, bool parents) {
+int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, bool parents, int iter, bool filter) {
 	switch (W) {
-	case 64: return launch_level<64>(c, g, b, cur, parents);
-	case 128: return launch_level<128>(c, g, b, cur, parents);
-	case 256: return launch_level<256>(c, g, b, cur, parents);
-	case 512: return launch_level<512>(c, g, b, cur, parents);
+	case 64: return launch_level<64>(c, g, b, cur, parents, iter, filter);
+	case 128: return launch_level<128>(c, g, b, cur, parents, iter, filter);
+	case 256: return launch_level<256>(c, g, b, cur, parents, iter, filter);
+	case 512: return launch_level<512>(c, g, b, cur, parents, iter, filter);
 	}
 	set_error("unsupported lane width %d", W);
 	return PGQ_ERR_INVALID;
 }
 
-// One top-down level over queue[q] (frontier in visit[cur]); builds queue[q^1].
+// One top-down level over queue[q] (frontier in visit[cur]); builds queue[q^1] and fbit[cur^1].
 template <int W>
 int launch_push(Ctx *c, Csr *g, const BatchBufs &b, int cur, int q) {
 	PushArgs a{};
 	a.off = g->d_off.as<int64_t>();
 	a.tgt = g->d_tgt.as<uint32_t>();
 	a.visit = b.visit[cur];
-	a.visit_rw = b.visit[cur];
 	a.next = b.visit[cur ^ 1];
 	a.seen = b.seen;
 	a.ctrl = b.ctrl;
 	a.queue = b.queue[q];
 	a.queue_next = b.queue[q ^ 1];
-	a.inq_next = b.inq[q ^ 1];
-	a.inq_cur = b.inq[q];
+	a.fnext = b.fbit[cur ^ 1];
+	// next/fnext still describe the frontier of two levels ago: zero exactly those words
+	clear_by_bitmap_kernel<W><<<div_up(b.fbit_words, 256), 256, 0, c->stream>>>(b.fbit[cur ^ 1], b.fbit_words,
+	                                                                           b.visit[cur ^ 1]);
 	const uint32_t grid = (uint32_t)c->sm_count * 8;
 	push_kernel<W><<<grid, 256, 0, c->stream>>>(a);
-	push_cleanup_kernel<W><<<grid, 256, 0, c->stream>>>(a);
 	count_launch(c, 2);
 	return PGQ_OK;
 }
@@ -109,22 +122,11 @@ int launch_push_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, int q) {
 	return PGQ_ERR_INVALID;
 }
 
-// pull -> push transition: queue[q] from the dense frontier visit[cur]; visit[cur^1] and the
-// dedupe bitmaps start clean.
-int launch_compact(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, int q) {
+// pull -> push transition: queue[q] from the frontier bitmap fbit[cur].
+int launch_compact(Ctx *c, Csr *g, const BatchBufs &b, int cur, int q) {
 	cudaStream_t st = c->stream;
-	const size_t bm = (size_t)g->V * (W / 8);
-	PGQ_CUDA(cudaMemsetAsync(b.visit[cur ^ 1], 0, bm, st));
-	PGQ_CUDA(cudaMemsetAsync(b.inq[0], 0, b.inq_bytes, st));
-	PGQ_CUDA(cudaMemsetAsync(b.inq[1], 0, b.inq_bytes, st));
-	const int64_t *off = g->d_off.as<int64_t>();
-	const uint32_t V = (uint32_t)g->V;
-	switch (W) {
-	case 64: compact_frontier_kernel<64><<<div_up((uint64_t)V * LaneCfg<64>::TPV, 256), 256, 0, st>>>(b.visit[cur], V, off, b.queue[q], b.ctrl); break;
-	case 128: compact_frontier_kernel<128><<<div_up((uint64_t)V * LaneCfg<128>::TPV, 256), 256, 0, st>>>(b.visit[cur], V, off, b.queue[q], b.ctrl); break;
-	case 256: compact_frontier_kernel<256><<<div_up((uint64_t)V * LaneCfg<256>::TPV, 256), 256, 0, st>>>(b.visit[cur], V, off, b.queue[q], b.ctrl); break;
-	case 512: compact_frontier_kernel<512><<<div_up((uint64_t)V * LaneCfg<512>::TPV, 256), 256, 0, st>>>(b.visit[cur], V, off, b.queue[q], b.ctrl); break;
-	}
+	compact_bitmap_kernel<<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[cur], b.fbit_words, (uint32_t)g->V,
+	                                                                 g->d_off.as<int64_t>(), b.queue[q], b.ctrl);
 	bfs_snapshot_kernel<<<1, 1, 0, st>>>(b.ctrl);
 	count_launch(c, 2);
 	return PGQ_OK;
@@ -170,12 +172,14 @@ int alloc_bufs(Ctx *c, Csr *g, int W, bool parents, BatchBufs *b) {
 	b->hubacc = c->bfs_hubacc.as<uint32_t>();
 	b->ctrl = c->bfs_ctrl.as<BfsCtrl>();
 	const size_t qcap = (size_t)g->V + (size_t)(g->E / PUSH_CHUNK) + 2;
-	b->inq_bytes = ((size_t)g->V / 32 + 1) * sizeof(uint32_t);
+	// padded: pull_small stores whole 8/16/32-vertex units, its grid may overhang V by < 256 vertices
+	b->fbit_words = (uint32_t)(((size_t)g->V + 256 + 31) / 32);
+	b->fbit_bytes = (size_t)b->fbit_words * sizeof(uint32_t);
 	for (int i = 0; i < 2; i++) {
 		PGQ_TRY(c->bfs_queue[i].reserve(qcap * sizeof(uint2)));
-		PGQ_TRY(c->bfs_inq[i].reserve(b->inq_bytes));
+		PGQ_TRY(c->bfs_inq[i].reserve(b->fbit_bytes));
 		b->queue[i] = c->bfs_queue[i].as<uint2>();
-		b->inq[i] = c->bfs_inq[i].as<uint32_t>();
+		b->fbit[i] = c->bfs_inq[i].as<uint32_t>();
 	}
 	return PGQ_OK;
 }
@@ -190,10 +194,10 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 		PGQ_CUDA(cudaMemsetAsync(b.visit[0], 0, bm, st));
 		PGQ_CUDA(cudaMemsetAsync(b.visit[1], 0, bm, st)); // a top-down level 1 ORs into it
 	}
-	PGQ_CUDA(cudaMemsetAsync(b.inq[0], 0, b.inq_bytes, st));
-	PGQ_CUDA(cudaMemsetAsync(b.inq[1], 0, b.inq_bytes, st));
+	PGQ_CUDA(cudaMemsetAsync(b.fbit[0], 0, b.fbit_bytes, st));
+	PGQ_CUDA(cudaMemsetAsync(b.fbit[1], 0, b.fbit_bytes, st));
 	bfs_init_kernel<<<1, W, 0, st>>>(d_lane_src, W, b.visit[0], d_found, b.ctrl, g->d_off.as<int64_t>(), b.queue[0],
-	                                 b.inq[0]);
+	                                 b.fbit[0]);
 	count_launch(c);
 	BfsCtrl h;
 	PGQ_TRY(read_ctrl(c, b, &h));
@@ -210,13 +214,16 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
 		uint64_t before = c->stats.kernel_launches;
 		if (push) {
-			if (!have_queue) PGQ_TRY(launch_compact(c, g, b, W, cur, q));
+			if (!have_queue) PGQ_TRY(launch_compact(c, g, b, cur, q));
 			PGQ_TRY(launch_push_w(c, g, b, W, cur, q));
 			have_queue = true;
 			q ^= 1;
 			c->stats.push_levels++;
 		} else {
-			PGQ_TRY(launch_level_w(c, g, b, W, cur, parents));
+			// the bitmap test is dead weight once the frontier holds most of the edges
+			const bool filter = (unsigned long long)h.out_edges * (unsigned long long)c->opt.filter_gamma <=
+			                    (unsigned long long)g->E;
+			PGQ_TRY(launch_level_w(c, g, b, W, cur, parents, iter, filter));
 			have_queue = false;
 		}
 		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));

@@ -56,6 +56,9 @@ struct PullArgs {
 	const HubChunk *chunks;
 	uint32_t nchunks;
 	uint32_t *hubacc;
+	const uint32_t *fcur; // 1 bit per vertex: visit word non-empty (may over-approximate, never under)
+	uint32_t *fnext;      // same for `next`, produced by this level
+	uint32_t touch_isolated; // 1: also rewrite next[] of in-degree-0 vertices (levels 1-2, stale source bits)
 };
 
 template <int W>
@@ -183,6 +186,26 @@ __device__ __forceinline__ void count_frontier(BfsCtrl *ctrl, const int64_t *off
 	}
 }
 
+__device__ __forceinline__ bool fbit_test(const uint32_t *f, uint32_t v) {
+	return (__ldg(f + (v >> 5)) >> (v & 31)) & 1u;
+}
+
+// pull_small: the warp owns G = 32/TPV consecutive vertices; lane 0 stores their frontier bits as one
+// naturally aligned G-bit unit (plain store: the small kernel runs first and owns every unit; the
+// mid/hub kernels add their vertices afterwards with atomicOr).
+template <int TPV>
+__device__ __forceinline__ void store_group_bits(uint32_t *fnext, uint64_t first_vertex, unsigned ballot) {
+	constexpr int G = 32 / TPV;
+	uint32_t b = 0;
+#pragma unroll
+	for (int k = 0; k < G; k++) b |= ((ballot >> (k * TPV)) & 1u) << k;
+	if ((threadIdx.x & 31) == 0) {
+		if (G == 32) fnext[first_vertex >> 5] = b;
+		else if (G == 16) reinterpret_cast<uint16_t *>(fnext)[first_vertex >> 4] = (uint16_t)b;
+		else reinterpret_cast<uint8_t *>(fnext)[first_vertex >> 3] = (uint8_t)b;
+	}
+}
+
 template <int TPV>
 __device__ __forceinline__ bool group_any(bool x) {
 	unsigned b = x ? 1u : 0u;
@@ -191,129 +214,129 @@ __device__ __forceinline__ bool group_any(bool x) {
 	return b != 0;
 }
 
-// ---- K4/K7 small: one TPV-thread group per vertex, in-degree <= small_max ---------------------
-template <int W, bool PARENTS>
-__global__ void __launch_bounds__(256) pull_small_kernel(PullArgs a) {
+// ---- K4/K7: pull over one in-degree class --------------------------------------------------------
+// A vertex is served by GPV thread groups (a group = the TPV threads that together hold one
+// W-bit word); a warp therefore serves VPW = G/GPV list entries.  Round r of a vertex covers
+// in-edges [lo + r*GPV*U, +GPV*U): sub-group sg takes edges base + u*GPV + sg.  The sources of
+// the NEXT round are fetched before the gathers of the current one are consumed, so a round costs
+// one gather latency instead of index + bitmap + gather.  FILTER skips in-neighbours whose
+// frontier bit is clear before their word is touched (pays off unless the frontier holds most
+// edges).  Loops are warp-uniform (trip count = the slowest vertex of the warp) because the
+// reductions use full-mask shuffles.
+//
+// PARENTS (R7): in-edges are consumed in ascending index; a lane bit offered by several
+// sub-groups in the same step goes to the lowest sub-group (exclusive prefix-OR) = lowest in-edge
+// index = (smallest source id, then lowest forward CSR offset).
+template <int W, int GPV, bool PARENTS, bool FILTER>
+__global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	using C = LaneCfg<W>;
-	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
-	const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	const uint64_t n64 = gid / TPV;
-	const uint32_t t = (uint32_t)(gid % TPV);
-	const bool inrange = n64 < a.V;
-	const uint32_t n = (uint32_t)n64;
+	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
+	static_assert(GPV >= 1 && GPV <= G, "groups per vertex");
+	constexpr int VPW = G / GPV;
+	constexpr uint32_t INV = 0xFFFFFFFFu, FULL = 0xffffffffu;
+	const uint32_t wid = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+	if ((uint64_t)wid * VPW >= a.nlist) return; // warp-uniform
+	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
+	const uint32_t vslot = g / GPV, sg = g % GPV;
+	const uint64_t idx = (uint64_t)wid * VPW + vslot;
+	const bool valid = idx < a.nlist;
+	const uint32_t n = valid ? a.list[idx] : 0u;
 	uint32_t lo = 0, hi = 0;
-	if (inrange) {
+	if (valid) {
 		lo = a.ioff[n];
 		hi = a.ioff[n + 1];
 	}
-	const bool mine = inrange && (hi - lo) <= a.small_max;
-	Slice<SW> news = slice_zero<SW>();
-	if (mine) {
-		const size_t wo = (size_t)n * WPV + (size_t)t * SW;
-		Slice<SW> s = ld_slice<SW>(a.seen + wo);
-		Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
-		Slice<SW> unseen;
+	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
+	Slice<SW> s = slice_zero<SW>(), unseen = slice_zero<SW>();
+	// first round's sources do not depend on `seen`: issue both loads together
+	uint32_t j = lo + sg;
+	uint32_t vs[U];
+#pragma unroll
+	for (int u = 0; u < U; u++) {
+		const uint32_t jj = j + u * GPV;
+		vs[u] = jj < hi ? a.isrc[jj] : INV;
+	}
+	if (valid) {
+		s = ld_slice<SW>(a.seen + wo);
+		const Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
 #pragma unroll
 		for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
-		Slice<SW> acc = slice_zero<SW>();
-		if (slice_any<SW>(unseen)) {
-			uint32_t *prow = PARENTS ? a.parent + (size_t)n * W + (size_t)t * (SW * 32) : nullptr;
-			uint32_t j = lo;
-			for (; j + 4 <= hi; j += 4) {
-				uint32_t v0 = a.isrc[j], v1 = a.isrc[j + 1], v2 = a.isrc[j + 2], v3 = a.isrc[j + 3];
-				Slice<SW> w0 = ldg_slice<SW>(a.visit + (size_t)v0 * WPV + t * SW);
-				Slice<SW> w1 = ldg_slice<SW>(a.visit + (size_t)v1 * WPV + t * SW);
-				Slice<SW> w2 = ldg_slice<SW>(a.visit + (size_t)v2 * WPV + t * SW);
-				Slice<SW> w3 = ldg_slice<SW>(a.visit + (size_t)v3 * WPV + t * SW);
-				Slice<SW> ws[4] = {w0, w1, w2, w3};
-#pragma unroll
-				for (int u = 0; u < 4; u++) {
-					if (PARENTS) {
-						Slice<SW> nb;
-#pragma unroll
-						for (int i = 0; i < SW; i++) nb.w[i] = ws[u].w[i] & unseen.w[i] & ~acc.w[i];
-						store_parents<SW>(prow, nb, j + u);
-					}
-#pragma unroll
-					for (int i = 0; i < SW; i++) acc.w[i] |= ws[u].w[i];
-				}
-				if (slice_covers<SW>(acc, unseen)) {
-					j = hi;
-					break;
-				}
-			}
-			for (; j < hi; j++) {
-				uint32_t v0 = a.isrc[j];
-				Slice<SW> w0 = ldg_slice<SW>(a.visit + (size_t)v0 * WPV + t * SW);
-				if (PARENTS) {
-					Slice<SW> nb;
-#pragma unroll
-					for (int i = 0; i < SW; i++) nb.w[i] = w0.w[i] & unseen.w[i] & ~acc.w[i];
-					store_parents<SW>(prow, nb, j);
-				}
-#pragma unroll
-				for (int i = 0; i < SW; i++) acc.w[i] |= w0.w[i];
-			}
-		}
-#pragma unroll
-		for (int i = 0; i < SW; i++) news.w[i] = acc.w[i] & unseen.w[i];
-		st_slice<SW>(a.next + wo, news);
-		if (slice_any<SW>(news)) {
-#pragma unroll
-			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
-			st_slice<SW>(a.seen + wo, s);
-		}
 	}
-	const bool anyn = slice_any<SW>(news);
-	flag_change(a.ctrl, anyn);
-	const bool gnew = group_any<TPV>(anyn);
-	count_frontier(a.ctrl, a.off, n, gnew && t == 0 && mine);
-}
-
-// ---- K4 mid: one warp per vertex (small_max < in-degree), lengths only -------------------------
-// G groups x TPV slice-threads; each group strides the in-list, 4 edges in flight per thread.
-template <int W>
-__global__ void __launch_bounds__(256) pull_warp_kernel(PullArgs a) {
-	using C = LaneCfg<W>;
-	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
-	const uint32_t wid = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-	if (wid >= a.nlist) return; // warp-uniform
-	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
-	const uint32_t n = a.list[wid];
-	const uint32_t lo = a.ioff[n], hi = a.ioff[n + 1];
-	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
-	Slice<SW> s = ld_slice<SW>(a.seen + wo);
-	Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
-	Slice<SW> unseen;
-#pragma unroll
-	for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
+	bool open = slice_any<SW>(unseen); // identical in all sub-groups of the vertex (same t)
+	Slice<SW> acc = slice_zero<SW>();  // PARENTS: lanes claimed so far; else: this sub-group's OR
 	Slice<SW> tot = slice_zero<SW>();
-	if (__any_sync(0xffffffffu, slice_any<SW>(unseen))) {
-		Slice<SW> acc = slice_zero<SW>();
-		for (uint32_t j0 = lo; j0 < hi; j0 += G * U) {
-			uint32_t vs[U];
+	uint32_t *prow = PARENTS ? a.parent + (size_t)n * W + (size_t)t * (SW * 32) : nullptr;
+	while (__any_sync(FULL, open && j < hi)) {
+		Slice<SW> w[U];
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			bool f = open && vs[u] != INV;
+			if (FILTER && f) f = fbit_test(a.fcur, vs[u]);
+			w[u] = f ? ldg_slice<SW>(a.visit + (size_t)vs[u] * WPV + t * SW) : slice_zero<SW>();
+		}
+		const uint32_t jn = j + GPV * U;
+		uint32_t vn[U];
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			const uint32_t jj = jn + u * GPV;
+			vn[u] = (open && jj < hi) ? a.isrc[jj] : INV;
+		}
+		if (!PARENTS) {
 #pragma unroll
 			for (int u = 0; u < U; u++) {
-				uint32_t j = j0 + u * G + g;
-				vs[u] = j < hi ? a.isrc[j] : 0xFFFFFFFFu;
+#pragma unroll
+				for (int i = 0; i < SW; i++) acc.w[i] |= w[u].w[i];
 			}
+			tot = acc;
+#pragma unroll
+			for (int d = TPV; d < TPV * GPV; d <<= 1) {
+#pragma unroll
+				for (int i = 0; i < SW; i++) tot.w[i] |= __shfl_xor_sync(FULL, tot.w[i], d);
+			}
+		} else {
 #pragma unroll
 			for (int u = 0; u < U; u++) {
-				if (vs[u] != 0xFFFFFFFFu) {
-					Slice<SW> w = ldg_slice<SW>(a.visit + (size_t)vs[u] * WPV + t * SW);
+				Slice<SW> cand;
 #pragma unroll
-					for (int i = 0; i < SW; i++) acc.w[i] |= w.w[i];
+				for (int i = 0; i < SW; i++) cand.w[i] = w[u].w[i] & unseen.w[i] & ~acc.w[i];
+				if (GPV == 1) {
+					store_parents<SW>(prow, cand, j + u * GPV);
+#pragma unroll
+					for (int i = 0; i < SW; i++) acc.w[i] |= cand.w[i];
+				} else if (__any_sync(FULL, slice_any<SW>(cand))) {
+					Slice<SW> incl = cand;
+#pragma unroll
+					for (int d = 1; d < GPV; d <<= 1) {
+#pragma unroll
+						for (int i = 0; i < SW; i++) {
+							const uint32_t y = __shfl_up_sync(FULL, incl.w[i], d * TPV);
+							if (sg >= (uint32_t)d) incl.w[i] |= y;
+						}
+					}
+					Slice<SW> take;
+#pragma unroll
+					for (int i = 0; i < SW; i++) {
+						const uint32_t y = __shfl_up_sync(FULL, incl.w[i], TPV);
+						const uint32_t excl = sg == 0 ? 0u : y;
+						const uint32_t all = __shfl_sync(FULL, incl.w[i], vslot * (GPV * TPV) + (GPV - 1) * TPV + t);
+						take.w[i] = cand.w[i] & ~excl;
+						acc.w[i] |= all;
+					}
+					store_parents<SW>(prow, take, j + u * GPV);
 				}
 			}
-			tot = warp_or_groups<SW, TPV>(acc);
-			if (__all_sync(0xffffffffu, slice_covers<SW>(tot, unseen))) break; // every unseen lane reached
+			tot = acc;
 		}
-		tot = warp_or_groups<SW, TPV>(acc);
+		open = open && !slice_covers<SW>(tot, unseen);
+		j = jn;
+#pragma unroll
+		for (int u = 0; u < U; u++) vs[u] = vn[u];
 	}
 	Slice<SW> news;
 #pragma unroll
 	for (int i = 0; i < SW; i++) news.w[i] = tot.w[i] & unseen.w[i];
-	if (g == 0) {
+	const bool writer = valid && sg == 0;
+	if (writer) {
 		st_slice<SW>(a.next + wo, news);
 		if (slice_any<SW>(news)) {
 #pragma unroll
@@ -321,94 +344,12 @@ __global__ void __launch_bounds__(256) pull_warp_kernel(PullArgs a) {
 			st_slice<SW>(a.seen + wo, s);
 		}
 	}
-	const bool wany = __any_sync(0xffffffffu, slice_any<SW>(news));
-	if (wany && lane == 0) {
-		a.ctrl->change = 1u;
-		atomicAdd(&a.ctrl->next_edges, (unsigned long long)(a.off[n + 1] - a.off[n]));
-		atomicAdd(&a.ctrl->next_verts, 1u);
-	}
-}
-
-// ---- K7 mid/hub with parents: one warp per vertex, in-edges consumed in ORDER -------------------
-// Round = G consecutive in-edges (group g takes edge j0+g).  A lane bit claimed by several groups
-// in one round goes to the lowest group (exclusive prefix-OR over groups) = lowest in-edge index.
-template <int W>
-__global__ void __launch_bounds__(256) pull_warp_parents_kernel(PullArgs a) {
-	using C = LaneCfg<W>;
-	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G;
-	const uint32_t wid = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-	if (wid >= a.nlist) return;
-	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
-	const uint32_t n = a.list[wid];
-	const uint32_t lo = a.ioff[n], hi = a.ioff[n + 1];
-	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
-	Slice<SW> s = ld_slice<SW>(a.seen + wo);
-	Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
-	Slice<SW> unseen;
-#pragma unroll
-	for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
-	Slice<SW> acc = slice_zero<SW>(); // lane bits already claimed (identical in all groups)
-	if (__any_sync(0xffffffffu, slice_any<SW>(unseen))) {
-		uint32_t *prow = a.parent + (size_t)n * W + (size_t)t * (SW * 32);
-		for (uint32_t j0 = lo; j0 < hi; j0 += 2 * G) {
-			// two rounds of loads in flight, consumed in order
-			uint32_t ja = j0 + g, jb = j0 + G + g;
-			uint32_t va = ja < hi ? a.isrc[ja] : 0xFFFFFFFFu;
-			uint32_t vb = jb < hi ? a.isrc[jb] : 0xFFFFFFFFu;
-			Slice<SW> wr[2];
-			wr[0] = va != 0xFFFFFFFFu ? ldg_slice<SW>(a.visit + (size_t)va * WPV + t * SW) : slice_zero<SW>();
-			wr[1] = vb != 0xFFFFFFFFu ? ldg_slice<SW>(a.visit + (size_t)vb * WPV + t * SW) : slice_zero<SW>();
-#pragma unroll
-			for (int r = 0; r < 2; r++) {
-				const uint32_t j = r == 0 ? ja : jb;
-				Slice<SW> cand;
-#pragma unroll
-				for (int i = 0; i < SW; i++) cand.w[i] = wr[r].w[i] & unseen.w[i] & ~acc.w[i];
-				if (__any_sync(0xffffffffu, slice_any<SW>(cand))) {
-					Slice<SW> incl = cand;
-#pragma unroll
-					for (int d = TPV; d < 32; d <<= 1) {
-#pragma unroll
-						for (int i = 0; i < SW; i++) {
-							uint32_t y = __shfl_up_sync(0xffffffffu, incl.w[i], d);
-							if (lane >= (uint32_t)d) incl.w[i] |= y;
-						}
-					}
-					Slice<SW> excl, all;
-#pragma unroll
-					for (int i = 0; i < SW; i++) {
-						uint32_t y = __shfl_up_sync(0xffffffffu, incl.w[i], TPV);
-						excl.w[i] = g == 0 ? 0u : y;
-						all.w[i] = __shfl_sync(0xffffffffu, incl.w[i], 32 - TPV + t);
-					}
-					Slice<SW> take;
-#pragma unroll
-					for (int i = 0; i < SW; i++) take.w[i] = cand.w[i] & ~excl.w[i];
-					store_parents<SW>(prow, take, j);
-#pragma unroll
-					for (int i = 0; i < SW; i++) acc.w[i] |= all.w[i];
-				}
-			}
-			if (__all_sync(0xffffffffu, slice_covers<SW>(acc, unseen))) break;
-		}
-	}
-	Slice<SW> news;
-#pragma unroll
-	for (int i = 0; i < SW; i++) news.w[i] = acc.w[i] & unseen.w[i];
-	if (g == 0) {
-		st_slice<SW>(a.next + wo, news);
-		if (slice_any<SW>(news)) {
-#pragma unroll
-			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
-			st_slice<SW>(a.seen + wo, s);
-		}
-	}
-	const bool wany = __any_sync(0xffffffffu, slice_any<SW>(news));
-	if (wany && lane == 0) {
-		a.ctrl->change = 1u;
-		atomicAdd(&a.ctrl->next_edges, (unsigned long long)(a.off[n + 1] - a.off[n]));
-		atomicAdd(&a.ctrl->next_verts, 1u);
-	}
+	const unsigned bal = __ballot_sync(FULL, writer && slice_any<SW>(news));
+	const bool vnew = ((bal >> (vslot * (GPV * TPV))) & ((1u << TPV) - 1u)) != 0;
+	const bool leader = writer && t == 0 && vnew;
+	if (leader) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+	if (bal && lane == 0) a.ctrl->change = 1u;
+	count_frontier(a.ctrl, a.off, n, leader);
 }
 
 // ---- K4 hubs: one block per chunk of a hub's in-list, partial ORs merged with atomicOr ---------
@@ -436,6 +377,9 @@ __global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
 			uint32_t j = j0 + u * G + g;
 			vs[u] = j < hc.end ? a.isrc[j] : 0xFFFFFFFFu;
 		}
+#pragma unroll
+		for (int u = 0; u < U; u++)
+			if (vs[u] != 0xFFFFFFFFu && !fbit_test(a.fcur, vs[u])) vs[u] = 0xFFFFFFFFu;
 #pragma unroll
 		for (int u = 0; u < U; u++) {
 			if (vs[u] != 0xFFFFFFFFu) {
@@ -486,7 +430,10 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 	const bool anyn = slice_any<SW>(news);
 	flag_change(a.ctrl, anyn);
 	const bool gnew = group_any<TPV>(anyn);
-	count_frontier(a.ctrl, a.off, h < a.nlist ? a.list[h] : 0u, gnew && t == 0 && h < a.nlist);
+	const bool leader = gnew && t == 0 && h < a.nlist;
+	const uint32_t hn = h < a.nlist ? a.list[h] : 0u;
+	if (leader) atomicOr(&a.fnext[hn >> 5], 1u << (hn & 31));
+	count_frontier(a.ctrl, a.off, hn, leader);
 }
 
 // ---- batch init / K6 destination check / stats / K8 path reconstruction -----------------------
@@ -571,6 +518,8 @@ __global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, const uint32
 	}
 }
 
+// after compact_bitmap_kernel: publish the rebuilt queue (the counters it re-accumulated replace
+// the ones the pull level had produced for the same frontier)
 __global__ void bfs_snapshot_kernel(BfsCtrl *ctrl) {
 	snapshot_frontier(ctrl);
 }
@@ -589,9 +538,7 @@ struct PushArgs {
 	BfsCtrl *ctrl;
 	const uint2 *queue;  // items of this level (count = ctrl->out_items)
 	uint2 *queue_next;   // items for the next level
-	uint32_t *inq_next;  // dedupe bitmap of queue_next
-	uint32_t *inq_cur;   // dedupe bitmap that built `queue` (cleared by the cleanup kernel)
-	uint32_t *visit_rw;  // same buffer as visit, for the cleanup kernel
+	uint32_t *fnext;     // frontier bitmap of `next` (doubles as the dedupe bitmap of queue_next)
 };
 
 template <int W>
@@ -633,50 +580,50 @@ __global__ void __launch_bounds__(256) push_kernel(PushArgs a) {
 			if (mynew) {
 				anynew = true;
 				const uint32_t bit = 1u << (n & 31);
-				if (!(atomicOr(&a.inq_next[n >> 5], bit) & bit)) enqueue_vertex(n, a.off, a.queue_next, a.ctrl);
+				if (!(atomicOr(&a.fnext[n >> 5], bit) & bit)) enqueue_vertex(n, a.off, a.queue_next, a.ctrl);
 			}
 		}
 	}
 	if (__any_sync(0xffffffffu, anynew) && lane == 0) a.ctrl->change = 1u;
 }
 
-// After a push level: consumed frontier words go back to zero (so the buffer can serve as `next`
-// two levels later) and the dedupe bits of the consumed queue are cleared.
+// Before a push level: the `next` buffer still holds the frontier of two levels ago, described by
+// its bitmap.  Zero exactly those words, then the bitmap (cost ~ that frontier, not V).
 template <int W>
-__global__ void __launch_bounds__(256) push_cleanup_kernel(PushArgs a) {
+__global__ void __launch_bounds__(256) clear_by_bitmap_kernel(uint32_t *__restrict__ fbit, uint32_t nwords,
+                                                              uint32_t *__restrict__ visit) {
 	constexpr int WPV = W / 32;
-	const uint32_t nitems = a.ctrl->out_items;
-	const uint32_t stride = gridDim.x * blockDim.x;
-	for (uint32_t it = blockIdx.x * blockDim.x + threadIdx.x; it < nitems; it += stride) {
-		const uint2 item = a.queue[it];
-		if (item.y != 0) continue;
-		const uint32_t v = item.x;
-		uint32_t *p = a.visit_rw + (size_t)v * WPV;
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= nwords) return;
+	uint32_t m = fbit[i];
+	if (!m) return;
+	fbit[i] = 0;
+	while (m) {
+		const int k = __ffs(m) - 1;
+		m &= m - 1;
+		uint32_t *p = visit + ((size_t)i * 32 + k) * WPV;
 		if (WPV >= 4) {
 #pragma unroll
-			for (int i = 0; i < WPV; i += 4) *reinterpret_cast<uint4 *>(p + i) = make_uint4(0, 0, 0, 0);
+			for (int q = 0; q < WPV; q += 4) *reinterpret_cast<uint4 *>(p + q) = make_uint4(0, 0, 0, 0);
 		} else {
-#pragma unroll
-			for (int i = 0; i < WPV; i++) p[i] = 0;
+			*reinterpret_cast<uint2 *>(p) = make_uint2(0, 0);
 		}
-		atomicAnd(&a.inq_cur[v >> 5], ~(1u << (v & 31)));
 	}
 }
 
-// pull -> push transition: rebuild the queue from a dense frontier buffer.
-template <int W>
-__global__ void __launch_bounds__(256) compact_frontier_kernel(const uint32_t *__restrict__ visit, uint32_t V,
-                                                               const int64_t *__restrict__ off,
-                                                               uint2 *__restrict__ queue, BfsCtrl *ctrl) {
-	using C = LaneCfg<W>;
-	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
-	const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	const uint64_t n64 = gid / TPV;
-	const uint32_t t = (uint32_t)(gid % TPV);
-	bool any = false;
-	if (n64 < V) any = slice_any<SW>(ld_slice<SW>(visit + (size_t)n64 * WPV + (size_t)t * SW));
-	const bool gany = group_any<TPV>(any);
-	if (gany && t == 0 && n64 < V) enqueue_vertex((uint32_t)n64, off, queue, ctrl);
+// pull -> push transition: rebuild the work queue from the frontier bitmap.
+__global__ void __launch_bounds__(256) compact_bitmap_kernel(const uint32_t *__restrict__ fbit, uint32_t nwords,
+                                                             uint32_t V, const int64_t *__restrict__ off,
+                                                             uint2 *__restrict__ queue, BfsCtrl *ctrl) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= nwords) return;
+	uint32_t m = fbit[i];
+	while (m) {
+		const int k = __ffs(m) - 1;
+		m &= m - 1;
+		const uint32_t n = i * 32 + k;
+		if (n < V) enqueue_vertex(n, off, queue, ctrl);
+	}
 }
 
 // TEPS numerator of the level about to run (stats mode only; not part of the timed path).

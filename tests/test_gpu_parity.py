@@ -151,28 +151,42 @@ def test_lengths_rmat_all_lane_widths(ctx, lanes):
     ctx.csr_delete(1)
 
 
-@pytest.mark.parametrize("bins", [(0, 1), (2, 8), (32, 4096), (1 << 30, 1 << 30)])
-def test_lengths_all_degree_bins(ctx, bins):
-    """Force every vertex through each of the small / warp / hub kernels."""
+@pytest.mark.parametrize("bins", [(0, 0, 1), (1, 2, 8), (4, 32, 4096), (0, 32, 64), (1 << 30, 1 << 30, 1 << 30),
+                                  (2, 1 << 30, 1 << 30)])
+@pytest.mark.parametrize("lanes", [64, 256, 512])
+def test_lengths_all_degree_bins(ctx, bins, lanes):
+    """Force every vertex through each in-degree class kernel (tiny / small / warp / hub), with and
+    without the frontier-bitmap filter, at every threads-per-word layout."""
     V, E = 3000, 90000
     src, dst = orc.gen_knows(33, V, E)
     v, e, _ = _build_both(ctx, V, src, dst)
     ps, pd = orc.gen_pairs(6, V, v, 700)
-    ctx.set_option("small_max", bins[0])
-    ctx.set_option("hub_min", bins[1])
+    eo, ev = orc.iterativelength(V, v, e, ps, pd)
+    _, _, eids = orc.csr_build(V, src, dst)
+    ep = orc.shortestpath(V, v, e, eids, ps, pd, mode=1)
+    ctx.set_option("tiny_max", bins[0])
+    ctx.set_option("small_max", bins[1])
+    ctx.set_option("hub_min", bins[2])
     ctx.set_option("hub_chunk", 256)
+    ctx.set_option("lanes", lanes)
     try:
-        out, ov = ctx.iterativelength(1, ps, pd)
+        for gamma in (0, 2, 1 << 20):
+            ctx.set_option("filter_gamma", gamma)
+            for direction in (0, 1):
+                ctx.set_option("direction", direction)
+                out, ov = ctx.iterativelength(1, ps, pd)
+                _cmp_arr("valid", ov, ev)
+                _cmp_arr("length", out, eo)
         p = ctx.shortestpath(1, ps, pd, mode=1)
     finally:
+        ctx.set_option("tiny_max", 4)
         ctx.set_option("small_max", 32)
         ctx.set_option("hub_min", 4096)
         ctx.set_option("hub_chunk", 4096)
-    eo, ev = orc.iterativelength(V, v, e, ps, pd)
-    _cmp_arr("valid", ov, ev)
-    _cmp_arr("length", out, eo)
-    _, _, eids = orc.csr_build(V, src, dst)
-    assert_paths_equal(p, orc.shortestpath(V, v, e, eids, ps, pd, mode=1), "paths bins=%s" % (bins,))
+        ctx.set_option("lanes", 0)
+        ctx.set_option("filter_gamma", 2)
+        ctx.set_option("direction", 0)
+    assert_paths_equal(p, ep, "paths bins=%s lanes=%d" % (bins, lanes))
     ctx.csr_delete(1)
 
 
@@ -195,7 +209,7 @@ def test_direction_switch(ctx, direction, beta, lanes):
         st = ctx.stats()
     finally:
         ctx.set_option("direction", 0)
-        ctx.set_option("push_beta", 4)
+        ctx.set_option("push_beta", 32)
         ctx.set_option("lanes", 0)
         ctx.set_option("stats", 0)
     eo, ev, est = orc.iterativelength(V, v, e, ps, pd, stats=True)
