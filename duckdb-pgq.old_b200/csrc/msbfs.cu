@@ -76,6 +76,9 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents, int 
 			count_launch(c, 2);
 		}
 	}
+	frontier_stats_kernel<<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[cur ^ 1], b.fbit_words, (uint32_t)g->V,
+	                                                               g->d_off.as<int64_t>(), b.ctrl);
+	count_launch(c);
 	return PGQ_OK;
 }
 

@@ -248,13 +248,20 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	}
 	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
 	Slice<SW> s = slice_zero<SW>(), unseen = slice_zero<SW>();
-	// first round's sources do not depend on `seen`: issue both loads together
+	// Software pipeline, three rounds deep: sources of round r+2 are being loaded and the frontier
+	// bits of round r+1 tested while the gathers of round r are in flight.  The first two rounds'
+	// sources do not depend on `seen`: issue them before it.
 	uint32_t j = lo + sg;
-	uint32_t vs[U];
+	uint32_t vs[U], v1[U];
 #pragma unroll
 	for (int u = 0; u < U; u++) {
 		const uint32_t jj = j + u * GPV;
 		vs[u] = jj < hi ? a.isrc[jj] : INV;
+	}
+#pragma unroll
+	for (int u = 0; u < U; u++) {
+		const uint32_t jj = j + GPV * U + u * GPV;
+		v1[u] = jj < hi ? a.isrc[jj] : INV;
 	}
 	if (valid) {
 		s = ld_slice<SW>(a.seen + wo);
@@ -266,20 +273,31 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	Slice<SW> acc = slice_zero<SW>();  // PARENTS: lanes claimed so far; else: this sub-group's OR
 	Slice<SW> tot = slice_zero<SW>();
 	uint32_t *prow = PARENTS ? a.parent + (size_t)n * W + (size_t)t * (SW * 32) : nullptr;
+	uint32_t fm = 0; // bit u: edge u of the current round has its source in the frontier
+#pragma unroll
+	for (int u = 0; u < U; u++) {
+		bool f = vs[u] != INV;
+		if (FILTER && f) f = fbit_test(a.fcur, vs[u]);
+		fm |= (f ? 1u : 0u) << u;
+	}
 	while (__any_sync(FULL, open && j < hi)) {
 		Slice<SW> w[U];
 #pragma unroll
-		for (int u = 0; u < U; u++) {
-			bool f = open && vs[u] != INV;
-			if (FILTER && f) f = fbit_test(a.fcur, vs[u]);
-			w[u] = f ? ldg_slice<SW>(a.visit + (size_t)vs[u] * WPV + t * SW) : slice_zero<SW>();
-		}
+		for (int u = 0; u < U; u++)
+			w[u] = (open && ((fm >> u) & 1u)) ? ldg_slice<SW>(a.visit + (size_t)vs[u] * WPV + t * SW) : slice_zero<SW>();
 		const uint32_t jn = j + GPV * U;
-		uint32_t vn[U];
+		uint32_t v2[U];
 #pragma unroll
 		for (int u = 0; u < U; u++) {
-			const uint32_t jj = jn + u * GPV;
-			vn[u] = (open && jj < hi) ? a.isrc[jj] : INV;
+			const uint32_t jj = jn + GPV * U + u * GPV;
+			v2[u] = (open && jj < hi) ? a.isrc[jj] : INV;
+		}
+		uint32_t fn = 0;
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			bool f = v1[u] != INV;
+			if (FILTER && f) f = fbit_test(a.fcur, v1[u]);
+			fn |= (f ? 1u : 0u) << u;
 		}
 		if (!PARENTS) {
 #pragma unroll
@@ -329,8 +347,12 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 		}
 		open = open && !slice_covers<SW>(tot, unseen);
 		j = jn;
+		fm = fn;
 #pragma unroll
-		for (int u = 0; u < U; u++) vs[u] = vn[u];
+		for (int u = 0; u < U; u++) {
+			vs[u] = v1[u];
+			v1[u] = v2[u];
+		}
 	}
 	Slice<SW> news;
 #pragma unroll
@@ -348,8 +370,7 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	const bool vnew = ((bal >> (vslot * (GPV * TPV))) & ((1u << TPV) - 1u)) != 0;
 	const bool leader = writer && t == 0 && vnew;
 	if (leader) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
-	if (bal && lane == 0) a.ctrl->change = 1u;
-	count_frontier(a.ctrl, a.off, n, leader);
+	// no global counters here: frontier_stats_kernel derives them from fnext afterwards
 }
 
 // ---- K4 hubs: one block per chunk of a hub's in-list, partial ORs merged with atomicOr ---------
@@ -428,12 +449,58 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 		}
 	}
 	const bool anyn = slice_any<SW>(news);
-	flag_change(a.ctrl, anyn);
 	const bool gnew = group_any<TPV>(anyn);
 	const bool leader = gnew && t == 0 && h < a.nlist;
 	const uint32_t hn = h < a.nlist ? a.list[h] : 0u;
 	if (leader) atomicOr(&a.fnext[hn >> 5], 1u << (hn & 31));
-	count_frontier(a.ctrl, a.off, hn, leader);
+}
+
+// After a pull level: vertices in the new frontier and the sum of their out-degrees (the inputs of
+// the direction switch), plus the `change` flag, from the frontier bitmap.  One atomic per block.
+__global__ void __launch_bounds__(256) frontier_stats_kernel(const uint32_t *__restrict__ fbit, uint32_t nwords,
+                                                             uint32_t V, const int64_t *__restrict__ off,
+                                                             BfsCtrl *ctrl) {
+	__shared__ unsigned long long sdeg[8];
+	__shared__ uint32_t scnt[8];
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t m = i < nwords ? fbit[i] : 0u;
+	uint32_t cnt = __popc(m);
+	unsigned long long deg = 0;
+	while (m) {
+		const int k = __ffs(m) - 1;
+		// runs of set bits: one subtraction per run instead of per vertex
+		const uint32_t inv = ~(m >> k);
+		const uint32_t run = inv ? (uint32_t)(__ffs(inv) - 1) : 32u; // consecutive ones starting at k (1..32)
+		const uint32_t n0 = i * 32 + k;
+		uint32_t n1 = n0 + run;
+		if (n1 > V) n1 = V;
+		if (n0 < V) deg += (unsigned long long)(off[n1] - off[n0]);
+		if (k + run >= 32) break;
+		m &= ~((1u << (k + run)) - 1u);
+	}
+#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) {
+		deg += __shfl_xor_sync(0xffffffffu, deg, d);
+		cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
+	}
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	if (lane == 0) {
+		sdeg[warp] = deg;
+		scnt[warp] = cnt;
+	}
+	__syncthreads();
+	if (threadIdx.x == 0) {
+#pragma unroll
+		for (int w = 1; w < 8; w++) {
+			deg += sdeg[w];
+			cnt += scnt[w];
+		}
+		if (cnt) {
+			atomicAdd(&ctrl->next_edges, deg);
+			atomicAdd(&ctrl->next_verts, cnt);
+			ctrl->change = 1u;
+		}
+	}
 }
 
 // ---- batch init / K6 destination check / stats / K8 path reconstruction -----------------------
