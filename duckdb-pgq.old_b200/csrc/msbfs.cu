@@ -61,7 +61,16 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents, int 
 	a.fnext = b.fbit[cur ^ 1];
 	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, parents, filter);
 	launch_class<W, 2>(c, a, g->d_small, g->n_small, parents, filter);
-	launch_class<W, C::G>(c, a, g->d_mid, g->n_mid, parents, filter);
+	if (parents) {
+		launch_class<W, C::G>(c, a, g->d_mid, g->n_mid, true, true);
+	} else if (g->n_mid) {
+		a.list = g->d_mid.as<uint32_t>();
+		a.nlist = g->n_mid;
+		const uint32_t grid = div_up((uint64_t)g->n_mid * 32, 128);
+		if (filter) pull_warp_kernel<W, true><<<grid, 128, 0, st>>>(a);
+		else pull_warp_kernel<W, false><<<grid, 128, 0, st>>>(a);
+		count_launch(c);
+	}
 	if (g->n_hub) {
 		if (parents) {
 			// ordered first-match needs a single consumer per vertex: one warp per hub

@@ -373,6 +373,76 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	// no global counters here: frontier_stats_kernel derives them from fnext afterwards
 }
 
+// ---- K4 mid (lengths): one warp per vertex, edge-parallel scan ------------------------------------
+// Each LANE owns one in-edge of a 32-edge round: one coalesced source load and one frontier-bit
+// test per edge (instead of once per thread of the group), a ballot, and then the G groups gather
+// only the words whose test passed (source ids handed over by shuffle).  Rounds are pipelined two
+// deep like pull_list_kernel.  Early exit once every unseen lane of the vertex is covered.
+template <int W, bool FILTER>
+__global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
+	using C = LaneCfg<W>;
+	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G;
+	constexpr int STEPS = 32 / G;
+	constexpr uint32_t INV = 0xFFFFFFFFu, FULL = 0xffffffffu;
+	const uint32_t wid = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+	if (wid >= a.nlist) return; // warp-uniform
+	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
+	const uint32_t n = a.list[wid];
+	const uint32_t lo = a.ioff[n], hi = a.ioff[n + 1];
+	uint32_t v0 = lo + lane < hi ? a.isrc[lo + lane] : INV;
+	uint32_t v1 = lo + 32 + lane < hi ? a.isrc[lo + 32 + lane] : INV;
+	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
+	Slice<SW> s = ld_slice<SW>(a.seen + wo);
+	const Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
+	Slice<SW> unseen;
+#pragma unroll
+	for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
+	Slice<SW> acc = slice_zero<SW>();
+	if (__any_sync(FULL, slice_any<SW>(unseen))) {
+		bool p0 = v0 != INV;
+		if (FILTER && p0) p0 = fbit_test(a.fcur, v0);
+		for (uint32_t base = lo; base < hi; base += 32) {
+			const unsigned mask = __ballot_sync(FULL, p0);
+			Slice<SW> w[STEPS];
+#pragma unroll
+			for (int u = 0; u < STEPS; u++) {
+				const int sl = u * G + g;
+				const uint32_t src = STEPS == 1 ? v0 : __shfl_sync(FULL, v0, sl);
+				w[u] = ((mask >> sl) & 1u) ? ldg_slice<SW>(a.visit + (size_t)src * WPV + t * SW) : slice_zero<SW>();
+			}
+			const uint32_t j2 = base + 64 + lane;
+			const uint32_t v2 = j2 < hi ? a.isrc[j2] : INV;
+			bool p1 = v1 != INV;
+			if (FILTER && p1) p1 = fbit_test(a.fcur, v1);
+#pragma unroll
+			for (int u = 0; u < STEPS; u++) {
+#pragma unroll
+				for (int i = 0; i < SW; i++) acc.w[i] |= w[u].w[i];
+			}
+			if (mask) {
+				const Slice<SW> tot = warp_or_groups<SW, TPV>(acc);
+				if (__all_sync(FULL, slice_covers<SW>(tot, unseen))) break; // every unseen lane reached
+			}
+			v0 = v1;
+			p0 = p1;
+			v1 = v2;
+		}
+	}
+	const Slice<SW> tot = warp_or_groups<SW, TPV>(acc);
+	Slice<SW> news;
+#pragma unroll
+	for (int i = 0; i < SW; i++) news.w[i] = tot.w[i] & unseen.w[i];
+	if (g == 0) {
+		st_slice<SW>(a.next + wo, news);
+		if (slice_any<SW>(news)) {
+#pragma unroll
+			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
+			st_slice<SW>(a.seen + wo, s);
+		}
+	}
+	if (__any_sync(FULL, slice_any<SW>(news)) && lane == 0) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+}
+
 // ---- K4 hubs: one block per chunk of a hub's in-list, partial ORs merged with atomicOr ---------
 template <int W>
 __global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
