@@ -162,7 +162,7 @@ int pgq_shutdown(pgq_ctx_t *ctx) {
 	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
 	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->bfs_seen, &c->bfs_visit[0],
 	                  &c->bfs_visit[1], &c->bfs_parent, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
-	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->l2_flush};
+	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->l2_flush};
 	for (DevBuf *b : bufs) b->release();
 	if (c->h_ctrl) cudaFreeHost(c->h_ctrl);
 	cudaEventDestroy(c->ev_a);
@@ -191,6 +191,7 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "hub_chunk")) c->opt.hub_chunk = value < 256 ? 256 : value;
 	else if (!strcmp(key, "direction")) c->opt.direction = value;
 	else if (!strcmp(key, "trace")) c->opt.trace = value;
+	else if (!strcmp(key, "push_vbeta")) c->opt.push_vbeta = value < 1 ? 1 : value;
 	else if (!strcmp(key, "filter_gamma")) c->opt.filter_gamma = value < 0 ? 0 : value;
 	else if (!strcmp(key, "push_beta")) c->opt.push_beta = value < 1 ? 1 : value;
 	else {

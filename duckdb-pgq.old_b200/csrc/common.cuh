@@ -123,6 +123,7 @@ struct Options {
 	int64_t direction = 0; // 0 auto (push when the frontier is sparse), 1 pull only
 	int64_t trace = 0;     // with timing=1: per-level line on stderr
 	int64_t push_beta = 32; // push when frontier out-edges * push_beta <= E
+	int64_t push_vbeta = 16; // ... and frontier vertices * push_vbeta <= V (+ slack for tiny graphs)
 	int64_t filter_gamma = 2; // pull tests the frontier bitmap while frontier out-edges * gamma <= E
 };
 
@@ -139,6 +140,7 @@ struct Ctx {
 	DevBuf sort_keys[2], sort_p0[2], sort_p1[2], sort_hist;
 	DevBuf bfs_seen, bfs_visit[2], bfs_parent, bfs_hubacc;
 	DevBuf bfs_queue[2], bfs_inq[2]; // push work queues + dedupe bitmaps
+	DevBuf bfs_alive; // per-block-slot alive lane masks (msbfs_kernels.cuh)
 	DevBuf bfs_lane; // per-call lane tables
 	DevBuf bfs_ctrl; // device control block
 	DevBuf l2_flush;

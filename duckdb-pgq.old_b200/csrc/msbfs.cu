@@ -14,6 +14,7 @@ struct BatchBufs {
 	uint32_t *fbit[2]; // frontier bitmap of visit[i] (1 bit per vertex, padded)
 	size_t fbit_bytes;
 	uint32_t fbit_words;
+	uint32_t *alive_slots; // [ALIVE_SLOTS][16], all-zero between levels
 	BfsCtrl *ctrl;
 };
 
@@ -59,6 +60,7 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents, int 
 	a.off = g->d_off.as<int64_t>();
 	a.fcur = b.fbit[cur];
 	a.fnext = b.fbit[cur ^ 1];
+	a.alive_slots = b.alive_slots;
 	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, parents, filter);
 	launch_class<W, 2>(c, a, g->d_small, g->n_small, parents, filter);
 	if (parents) {
@@ -119,6 +121,7 @@ int launch_push(Ctx *c, Csr *g, const BatchBufs &b, int cur, int q) {
 	clear_by_bitmap_kernel<W><<<div_up(b.fbit_words, 256), 256, 0, c->stream>>>(b.fbit[cur ^ 1], b.fbit_words,
 	                                                                           b.visit[cur ^ 1]);
 	const uint32_t grid = (uint32_t)c->sm_count * 8;
+	a.alive_slots = b.alive_slots;
 	push_kernel<W><<<grid, 256, 0, c->stream>>>(a);
 	count_launch(c, 2);
 	return PGQ_OK;
@@ -139,7 +142,7 @@ int launch_compact(Ctx *c, Csr *g, const BatchBufs &b, int cur, int q) {
 	cudaStream_t st = c->stream;
 	compact_bitmap_kernel<<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[cur], b.fbit_words, (uint32_t)g->V,
 	                                                                 g->d_off.as<int64_t>(), b.queue[q], b.ctrl);
-	bfs_snapshot_kernel<<<1, 1, 0, st>>>(b.ctrl);
+	bfs_snapshot_items_kernel<<<1, 1, 0, st>>>(b.ctrl);
 	count_launch(c, 2);
 	return PGQ_OK;
 }
@@ -183,6 +186,9 @@ int alloc_bufs(Ctx *c, Csr *g, int W, bool parents, BatchBufs *b) {
 	b->parent = parents ? c->bfs_parent.as<uint32_t>() : nullptr;
 	b->hubacc = c->bfs_hubacc.as<uint32_t>();
 	b->ctrl = c->bfs_ctrl.as<BfsCtrl>();
+	PGQ_TRY(c->bfs_alive.reserve((size_t)ALIVE_SLOTS * 16 * sizeof(uint32_t)));
+	PGQ_CUDA(cudaMemsetAsync(c->bfs_alive.p, 0, (size_t)ALIVE_SLOTS * 16 * sizeof(uint32_t), c->stream));
+	b->alive_slots = c->bfs_alive.as<uint32_t>();
 	const size_t qcap = (size_t)g->V + (size_t)(g->E / PUSH_CHUNK) + 2;
 	// padded: pull_small stores whole 8/16/32-vertex units, its grid may overhang V by < 256 vertices
 	b->fbit_words = (uint32_t)(((size_t)g->V + 256 + 31) / 32);
@@ -221,7 +227,9 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 		// direction switch on frontier density: top-down while the frontier's out-edges are few
 		const bool push = !parents && c->opt.direction == 0 &&
 		                  (unsigned long long)h.out_edges * (unsigned long long)c->opt.push_beta <=
-		                      (unsigned long long)g->E;
+		                      (unsigned long long)g->E &&
+		                  (unsigned long long)h.out_verts * (unsigned long long)c->opt.push_vbeta <=
+		                      (unsigned long long)g->V + (unsigned long long)c->opt.push_vbeta * 1024ull;
 		if (c->opt.stats) launch_count(c, g, b, W, cur);
 		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
 		uint64_t before = c->stats.kernel_launches;
@@ -239,7 +247,7 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 			have_queue = false;
 		}
 		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
-		bfs_check_kernel<<<1, W, 0, st>>>(b.seen, d_lane_dst, W, d_found, b.ctrl, iter);
+		bfs_check_kernel<<<1, W, 0, st>>>(b.seen, d_lane_dst, W, d_found, b.ctrl, iter, b.alive_slots);
 		count_launch(c);
 		PGQ_TRY(read_ctrl(c, b, &h));
 		c->stats.levels++;

@@ -20,6 +20,7 @@ namespace pgq {
 
 struct BfsCtrl {
 	uint32_t active[32]; // lane mask, W/32 words used (W <= 1024); first so slices are 16 B aligned
+	uint32_t alive[32];  // lanes that gained a frontier bit in the running level (others are exhausted)
 	uint32_t change;     // set by level kernels when any new bit appeared
 	uint32_t change_out; // snapshot taken by the check kernel
 	uint32_t n_active;   // lanes still searching
@@ -36,6 +37,33 @@ struct BfsCtrl {
 	uint32_t out_verts;
 	uint32_t out_items;
 };
+
+// Lanes that gained a frontier bit in the running level ("alive").  A lane with an empty frontier
+// can never reach anything new; the check kernel retires it so it stops blocking the pull
+// kernels' early exit.  Producers OR their new words into a block-shared mask and flush it once
+// per block into slot blockIdx % ALIVE_SLOTS (spread addresses: no hot atomics); the check kernel
+// folds the slots into BfsCtrl::alive.
+static constexpr uint32_t ALIVE_SLOTS = 1024;
+
+// Producers keep a block-shared copy of their slot (blockIdx % ALIVE_SLOTS), preloaded from the
+// slot so knowledge carries over between blocks, and touch the global slot only for bits the copy
+// does not have yet: after the first few blocks of a level this is shared-memory reads only.
+__device__ __forceinline__ void alive_init(uint32_t *salive, const uint32_t *alive_slots) {
+	if (threadIdx.x < 16) salive[threadIdx.x] = alive_slots[(blockIdx.x % ALIVE_SLOTS) * 16 + threadIdx.x];
+	__syncthreads();
+}
+
+template <int SW>
+__device__ __forceinline__ void alive_note(uint32_t *salive, uint32_t *alive_slots, uint32_t word0, const uint32_t *w) {
+#pragma unroll
+	for (int i = 0; i < SW; i++) {
+		const uint32_t nb = w[i] & ~salive[word0 + i];
+		if (nb) {
+			atomicOr(&salive[word0 + i], nb);
+			atomicOr(&alive_slots[(blockIdx.x % ALIVE_SLOTS) * 16 + word0 + i], nb);
+		}
+	}
+}
 
 // Push work item: out-edges [off[v] + chunk*PUSH_CHUNK, +PUSH_CHUNK) of frontier vertex v.
 static constexpr uint32_t PUSH_CHUNK = 1024;
@@ -58,7 +86,7 @@ struct PullArgs {
 	uint32_t *hubacc;
 	const uint32_t *fcur; // 1 bit per vertex: visit word non-empty (may over-approximate, never under)
 	uint32_t *fnext;      // same for `next`, produced by this level
-	uint32_t touch_isolated; // 1: also rewrite next[] of in-degree-0 vertices (levels 1-2, stale source bits)
+	uint32_t *alive_slots;   // [ALIVE_SLOTS][16] per-block-slot OR of the words produced this level
 };
 
 template <int W>
@@ -234,8 +262,10 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	static_assert(GPV >= 1 && GPV <= G, "groups per vertex");
 	constexpr int VPW = G / GPV;
 	constexpr uint32_t INV = 0xFFFFFFFFu, FULL = 0xffffffffu;
+	__shared__ uint32_t salive[16];
+	alive_init(salive, a.alive_slots);
 	const uint32_t wid = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-	if ((uint64_t)wid * VPW >= a.nlist) return; // warp-uniform
+	if ((uint64_t)wid * VPW >= a.nlist) return; // warp-uniform (an exited warp counts as arrived at barriers)
 	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
 	const uint32_t vslot = g / GPV, sg = g % GPV;
 	const uint64_t idx = (uint64_t)wid * VPW + vslot;
@@ -364,6 +394,7 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
 			st_slice<SW>(a.seen + wo, s);
+			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 		}
 	}
 	const unsigned bal = __ballot_sync(FULL, writer && slice_any<SW>(news));
@@ -384,6 +415,8 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G;
 	constexpr int STEPS = 32 / G;
 	constexpr uint32_t INV = 0xFFFFFFFFu, FULL = 0xffffffffu;
+	__shared__ uint32_t salive[16];
+	alive_init(salive, a.alive_slots);
 	const uint32_t wid = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
 	if (wid >= a.nlist) return; // warp-uniform
 	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
@@ -438,6 +471,7 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
 			st_slice<SW>(a.seen + wo, s);
+			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 		}
 	}
 	if (__any_sync(FULL, slice_any<SW>(news)) && lane == 0) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
@@ -498,6 +532,8 @@ template <int W>
 __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
+	__shared__ uint32_t salive[16];
+	alive_init(salive, a.alive_slots);
 	const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
 	const uint32_t h = gid / TPV, t = gid % TPV;
 	Slice<SW> news = slice_zero<SW>();
@@ -523,6 +559,7 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 	const bool leader = gnew && t == 0 && h < a.nlist;
 	const uint32_t hn = h < a.nlist ? a.list[h] : 0u;
 	if (leader) atomicOr(&a.fnext[hn >> 5], 1u << (hn & 31));
+	if (anyn) alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 }
 
 // After a pull level: vertices in the new frontier and the sum of their out-degrees (the inputs of
@@ -530,9 +567,11 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 __global__ void __launch_bounds__(256) frontier_stats_kernel(const uint32_t *__restrict__ fbit, uint32_t nwords,
                                                              uint32_t V, const int64_t *__restrict__ off,
                                                              BfsCtrl *ctrl) {
+	constexpr uint32_t FULL = 0xffffffffu;
 	__shared__ unsigned long long sdeg[8];
 	__shared__ uint32_t scnt[8];
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	uint32_t m = i < nwords ? fbit[i] : 0u;
 	uint32_t cnt = __popc(m);
 	unsigned long long deg = 0;
@@ -550,10 +589,9 @@ __global__ void __launch_bounds__(256) frontier_stats_kernel(const uint32_t *__r
 	}
 #pragma unroll
 	for (int d = 16; d > 0; d >>= 1) {
-		deg += __shfl_xor_sync(0xffffffffu, deg, d);
-		cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
+		deg += __shfl_xor_sync(FULL, deg, d);
+		cnt += __shfl_xor_sync(FULL, cnt, d);
 	}
-	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	if (lane == 0) {
 		sdeg[warp] = deg;
 		scnt[warp] = cnt;
@@ -613,6 +651,7 @@ __global__ void bfs_init_kernel(const uint32_t *__restrict__ lane_src, int W, ui
 	const unsigned m = __ballot_sync(0xffffffffu, used);
 	if ((lane & 31) == 0) {
 		ctrl->active[lane >> 5] = m;
+		ctrl->alive[lane >> 5] = 0;
 		atomicAdd(&cnt, (uint32_t)__popc(m));
 	}
 	__syncthreads();
@@ -626,10 +665,22 @@ __global__ void bfs_init_kernel(const uint32_t *__restrict__ lane_src, int W, ui
 // After a level: lanes whose destination has been seen get found=iter and leave the active mask;
 // the frontier statistics of the level are snapshotted for the host's direction decision.
 __global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, const uint32_t *__restrict__ lane_dst, int W,
-                                 int32_t *__restrict__ found, BfsCtrl *ctrl, int iter) {
+                                 int32_t *__restrict__ found, BfsCtrl *ctrl, int iter,
+                                 uint32_t *__restrict__ alive_slots) {
 	__shared__ uint32_t cnt;
+	__shared__ uint32_t salive[16];
 	const int lane = threadIdx.x;
 	if (lane == 0) cnt = 0;
+	if (lane < 16) salive[lane] = 0;
+	__syncthreads();
+	// fold (and re-zero) the per-slot alive masks of the level that just ran
+	for (uint32_t idx = lane; idx < ALIVE_SLOTS * 16; idx += blockDim.x) {
+		const uint32_t v = alive_slots[idx];
+		if (v) {
+			alive_slots[idx] = 0;
+			atomicOr(&salive[idx & 15], v);
+		}
+	}
 	__syncthreads();
 	const uint32_t word = ctrl->active[lane >> 5];
 	const bool act = (word >> (lane & 31)) & 1u;
@@ -642,7 +693,8 @@ __global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, const uint32
 	const unsigned hm = __ballot_sync(0xffffffffu, hit);
 	__syncthreads(); // all reads of active[] done before any warp rewrites its word
 	if ((lane & 31) == 0) {
-		const uint32_t nw = word & ~hm;
+		const uint32_t nw = word & ~hm & salive[lane >> 5]; // found or exhausted lanes retire
+		ctrl->alive[lane >> 5] = salive[lane >> 5];
 		ctrl->active[lane >> 5] = nw;
 		atomicAdd(&cnt, (uint32_t)__popc(nw));
 	}
@@ -653,12 +705,6 @@ __global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, const uint32
 		ctrl->change = 0;
 		snapshot_frontier(ctrl);
 	}
-}
-
-// after compact_bitmap_kernel: publish the rebuilt queue (the counters it re-accumulated replace
-// the ones the pull level had produced for the same frontier)
-__global__ void bfs_snapshot_kernel(BfsCtrl *ctrl) {
-	snapshot_frontier(ctrl);
 }
 
 // ---- K4 top-down (push) for sparse frontiers ---------------------------------------------------
@@ -676,11 +722,14 @@ struct PushArgs {
 	const uint2 *queue;  // items of this level (count = ctrl->out_items)
 	uint2 *queue_next;   // items for the next level
 	uint32_t *fnext;     // frontier bitmap of `next` (doubles as the dedupe bitmap of queue_next)
+	uint32_t *alive_slots;
 };
 
 template <int W>
 __global__ void __launch_bounds__(256) push_kernel(PushArgs a) {
 	constexpr int WPV = W / 32;
+	__shared__ uint32_t salive[16];
+	alive_init(salive, a.alive_slots);
 	const uint32_t nitems = a.ctrl->out_items;
 	const uint32_t lane = threadIdx.x & 31;
 	const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -710,6 +759,7 @@ __global__ void __launch_bounds__(256) push_kernel(PushArgs a) {
 					const uint32_t nb = bits & ~old;
 					if (nb) {
 						atomicOr(&a.next[(size_t)n * WPV + w], nb);
+						alive_note<1>(salive, a.alive_slots, (uint32_t)w, &nb);
 						mynew = true;
 					}
 				}
@@ -748,19 +798,49 @@ __global__ void __launch_bounds__(256) clear_by_bitmap_kernel(uint32_t *__restri
 	}
 }
 
-// pull -> push transition: rebuild the work queue from the frontier bitmap.
+// pull -> push transition: rebuild the work queue from the frontier bitmap.  One thread per bitmap
+// word, two passes (count items, warp-scan, one atomic per warp, write).  The vertex / edge totals
+// of this frontier were already published by frontier_stats_kernel; only the item count is new.
 __global__ void __launch_bounds__(256) compact_bitmap_kernel(const uint32_t *__restrict__ fbit, uint32_t nwords,
                                                              uint32_t V, const int64_t *__restrict__ off,
                                                              uint2 *__restrict__ queue, BfsCtrl *ctrl) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= nwords) return;
-	uint32_t m = fbit[i];
-	while (m) {
-		const int k = __ffs(m) - 1;
-		m &= m - 1;
-		const uint32_t n = i * 32 + k;
-		if (n < V) enqueue_vertex(n, off, queue, ctrl);
+	const uint32_t lane = threadIdx.x & 31;
+	const uint32_t m = i < nwords ? fbit[i] : 0u;
+	uint32_t items = 0;
+	for (uint32_t mm = m; mm; mm &= mm - 1) {
+		const uint32_t n = i * 32 + (__ffs(mm) - 1);
+		if (n >= V) break;
+		const unsigned long long deg = (unsigned long long)(off[n + 1] - off[n]);
+		const uint32_t k = (uint32_t)((deg + PUSH_CHUNK - 1) / PUSH_CHUNK);
+		items += k ? k : 1u;
 	}
+	uint32_t incl = items;
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) {
+		const uint32_t y = __shfl_up_sync(0xffffffffu, incl, d);
+		if (lane >= (uint32_t)d) incl += y;
+	}
+	const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+	if (total == 0) return; // warp-uniform
+	uint32_t base = 0;
+	if (lane == 0) base = atomicAdd(&ctrl->next_items, total);
+	base = __shfl_sync(0xffffffffu, base, 0);
+	uint32_t pos = base + incl - items;
+	for (uint32_t mm = m; mm; mm &= mm - 1) {
+		const uint32_t n = i * 32 + (__ffs(mm) - 1);
+		if (n >= V) break;
+		const unsigned long long deg = (unsigned long long)(off[n + 1] - off[n]);
+		uint32_t k = (uint32_t)((deg + PUSH_CHUNK - 1) / PUSH_CHUNK);
+		if (k == 0) k = 1;
+		for (uint32_t c = 0; c < k; c++) queue[pos++] = make_uint2(n, c);
+	}
+}
+
+// publish the rebuilt queue's item count
+__global__ void bfs_snapshot_items_kernel(BfsCtrl *ctrl) {
+	ctrl->out_items = ctrl->next_items;
+	ctrl->next_items = 0;
 }
 
 // TEPS numerator of the level about to run (stats mode only; not part of the timed path).

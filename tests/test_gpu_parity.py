@@ -201,6 +201,7 @@ def test_direction_switch(ctx, direction, beta, lanes):
     ps, pd = orc.gen_pairs(12, V, v, 1100)
     ctx.set_option("direction", direction)
     ctx.set_option("push_beta", beta)
+    ctx.set_option("push_vbeta", 1 if beta == 1 else 16)
     ctx.set_option("lanes", lanes)
     ctx.set_option("stats", 1)
     ctx.reset_stats()
@@ -210,6 +211,7 @@ def test_direction_switch(ctx, direction, beta, lanes):
     finally:
         ctx.set_option("direction", 0)
         ctx.set_option("push_beta", 32)
+        ctx.set_option("push_vbeta", 16)
         ctx.set_option("lanes", 0)
         ctx.set_option("stats", 0)
     eo, ev, est = orc.iterativelength(V, v, e, ps, pd, stats=True)
