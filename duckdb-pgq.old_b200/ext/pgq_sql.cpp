@@ -1,0 +1,44 @@
+// pgq_sql — minimal SQL driver over the reference DuckDB's C++ API (Connection::Query,
+// /root/reference/src/include/duckdb/main/connection.hpp).  Reads statements from stdin (separated by
+// ';' at end of line), prints each result row as comma-separated values after a "-- result N" line,
+// and errors as "-- error N: <message>".  It links the same libduckdb.so as the extension, so the
+// plugin and the host share one copy of DuckDB (SURVEY.md §8(b) caveat about the static shell).
+#include "duckdb.hpp"
+
+#include <iostream>
+#include <sstream>
+#include <string>
+
+using namespace duckdb;
+
+int main(int argc, char **argv) {
+	DuckDB db(argc > 1 ? argv[1] : nullptr);
+	Connection con(db);
+	std::string line, stmt;
+	int n = 0, failed = 0;
+	while (std::getline(std::cin, line)) {
+		stmt += line;
+		stmt += "\n";
+		size_t end = line.find_last_not_of(" \t\r");
+		if (end == std::string::npos || line[end] != ';') continue;
+		auto res = con.Query(stmt);
+		stmt.clear();
+		n++;
+		if (!res->success) {
+			std::cout << "-- error " << n << ": " << res->error << "\n";
+			failed++;
+			continue;
+		}
+		std::cout << "-- result " << n << "\n";
+		for (idx_t r = 0; r < res->collection.Count(); r++) {
+			for (idx_t c = 0; c < res->ColumnCount(); c++) {
+				if (c) std::cout << ",";
+				Value v = res->GetValue(c, r);
+				std::cout << (v.is_null ? std::string("NULL") : v.ToString());
+			}
+			std::cout << "\n";
+		}
+	}
+	std::cout << "-- done " << n << " statements, " << failed << " errors\n";
+	return 0;
+}

@@ -1,0 +1,161 @@
+"""The drop-in boundary through SQL: the DuckDB extension (duckdb-pgq.old_b200/ext) LOADed into the
+reference DuckDB (libduckdb.so built from /root/reference, baseline/_ref/duckdb), driven by SQL text
+the way DuckPGQ's rewriter calls the functions (SURVEY.md §8(f) f3 template), checked against the
+oracle.  Mirrors /root/reference/test/extension/load_extension.test (LOAD + call)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXT = os.path.join(ROOT, "duckdb-pgq.old_b200", "ext", "pgq_b200.duckdb_extension")
+DRIVER = os.path.join(ROOT, "duckdb-pgq.old_b200", "ext", "pgq_sql")
+HOSTLIB = os.path.join(ROOT, "baseline", "_ref", "duckdb", "libduckdb.so")
+
+needs_host = pytest.mark.skipif(not (os.path.exists(EXT) and os.path.exists(DRIVER) and os.path.exists(HOSTLIB)),
+                                reason="reference DuckDB host / extension not built (build container only)")
+
+
+def run_sql(sql):
+    """-> list of (kind, payload): ('result', [rows as lists of str]) or ('error', message)."""
+    out = subprocess.run([DRIVER], input=sql, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    res, cur = [], None
+    for line in out.stdout.splitlines():
+        if line.startswith("-- result "):
+            cur = []
+            res.append(("result", cur))
+        elif line.startswith("-- error "):
+            res.append(("error", line.split(":", 1)[1].strip()))
+            cur = None
+        elif line.startswith("-- done "):
+            cur = None
+        elif cur is not None:
+            cur.append(line)
+    return res
+
+
+@needs_host
+def test_extension_loads_and_fails_loudly_without_gpu():
+    """LOAD registers every function; with no GPU a call raises (no CPU fallback), never crashes."""
+    import torch
+    sql = "LOAD '%s';\n" % EXT
+    sql += "SELECT name FROM pragma_functions() WHERE name IN ('create_csr_vertex'," \
+           "'create_csr_edge','iterativelength','reachability','shortestpath','shortestpath_with_edges'," \
+           "'delete_csr') GROUP BY name ORDER BY name;\n"
+    sql += "SELECT iterativelength(0, CAST(10 AS BIGINT), CAST(1 AS BIGINT), CAST(2 AS BIGINT));\n"
+    r = run_sql(sql)
+    assert r[0][0] == "result"
+    assert r[1] == ("result", ["create_csr_edge", "create_csr_vertex", "delete_csr", "iterativelength",
+                               "reachability", "shortestpath", "shortestpath_with_edges"])
+    assert r[2][0] == "error"
+    if not torch.cuda.is_available():
+        assert "no CPU fallback" in r[2][1] or "CUDA" in r[2][1]
+    else:
+        assert "does not exist" in r[2][1]
+
+
+def _write_csv(path, cols):
+    with open(path, "w") as f:
+        for row in zip(*cols):
+            f.write(",".join("" if x is None else str(int(x)) for x in row) + "\n")
+
+
+def _parse_list(s):
+    s = s.strip()
+    if s == "NULL":
+        return None
+    return [int(x) for x in s.strip("[]").split(",") if x.strip()]
+
+
+@pytest.mark.gpu
+@needs_host
+def test_sql_pgq_functions_match_oracle(tmp_path):
+    V, E = 2500, 40000
+    src, dst = orc.gen_knows(77, V, E)
+    v, e, eids = orc.csr_build(V, src, dst)
+    n = 2300  # > 2 chunks of 1024 rows
+    ps, pd = orc.gen_pairs(5, V, v, n)
+    ps = ps.astype(object)
+    pd = pd.astype(object)
+    for i in range(0, n, 97):
+        ps[i] = None  # NULL src
+    for i in range(5, n, 131):
+        pd[i] = ps[i]  # src == dst
+    sv = np.array([x is not None for x in ps], dtype=np.uint8)
+    ps_i = np.array([0 if x is None else x for x in ps], dtype=np.int64)
+    pd_i = np.array([0 if x is None else x for x in pd], dtype=np.int64)
+    _write_csv(tmp_path / "person.csv", [np.arange(V) * 7 + 3])  # sparse ids: dense id = rowid
+    _write_csv(tmp_path / "knows.csv", [src * 7 + 3, dst * 7 + 3])
+    _write_csv(tmp_path / "pairs.csv", [np.arange(n), ps, pd])
+    sql = """LOAD '%s';
+PRAGMA threads=1;
+CREATE TABLE person(id BIGINT);
+CREATE TABLE knows(p1 BIGINT, p2 BIGINT);
+CREATE TABLE pairs(i BIGINT, s BIGINT, d BIGINT);
+COPY person FROM '%s';
+COPY knows FROM '%s';
+COPY pairs FROM '%s';
+SELECT sum(create_csr_edge(0, (SELECT count(*) FROM person),
+    CAST((SELECT sum(create_csr_vertex(0, (SELECT count(*) FROM person), sub.dense_id, sub.cnt))
+          FROM (SELECT p.rowid AS dense_id, count(k.p1) AS cnt FROM person p LEFT JOIN knows k ON k.p1 = p.id
+                GROUP BY p.rowid) sub) AS BIGINT),
+    a.rowid, b.rowid, k.rowid))
+  FROM knows k JOIN person a ON k.p1 = a.id JOIN person b ON k.p2 = b.id;
+SELECT i, iterativelength(0, (SELECT count(*) FROM person), s, d) FROM pairs ORDER BY i;
+SELECT i, reachability(0, (SELECT count(*) FROM person), s, d) FROM pairs ORDER BY i;
+SELECT i, shortestpath(0, (SELECT count(*) FROM person), s, d) FROM pairs ORDER BY i;
+SELECT delete_csr(0);
+SELECT iterativelength(0, CAST(5 AS BIGINT), CAST(1 AS BIGINT), CAST(2 AS BIGINT));
+""" % (EXT, tmp_path / "person.csv", tmp_path / "knows.csv", tmp_path / "pairs.csv")
+    r = run_sql(sql)
+    kinds = [k for k, _ in r]
+    assert kinds[:8] == ["result"] * 8, r[:8]
+    assert r[8] == ("result", [str(E)])  # every edge row accepted
+    eo, ev = orc.iterativelength(V, v, e, ps_i, pd_i, src_valid=sv)
+    got = [row.split(",", 1)[1] for row in r[9][1]]
+    assert got == ["NULL" if not ev[i] else str(int(eo[i])) for i in range(n)]
+    er, erv = orc.reachability(V, v, e, ps_i, pd_i, src_valid=sv)
+    got = [row.split(",", 1)[1] for row in r[10][1]]
+    assert got == ["NULL" if not erv[i] else ("True" if er[i] else "False") for i in range(n)]
+    off, ln, pv, vals = orc.shortestpath(V, v, e, eids, ps_i, pd_i, src_valid=sv, mode=0)
+    got = [_parse_list(row.split(",", 1)[1]) for row in r[11][1]]
+    exp = [None if not pv[i] else [int(x) for x in vals[int(off[i]):int(off[i]) + int(ln[i])]] for i in range(n)]
+    assert got == exp
+    assert r[12] == ("result", ["True"])
+    assert r[13][0] == "error" and "does not exist" in r[13][1]
+
+
+@pytest.mark.gpu
+@needs_host
+def test_sql_edge_ids_in_scan_order(tmp_path):
+    """Direct scan (no join), threads=1: rows reach create_csr_edge in table order, so the
+    edge-id-interleaved paths equal the oracle's byte for byte (R3, R7, R8)."""
+    scale = 10
+    V = 1 << scale
+    src, dst = orc.gen_rmat(0x5eed0000 + scale, scale)
+    E = len(src)
+    v, e, eids = orc.csr_build(V, src, dst)
+    n = 600
+    ps, pd = orc.gen_pairs(9, V, v, n)
+    _write_csv(tmp_path / "e.csv", [src, dst])
+    _write_csv(tmp_path / "pairs.csv", [np.arange(n), ps, pd])
+    sql = """LOAD '%s';
+PRAGMA threads=1;
+CREATE TABLE e(s BIGINT, d BIGINT);
+CREATE TABLE pairs(i BIGINT, s BIGINT, d BIGINT);
+COPY e FROM '%s';
+COPY pairs FROM '%s';
+SELECT sum(create_csr_edge(3, CAST(%d AS BIGINT), CAST(%d AS BIGINT), s, d, rowid)) FROM e;
+SELECT i, shortestpath_with_edges(3, CAST(%d AS BIGINT), s, d) FROM pairs ORDER BY i;
+""" % (EXT, tmp_path / "e.csv", tmp_path / "pairs.csv", V, E, V)
+    r = run_sql(sql)
+    assert [k for k, _ in r] == ["result"] * 8, r
+    assert r[6] == ("result", [str(E)])
+    off, ln, pv, vals = orc.shortestpath(V, v, e, eids, ps, pd, mode=1)
+    got = [_parse_list(row.split(",", 1)[1]) for row in r[7][1]]
+    exp = [None if not pv[i] else [int(x) for x in vals[int(off[i]):int(off[i]) + int(ln[i])]] for i in range(n)]
+    assert got == exp
