@@ -308,3 +308,46 @@ def pinned_empty(n, dtype):
 
 def pinned_free(hptr):
     load_library().pgq_host_free_pinned(C.c_void_p(hptr))
+
+
+# ---- multi-GPU host logic: source-batch sharding ---------------------------------
+def shard_rows(n, world, rank, lanes=512):
+    """Rows [lo, hi) of an n-row pair set that `rank` answers.  Shards are contiguous runs of whole
+    `lanes`-row batches (a batch is the independent unit: SURVEY.md §8(e)), sizes differing by at
+    most one batch, so rank r's results are rows lo..hi of the caller's result vector."""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError("bad world/rank")
+    batches = (n + lanes - 1) // lanes
+    b_lo = batches * rank // world
+    b_hi = batches * (rank + 1) // world
+    return min(n, b_lo * lanes), min(n, b_hi * lanes)
+
+
+def sharded_query(fn, dist, n, world, rank, src, dst, lanes=512):
+    """Run `fn(src_shard, dst_shard) -> (out int64[], valid uint8[])` on this rank's shard and
+    all-gather the shards into full-length arrays on every rank (torch.distributed: NCCL on GPUs,
+    gloo in the CPU tests).  `fn` is the per-GPU query, e.g. Context.iterativelength bound to a
+    csr id; nothing here touches the data path."""
+    import torch
+    lo, hi = shard_rows(n, world, rank, lanes)
+    out, valid = fn(src[lo:hi], dst[lo:hi])
+    if dist is None or world == 1:
+        return np.asarray(out), np.asarray(valid)
+    cap = max(shard_rows(n, world, r, lanes)[1] - shard_rows(n, world, r, lanes)[0] for r in range(world))
+    buf = torch.full((cap, 2), -1, dtype=torch.int64)
+    buf[:hi - lo, 0] = torch.from_numpy(np.ascontiguousarray(out, dtype=np.int64))
+    buf[:hi - lo, 1] = torch.from_numpy(np.ascontiguousarray(valid, dtype=np.int64))
+    dev = None
+    if dist.get_backend() == "nccl":
+        dev = torch.device("cuda", torch.cuda.current_device())
+        buf = buf.to(dev)
+    parts = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(parts, buf)
+    full_out = np.empty(n, dtype=np.int64)
+    full_valid = np.empty(n, dtype=np.uint8)
+    for r in range(world):
+        a, b = shard_rows(n, world, r, lanes)
+        p = parts[r].cpu().numpy()
+        full_out[a:b] = p[:b - a, 0]
+        full_valid[a:b] = p[:b - a, 1]
+    return full_out, full_valid

@@ -354,3 +354,25 @@ def test_large_scale_properties(ctx):
         else:
             assert paths[i] is None
     ctx.csr_delete(9)
+
+
+@pytest.mark.gpu
+def test_sharded_query_gpu(ctx):
+    """The multi-GPU host wrapper around the real per-GPU query (single rank = whole set)."""
+    import pgq_b200
+    scale = 12
+    V = 1 << scale
+    src, dst = orc.gen_rmat(0x5eed0000 + scale, scale)
+    v, e, _ = _build_both(ctx, V, src, dst)
+    ps, pd = orc.gen_pairs(8, V, v, 1500)
+    outs, valids = [], []
+    for r in range(3):  # what three ranks would each compute, stitched by hand
+        lo, hi = pgq_b200.shard_rows(len(ps), 3, r)
+        o, ok = pgq_b200.sharded_query(lambda s, d: ctx.iterativelength(1, s, d), None, hi - lo, 1, 0, ps[lo:hi],
+                                       pd[lo:hi])
+        outs.append(o)
+        valids.append(ok)
+    eo, ev = orc.iterativelength(V, v, e, ps, pd)
+    _cmp_arr("valid", np.concatenate(valids), ev)
+    _cmp_arr("length", np.concatenate(outs), eo)
+    ctx.csr_delete(1)
