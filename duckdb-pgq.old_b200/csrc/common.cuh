@@ -95,6 +95,7 @@ struct Csr {
 	DevBuf d_tgt;  // uint32[E], reference `e` narrowed
 	DevBuf d_row;  // uint32[E] input row of each CSR slot (only when edge ids are kept)
 	DevBuf d_eid;  // int64[E] edge ids in CSR order (only when caller gave eids)
+	DevBuf d_fsrc; // uint32[E] source of each forward slot (sorted keys of the build; consumed by csr_prepare)
 	bool keep_rows = false;
 	// reverse CSR (lazy)
 	bool prepared = false;
@@ -127,6 +128,15 @@ struct Options {
 	int64_t filter_gamma = 2; // pull tests the frontier bitmap while frontier out-edges * gamma <= E
 };
 
+// What the two frontier buffers hold after the last completed batch (msbfs.cu run_batch).
+struct BfsDirty {
+	bool valid = false;
+	int W = 0;
+	int64_t V = 0;
+	const void *visit0 = nullptr, *fbit0 = nullptr;
+	int map[2] = {0, 0}; // bitmap index describing visit[0] / visit[1]
+};
+
 struct Ctx {
 	int device = 0;
 	int sm_count = 148;
@@ -140,6 +150,7 @@ struct Ctx {
 	DevBuf sort_keys[2], sort_p0[2], sort_p1[2], sort_hist;
 	DevBuf bfs_seen, bfs_visit[2], bfs_parent, bfs_hubacc;
 	DevBuf bfs_queue[2], bfs_inq[2]; // push work queues + dedupe bitmaps
+	BfsDirty bfs_dirty;
 	DevBuf bfs_alive; // per-block-slot alive lane masks (msbfs_kernels.cuh)
 	DevBuf bfs_lane; // per-call lane tables
 	DevBuf bfs_ctrl; // device control block
@@ -173,6 +184,11 @@ struct SortIO {
 	int key_bits = 1;
 	uint32_t *out_p0 = nullptr; // payload0 in sorted order
 	uint32_t *out_p1 = nullptr; // original index in sorted order (nullptr = not wanted)
+	uint32_t *out_keys = nullptr; // sorted keys (nullptr = not wanted)
+	const uint32_t **keys_scratch = nullptr; // or: sorted keys left in the context's free ping-pong buffer
+	// first-pass validation of 64-bit inputs: sets *err |= 1 when a key or payload is outside [0, vmax)
+	uint64_t vmax = 0;
+	uint32_t *err = nullptr;
 };
 
 int radix_sort_stable(Ctx *c, const SortIO &io);

@@ -8,35 +8,33 @@
 
 namespace pgq {
 
-// ---- K1 ----------------------------------------------------------------------------------
-// deg[src]++ ; also validates 0 <= src,dst < V (the reference would write out of bounds).
-__global__ void __launch_bounds__(256) degree_hist_kernel(const int64_t *__restrict__ src,
-                                                          const int64_t *__restrict__ dst, uint32_t n,
-                                                          uint64_t V, uint32_t *__restrict__ deg,
-                                                          uint32_t *__restrict__ err) {
-	uint32_t stride = gridDim.x * blockDim.x;
-	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-		uint64_t s = (uint64_t)src[i], d = (uint64_t)dst[i];
-		if (s >= V || d >= V) {
-			atomicOr(err, 1u);
-			continue;
-		}
-		atomicAdd(&deg[s], 1u);
+// ---- K1+K2 ----------------------------------------------------------------------------------
+// Offsets from the SORTED key array (no atomics, no hot hub counters): position p starts the range
+// of key[p] when key[p-1] differs; the vertices in between are empty and start at p too.
+//   off[s] = first position whose key >= s,  off[nv .. nv+tail) = n.
+template <typename OutT>
+__global__ void __launch_bounds__(256) offsets_from_sorted_kernel(const uint32_t *__restrict__ key, uint32_t n,
+                                                                  uint32_t nv, uint32_t tail,
+                                                                  OutT *__restrict__ off) {
+	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p > n) return;
+	if (p == n) { // one extra thread closes the array
+		const uint32_t first = n ? key[n - 1] + 1 : 0;
+		for (uint32_t s = first; s < nv + tail; s++) off[s] = (OutT)n;
+		return;
 	}
-}
-
-__global__ void __launch_bounds__(256) hist_u32_kernel(const uint32_t *__restrict__ key, uint32_t n,
-                                                       uint32_t *__restrict__ deg) {
-	uint32_t stride = gridDim.x * blockDim.x;
-	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) atomicAdd(&deg[key[i]], 1u);
+	const uint32_t k = key[p];
+	const uint32_t first = p ? key[p - 1] + 1 : 0; // keys (first .. k] start here (empty when k == key[p-1])
+	if (p && key[p - 1] == k) return;
+	for (uint32_t s = first; s <= k && s < nv; s++) off[s] = (OutT)p;
 }
 
 // create_csr_vertex counts (host-provided, uploaded) must equal the histogram.
 __global__ void __launch_bounds__(256) check_cnt_kernel(const int64_t *__restrict__ cnt,
-                                                        const uint32_t *__restrict__ deg, uint32_t V,
+                                                        const int64_t *__restrict__ off, uint32_t V,
                                                         uint32_t *__restrict__ err) {
 	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i < V && cnt[i] != (int64_t)deg[i]) atomicOr(err, 2u);
+	if (i < V && cnt[i] != off[i + 1] - off[i]) atomicOr(err, 2u);
 }
 
 // eid_csr[p] = eid_in[row[p]]
@@ -45,20 +43,6 @@ __global__ void __launch_bounds__(256) gather_eid_kernel(const int64_t *__restri
                                                          int64_t *__restrict__ out) {
 	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i < n) out[i] = eid_in[row[i]];
-}
-
-// src_of[p] = vertex whose forward range contains slot p  (upper_bound(off, p) - 1)
-__global__ void __launch_bounds__(256) expand_src_kernel(const int64_t *__restrict__ off, uint32_t V, uint32_t n,
-                                                         uint32_t *__restrict__ out) {
-	uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-	if (p >= n) return;
-	uint32_t lo = 0, hi = V; // find first index in [0,V] with off[idx] > p
-	while (lo < hi) {
-		uint32_t mid = lo + ((hi - lo) >> 1);
-		if (off[mid] > (int64_t)p) hi = mid;
-		else lo = mid + 1;
-	}
-	out[p] = lo - 1;
 }
 
 static int key_bits_for(int64_t V) {
@@ -80,33 +64,14 @@ int csr_device_build(Ctx *c, Csr *g) {
 	PGQ_TRY(g->d_tgt.reserve((size_t)(E > 0 ? E : 1) * sizeof(uint32_t)));
 	if (g->keep_rows) PGQ_TRY(g->d_row.reserve((size_t)(E > 0 ? E : 1) * sizeof(uint32_t)));
 	if (g->have_eid && E > 0) PGQ_TRY(g->d_eid.reserve((size_t)E * sizeof(int64_t)));
-	// deg[V+2] (two trailing zeros so the exclusive scan yields v[V] = v[V+1] = E)
-	TmpBuf deg;
-	PGQ_TRY(deg.reserve((size_t)(V + 2) * sizeof(uint32_t) + 16));
-	uint32_t *d_deg = deg.as<uint32_t>();
-	uint32_t *d_err = d_deg + (V + 2);
+	TmpBuf errbuf;
+	PGQ_TRY(errbuf.reserve(16));
+	uint32_t *d_err = errbuf.as<uint32_t>();
+	PGQ_TRY(g->d_fsrc.reserve((size_t)(E > 0 ? E : 1) * sizeof(uint32_t)));
 	PGQ_CUDA(cudaEventRecord(c->ev_a, st));
-	PGQ_CUDA(cudaMemsetAsync(d_deg, 0, (size_t)(V + 2) * sizeof(uint32_t) + 16, st));
+	PGQ_CUDA(cudaMemsetAsync(d_err, 0, 16, st));
 	const int64_t *s64 = g->d_src64.as<int64_t>(), *d64 = g->d_dst64.as<int64_t>();
-	if (E > 0) {
-		uint32_t grid = div_up(E, 256);
-		uint32_t cap = (uint32_t)c->sm_count * 32;
-		if (grid > cap) grid = cap;
-		degree_hist_kernel<<<grid, 256, 0, st>>>(s64, d64, (uint32_t)E, (uint64_t)V, d_deg, d_err);
-		count_launch(c);
-	}
-	TmpBuf d_cnt;
-	if (g->have_cnt && V > 0) {
-		PGQ_TRY(d_cnt.reserve((size_t)V * sizeof(int64_t)));
-		PGQ_CUDA(cudaMemcpyAsync(d_cnt.p, g->cnt_host.data(), (size_t)V * sizeof(int64_t),
-		                         cudaMemcpyHostToDevice, st));
-		c->stats.h2d_bytes += (uint64_t)V * sizeof(int64_t);
-		check_cnt_kernel<<<div_up(V, 256), 256, 0, st>>>(d_cnt.as<int64_t>(), d_deg, (uint32_t)V, d_err);
-		count_launch(c);
-	}
-	// K2
-	PGQ_TRY(exclusive_scan_u32_to_i64(c, d_deg, g->d_off.as<int64_t>(), (uint64_t)(V + 2)));
-	// K3
+	// K3 first: stable sort by src; its sorted keys give K1+K2 (offsets) without a histogram
 	if (E > 0) {
 		SortIO io;
 		io.k64 = s64;
@@ -115,7 +80,25 @@ int csr_device_build(Ctx *c, Csr *g) {
 		io.key_bits = key_bits_for(V);
 		io.out_p0 = g->d_tgt.as<uint32_t>();
 		io.out_p1 = g->keep_rows ? g->d_row.as<uint32_t>() : nullptr;
+		io.out_keys = g->d_fsrc.as<uint32_t>();
+		io.vmax = (uint64_t)V;
+		io.err = d_err;
 		PGQ_TRY(radix_sort_stable(c, io));
+	}
+	offsets_from_sorted_kernel<int64_t><<<div_up((uint64_t)E + 1, 256), 256, 0, st>>>(
+	    g->d_fsrc.as<uint32_t>(), (uint32_t)E, (uint32_t)V, 2u, g->d_off.as<int64_t>());
+	count_launch(c);
+	TmpBuf d_cnt;
+	if (g->have_cnt && V > 0) {
+		PGQ_TRY(d_cnt.reserve((size_t)V * sizeof(int64_t)));
+		PGQ_CUDA(cudaMemcpyAsync(d_cnt.p, g->cnt_host.data(), (size_t)V * sizeof(int64_t),
+		                         cudaMemcpyHostToDevice, st));
+		c->stats.h2d_bytes += (uint64_t)V * sizeof(int64_t);
+		check_cnt_kernel<<<div_up(V, 256), 256, 0, st>>>(d_cnt.as<int64_t>(), g->d_off.as<int64_t>(), (uint32_t)V,
+		                                                 d_err);
+		count_launch(c);
+	}
+	if (E > 0) {
 		if (g->have_eid) {
 			gather_eid_kernel<<<div_up(E, 256), 256, 0, st>>>(g->d_eid64.as<int64_t>(), g->d_row.as<uint32_t>(),
 			                                                  (uint32_t)E, g->d_eid.as<int64_t>());
@@ -129,7 +112,6 @@ int csr_device_build(Ctx *c, Csr *g) {
 	float ms = 0;
 	PGQ_CUDA(cudaEventElapsedTime(&ms, c->ev_a, c->ev_b));
 	c->stats.csr_build_ms = ms;
-	deg.release();
 	d_cnt.release();
 	if (h_err & 1u) {
 		set_error("create_csr_edge: src/dst id outside [0, v_size)");
@@ -215,37 +197,27 @@ int csr_prepare(Ctx *c, Csr *g) {
 	if (!need_bins) return PGQ_OK;
 	PGQ_CUDA(cudaEventRecord(c->ev_a, st));
 	if (need_rev) {
-		TmpBuf ideg, srcof;
-		PGQ_TRY(ideg.reserve((size_t)(V + 1) * sizeof(uint32_t)));
-		PGQ_CUDA(cudaMemsetAsync(ideg.p, 0, (size_t)(V + 1) * sizeof(uint32_t), st));
+		const uint32_t *tkeys = nullptr; // sorted targets, left in the sort's scratch
 		PGQ_TRY(g->d_ioff.reserve((size_t)(V + 1) * sizeof(uint32_t)));
 		PGQ_TRY(g->d_isrc.reserve((size_t)(E > 0 ? E : 1) * sizeof(uint32_t)));
 		PGQ_TRY(g->d_ipos.reserve((size_t)(E > 0 ? E : 1) * sizeof(uint32_t)));
 		if (E > 0) {
-			uint32_t grid = div_up(E, 256);
-			uint32_t cap = (uint32_t)c->sm_count * 32;
-			hist_u32_kernel<<<grid > cap ? cap : grid, 256, 0, st>>>(g->d_tgt.as<uint32_t>(), (uint32_t)E,
-			                                                         ideg.as<uint32_t>());
-			count_launch(c);
-		}
-		PGQ_TRY(exclusive_scan_u32(c, ideg.as<uint32_t>(), g->d_ioff.as<uint32_t>(), (uint64_t)(V + 1), nullptr));
-		if (E > 0) {
-			PGQ_TRY(srcof.reserve((size_t)E * sizeof(uint32_t)));
-			expand_src_kernel<<<div_up(E, 256), 256, 0, st>>>(g->d_off.as<int64_t>(), (uint32_t)V, (uint32_t)E,
-			                                                  srcof.as<uint32_t>());
-			count_launch(c);
+			// key = target, payload = source of each forward slot (= the forward build's sorted keys)
 			SortIO io;
 			io.k32 = g->d_tgt.as<uint32_t>();
-			io.p32 = srcof.as<uint32_t>();
+			io.p32 = g->d_fsrc.as<uint32_t>();
 			io.n = (uint32_t)E;
 			io.key_bits = key_bits_for(V);
 			io.out_p0 = g->d_isrc.as<uint32_t>();
 			io.out_p1 = g->d_ipos.as<uint32_t>();
+			io.keys_scratch = &tkeys;
 			PGQ_TRY(radix_sort_stable(c, io));
 		}
+		offsets_from_sorted_kernel<uint32_t><<<div_up((uint64_t)E + 1, 256), 256, 0, st>>>(
+		    tkeys, (uint32_t)E, (uint32_t)V, 1u, g->d_ioff.as<uint32_t>());
+		count_launch(c);
 		PGQ_CUDA(cudaStreamSynchronize(st));
-		ideg.release();
-		srcof.release();
+		g->d_fsrc.release(); // only needed to seed the reverse build
 		g->prepared = true;
 	}
 	// in-degree classes
@@ -295,7 +267,7 @@ void Csr::free_all() {
 	if (h_eid) cudaFreeHost(h_eid);
 	h_src = h_dst = h_eid = nullptr;
 	d_src64.release(); d_dst64.release(); d_eid64.release();
-	d_off.release(); d_tgt.release(); d_row.release(); d_eid.release();
+	d_off.release(); d_tgt.release(); d_row.release(); d_eid.release(); d_fsrc.release();
 	d_ioff.release(); d_isrc.release(); d_ipos.release();
 	d_tiny.release(); d_small.release(); d_mid.release(); d_hub.release(); d_hubchunks.release();
 }

@@ -11,7 +11,7 @@ namespace {
 struct BatchBufs {
 	uint32_t *seen, *visit[2], *parent, *hubacc;
 	uint2 *queue[2];
-	uint32_t *fbit[2]; // frontier bitmap of visit[i] (1 bit per vertex, padded)
+	uint32_t *fbit[3]; // rotating frontier bitmaps (1 bit per vertex, padded): current / next / two levels ago
 	size_t fbit_bytes;
 	uint32_t fbit_words;
 	uint32_t *alive_slots; // [ALIVE_SLOTS][16], all-zero between levels
@@ -35,17 +35,18 @@ void launch_class(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool 
 
 // One bottom-up level: frontier visit[cur]/fbit[cur] -> next visit[cur^1]/fbit[cur^1].
 template <int W>
-int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents, int iter, bool filter) {
+int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, bool parents, int iter, bool filter) {
 	using C = LaneCfg<W>;
 	cudaStream_t st = c->stream;
+	// fb[0] describes visit[cur], fb[1] is built for visit[cur^1], fb[2] describes what visit[cur^1]
+	// still holds (the frontier of two levels ago).
 	// fnext is built with atomicOr: start from zero.  At level 2 `next` still holds the source words
 	// (level-0 frontier), some at in-degree-0 vertices that no class rewrites: clear them by bitmap.
+	PGQ_CUDA(cudaMemsetAsync(b.fbit[fb[1]], 0, b.fbit_bytes, st));
 	if (iter == 2) {
-		clear_by_bitmap_kernel<W><<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[cur ^ 1], b.fbit_words,
+		clear_by_bitmap_kernel<W><<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[fb[2]], b.fbit_words,
 		                                                                    b.visit[cur ^ 1]);
 		count_launch(c);
-	} else {
-		PGQ_CUDA(cudaMemsetAsync(b.fbit[cur ^ 1], 0, b.fbit_bytes, st));
 	}
 	PullArgs a{};
 	a.ioff = g->d_ioff.as<uint32_t>();
@@ -58,8 +59,8 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents, int 
 	a.V = (uint32_t)g->V;
 	a.hubacc = b.hubacc;
 	a.off = g->d_off.as<int64_t>();
-	a.fcur = b.fbit[cur];
-	a.fnext = b.fbit[cur ^ 1];
+	a.fcur = b.fbit[fb[0]];
+	a.fnext = b.fbit[fb[1]];
 	a.alive_slots = b.alive_slots;
 	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, parents, filter);
 	launch_class<W, 2>(c, a, g->d_small, g->n_small, parents, filter);
@@ -87,18 +88,19 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, bool parents, int 
 			count_launch(c, 2);
 		}
 	}
-	frontier_stats_kernel<<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[cur ^ 1], b.fbit_words, (uint32_t)g->V,
+	frontier_stats_kernel<<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[fb[1]], b.fbit_words, (uint32_t)g->V,
 	                                                               g->d_off.as<int64_t>(), b.ctrl);
 	count_launch(c);
 	return PGQ_OK;
 }
 
-int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, bool parents, int iter, bool filter) {
+int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, const int *fb, bool parents, int iter,
+                   bool filter) {
 	switch (W) {
-	case 64: return launch_level<64>(c, g, b, cur, parents, iter, filter);
-	case 128: return launch_level<128>(c, g, b, cur, parents, iter, filter);
-	case 256: return launch_level<256>(c, g, b, cur, parents, iter, filter);
-	case 512: return launch_level<512>(c, g, b, cur, parents, iter, filter);
+	case 64: return launch_level<64>(c, g, b, cur, fb, parents, iter, filter);
+	case 128: return launch_level<128>(c, g, b, cur, fb, parents, iter, filter);
+	case 256: return launch_level<256>(c, g, b, cur, fb, parents, iter, filter);
+	case 512: return launch_level<512>(c, g, b, cur, fb, parents, iter, filter);
 	}
 	set_error("unsupported lane width %d", W);
 	return PGQ_ERR_INVALID;
@@ -106,7 +108,7 @@ int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, bool pare
 
 // One top-down level over queue[q] (frontier in visit[cur]); builds queue[q^1] and fbit[cur^1].
 template <int W>
-int launch_push(Ctx *c, Csr *g, const BatchBufs &b, int cur, int q) {
+int launch_push(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, int q) {
 	PushArgs a{};
 	a.off = g->d_off.as<int64_t>();
 	a.tgt = g->d_tgt.as<uint32_t>();
@@ -116,9 +118,10 @@ int launch_push(Ctx *c, Csr *g, const BatchBufs &b, int cur, int q) {
 	a.ctrl = b.ctrl;
 	a.queue = b.queue[q];
 	a.queue_next = b.queue[q ^ 1];
-	a.fnext = b.fbit[cur ^ 1];
-	// next/fnext still describe the frontier of two levels ago: zero exactly those words
-	clear_by_bitmap_kernel<W><<<div_up(b.fbit_words, 256), 256, 0, c->stream>>>(b.fbit[cur ^ 1], b.fbit_words,
+	a.fnext = b.fbit[fb[1]];
+	// `next` still holds the frontier of two levels ago, described by fb[2]: zero exactly those words
+	PGQ_CUDA(cudaMemsetAsync(b.fbit[fb[1]], 0, b.fbit_bytes, c->stream));
+	clear_by_bitmap_kernel<W><<<div_up(b.fbit_words, 256), 256, 0, c->stream>>>(b.fbit[fb[2]], b.fbit_words,
 	                                                                           b.visit[cur ^ 1]);
 	const uint32_t grid = (uint32_t)c->sm_count * 8;
 	a.alive_slots = b.alive_slots;
@@ -127,20 +130,34 @@ int launch_push(Ctx *c, Csr *g, const BatchBufs &b, int cur, int q) {
 	return PGQ_OK;
 }
 
-int launch_push_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, int q) {
+int launch_push_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, const int *fb, int q) {
 	switch (W) {
-	case 64: return launch_push<64>(c, g, b, cur, q);
-	case 128: return launch_push<128>(c, g, b, cur, q);
-	case 256: return launch_push<256>(c, g, b, cur, q);
-	case 512: return launch_push<512>(c, g, b, cur, q);
+	case 64: return launch_push<64>(c, g, b, cur, fb, q);
+	case 128: return launch_push<128>(c, g, b, cur, fb, q);
+	case 256: return launch_push<256>(c, g, b, cur, fb, q);
+	case 512: return launch_push<512>(c, g, b, cur, fb, q);
 	}
 	return PGQ_ERR_INVALID;
 }
 
+// zero the words of visit[which] named by bitmap fbit[bi] (and the bitmap)
+int launch_clear_w(Ctx *c, const BatchBufs &b, int W, int bi, int which) {
+	const uint32_t grid = div_up(b.fbit_words, 256);
+	switch (W) {
+	case 64: clear_by_bitmap_kernel<64><<<grid, 256, 0, c->stream>>>(b.fbit[bi], b.fbit_words, b.visit[which]); break;
+	case 128: clear_by_bitmap_kernel<128><<<grid, 256, 0, c->stream>>>(b.fbit[bi], b.fbit_words, b.visit[which]); break;
+	case 256: clear_by_bitmap_kernel<256><<<grid, 256, 0, c->stream>>>(b.fbit[bi], b.fbit_words, b.visit[which]); break;
+	case 512: clear_by_bitmap_kernel<512><<<grid, 256, 0, c->stream>>>(b.fbit[bi], b.fbit_words, b.visit[which]); break;
+	default: return PGQ_ERR_INVALID;
+	}
+	count_launch(c);
+	return PGQ_OK;
+}
+
 // pull -> push transition: queue[q] from the frontier bitmap fbit[cur].
-int launch_compact(Ctx *c, Csr *g, const BatchBufs &b, int cur, int q) {
+int launch_compact(Ctx *c, Csr *g, const BatchBufs &b, const int *fb, int q) {
 	cudaStream_t st = c->stream;
-	compact_bitmap_kernel<<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[cur], b.fbit_words, (uint32_t)g->V,
+	compact_bitmap_kernel<<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[fb[0]], b.fbit_words, (uint32_t)g->V,
 	                                                                 g->d_off.as<int64_t>(), b.queue[q], b.ctrl);
 	bfs_snapshot_items_kernel<<<1, 1, 0, st>>>(b.ctrl);
 	count_launch(c, 2);
@@ -195,10 +212,11 @@ int alloc_bufs(Ctx *c, Csr *g, int W, bool parents, BatchBufs *b) {
 	b->fbit_bytes = (size_t)b->fbit_words * sizeof(uint32_t);
 	for (int i = 0; i < 2; i++) {
 		PGQ_TRY(c->bfs_queue[i].reserve(qcap * sizeof(uint2)));
-		PGQ_TRY(c->bfs_inq[i].reserve(b->fbit_bytes));
 		b->queue[i] = c->bfs_queue[i].as<uint2>();
-		b->fbit[i] = c->bfs_inq[i].as<uint32_t>();
 	}
+	// three frontier bitmaps in one allocation
+	PGQ_TRY(c->bfs_inq[0].reserve(3 * b->fbit_bytes));
+	for (int i = 0; i < 3; i++) b->fbit[i] = c->bfs_inq[0].as<uint32_t>() + (size_t)i * b->fbit_words;
 	return PGQ_OK;
 }
 
@@ -209,11 +227,20 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 	const size_t bm = (size_t)g->V * (W / 8);
 	if (bm) {
 		PGQ_CUDA(cudaMemsetAsync(b.seen, 0, bm, st));
-		PGQ_CUDA(cudaMemsetAsync(b.visit[0], 0, bm, st));
-		PGQ_CUDA(cudaMemsetAsync(b.visit[1], 0, bm, st)); // a top-down level 1 ORs into it
+		// The frontier buffers must start all-zero (a top-down level ORs into them).  After a clean
+		// batch on the same buffers their only non-zero words are the ones the last two frontier
+		// bitmaps name: scrub those instead of streaming 2 x V x W/8 bytes of zeros.
+		BfsDirty &d = c->bfs_dirty;
+		if (d.valid && d.W == W && d.V == g->V && d.visit0 == b.visit[0] && d.fbit0 == b.fbit[0]) {
+			PGQ_TRY(launch_clear_w(c, b, W, d.map[0], 0));
+			PGQ_TRY(launch_clear_w(c, b, W, d.map[1], 1));
+		} else {
+			PGQ_CUDA(cudaMemsetAsync(b.visit[0], 0, bm, st));
+			PGQ_CUDA(cudaMemsetAsync(b.visit[1], 0, bm, st));
+		}
+		d.valid = false; // until this batch completes
 	}
-	PGQ_CUDA(cudaMemsetAsync(b.fbit[0], 0, b.fbit_bytes, st));
-	PGQ_CUDA(cudaMemsetAsync(b.fbit[1], 0, b.fbit_bytes, st));
+	PGQ_CUDA(cudaMemsetAsync(b.fbit[0], 0, 3 * b.fbit_bytes, st)); // all three frontier bitmaps
 	bfs_init_kernel<<<1, W, 0, st>>>(d_lane_src, W, b.visit[0], d_found, b.ctrl, g->d_off.as<int64_t>(), b.queue[0],
 	                                 b.fbit[0]);
 	count_launch(c);
@@ -222,6 +249,7 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 	c->stats.batches++;
 	uint32_t active = h.n_active;
 	int cur = 0, q = 0;
+	int fb[3] = {0, 1, 2}; // bitmap of visit[cur] / being built for visit[cur^1] / of what visit[cur^1] holds
 	bool have_queue = true; // queue[q] describes visit[cur] and visit[cur^1] is all-zero
 	for (int iter = 1; active; iter++) {
 		// direction switch on frontier density: top-down while the frontier's out-edges are few
@@ -234,8 +262,8 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
 		uint64_t before = c->stats.kernel_launches;
 		if (push) {
-			if (!have_queue) PGQ_TRY(launch_compact(c, g, b, cur, q));
-			PGQ_TRY(launch_push_w(c, g, b, W, cur, q));
+			if (!have_queue) PGQ_TRY(launch_compact(c, g, b, fb, q));
+			PGQ_TRY(launch_push_w(c, g, b, W, cur, fb, q));
 			have_queue = true;
 			q ^= 1;
 			c->stats.push_levels++;
@@ -243,7 +271,7 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 			// the bitmap test is dead weight once the frontier holds most of the edges
 			const bool filter = (unsigned long long)h.out_edges * (unsigned long long)c->opt.filter_gamma <=
 			                    (unsigned long long)g->E;
-			PGQ_TRY(launch_level_w(c, g, b, W, cur, parents, iter, filter));
+			PGQ_TRY(launch_level_w(c, g, b, W, cur, fb, parents, iter, filter));
 			have_queue = false;
 		}
 		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
@@ -261,9 +289,26 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 				        iter, push ? "push" : "pull", ms, h.out_verts, (unsigned long long)h.out_edges, h.out_items,
 				        h.n_active, h.change_out);
 		}
+		// the level's output becomes the current frontier
+		cur ^= 1;
+		{
+			const int t = fb[0];
+			fb[0] = fb[1];
+			fb[1] = fb[2];
+			fb[2] = t;
+		}
 		if (!h.change_out) break;
 		active = h.n_active;
-		cur ^= 1;
+	}
+	if (bm) { // what the frontier buffers hold now, for the next batch's scrub
+		BfsDirty &d = c->bfs_dirty;
+		d.valid = true;
+		d.W = W;
+		d.V = g->V;
+		d.visit0 = b.visit[0];
+		d.fbit0 = b.fbit[0];
+		d.map[cur] = fb[0];
+		d.map[cur ^ 1] = fb[2];
 	}
 	if (c->opt.stats) {
 		// counters accumulate in the control block over the batch (reset by the init kernel)

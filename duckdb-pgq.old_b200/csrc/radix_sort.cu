@@ -32,11 +32,17 @@ struct RsArgs {
 	uint32_t n;
 	uint32_t ntiles;
 	int shift;
+	uint64_t vmax;        // FIRST64 only: ids must be < vmax
+	uint32_t *err;
 };
 
 template <bool FIRST64>
 __device__ __forceinline__ uint32_t rs_load_key(const RsArgs &a, uint32_t i) {
-	if (FIRST64) return (uint32_t)a.k64[i];
+	if (FIRST64) {
+		const uint64_t k = (uint64_t)a.k64[i];
+		if (a.err && k >= a.vmax) atomicOr(a.err, 1u); // the reference would write out of bounds here
+		return (uint32_t)k;
+	}
 	return a.kin[i];
 }
 
@@ -110,7 +116,13 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(RsArgs a) {
 			uint32_t d = (keys[r] >> a.shift) & 0xFFu;
 			uint32_t pos = tot[d] + cnt[warp][d] + rank[r];
 			if (a.kout) a.kout[pos] = keys[r];
-			a.p0out[pos] = FIRST64 ? (uint32_t)a.p64[i] : a.p0in[i];
+			if (FIRST64) {
+				const uint64_t pv = (uint64_t)a.p64[i];
+				if (a.err && pv >= a.vmax) atomicOr(a.err, 1u);
+				a.p0out[pos] = (uint32_t)pv;
+			} else {
+				a.p0out[pos] = a.p0in[i];
+			}
 			if (a.p1out) a.p1out[pos] = a.p1in ? a.p1in[i] : i;
 		}
 	}
@@ -123,6 +135,7 @@ int radix_sort_stable(Ctx *c, const SortIO &io) {
 	const uint32_t ntiles = div_up(io.n, RS_TILE);
 	const bool want_p1 = io.out_p1 != nullptr;
 	const size_t bytes = (size_t)io.n * sizeof(uint32_t);
+	if (io.keys_scratch) PGQ_TRY(c->sort_keys[(passes - 1) & 1].reserve(bytes));
 	if (passes > 1) {
 		for (int b = 0; b < (passes > 2 ? 2 : 1); b++) {
 			PGQ_TRY(c->sort_keys[b].reserve(bytes));
@@ -144,7 +157,11 @@ int radix_sort_stable(Ctx *c, const SortIO &io) {
 			a.p1in = want_p1 ? c->sort_p1[in].as<uint32_t>() : nullptr;
 		}
 		if (last) {
-			a.kout = nullptr; a.p0out = io.out_p0; a.p1out = io.out_p1;
+			a.kout = io.out_keys; a.p0out = io.out_p0; a.p1out = io.out_p1;
+			if (io.keys_scratch) { // the ping-pong buffer the last pass does not read is free
+				a.kout = c->sort_keys[p & 1].as<uint32_t>();
+				*io.keys_scratch = a.kout;
+			}
 		} else {
 			int out = p & 1;
 			a.kout = c->sort_keys[out].as<uint32_t>();
@@ -153,6 +170,7 @@ int radix_sort_stable(Ctx *c, const SortIO &io) {
 		}
 		a.hist = c->sort_hist.as<uint32_t>();
 		a.n = io.n; a.ntiles = ntiles; a.shift = 8 * p;
+		a.vmax = io.vmax; a.err = first64 ? io.err : nullptr;
 		if (first64) rs_hist_kernel<true><<<ntiles, RS_THREADS, 0, c->stream>>>(a);
 		else rs_hist_kernel<false><<<ntiles, RS_THREADS, 0, c->stream>>>(a);
 		count_launch(c);
