@@ -41,6 +41,7 @@ def parse():
     ap.add_argument("--csr-scale", type=int, default=22)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-csr", action="store_true")
+    ap.add_argument("--no-paths", action="store_true")
     ap.add_argument("--cpu-threads", type=int, default=0)
     return ap.parse_args()
 
@@ -223,6 +224,56 @@ def bench_csr(ctx, scale, ef, steps, warmup, peak_gbs):
                          "algo_bytes": algo, "kernels": "K1 hist + K2 scan + K3 radix passes (whole build)"}}
 
 
+def knows_params(V):
+    """Affine spread of the knows generator (same arithmetic as oracle/pgq_oracle_util.c:160-167)."""
+    import math
+    m = 2654435761 % V
+    if m < 2:
+        m = 1
+    while math.gcd(m, V) != 1:
+        m += 1
+    return m, 0x9E3779B9 % V
+
+
+def bench_paths(ctx, V, E, npairs, steps, warmup):
+    """BASELINE config 4: shortestpath with path reconstruction on an LDBC-SF100-shaped knows graph
+    (V persons, E directed knows rows = both directions), npairs (src,dst) pairs, host buffers in and
+    the LIST<BIGINT> child buffer out (the scalar function's own data flow)."""
+    import pgq_b200
+    mult, add = knows_params(V)
+    d_src, d_dst = ctx.dev_alloc(E * 8), ctx.dev_alloc(E * 8)
+    ctx.gen_knows_device(SEED_BASE + 100, V, E, mult, add, d_src, d_dst)
+    ctx.csr_build_device(200, V, E, d_src, d_dst, rowids=True)
+    ctx.dev_free(d_src)
+    ctx.dev_free(d_dst)
+    ctx.csr_prepare(200)
+    v_off = np.empty(V + 2, dtype=np.int64)
+    ctx._chk(ctx.lib.pgq_csr_download(ctx._ctx, 200, v_off.ctypes.data_as(pgq_b200.I64P), None, None))
+    src, dst = make_pairs(V, v_off, npairs, 4242)
+    out = {}
+    for name, fn in (("shortestpath", lambda: ctx.shortestpath(200, src, dst, mode=0)),
+                     ("iterativelength", lambda: ctx.iterativelength(200, src, dst))):
+        for _ in range(min(warmup, 2)):
+            res = fn()
+        ctx.reset_stats()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            res = fn()
+        secs = (time.perf_counter() - t0) / steps
+        st = ctx.stats()
+        out[name] = {"pairs_per_s": npairs / secs, "ms": secs * 1e3, "batches": int(st["batches"] // steps),
+                     "levels": int(st["levels"] // steps),
+                     "h2d_bytes_per_step": int(st["h2d_bytes"] // steps),
+                     "d2h_bytes_per_step": int(st["d2h_bytes"] // steps)}
+        if name == "shortestpath":
+            off, ln, valid, vals = res
+            out[name]["found"] = int(np.sum(valid))
+            out[name]["path_values"] = int(len(vals))
+    ctx.csr_delete(200)
+    return {"workload": "BASELINE configs[3]: LDBC-SF100-shaped knows graph V=%d E=%d, %d pairs, host buffers "
+                        "(e2e through the C ABI)" % (V, E, npairs), **out}
+
+
 def main_ours(a):
     import pgq_b200
     rank, world, local, dist = dist_setup(a.gpus)
@@ -298,6 +349,15 @@ def main_ours(a):
     value = total_edges / (ms_per_step * 1e-3) / 1e9
     e2e_value = total_edges / (e2e_ms / a.steps * 1e-3) / 1e9
     achieved = algo_bytes * a.steps / (level_ms * 1e-3) / 1e9 if level_ms > 0 else 0.0
+    # measured DRAM traffic of the level kernels (ncu pass committed under profiles/, per 512-lane batch)
+    traffic = dram_frac = traffic_src = None
+    try:
+        prof = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        traffic = float(prof["level_kernel_dram_bytes_per_batch"]) * float(batches)
+        dram_frac = traffic * a.steps / (level_ms * 1e-3) / 1e9 / peak_gbs if level_ms > 0 else None
+        traffic_src = "profiles/r01_traffic.json (%s)" % prof.get("command", "")
+    except Exception:
+        pass
     line = {
         "metric": "msbfs_gteps", "value": value, "unit": "GTEPS", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -313,8 +373,13 @@ def main_ours(a):
                 "d2h_bytes_per_step": int(st2["d2h_bytes"] // a.steps)},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
-                     "frac": achieved / peak_gbs, "traffic": None, "peak_source": peak_src,
-                     "kernel": "pull_* level kernels (small+warp+hub)", "launches": level_launches,
+                     "frac": achieved / peak_gbs, "traffic": traffic, "dram_frac": dram_frac,
+                     "traffic_source": traffic_src, "peak_source": peak_src,
+                     "kernel": "MS-BFS level step = pull_list/pull_warp/pull_hub (+push, bitmap) kernels",
+                     "note": "achieved = the REFERENCE algorithm's bytes per level (SURVEY.md 8(d)) / time; the "
+                             "frontier filter, early exit and L2 hits move fewer DRAM bytes (traffic, dram_frac), "
+                             "so frac can exceed 1",
+                     "launches": level_launches,
                      "algo_bytes_per_step": int(algo_bytes), "level_kernel_ms_per_step": level_ms / a.steps,
                      "share_of_step": level_ms / ms_total if ms_total else None},
         "setup": {"csr_build_ms": build_ms, "reverse_csr_ms": transpose_ms},
@@ -322,6 +387,8 @@ def main_ours(a):
     }
     if rank == 0 and world == 1 and not a.no_csr:
         line["csr_build"] = bench_csr(ctx, a.csr_scale, ef, a.steps, a.warmup, peak_gbs)
+    if rank == 0 and world == 1 and not a.no_paths:
+        line["paths"] = bench_paths(ctx, 450000, 40000000, 16384, max(1, a.steps // 2), a.warmup)
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         e_h = np.empty(E, dtype=np.int64)
         ctx._chk(ctx.lib.pgq_csr_download(ctx._ctx, 0, None, e_h.ctypes.data_as(pgq_b200.I64P), None))
