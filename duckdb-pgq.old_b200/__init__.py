@@ -32,7 +32,8 @@ class Stats(C.Structure):
                 ("edges_lane", C.c_uint64), ("edges_unique", C.c_uint64), ("algo_bytes", C.c_uint64),
                 ("level_kernel_ms", C.c_double), ("level_kernel_launches", C.c_uint64),
                 ("csr_build_ms", C.c_double), ("transpose_ms", C.c_double),
-                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("coll_bytes", C.c_uint64), ("coll_ms", C.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -245,6 +246,50 @@ class Context:
         ent = np.frombuffer(entries, dtype=np.uint64).reshape(-1, 2)[:n]
         return ent[:, 0].copy(), ent[:, 1].copy(), ov, values
 
+    # ---- 1-D vertex partition (collective; include/pgq_b200.h) ----
+    def part_init(self, rank, world, unique_id=None):
+        self._chk(self.lib.pgq_part_init(self._ctx, C.c_int(rank), C.c_int(world),
+                                         C.c_char_p(unique_id) if unique_id is not None else None))
+
+    def part_range(self, v_size):
+        base, cnt = C.c_int64(0), C.c_int64(0)
+        self._chk(self.lib.pgq_part_range(self._ctx, C.c_int64(v_size), C.byref(base), C.byref(cnt)))
+        return int(base.value), int(cnt.value)
+
+    def part_csr_create(self, csr_id, v_size):
+        self._chk(self.lib.pgq_part_csr_create(self._ctx, C.c_int32(csr_id), C.c_int64(v_size)))
+
+    def part_csr_add_edges_device(self, csr_id, d_src, d_dst, n):
+        self._chk(self.lib.pgq_part_csr_add_edges_device(self._ctx, C.c_int32(csr_id), C.c_void_p(d_src),
+                                                         C.c_void_p(d_dst), C.c_int64(n)))
+
+    def part_csr_finalize(self, csr_id):
+        self._chk(self.lib.pgq_part_csr_finalize(self._ctx, C.c_int32(csr_id)))
+
+    def part_iterativelength(self, csr_id, src, dst, src_valid=None, dst_valid=None):
+        src, ps = _i64(src)
+        dst, pd = _i64(dst)
+        n = src.shape[0]
+        sv, psv = _u8(src_valid, n)
+        dv, pdv = _u8(dst_valid, n)
+        out = np.empty(n, dtype=np.int64)
+        ov = np.zeros(n, dtype=np.uint8)
+        self._chk(self.lib.pgq_part_iterativelength(self._ctx, C.c_int32(csr_id), C.c_int64(n), ps, pd, psv, pdv,
+                                                    out.ctypes.data_as(I64P), ov.ctypes.data_as(U8P)))
+        return out, ov
+
+    def part_reachability(self, csr_id, src, dst, src_valid=None, dst_valid=None):
+        src, ps = _i64(src)
+        dst, pd = _i64(dst)
+        n = src.shape[0]
+        sv, psv = _u8(src_valid, n)
+        dv, pdv = _u8(dst_valid, n)
+        out = np.zeros(n, dtype=np.uint8)
+        ov = np.zeros(n, dtype=np.uint8)
+        self._chk(self.lib.pgq_part_reachability(self._ctx, C.c_int32(csr_id), C.c_int64(n), ps, pd, psv, pdv,
+                                                 out.ctypes.data_as(U8P), ov.ctypes.data_as(U8P)))
+        return out, ov
+
     def iterativelength_device(self, csr_id, n, d_src, d_dst, d_out, d_out_valid):
         self._chk(self.lib.pgq_iterativelength_device(self._ctx, C.c_int32(csr_id), C.c_int64(n),
                                                       C.c_void_p(d_src), C.c_void_p(d_dst), C.c_void_p(d_out),
@@ -351,3 +396,55 @@ def sharded_query(fn, dist, n, world, rank, src, dst, lanes=512):
         full_out[a:b] = p[:b - a, 0]
         full_valid[a:b] = p[:b - a, 1]
     return full_out, full_valid
+
+
+def nccl_unique_id():
+    """128-byte NCCL unique id (rank 0 creates it; broadcast it to the other ranks)."""
+    buf = C.create_string_buffer(128)
+    lib = load_library()
+    rc = lib.pgq_nccl_unique_id(buf)
+    if rc != 0:
+        raise PgqError(rc, lib.pgq_last_error().decode())
+    return buf.raw
+
+
+def _part_kbits(v_size):
+    nblk = (v_size + 31) // 32
+    k = 0
+    while (1 << k) < nblk:
+        k += 1
+    return k
+
+
+def _part_mix(blk, k):
+    """Bijection on k-bit block indices (host mirror of part_mix, csrc/common.cuh)."""
+    blk = np.asarray(blk, dtype=np.uint64)
+    if k < 2:
+        return blk
+    mask = np.uint64((1 << k) - 1)
+    h = np.uint64((k + 1) // 2)
+    with np.errstate(over="ignore"):
+        x = blk ^ (blk >> h)
+        x = (x * np.uint64(0x9E3779B97F4A7C15)) & mask
+        x ^= x >> h
+        x = (x * np.uint64(0xC2B2AE3D27D4EB4F)) & mask
+        x ^= x >> h
+    return x
+
+
+def part_owner(v, v_size, world):
+    """Owner rank of vertex v in the 1-D partition (scrambled 32-vertex blocks dealt round-robin)."""
+    v = np.asarray(v, dtype=np.uint64)
+    return (_part_mix(v >> np.uint64(5), _part_kbits(v_size)) % np.uint64(world)).astype(np.int64)
+
+
+def part_local(v, v_size, world):
+    v = np.asarray(v, dtype=np.uint64)
+    m = _part_mix(v >> np.uint64(5), _part_kbits(v_size))
+    return (((m // np.uint64(world)) << np.uint64(5)) | (v & np.uint64(31))).astype(np.int64)
+
+
+def part_slice(v_size, world):
+    """Vertices per rank in the replicated structures (multiple of 256)."""
+    lblk = ((1 << _part_kbits(v_size)) + world - 1) // world
+    return (lblk * 32 + 255) // 256 * 256

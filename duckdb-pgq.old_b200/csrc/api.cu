@@ -5,6 +5,7 @@
 #include <string.h>
 
 #include "common.cuh"
+#include "nccl_dl.cuh"
 
 namespace pgq {
 
@@ -142,6 +143,7 @@ int pgq_init(int device, pgq_ctx_t **out_ctx) {
 	PGQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
 	PGQ_CUDA(cudaEventCreate(&c->ev_a));
 	PGQ_CUDA(cudaEventCreate(&c->ev_b));
+	PGQ_CUDA(cudaEventCreate(&c->ev_c));
 	PGQ_CUDA(cudaEventCreate(&c->ev_timer));
 	PGQ_CUDA(cudaEventCreate(&c->ev_timer2));
 	PGQ_CUDA(cudaHostAlloc(&c->h_ctrl, 4096, cudaHostAllocDefault));
@@ -159,14 +161,20 @@ int pgq_shutdown(pgq_ctx_t *ctx) {
 		delete kv.second;
 	}
 	c->csrs.clear();
+	if (c->nccl_comm) {
+		const NcclApi *nc = nccl_api();
+		if (nc) nc->CommDestroy((ncclComm_t)c->nccl_comm);
+		c->nccl_comm = nullptr;
+	}
 	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
 	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->bfs_seen, &c->bfs_visit[0],
 	                  &c->bfs_visit[1], &c->bfs_parent, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
-	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->l2_flush};
+	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->l2_flush};
 	for (DevBuf *b : bufs) b->release();
 	if (c->h_ctrl) cudaFreeHost(c->h_ctrl);
 	cudaEventDestroy(c->ev_a);
 	cudaEventDestroy(c->ev_b);
+	cudaEventDestroy(c->ev_c);
 	cudaEventDestroy(c->ev_timer);
 	cudaEventDestroy(c->ev_timer2);
 	cudaStreamDestroy(c->stream);
@@ -411,6 +419,10 @@ int pgq_csr_download(pgq_ctx_t *ctx, int32_t id, int64_t *v, int64_t *e, int64_t
 		set_error("csr %d not finalized", id);
 		return PGQ_ERR_STATE;
 	}
+	if (g->is_part) {
+		set_error("csr %d is vertex-partitioned: only pgq_part_iterativelength / pgq_part_reachability apply", id);
+		return PGQ_ERR_STATE;
+	}
 	cudaStream_t st = c->stream;
 	if (v) {
 		PGQ_CUDA(cudaMemcpyAsync(v, g->d_off.p, (size_t)(g->V + 2) * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
@@ -485,7 +497,8 @@ static int build_lane_table(Ctx *c, Csr *g, int64_t n, const int64_t *src, const
 	int64_t need = 0;
 	for (int64_t i = 0; i < n; i++) {
 		if ((sv && !sv[i]) || (dv && !dv[i])) continue;
-		if (src[i] < 0 || src[i] >= g->V || dst[i] < 0 || dst[i] >= g->V) {
+		const int64_t vmax = g->is_part ? g->gV : g->V;
+		if (src[i] < 0 || src[i] >= vmax || dst[i] < 0 || dst[i] >= vmax) {
 			set_error("vertex id outside [0, v_size) in row %lld", (long long)i);
 			return PGQ_ERR_INVALID;
 		}
@@ -533,7 +546,17 @@ static int query_lengths(Ctx *c, int32_t id, int64_t n, const int64_t *src, cons
 	LaneTable lt;
 	PGQ_TRY(build_lane_table(c, g, n, src, dst, sv, dv, &lt));
 	std::vector<int32_t> found((size_t)lt.nbatch * lt.W, -1);
-	PGQ_TRY(msbfs_run(c, g, lt, found.data(), nullptr, src, n));
+	if (g->is_part) {
+		// lanes address the replicated frontier structures by the internal rank-major numbering
+		const PartMap pm = part_map(g->gV, c->part_world);
+		for (size_t k = 0; k < lt.src.size(); k++) {
+			if (lt.src[k] == 0xFFFFFFFFu) continue;
+			lt.src[k] = part_newid(lt.src[k], pm);
+			lt.dst[k] = part_newid(lt.dst[k], pm);
+		}
+		PGQ_TRY(msbfs_part_run(c, g, lt, found.data()));
+	}
+	else PGQ_TRY(msbfs_run(c, g, lt, found.data(), nullptr, src, n));
 	for (int64_t i = 0; i < n; i++) {
 		if (lt.kind[i] == 0) {
 			out_valid[i] = 0;
@@ -581,6 +604,10 @@ int pgq_shortestpath(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, 
 		set_error("csr %d not finalized", id);
 		return PGQ_ERR_STATE;
 	}
+	if (g->is_part) {
+		set_error("csr %d is vertex-partitioned: only pgq_part_iterativelength / pgq_part_reachability apply", id);
+		return PGQ_ERR_STATE;
+	}
 	if (mode != 0 && mode != 1) {
 		set_error("shortestpath mode must be 0 or 1");
 		return PGQ_ERR_INVALID;
@@ -624,10 +651,129 @@ int pgq_iterativelength_device(pgq_ctx_t *ctx, int32_t id, int64_t n, const int6
 		set_error("csr %d not finalized", id);
 		return PGQ_ERR_STATE;
 	}
+	if (g->is_part) {
+		set_error("csr %d is vertex-partitioned: only pgq_part_iterativelength / pgq_part_reachability apply", id);
+		return PGQ_ERR_STATE;
+	}
 	return msbfs_run_device(c, g, n, d_src, d_dst, d_out, d_out_valid);
 }
 
 // ---- bench / test helpers -----------------------------------------------------------------------
+
+// ---- 1-D vertex partition (collective entry points) ------------------------------------------------
+int pgq_nccl_unique_id(void *out128) {
+	const NcclApi *nc = nccl_api();
+	if (!nc) return PGQ_ERR_CUDA;
+	ncclUniqueId id;
+	PGQ_NCCL(nc, nc->GetUniqueId(&id));
+	static_assert(sizeof(id) == 128, "ncclUniqueId is 128 bytes");
+	memcpy(out128, &id, sizeof(id));
+	return PGQ_OK;
+}
+
+int pgq_part_init(pgq_ctx_t *ctx, int rank, int world, const void *unique_id128) {
+	LOCK(ctx);
+	if (world < 1 || rank < 0 || rank >= world) {
+		set_error("pgq_part_init: bad rank/world");
+		return PGQ_ERR_INVALID;
+	}
+	PGQ_CUDA(cudaSetDevice(c->device));
+	c->part_rank = rank;
+	c->part_world = world;
+	if (world > 1) {
+		const NcclApi *nc = nccl_api();
+		if (!nc) return PGQ_ERR_CUDA;
+		if (!unique_id128) {
+			set_error("pgq_part_init: unique id required for world > 1");
+			return PGQ_ERR_INVALID;
+		}
+		ncclUniqueId id;
+		memcpy(&id, unique_id128, sizeof(id));
+		ncclComm_t comm;
+		PGQ_NCCL(nc, nc->CommInitRank(&comm, world, id, rank));
+		c->nccl_comm = comm;
+	}
+	return PGQ_OK;
+}
+
+int pgq_part_range(pgq_ctx_t *ctx, int64_t v_size, int64_t *out_base, int64_t *out_count) {
+	LOCK(ctx);
+	// scrambled block-cyclic ownership (common.cuh PartMap): *out_count = slice size of the replicas
+	const PartMap pm = part_map(v_size, c->part_world);
+	if (out_base) *out_base = (int64_t)pm.Vp * c->part_rank;
+	if (out_count) *out_count = (int64_t)pm.Vp;
+	return PGQ_OK;
+}
+
+int pgq_part_csr_create(pgq_ctx_t *ctx, int32_t id, int64_t v_size) {
+	LOCK(ctx);
+	if (v_size < 0 || v_size > ((int64_t)1 << 30)) {
+		set_error("pgq_part_csr_create: v_size out of range (32-bit vertex ids)");
+		return PGQ_ERR_INVALID;
+	}
+	auto it = c->csrs.find(id);
+	if (it != c->csrs.end()) {
+		it->second->free_all();
+		delete it->second;
+		c->csrs.erase(it);
+	}
+	Csr *g = new Csr();
+	g->is_part = true;
+	g->gV = v_size;
+	g->V = (int64_t)part_map(v_size, c->part_world).Vp;
+	g->part_base = g->V * c->part_rank;
+	g->state = Csr::EDGES_OPEN;
+	c->csrs[id] = g;
+	return PGQ_OK;
+}
+
+int pgq_part_csr_add_edges_device(pgq_ctx_t *ctx, int32_t id, const int64_t *d_src, const int64_t *d_dst,
+                                  int64_t n) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (!g->is_part || g->state != Csr::EDGES_OPEN) {
+		set_error("csr %d is not an open partitioned csr", id);
+		return PGQ_ERR_STATE;
+	}
+	return part_add_edges_device(c, g, d_src, d_dst, n);
+}
+
+int pgq_part_csr_finalize(pgq_ctx_t *ctx, int32_t id) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (!g->is_part || g->state != Csr::EDGES_OPEN) {
+		set_error("csr %d is not an open partitioned csr", id);
+		return PGQ_ERR_STATE;
+	}
+	return part_finalize(c, g);
+}
+
+int pgq_part_iterativelength(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                             const uint8_t *src_valid, const uint8_t *dst_valid, int64_t *out,
+                             uint8_t *out_valid) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (!g->is_part) {
+		set_error("csr %d is not partitioned", id);
+		return PGQ_ERR_STATE;
+	}
+	return query_lengths(c, id, n, src, dst, src_valid, dst_valid, out, nullptr, out_valid);
+}
+
+int pgq_part_reachability(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                          const uint8_t *src_valid, const uint8_t *dst_valid, uint8_t *out, uint8_t *out_valid) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (!g->is_part) {
+		set_error("csr %d is not partitioned", id);
+		return PGQ_ERR_STATE;
+	}
+	return query_lengths(c, id, n, src, dst, src_valid, dst_valid, nullptr, out, out_valid);
+}
 
 int pgq_dev_alloc(pgq_ctx_t *ctx, uint64_t bytes, void **out_dptr) {
 	LOCK(ctx);
@@ -689,6 +835,13 @@ int pgq_gen_rmat_device(pgq_ctx_t *ctx, uint64_t seed, int scale, int64_t e_size
 	LOCK(ctx);
 	PGQ_TRY(gen_rmat_device(c, seed, scale, e_size, d_src, d_dst));
 	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	return PGQ_OK;
+}
+
+int pgq_gen_rmat_rows_device(pgq_ctx_t *ctx, uint64_t seed, int scale, int64_t row0, int64_t n, int64_t *d_src,
+                             int64_t *d_dst) {
+	LOCK(ctx);
+	PGQ_TRY(gen_rmat_rows_device(c, seed, scale, row0, n, d_src, d_dst));
 	return PGQ_OK;
 }
 

@@ -110,6 +110,13 @@ struct Csr {
 	DevBuf d_hubchunks; // HubChunk[]
 	uint32_t n_tiny = 0, n_small = 0, n_mid = 0, n_hub = 0, n_hubchunks = 0;
 	int64_t bins_tiny_max = -1, bins_small_max = -1, bins_hub_min = -1;
+	// 1-D partition (part.cu): this object then describes the slice of the reverse CSR owned by the
+	// rank — V = owned vertex count (local index space), E = local in-edges, d_isrc = GLOBAL sources
+	bool is_part = false;
+	int64_t gV = 0;         // global vertex count
+	int64_t part_base = 0;  // first owned vertex
+	DevBuf d_ltgt, d_lsrc;  // staged local in-edges: local target index, global source
+	uint64_t n_local = 0;
 	void free_all();
 };
 
@@ -151,12 +158,16 @@ struct Ctx {
 	DevBuf bfs_seen, bfs_visit[2], bfs_parent, bfs_hubacc;
 	DevBuf bfs_queue[2], bfs_inq[2]; // push work queues + dedupe bitmaps
 	BfsDirty bfs_dirty;
+	// 1-D partition
+	int part_rank = 0, part_world = 1;
+	void *nccl_comm = nullptr;
+	DevBuf part_alive; // [1 + world][16] local / gathered alive masks
 	DevBuf bfs_alive; // per-block-slot alive lane masks (msbfs_kernels.cuh)
 	DevBuf bfs_lane; // per-call lane tables
 	DevBuf bfs_ctrl; // device control block
 	DevBuf l2_flush;
 	void *h_ctrl = nullptr; // pinned host mirror of the control block
-	cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_timer = nullptr, ev_timer2 = nullptr;
+	cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_timer = nullptr, ev_timer2 = nullptr;
 	std::vector<cudaEvent_t> ev_pool; // level-kernel timing events
 	size_t ev_used = 0;
 };
@@ -222,9 +233,81 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
               const int64_t *row_src /*host, for trivial rows in path mode*/, int64_t nrows);
 int msbfs_run_device(Ctx *c, Csr *g, int64_t n, const int64_t *d_src, const int64_t *d_dst, int64_t *d_out,
                      uint8_t *d_out_valid);
+// partitioned variant (collective): g is the rank's slice
+int msbfs_part_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found);
+
+// ---- part.cu ----
+int part_add_edges_device(Ctx *c, Csr *g, const int64_t *d_src, const int64_t *d_dst, int64_t n);
+int part_finalize(Ctx *c, Csr *g);
+int part_offsets_u32(Ctx *c, const uint32_t *keys, uint32_t n, uint32_t nv, uint32_t *off); // csr_build.cu
+// Ownership of the 1-D partition.  Vertices are grouped in 32-vertex blocks (one frontier-bitmap
+// word); the block index is scrambled by a bijection on k-bit integers (k = ceil(log2(#blocks)))
+// and dealt round-robin: owner = mix(blk) % G, local block = mix(blk) / G.  Plain ranges or plain
+// block-cyclic dealing leave R-MAT 3:1 unbalanced between ranks because in-degree correlates with
+// every id bit.  Internally vertices are renumbered rank-major, new(v) = owner*Vp + local(v), so a
+// rank's slice of the replicated frontier structures is contiguous (in-place allgather) and the
+// stored sources index those structures directly.  Non-power-of-two block counts pad to 2^k.
+struct PartMap {
+	uint32_t G = 1;
+	uint32_t kbits = 0;
+	uint64_t Vp = 0; // vertices per rank in the replicated structures (multiple of 256)
+};
+static inline PartMap part_map(int64_t V, int world) {
+	PartMap m;
+	m.G = (uint32_t)world;
+	const uint64_t nblk = (uint64_t)(V + 31) / 32;
+	while (((uint64_t)1 << m.kbits) < nblk) m.kbits++;
+	const uint64_t lblk = (((uint64_t)1 << m.kbits) + m.G - 1) / m.G;
+	m.Vp = (lblk * 32 + 255) / 256 * 256;
+	return m;
+}
+__host__ __device__ static inline uint64_t part_mix(uint64_t blk, uint32_t k) {
+	if (k < 2) return blk;
+	const uint64_t mask = ((uint64_t)1 << k) - 1;
+	const uint32_t h = (k + 1) / 2;
+	uint64_t x = blk;
+	x ^= x >> h;
+	x = (x * 0x9E3779B97F4A7C15ull) & mask;
+	x ^= x >> h;
+	x = (x * 0xC2B2AE3D27D4EB4Full) & mask;
+	x ^= x >> h;
+	return x;
+}
+__host__ __device__ static inline uint32_t part_owner(uint64_t v, const PartMap &m) {
+	return (uint32_t)(part_mix(v >> 5, m.kbits) % m.G);
+}
+__host__ __device__ static inline uint32_t part_local(uint64_t v, const PartMap &m) {
+	return (uint32_t)(((part_mix(v >> 5, m.kbits) / m.G) << 5) | (v & 31u));
+}
+__host__ __device__ static inline uint32_t part_newid(uint64_t v, const PartMap &m) {
+	return (uint32_t)(part_owner(v, m) * m.Vp + part_local(v, m));
+}
+int part_add_edges_device(Ctx *c, Csr *g, const int64_t *d_src, const int64_t *d_dst, int64_t n);
+int part_finalize(Ctx *c, Csr *g);
+int part_offsets_u32(Ctx *c, const uint32_t *keys, uint32_t n, uint32_t nv, uint32_t *off); // csr_build.cu
+// Ownership is block-cyclic over 32-vertex blocks (one frontier-bitmap word): vertex v belongs to
+// rank (v/32) % G.  Contiguous ranges would put all R-MAT hubs on rank 0.  Internally vertices are
+// renumbered rank-major, new(v) = owner*Vp + local(v), so every rank's slice of the replicated
+// frontier structures is contiguous (in-place allgather) and sources index them directly.
+static constexpr int PART_BLOCK_LOG2 = 5;
+static inline int64_t part_slice(int64_t V, int world) {
+	const int64_t nblk = (V + 31) / 32;
+	const int64_t vp = (nblk + world - 1) / world * 32;
+	return (vp + 255) / 256 * 256;
+}
+__host__ __device__ static inline uint32_t part_owner(uint64_t v, uint32_t G) {
+	return (uint32_t)((v >> PART_BLOCK_LOG2) % G);
+}
+__host__ __device__ static inline uint32_t part_local(uint64_t v, uint32_t G) {
+	return (uint32_t)((((v >> PART_BLOCK_LOG2) / G) << PART_BLOCK_LOG2) | (v & 31u));
+}
+__host__ __device__ static inline uint32_t part_newid(uint64_t v, uint32_t G, uint64_t Vp) {
+	return (uint32_t)(part_owner(v, G) * Vp + part_local(v, G));
+}
 
 // ---- gen.cu ----
 int gen_rmat_device(Ctx *c, uint64_t seed, int scale, int64_t E, int64_t *d_src, int64_t *d_dst);
+int gen_rmat_rows_device(Ctx *c, uint64_t seed, int scale, int64_t row0, int64_t n, int64_t *d_src, int64_t *d_dst);
 int gen_knows_device(Ctx *c, uint64_t seed, int64_t V, int64_t E, uint64_t mult, uint64_t add, int64_t *d_src,
                      int64_t *d_dst);
 

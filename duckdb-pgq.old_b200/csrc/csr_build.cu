@@ -45,6 +45,13 @@ __global__ void __launch_bounds__(256) gather_eid_kernel(const int64_t *__restri
 	if (i < n) out[i] = eid_in[row[i]];
 }
 
+int part_offsets_u32(Ctx *c, const uint32_t *keys, uint32_t n, uint32_t nv, uint32_t *off) {
+	offsets_from_sorted_kernel<uint32_t><<<div_up((uint64_t)n + 1, 256), 256, 0, c->stream>>>(keys, n, nv, 1u, off);
+	count_launch(c);
+	PGQ_CUDA(cudaGetLastError());
+	return PGQ_OK;
+}
+
 static int key_bits_for(int64_t V) {
 	int b = 1;
 	while (b < 32 && ((int64_t)1 << b) < V) b++;
@@ -270,6 +277,7 @@ void Csr::free_all() {
 	d_off.release(); d_tgt.release(); d_row.release(); d_eid.release(); d_fsrc.release();
 	d_ioff.release(); d_isrc.release(); d_ipos.release();
 	d_tiny.release(); d_small.release(); d_mid.release(); d_hub.release(); d_hubchunks.release();
+	d_ltgt.release(); d_lsrc.release();
 }
 
 } // namespace pgq

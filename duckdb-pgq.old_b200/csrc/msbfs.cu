@@ -3,6 +3,7 @@
 // run level steps while a lane is active and something changed, check destinations after each
 // level, retire found lanes.  One stream, one host sync per level (reads 16 bytes of control).
 #include "msbfs_kernels.cuh"
+#include "nccl_dl.cuh"
 
 namespace pgq {
 
@@ -405,6 +406,189 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 	}
 	if (c->opt.stats)
 		c->stats.algo_bytes += (c->stats.levels - levels_before) * 4ull * (uint64_t)g->V * (uint64_t)(W / 8);
+	return PGQ_OK;
+}
+
+// ---- 1-D vertex-partitioned variant (BASELINE.json configs[4]) ------------------------------------
+// g is this rank's slice of the reverse CSR (local index space, global sources).  Frontier words
+// and bitmap are replicated at G*Vp vertices; each level every rank fills its slice and one
+// grouped ncclAllGather (words, bitmap, alive masks) completes all replicas.  Bottom-up only, the
+// bitmap filter always on (so words outside the bitmap are never read).
+
+namespace {
+
+struct PartBufs {
+	uint32_t *visit[2], *fbit[2], *seen, *hubacc, *alive_slots, *alive_local, *alive_all;
+	BfsCtrl *ctrl;
+	size_t words_per_slice, fwords_per_slice; // uint32 counts
+};
+
+template <int W>
+int launch_part_level(Ctx *c, Csr *g, const PartBufs &b, int cur, int iter) {
+	using C = LaneCfg<W>;
+	cudaStream_t st = c->stream;
+	const int G = c->part_world, r = c->part_rank;
+	const size_t fwords = b.fwords_per_slice * G;
+	if (iter == 2) { // scrub the source words of level 0 out of the buffer that becomes `next` (zeroes the bitmap too)
+		clear_by_bitmap_kernel<W><<<div_up(fwords, 256), 256, 0, st>>>(b.fbit[cur ^ 1], (uint32_t)fwords,
+		                                                              b.visit[cur ^ 1]);
+		count_launch(c);
+	} else {
+		PGQ_CUDA(cudaMemsetAsync(b.fbit[cur ^ 1], 0, fwords * sizeof(uint32_t), st));
+	}
+	PullArgs a{};
+	a.ioff = g->d_ioff.as<uint32_t>();
+	a.isrc = g->d_isrc.as<uint32_t>();
+	a.visit = b.visit[cur];
+	a.next = b.visit[cur ^ 1] + b.words_per_slice * r; // local vertex 0 = global vertex part_base
+	a.seen = b.seen;
+	a.ctrl = b.ctrl;
+	a.V = (uint32_t)g->V;
+	a.hubacc = b.hubacc;
+	a.fcur = b.fbit[cur];
+	a.fnext = b.fbit[cur ^ 1] + b.fwords_per_slice * r;
+	a.alive_slots = b.alive_slots;
+	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, false, true);
+	launch_class<W, 2>(c, a, g->d_small, g->n_small, false, true);
+	if (g->n_mid) {
+		a.list = g->d_mid.as<uint32_t>();
+		a.nlist = g->n_mid;
+		pull_warp_kernel<W, true><<<div_up((uint64_t)g->n_mid * 32, 128), 128, 0, st>>>(a);
+		count_launch(c);
+	}
+	if (g->n_hub) {
+		a.list = g->d_hub.as<uint32_t>();
+		a.nlist = g->n_hub;
+		a.chunks = g->d_hubchunks.as<HubChunk>();
+		a.nchunks = g->n_hubchunks;
+		pull_hub_kernel<W><<<g->n_hubchunks, 256, 0, st>>>(a);
+		hub_finalize_kernel<W><<<div_up((uint64_t)g->n_hub * C::TPV, 256), 256, 0, st>>>(a);
+		count_launch(c, 2);
+	}
+	alive_fold_kernel<<<1, 1024, 0, st>>>(b.alive_slots, b.alive_local);
+	count_launch(c);
+	return PGQ_OK;
+}
+
+int launch_part_level_w(Ctx *c, Csr *g, const PartBufs &b, int W, int cur, int iter) {
+	switch (W) {
+	case 64: return launch_part_level<64>(c, g, b, cur, iter);
+	case 128: return launch_part_level<128>(c, g, b, cur, iter);
+	case 256: return launch_part_level<256>(c, g, b, cur, iter);
+	case 512: return launch_part_level<512>(c, g, b, cur, iter);
+	}
+	return PGQ_ERR_INVALID;
+}
+
+// exchange of one level: next words, frontier bitmap, alive masks (in place, one NCCL group)
+int part_exchange(Ctx *c, const PartBufs &b, int nxt) {
+	const int G = c->part_world, r = c->part_rank;
+	cudaStream_t st = c->stream;
+	if (G == 1) {
+		PGQ_CUDA(cudaMemcpyAsync(b.alive_all, b.alive_local, 16 * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+		return PGQ_OK;
+	}
+	const NcclApi *nc = nccl_api();
+	if (!nc) return PGQ_ERR_CUDA;
+	ncclComm_t comm = (ncclComm_t)c->nccl_comm;
+	PGQ_NCCL(nc, nc->GroupStart());
+	PGQ_NCCL(nc, nc->AllGather(b.visit[nxt] + b.words_per_slice * r, b.visit[nxt], b.words_per_slice, ncclUint32, comm, st));
+	PGQ_NCCL(nc, nc->AllGather(b.fbit[nxt] + b.fwords_per_slice * r, b.fbit[nxt], b.fwords_per_slice, ncclUint32, comm, st));
+	PGQ_NCCL(nc, nc->AllGather(b.alive_local, b.alive_all, 16, ncclUint32, comm, st));
+	PGQ_NCCL(nc, nc->GroupEnd());
+	c->stats.coll_bytes += (b.words_per_slice + b.fwords_per_slice + 16) * sizeof(uint32_t);
+	return PGQ_OK;
+}
+
+} // namespace
+
+int msbfs_part_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found) {
+	const int W = lt.W, G = c->part_world;
+	const int64_t nslots = lt.nbatch * W;
+	if (nslots == 0) return PGQ_OK;
+	cudaStream_t st = c->stream;
+	const size_t Vp = (size_t)g->V, WPV = (size_t)W / 32;
+	PartBufs b{};
+	b.words_per_slice = Vp * WPV;
+	b.fwords_per_slice = Vp / 32; // Vp is a multiple of 256
+	const size_t bm = b.words_per_slice * G * sizeof(uint32_t), fb = b.fwords_per_slice * G * sizeof(uint32_t);
+	PGQ_TRY(c->bfs_visit[0].reserve(bm));
+	PGQ_TRY(c->bfs_visit[1].reserve(bm));
+	PGQ_TRY(c->bfs_seen.reserve(b.words_per_slice * sizeof(uint32_t)));
+	PGQ_TRY(c->bfs_inq[0].reserve(2 * fb));
+	PGQ_TRY(c->bfs_ctrl.reserve(sizeof(BfsCtrl)));
+	PGQ_TRY(c->bfs_alive.reserve((size_t)ALIVE_SLOTS * 16 * sizeof(uint32_t)));
+	PGQ_TRY(c->part_alive.reserve((size_t)(1 + G) * 16 * sizeof(uint32_t)));
+	const size_t hb = (size_t)(g->n_hub > 0 ? g->n_hub : 1) * (W / 8);
+	PGQ_TRY(c->bfs_hubacc.reserve(hb));
+	PGQ_CUDA(cudaMemsetAsync(c->bfs_hubacc.p, 0, c->bfs_hubacc.cap, st));
+	PGQ_CUDA(cudaMemsetAsync(c->bfs_alive.p, 0, (size_t)ALIVE_SLOTS * 16 * sizeof(uint32_t), st));
+	c->bfs_dirty.valid = false; // the shared frontier buffers are used with another geometry here
+	b.visit[0] = c->bfs_visit[0].as<uint32_t>();
+	b.visit[1] = c->bfs_visit[1].as<uint32_t>();
+	b.seen = c->bfs_seen.as<uint32_t>();
+	b.fbit[0] = c->bfs_inq[0].as<uint32_t>();
+	b.fbit[1] = b.fbit[0] + b.fwords_per_slice * G;
+	b.hubacc = c->bfs_hubacc.as<uint32_t>();
+	b.alive_slots = c->bfs_alive.as<uint32_t>();
+	b.alive_local = c->part_alive.as<uint32_t>();
+	b.alive_all = b.alive_local + 16;
+	b.ctrl = c->bfs_ctrl.as<BfsCtrl>();
+	PGQ_TRY(c->bfs_lane.reserve((size_t)nslots * 12 + 64));
+	uint32_t *d_src = c->bfs_lane.as<uint32_t>();
+	uint32_t *d_dst = d_src + nslots;
+	int32_t *d_found = reinterpret_cast<int32_t *>(d_dst + nslots);
+	PGQ_CUDA(cudaMemcpyAsync(d_src, lt.src.data(), (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
+	PGQ_CUDA(cudaMemcpyAsync(d_dst, lt.dst.data(), (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
+	c->stats.h2d_bytes += (uint64_t)nslots * 8;
+	for (int64_t bi = 0; bi < lt.nbatch; bi++) {
+		PGQ_CUDA(cudaMemsetAsync(b.seen, 0, b.words_per_slice * sizeof(uint32_t), st));
+		PGQ_CUDA(cudaMemsetAsync(b.visit[0], 0, bm, st));
+		PGQ_CUDA(cudaMemsetAsync(b.visit[1], 0, bm, st));
+		PGQ_CUDA(cudaMemsetAsync(b.fbit[0], 0, 2 * fb, st));
+		bfs_init_part_kernel<<<1, W, 0, st>>>(d_src + bi * W, W, b.visit[0], d_found + bi * W, b.ctrl, b.fbit[0]);
+		count_launch(c);
+		BfsCtrl h;
+		PGQ_CUDA(cudaMemcpyAsync(c->h_ctrl, b.ctrl, sizeof(BfsCtrl), cudaMemcpyDeviceToHost, st));
+		PGQ_CUDA(cudaStreamSynchronize(st));
+		h = *reinterpret_cast<BfsCtrl *>(c->h_ctrl);
+		c->stats.batches++;
+		uint32_t active = h.n_active;
+		int cur = 0;
+		for (int iter = 1; active; iter++) {
+			if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
+			uint64_t before = c->stats.kernel_launches;
+			PGQ_TRY(launch_part_level_w(c, g, b, W, cur, iter));
+			if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
+			PGQ_TRY(part_exchange(c, b, cur ^ 1));
+			if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_c, st));
+			bfs_check_part_kernel<<<1, W, 0, st>>>(b.visit[cur ^ 1], d_dst + bi * W, W, d_found + bi * W, b.ctrl, iter,
+			                                       b.alive_all, G);
+			count_launch(c);
+			PGQ_CUDA(cudaMemcpyAsync(c->h_ctrl, b.ctrl, sizeof(BfsCtrl), cudaMemcpyDeviceToHost, st));
+			PGQ_CUDA(cudaStreamSynchronize(st));
+			h = *reinterpret_cast<BfsCtrl *>(c->h_ctrl);
+			c->stats.levels++;
+			if (c->opt.timing) {
+				float ms = 0, cms = 0;
+				PGQ_CUDA(cudaEventElapsedTime(&ms, c->ev_a, c->ev_b));
+				PGQ_CUDA(cudaEventElapsedTime(&cms, c->ev_b, c->ev_c));
+				c->stats.level_kernel_ms += ms;
+				c->stats.coll_ms += cms;
+				c->stats.level_kernel_launches += c->stats.kernel_launches - before;
+				if (c->opt.trace)
+					fprintf(stderr, "[pgq part r%d] iter %d pull %.3f ms  exchange %.3f ms  active %u alive %u\n",
+					        c->part_rank, iter, ms, cms, h.n_active, h.change_out);
+			}
+			cur ^= 1;
+			if (!h.change_out) break;
+			active = h.n_active;
+		}
+	}
+	PGQ_CUDA(cudaMemcpyAsync(h_found, d_found, (size_t)nslots * 4, cudaMemcpyDeviceToHost, st));
+	PGQ_CUDA(cudaStreamSynchronize(st));
+	c->stats.d2h_bytes += (uint64_t)nslots * 4;
+	PGQ_CUDA(cudaGetLastError());
 	return PGQ_OK;
 }
 

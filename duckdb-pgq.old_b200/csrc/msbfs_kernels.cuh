@@ -873,6 +873,96 @@ __global__ void __launch_bounds__(256) bfs_count_kernel(const uint32_t *__restri
 	}
 }
 
+// ---- 1-D partitioned variants (msbfs_part_run) -----------------------------------------------------
+// Every rank runs these on its own replica of the full frontier structures, with identical inputs.
+
+// source bits + frontier bitmap + active mask (no push queue: this path is bottom-up only)
+__global__ void bfs_init_part_kernel(const uint32_t *__restrict__ lane_src, int W, uint32_t *__restrict__ visit,
+                                     int32_t *__restrict__ found, BfsCtrl *ctrl, uint32_t *__restrict__ fbit0) {
+	__shared__ uint32_t cnt;
+	const int lane = threadIdx.x;
+	if (lane == 0) {
+		cnt = 0;
+		ctrl->change = 0; ctrl->change_out = 0;
+		ctrl->edges_lane = 0; ctrl->edges_unique = 0; ctrl->verts_active = 0;
+		ctrl->next_edges = 0; ctrl->next_verts = 0; ctrl->next_items = 0;
+		ctrl->out_edges = 0; ctrl->out_verts = 0; ctrl->out_items = 0;
+	}
+	__syncthreads();
+	const uint32_t s = lane_src[lane];
+	const bool used = s != 0xFFFFFFFFu;
+	found[lane] = -1;
+	if (used) {
+		atomicOr(&visit[(size_t)s * (W / 32) + (lane >> 5)], 1u << (lane & 31));
+		atomicOr(&fbit0[s >> 5], 1u << (s & 31));
+	}
+	const unsigned m = __ballot_sync(0xffffffffu, used);
+	if ((lane & 31) == 0) {
+		ctrl->active[lane >> 5] = m;
+		ctrl->alive[lane >> 5] = 0;
+		atomicAdd(&cnt, (uint32_t)__popc(m));
+	}
+	__syncthreads();
+	if (lane == 0) ctrl->n_active = cnt;
+}
+
+// fold (and re-zero) this rank's alive slots into 16 words for the allgather
+__global__ void alive_fold_kernel(uint32_t *__restrict__ alive_slots, uint32_t *__restrict__ out16) {
+	__shared__ uint32_t salive[16];
+	if (threadIdx.x < 16) salive[threadIdx.x] = 0;
+	__syncthreads();
+	for (uint32_t idx = threadIdx.x; idx < ALIVE_SLOTS * 16; idx += blockDim.x) {
+		const uint32_t v = alive_slots[idx];
+		if (v) {
+			alive_slots[idx] = 0;
+			atomicOr(&salive[idx & 15], v);
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x < 16) out16[threadIdx.x] = salive[threadIdx.x];
+}
+
+// After the allgather every rank holds the complete new frontier: a lane is found at this level iff
+// next[dst] carries its bit (seen[dst] gains a bit exactly when next[dst] does), and a lane is
+// alive iff some rank produced a bit for it.  Identical on all ranks, no further exchange.
+__global__ void bfs_check_part_kernel(const uint32_t *__restrict__ next, const uint32_t *__restrict__ lane_dst, int W,
+                                      int32_t *__restrict__ found, BfsCtrl *ctrl, int iter,
+                                      const uint32_t *__restrict__ alive_all, int world) {
+	__shared__ uint32_t cnt;
+	__shared__ uint32_t anyalive;
+	const int lane = threadIdx.x;
+	if (lane == 0) {
+		cnt = 0;
+		anyalive = 0;
+	}
+	__syncthreads();
+	const uint32_t word = ctrl->active[lane >> 5];
+	const bool act = (word >> (lane & 31)) & 1u;
+	bool hit = false;
+	if (act) {
+		const uint32_t d = lane_dst[lane];
+		hit = (next[(size_t)d * (W / 32) + (lane >> 5)] >> (lane & 31)) & 1u;
+		if (hit) found[lane] = iter;
+	}
+	const unsigned hm = __ballot_sync(0xffffffffu, hit);
+	__syncthreads();
+	if ((lane & 31) == 0) {
+		uint32_t al = 0;
+		for (int r = 0; r < world; r++) al |= alive_all[r * 16 + (lane >> 5)];
+		if (al) atomicOr(&anyalive, 1u);
+		const uint32_t nw = word & ~hm & al;
+		ctrl->alive[lane >> 5] = al;
+		ctrl->active[lane >> 5] = nw;
+		atomicAdd(&cnt, (uint32_t)__popc(nw));
+	}
+	__syncthreads();
+	if (lane == 0) {
+		ctrl->n_active = cnt;
+		ctrl->change_out = anyalive;
+		ctrl->change = 0;
+	}
+}
+
 // K8: one thread per lane walks dst -> parent in-edges -> src and writes the list back to front.
 // mode 0: [src,..,dst] (len L+1); mode 1: [src,e0,v1,..,dst] (len 2L+1).  R7/R8.
 __global__ void bfs_paths_kernel(const uint32_t *__restrict__ parent, const uint32_t *__restrict__ isrc,

@@ -56,6 +56,8 @@ typedef struct {
 	double transpose_ms;      /* CUDA-event time of the last reverse-CSR build */
 	uint64_t h2d_bytes;       /* bytes copied host->device by this library since reset */
 	uint64_t d2h_bytes;
+	uint64_t coll_bytes;      /* bytes this rank contributed to per-level collectives (partitioned path) */
+	double coll_ms;           /* CUDA-event time of those collectives ("timing"=1) */
 } pgq_stats_t;
 
 /* ---- context ------------------------------------------------------------------------- */
@@ -117,6 +119,30 @@ void pgq_free(void *p);
 int pgq_iterativelength_device(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *d_src,
                                const int64_t *d_dst, int64_t *d_out, uint8_t *d_out_valid);
 
+/* ---- 1-D vertex partition across GPUs (BASELINE.json configs[4]) -------------------------------
+ * One process per GPU.  32-vertex blocks are dealt to the ranks by a scrambling bijection of the
+ * block index (plain ranges or plain block-cyclic dealing leave R-MAT ranks 3:1 unbalanced); a rank
+ * owns its blocks' vertices as targets, together with
+ * their in-edges (a slice of the reverse CSR).  The W-bit
+ * frontier words and the frontier bitmap are replicated; after every bottom-up level each rank's
+ * slice is exchanged with ncclAllGather over NVLink.  `seen` exists only for owned vertices.
+ * Every function below is COLLECTIVE: all ranks call it with identical arguments; query results
+ * are produced on every rank.  Lengths / reachability only (no parents). */
+int pgq_nccl_unique_id(void *out128); /* rank 0; the caller broadcasts the 128 bytes */
+int pgq_part_init(pgq_ctx_t *ctx, int rank, int world, const void *unique_id128);
+int pgq_part_range(pgq_ctx_t *ctx, int64_t v_size, int64_t *out_base, int64_t *out_count);
+int pgq_part_csr_create(pgq_ctx_t *ctx, int32_t id, int64_t v_size);
+/* Rows of the GLOBAL edge table in arrival order (device int64 arrays).  Every rank is shown every
+ * row (or at least the rows whose dst it owns); rows owned by other ranks are dropped. */
+int pgq_part_csr_add_edges_device(pgq_ctx_t *ctx, int32_t id, const int64_t *d_src, const int64_t *d_dst,
+                                  int64_t n);
+int pgq_part_csr_finalize(pgq_ctx_t *ctx, int32_t id);
+int pgq_part_iterativelength(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                             const uint8_t *src_valid, const uint8_t *dst_valid, int64_t *out,
+                             uint8_t *out_valid);
+int pgq_part_reachability(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                          const uint8_t *src_valid, const uint8_t *dst_valid, uint8_t *out, uint8_t *out_valid);
+
 /* ---- bench / test helpers (not part of the reference surface) ------------------------------ */
 int pgq_dev_alloc(pgq_ctx_t *ctx, uint64_t bytes, void **out_dptr);
 int pgq_dev_free(pgq_ctx_t *ctx, void *dptr);
@@ -128,6 +154,9 @@ int pgq_sync(pgq_ctx_t *ctx);
 /* synthetic edge tables written straight into HBM (same streams as oracle/pgq_gen.h) */
 int pgq_gen_rmat_device(pgq_ctx_t *ctx, uint64_t seed, int scale, int64_t e_size, int64_t *d_src,
                         int64_t *d_dst);
+/* rows [row0, row0+n) of the same R-MAT stream (chunked generation for graphs larger than a buffer) */
+int pgq_gen_rmat_rows_device(pgq_ctx_t *ctx, uint64_t seed, int scale, int64_t row0, int64_t n, int64_t *d_src,
+                             int64_t *d_dst);
 int pgq_gen_knows_device(pgq_ctx_t *ctx, uint64_t seed, int64_t v_size, int64_t e_size, uint64_t mult,
                          uint64_t add, int64_t *d_src, int64_t *d_dst);
 /* write >L2-sized scratch so the next timed step starts with a cold L2 */

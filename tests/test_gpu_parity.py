@@ -376,3 +376,47 @@ def test_sharded_query_gpu(ctx):
     _cmp_arr("valid", np.concatenate(valids), ev)
     _cmp_arr("length", np.concatenate(outs), eo)
     ctx.csr_delete(1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("lanes", [64, 512])
+def test_partitioned_path_world1(ctx, lanes):
+    """1-D vertex-partitioned MS-BFS (BASELINE configs[4]) degenerated to one rank: the slice build
+    (owner filter, renumbering, stable sort), the replicated-frontier level loop and the
+    next[dst]-based destination check give the oracle's lengths / reachability.  The multi-rank run
+    of the same code is tools/part_check.py --check under torchrun (2 GPUs)."""
+    scale = 13
+    V = 1 << scale
+    src, dst = orc.gen_rmat(0x5eed0000 + scale, scale)
+    E = len(src)
+    v, e, _ = orc.csr_build(V, src, dst)
+    ps, pd = orc.gen_pairs(21, V, v, 1300)
+    sv = np.ones(len(ps), dtype=np.uint8)
+    sv[::53] = 0
+    pd[7::61] = ps[7::61]
+    d_src, d_dst = ctx.dev_alloc(E * 8), ctx.dev_alloc(E * 8)
+    ctx.h2d(d_src, src)
+    ctx.h2d(d_dst, dst)
+    ctx.part_init(0, 1)
+    ctx.part_csr_create(7, V)
+    half = E // 2
+    ctx.part_csr_add_edges_device(7, d_src, d_dst, half)  # two chunks, arrival order
+    ctx.part_csr_add_edges_device(7, d_src + half * 8, d_dst + half * 8, E - half)
+    ctx.part_csr_finalize(7)
+    ctx.set_option("lanes", lanes)
+    try:
+        out, ov = ctx.part_iterativelength(7, ps, pd, src_valid=sv)
+        r, rv = ctx.part_reachability(7, ps, pd, src_valid=sv)
+        with pytest.raises(Exception):
+            ctx.shortestpath(7, ps[:4], pd[:4])  # not offered on the partitioned path
+    finally:
+        ctx.set_option("lanes", 0)
+    eo, ev = orc.iterativelength(V, v, e, ps, pd, src_valid=sv)
+    _cmp_arr("valid", ov, ev)
+    _cmp_arr("length", out, eo)
+    er, erv = orc.reachability(V, v, e, ps, pd, src_valid=sv)
+    _cmp_arr("reach valid", rv, erv)
+    _cmp_arr("reach", r, er)
+    ctx.dev_free(d_src)
+    ctx.dev_free(d_dst)
+    ctx.csr_delete(7)
