@@ -266,6 +266,15 @@ class Context:
     def part_csr_finalize(self, csr_id):
         self._chk(self.lib.pgq_part_csr_finalize(self._ctx, C.c_int32(csr_id)))
 
+    def part_p2p_setup(self, dist, csr_id, lanes, world):
+        """Enable the fused exchange: export this rank's replica handles, all-gather them with the
+        host plumbing (torch.distributed), map every peer's replicas (CUDA IPC over NVLink)."""
+        mine = C.create_string_buffer(128)
+        self._chk(self.lib.pgq_part_p2p_export(self._ctx, C.c_int32(csr_id), C.c_int(lanes), mine))
+        box = [None] * world
+        dist.all_gather_object(box, mine.raw)
+        self._chk(self.lib.pgq_part_p2p_import(self._ctx, C.c_char_p(b"".join(box))))
+
     def part_iterativelength(self, csr_id, src, dst, src_valid=None, dst_valid=None):
         src, ps = _i64(src)
         dst, pd = _i64(dst)

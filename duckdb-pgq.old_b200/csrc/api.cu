@@ -161,6 +161,8 @@ int pgq_shutdown(pgq_ctx_t *ctx) {
 		delete kv.second;
 	}
 	c->csrs.clear();
+	for (void *m : c->part_peer_open) cudaIpcCloseMemHandle(m);
+	c->part_peer_open.clear();
 	if (c->nccl_comm) {
 		const NcclApi *nc = nccl_api();
 		if (nc) nc->CommDestroy((ncclComm_t)c->nccl_comm);
@@ -169,7 +171,7 @@ int pgq_shutdown(pgq_ctx_t *ctx) {
 	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
 	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->bfs_seen, &c->bfs_visit[0],
 	                  &c->bfs_visit[1], &c->bfs_parent, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
-	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->l2_flush};
+	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->part_visit[0], &c->part_visit[1], &c->part_peer_tab, &c->l2_flush};
 	for (DevBuf *b : bufs) b->release();
 	if (c->h_ctrl) cudaFreeHost(c->h_ctrl);
 	cudaEventDestroy(c->ev_a);
@@ -748,6 +750,57 @@ int pgq_part_csr_finalize(pgq_ctx_t *ctx, int32_t id) {
 		return PGQ_ERR_STATE;
 	}
 	return part_finalize(c, g);
+}
+
+int pgq_part_p2p_export(pgq_ctx_t *ctx, int32_t id, int lanes, void *out_handles128) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (!g->is_part || (lanes != 64 && lanes != 128 && lanes != 256 && lanes != 512)) {
+		set_error("pgq_part_p2p_export: partitioned csr and lanes in {64,128,256,512} required");
+		return PGQ_ERR_INVALID;
+	}
+	PGQ_CUDA(cudaSetDevice(c->device));
+	c->part_p2p = false;
+	const size_t bytes = (size_t)g->V * c->part_world * (lanes / 8);
+	cudaIpcMemHandle_t h[2];
+	static_assert(sizeof(h) == PGQ_P2P_HANDLE_BYTES, "two 64-byte IPC handles");
+	for (int j = 0; j < 2; j++) {
+		c->part_visit[j].release();
+		PGQ_TRY(c->part_visit[j].reserve(bytes));
+		PGQ_CUDA(cudaIpcGetMemHandle(&h[j], c->part_visit[j].p));
+	}
+	memcpy(out_handles128, h, sizeof(h));
+	c->part_p2p_W = lanes;
+	c->part_p2p_Vp = g->V;
+	return PGQ_OK;
+}
+
+int pgq_part_p2p_import(pgq_ctx_t *ctx, const void *all_handles) {
+	LOCK(ctx);
+	PGQ_CUDA(cudaSetDevice(c->device));
+	const int G = c->part_world, r = c->part_rank;
+	if (G < 2 || !c->part_visit[0].p) {
+		set_error("pgq_part_p2p_import: export first (world > 1)");
+		return PGQ_ERR_STATE;
+	}
+	const size_t slice_words = (size_t)c->part_p2p_Vp * (c->part_p2p_W / 32);
+	std::vector<uint32_t *> tab((size_t)2 * (G - 1));
+	const cudaIpcMemHandle_t *hs = reinterpret_cast<const cudaIpcMemHandle_t *>(all_handles);
+	for (int p = 0, k = 0; p < G; p++) {
+		if (p == r) continue;
+		for (int j = 0; j < 2; j++) {
+			void *base = nullptr;
+			PGQ_CUDA(cudaIpcOpenMemHandle(&base, hs[(size_t)p * 2 + j], cudaIpcMemLazyEnablePeerAccess));
+			c->part_peer_open.push_back(base);
+			tab[(size_t)j * (G - 1) + k] = reinterpret_cast<uint32_t *>(base) + slice_words * r;
+		}
+		k++;
+	}
+	PGQ_TRY(c->part_peer_tab.reserve(tab.size() * sizeof(uint32_t *)));
+	PGQ_CUDA(cudaMemcpy(c->part_peer_tab.p, tab.data(), tab.size() * sizeof(uint32_t *), cudaMemcpyHostToDevice));
+	c->part_p2p = true;
+	return PGQ_OK;
 }
 
 int pgq_part_iterativelength(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,

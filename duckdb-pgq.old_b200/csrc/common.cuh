@@ -162,6 +162,13 @@ struct Ctx {
 	int part_rank = 0, part_world = 1;
 	void *nccl_comm = nullptr;
 	DevBuf part_alive; // [1 + world][16] local / gathered alive masks
+	// fused exchange over peer memory (pgq_part_p2p_export / _import)
+	DevBuf part_visit[2];     // this rank's replicas of the frontier words, IPC-exported
+	DevBuf part_peer_tab;     // device: uint32_t* [2][world-1] peers' replicas, offset to this rank's slice
+	std::vector<void *> part_peer_open; // IPC mappings to close at shutdown
+	bool part_p2p = false;
+	int part_p2p_W = 0;
+	int64_t part_p2p_Vp = 0;
 	DevBuf bfs_alive; // per-block-slot alive lane masks (msbfs_kernels.cuh)
 	DevBuf bfs_lane; // per-call lane tables
 	DevBuf bfs_ctrl; // device control block

@@ -419,6 +419,7 @@ namespace {
 
 struct PartBufs {
 	uint32_t *visit[2], *fbit[2], *seen, *hubacc, *alive_slots, *alive_local, *alive_all;
+	uint32_t *const *peer_tab; // fused exchange: [2][G-1] peers' replicas offset to my slice, or nullptr
 	BfsCtrl *ctrl;
 	size_t words_per_slice, fwords_per_slice; // uint32 counts
 };
@@ -429,7 +430,7 @@ int launch_part_level(Ctx *c, Csr *g, const PartBufs &b, int cur, int iter) {
 	cudaStream_t st = c->stream;
 	const int G = c->part_world, r = c->part_rank;
 	const size_t fwords = b.fwords_per_slice * G;
-	if (iter == 2) { // scrub the source words of level 0 out of the buffer that becomes `next` (zeroes the bitmap too)
+	if (iter == 2 && !b.peer_tab) { // scrub the source words of level 0 out of the buffer that becomes `next` (zeroes the bitmap too)
 		clear_by_bitmap_kernel<W><<<div_up(fwords, 256), 256, 0, st>>>(b.fbit[cur ^ 1], (uint32_t)fwords,
 		                                                              b.visit[cur ^ 1]);
 		count_launch(c);
@@ -448,6 +449,10 @@ int launch_part_level(Ctx *c, Csr *g, const PartBufs &b, int cur, int iter) {
 	a.fcur = b.fbit[cur];
 	a.fnext = b.fbit[cur ^ 1] + b.fwords_per_slice * r;
 	a.alive_slots = b.alive_slots;
+	if (b.peer_tab) { // fused exchange: kernels store new words into every peer's replica
+		a.peer_next = b.peer_tab + (size_t)(cur ^ 1) * (G - 1);
+		a.npeers = (uint32_t)(G - 1);
+	}
 	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, false, true);
 	launch_class<W, 2>(c, a, g->d_small, g->n_small, false, true);
 	if (g->n_mid) {
@@ -492,11 +497,14 @@ int part_exchange(Ctx *c, const PartBufs &b, int nxt) {
 	if (!nc) return PGQ_ERR_CUDA;
 	ncclComm_t comm = (ncclComm_t)c->nccl_comm;
 	PGQ_NCCL(nc, nc->GroupStart());
-	PGQ_NCCL(nc, nc->AllGather(b.visit[nxt] + b.words_per_slice * r, b.visit[nxt], b.words_per_slice, ncclUint32, comm, st));
+	if (!b.peer_tab) {
+		PGQ_NCCL(nc, nc->AllGather(b.visit[nxt] + b.words_per_slice * r, b.visit[nxt], b.words_per_slice, ncclUint32, comm, st));
+		c->stats.coll_bytes += b.words_per_slice * sizeof(uint32_t);
+	}
 	PGQ_NCCL(nc, nc->AllGather(b.fbit[nxt] + b.fwords_per_slice * r, b.fbit[nxt], b.fwords_per_slice, ncclUint32, comm, st));
 	PGQ_NCCL(nc, nc->AllGather(b.alive_local, b.alive_all, 16, ncclUint32, comm, st));
 	PGQ_NCCL(nc, nc->GroupEnd());
-	c->stats.coll_bytes += (b.words_per_slice + b.fwords_per_slice + 16) * sizeof(uint32_t);
+	c->stats.coll_bytes += (b.fwords_per_slice + 16) * sizeof(uint32_t);
 	return PGQ_OK;
 }
 
@@ -512,8 +520,11 @@ int msbfs_part_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found) {
 	b.words_per_slice = Vp * WPV;
 	b.fwords_per_slice = Vp / 32; // Vp is a multiple of 256
 	const size_t bm = b.words_per_slice * G * sizeof(uint32_t), fb = b.fwords_per_slice * G * sizeof(uint32_t);
-	PGQ_TRY(c->bfs_visit[0].reserve(bm));
-	PGQ_TRY(c->bfs_visit[1].reserve(bm));
+	const bool p2p = G > 1 && c->part_p2p && c->part_p2p_W == W && c->part_p2p_Vp == g->V;
+	if (!p2p) {
+		PGQ_TRY(c->bfs_visit[0].reserve(bm));
+		PGQ_TRY(c->bfs_visit[1].reserve(bm));
+	}
 	PGQ_TRY(c->bfs_seen.reserve(b.words_per_slice * sizeof(uint32_t)));
 	PGQ_TRY(c->bfs_inq[0].reserve(2 * fb));
 	PGQ_TRY(c->bfs_ctrl.reserve(sizeof(BfsCtrl)));
@@ -524,8 +535,9 @@ int msbfs_part_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found) {
 	PGQ_CUDA(cudaMemsetAsync(c->bfs_hubacc.p, 0, c->bfs_hubacc.cap, st));
 	PGQ_CUDA(cudaMemsetAsync(c->bfs_alive.p, 0, (size_t)ALIVE_SLOTS * 16 * sizeof(uint32_t), st));
 	c->bfs_dirty.valid = false; // the shared frontier buffers are used with another geometry here
-	b.visit[0] = c->bfs_visit[0].as<uint32_t>();
-	b.visit[1] = c->bfs_visit[1].as<uint32_t>();
+	b.visit[0] = p2p ? c->part_visit[0].as<uint32_t>() : c->bfs_visit[0].as<uint32_t>();
+	b.visit[1] = p2p ? c->part_visit[1].as<uint32_t>() : c->bfs_visit[1].as<uint32_t>();
+	b.peer_tab = p2p ? c->part_peer_tab.as<uint32_t *const>() : nullptr;
 	b.seen = c->bfs_seen.as<uint32_t>();
 	b.fbit[0] = c->bfs_inq[0].as<uint32_t>();
 	b.fbit[1] = b.fbit[0] + b.fwords_per_slice * G;
@@ -543,8 +555,10 @@ int msbfs_part_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found) {
 	c->stats.h2d_bytes += (uint64_t)nslots * 8;
 	for (int64_t bi = 0; bi < lt.nbatch; bi++) {
 		PGQ_CUDA(cudaMemsetAsync(b.seen, 0, b.words_per_slice * sizeof(uint32_t), st));
-		PGQ_CUDA(cudaMemsetAsync(b.visit[0], 0, bm, st));
-		PGQ_CUDA(cudaMemsetAsync(b.visit[1], 0, bm, st));
+		if (!p2p) { // with the fused exchange no word outside the bitmap is ever read: nothing to clear
+			PGQ_CUDA(cudaMemsetAsync(b.visit[0], 0, bm, st));
+			PGQ_CUDA(cudaMemsetAsync(b.visit[1], 0, bm, st));
+		}
 		PGQ_CUDA(cudaMemsetAsync(b.fbit[0], 0, 2 * fb, st));
 		bfs_init_part_kernel<<<1, W, 0, st>>>(d_src + bi * W, W, b.visit[0], d_found + bi * W, b.ctrl, b.fbit[0]);
 		count_launch(c);
@@ -563,7 +577,7 @@ int msbfs_part_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found) {
 			PGQ_TRY(part_exchange(c, b, cur ^ 1));
 			if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_c, st));
 			bfs_check_part_kernel<<<1, W, 0, st>>>(b.visit[cur ^ 1], d_dst + bi * W, W, d_found + bi * W, b.ctrl, iter,
-			                                       b.alive_all, G);
+			                                       b.alive_all, G, b.fbit[cur ^ 1]);
 			count_launch(c);
 			PGQ_CUDA(cudaMemcpyAsync(c->h_ctrl, b.ctrl, sizeof(BfsCtrl), cudaMemcpyDeviceToHost, st));
 			PGQ_CUDA(cudaStreamSynchronize(st));

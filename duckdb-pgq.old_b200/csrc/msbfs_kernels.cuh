@@ -87,7 +87,13 @@ struct PullArgs {
 	const uint32_t *fcur; // 1 bit per vertex: visit word non-empty (may over-approximate, never under)
 	uint32_t *fnext;      // same for `next`, produced by this level
 	uint32_t *alive_slots;   // [ALIVE_SLOTS][16] per-block-slot OR of the words produced this level
+	// 1-D partition, fused exchange: the other ranks' `next` replicas (peer memory over NVLink), each
+	// already offset to THIS rank's slice.  A vertex that gained bits is stored to every replica by
+	// the thread that produced it, so the frontier words never go through a separate collective.
+	uint32_t *const *peer_next;
+	uint32_t npeers;
 };
+
 
 template <int W>
 struct LaneCfg {
@@ -141,6 +147,11 @@ template <int SW>
 __device__ __forceinline__ void st_slice(uint32_t *p, const Slice<SW> &s) {
 	if (SW == 4) *reinterpret_cast<uint4 *>(p) = make_uint4(s.w[0], s.w[1], s.w[2], s.w[3]);
 	else *reinterpret_cast<uint2 *>(p) = make_uint2(s.w[0], s.w[1]);
+}
+
+template <int SW>
+__device__ __forceinline__ void st_peers(const PullArgs &a, size_t wo, const Slice<SW> &news) {
+	for (uint32_t p = 0; p < a.npeers; p++) st_slice<SW>(a.peer_next[p] + wo, news);
 }
 
 template <int SW>
@@ -401,6 +412,7 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	const bool vnew = ((bal >> (vslot * (GPV * TPV))) & ((1u << TPV) - 1u)) != 0;
 	const bool leader = writer && t == 0 && vnew;
 	if (leader) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+	if (a.npeers && writer && vnew) st_peers<SW>(a, wo, news); // whole word, zero slices included
 	// no global counters here: frontier_stats_kernel derives them from fnext afterwards
 }
 
@@ -474,7 +486,9 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 		}
 	}
-	if (__any_sync(FULL, slice_any<SW>(news)) && lane == 0) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+	const bool wany = __any_sync(FULL, slice_any<SW>(news));
+	if (wany && lane == 0) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+	if (a.npeers && wany && g == 0) st_peers<SW>(a, wo, news);
 }
 
 // ---- K4 hubs: one block per chunk of a hub's in-list, partial ORs merged with atomicOr ---------
@@ -560,6 +574,7 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 	const uint32_t hn = h < a.nlist ? a.list[h] : 0u;
 	if (leader) atomicOr(&a.fnext[hn >> 5], 1u << (hn & 31));
 	if (anyn) alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
+	if (a.npeers && gnew && h < a.nlist) st_peers<SW>(a, (size_t)hn * WPV + (size_t)t * SW, news);
 }
 
 // After a pull level: vertices in the new frontier and the sum of their out-degrees (the inputs of
@@ -892,6 +907,10 @@ __global__ void bfs_init_part_kernel(const uint32_t *__restrict__ lane_src, int 
 	const uint32_t s = lane_src[lane];
 	const bool used = s != 0xFFFFFFFFu;
 	found[lane] = -1;
+	// words outside the bitmap are never read, so only the source words need a defined value
+	if (used)
+		for (int i = 0; i < W / 32; i++) visit[(size_t)s * (W / 32) + i] = 0;
+	__syncthreads();
 	if (used) {
 		atomicOr(&visit[(size_t)s * (W / 32) + (lane >> 5)], 1u << (lane & 31));
 		atomicOr(&fbit0[s >> 5], 1u << (s & 31));
@@ -927,7 +946,8 @@ __global__ void alive_fold_kernel(uint32_t *__restrict__ alive_slots, uint32_t *
 // alive iff some rank produced a bit for it.  Identical on all ranks, no further exchange.
 __global__ void bfs_check_part_kernel(const uint32_t *__restrict__ next, const uint32_t *__restrict__ lane_dst, int W,
                                       int32_t *__restrict__ found, BfsCtrl *ctrl, int iter,
-                                      const uint32_t *__restrict__ alive_all, int world) {
+                                      const uint32_t *__restrict__ alive_all, int world,
+                                      const uint32_t *__restrict__ fnext) {
 	__shared__ uint32_t cnt;
 	__shared__ uint32_t anyalive;
 	const int lane = threadIdx.x;
@@ -941,7 +961,8 @@ __global__ void bfs_check_part_kernel(const uint32_t *__restrict__ next, const u
 	bool hit = false;
 	if (act) {
 		const uint32_t d = lane_dst[lane];
-		hit = (next[(size_t)d * (W / 32) + (lane >> 5)] >> (lane & 31)) & 1u;
+		// the word is meaningful only when the vertex is in the new frontier
+		hit = ((fnext[d >> 5] >> (d & 31)) & 1u) && ((next[(size_t)d * (W / 32) + (lane >> 5)] >> (lane & 31)) & 1u);
 		if (hit) found[lane] = iter;
 	}
 	const unsigned hm = __ballot_sync(0xffffffffu, hit);

@@ -137,6 +137,15 @@ int pgq_part_csr_create(pgq_ctx_t *ctx, int32_t id, int64_t v_size);
 int pgq_part_csr_add_edges_device(pgq_ctx_t *ctx, int32_t id, const int64_t *d_src, const int64_t *d_dst,
                                   int64_t n);
 int pgq_part_csr_finalize(pgq_ctx_t *ctx, int32_t id);
+/* Fused exchange (optional, world > 1): the level kernels store new frontier words straight into
+ * every rank's replica through NVLink peer memory instead of a per-level ncclAllGather of the word
+ * array; only the 1-bit frontier bitmap and the 64-byte alive masks still go through NCCL (which
+ * doubles as the level barrier).  export: allocates this rank's replicas for (csr id, lanes) and
+ * writes 2 x 64 bytes of CUDA IPC handles; the caller all-gathers them (rank-major) and every rank
+ * calls import with the world x 2 x 64 bytes. */
+#define PGQ_P2P_HANDLE_BYTES 128
+int pgq_part_p2p_export(pgq_ctx_t *ctx, int32_t id, int lanes, void *out_handles128);
+int pgq_part_p2p_import(pgq_ctx_t *ctx, const void *all_handles);
 int pgq_part_iterativelength(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
                              const uint8_t *src_valid, const uint8_t *dst_valid, int64_t *out,
                              uint8_t *out_valid);

@@ -29,6 +29,9 @@ def main():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--check", action="store_true")
     ap.add_argument("--trace", action="store_true")
+    ap.add_argument("--p2p", action="store_true", help="fused exchange over NVLink peer memory")
+    ap.add_argument("--check-single", action="store_true",
+                    help="rank 0 also answers the pairs with the (oracle-verified) single-GPU path and compares")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -67,6 +70,8 @@ def main():
     ps = rng.randint(0, V, size=a.pairs).astype(np.int64)
     pd = rng.randint(0, V, size=a.pairs).astype(np.int64)
     ctx.set_option("lanes", a.lanes)
+    if a.p2p and world > 1:
+        ctx.part_p2p_setup(dist, 0, a.lanes, world)
     out, ov = ctx.part_iterativelength(0, ps, pd)  # warm
     ctx.set_option("timing", 1)
     if a.trace:
@@ -84,7 +89,7 @@ def main():
             "ms_per_step": secs * 1e3, "pairs_per_s": a.pairs / secs, "levels": int(st["levels"] // a.steps),
             "batches": int(st["batches"] // a.steps), "pull_ms": st["level_kernel_ms"] / a.steps,
             "exchange_ms": st["coll_ms"] / a.steps, "coll_bytes_per_step": int(st["coll_bytes"] // a.steps),
-            "build_s": build_s, "found": int(ov.sum())}
+            "build_s": build_s, "found": int(ov.sum()), "p2p": bool(a.p2p and world > 1)}
     if a.check and rank == 0:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import orc
@@ -93,6 +98,16 @@ def main():
         eo, ev = orc.iterativelength(V, v, e, ps, pd)
         ok = bool(np.array_equal(ov, ev) and np.array_equal(np.where(ev == 1, out, -1), np.where(ev == 1, eo, -1)))
         line["parity_vs_oracle"] = ok
+    if a.check_single and rank == 0:
+        d_s, d_d = ctx.dev_alloc(E * 8), ctx.dev_alloc(E * 8)
+        ctx.gen_rmat_device(SEED_BASE + a.scale, a.scale, E, d_s, d_d)
+        ctx.csr_build_device(1, V, E, d_s, d_d)
+        ctx.dev_free(d_s)
+        ctx.dev_free(d_d)
+        ctx.set_option("lanes", 0)
+        so, sv = ctx.iterativelength(1, ps, pd)
+        line["parity_vs_single_gpu"] = bool(np.array_equal(sv, ov) and
+                                            np.array_equal(np.where(sv == 1, so, -1), np.where(ov == 1, out, -1)))
     print(json.dumps(line), flush=True)
     ctx.close()
     if dist is not None:
