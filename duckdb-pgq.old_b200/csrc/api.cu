@@ -170,9 +170,11 @@ int pgq_shutdown(pgq_ctx_t *ctx) {
 	}
 	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
 	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->bfs_seen, &c->bfs_visit[0],
-	                  &c->bfs_visit[1], &c->bfs_parent, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
+	                  &c->bfs_visit[1], &c->bfs_hist_tab, &c->bfs_pathout, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
 	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->part_visit[0], &c->part_visit[1], &c->part_peer_tab, &c->l2_flush};
 	for (DevBuf *b : bufs) b->release();
+	for (DevBuf &hb : c->bfs_hist) hb.release();
+	c->bfs_hist.clear();
 	if (c->h_ctrl) cudaFreeHost(c->h_ctrl);
 	cudaEventDestroy(c->ev_a);
 	cudaEventDestroy(c->ev_b);

@@ -155,7 +155,10 @@ struct Ctx {
 	// scratch reused across calls
 	DevBuf scan_tmp;
 	DevBuf sort_keys[2], sort_p0[2], sort_p1[2], sort_hist;
-	DevBuf bfs_seen, bfs_visit[2], bfs_parent, bfs_hubacc;
+	DevBuf bfs_seen, bfs_visit[2], bfs_hubacc;
+	std::vector<DevBuf> bfs_hist; // shortestpath: one frontier buffer per level of the running batch
+	DevBuf bfs_hist_tab;          // device pointer table of bfs_hist
+	DevBuf bfs_pathout;           // path values of one batch before the D2H copy
 	DevBuf bfs_queue[2], bfs_inq[2]; // push work queues + dedupe bitmaps
 	BfsDirty bfs_dirty;
 	// 1-D partition

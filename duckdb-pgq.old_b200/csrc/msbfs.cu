@@ -10,7 +10,7 @@ namespace pgq {
 namespace {
 
 struct BatchBufs {
-	uint32_t *seen, *visit[2], *parent, *hubacc;
+	uint32_t *seen, *visit[2], *hubacc;
 	uint2 *queue[2];
 	uint32_t *fbit[3]; // rotating frontier bitmaps (1 bit per vertex, padded): current / next / two levels ago
 	size_t fbit_bytes;
@@ -20,7 +20,7 @@ struct BatchBufs {
 };
 
 template <int W, int GPV>
-void launch_class(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool parents, bool filter) {
+void launch_class(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter) {
 	if (!nlist) return;
 	using C = LaneCfg<W>;
 	constexpr int VPW = C::G / GPV;
@@ -28,15 +28,14 @@ void launch_class(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool 
 	a.nlist = nlist;
 	const uint32_t warps = div_up(nlist, VPW);
 	const uint32_t grid = div_up((uint64_t)warps * 32, 128);
-	if (parents) pull_list_kernel<W, GPV, true, true><<<grid, 128, 0, c->stream>>>(a);
-	else if (filter) pull_list_kernel<W, GPV, false, true><<<grid, 128, 0, c->stream>>>(a);
-	else pull_list_kernel<W, GPV, false, false><<<grid, 128, 0, c->stream>>>(a);
+	if (filter) pull_list_kernel<W, GPV, true><<<grid, 128, 0, c->stream>>>(a);
+	else pull_list_kernel<W, GPV, false><<<grid, 128, 0, c->stream>>>(a);
 	count_launch(c);
 }
 
 // One bottom-up level: frontier visit[cur]/fbit[cur] -> next visit[cur^1]/fbit[cur^1].
 template <int W>
-int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, bool parents, int iter, bool filter) {
+int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, int iter, bool filter) {
 	using C = LaneCfg<W>;
 	cudaStream_t st = c->stream;
 	// fb[0] describes visit[cur], fb[1] is built for visit[cur^1], fb[2] describes what visit[cur^1]
@@ -55,7 +54,6 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, boo
 	a.visit = b.visit[cur];
 	a.next = b.visit[cur ^ 1];
 	a.seen = b.seen;
-	a.parent = b.parent;
 	a.ctrl = b.ctrl;
 	a.V = (uint32_t)g->V;
 	a.hubacc = b.hubacc;
@@ -63,11 +61,9 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, boo
 	a.fcur = b.fbit[fb[0]];
 	a.fnext = b.fbit[fb[1]];
 	a.alive_slots = b.alive_slots;
-	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, parents, filter);
-	launch_class<W, 2>(c, a, g->d_small, g->n_small, parents, filter);
-	if (parents) {
-		launch_class<W, C::G>(c, a, g->d_mid, g->n_mid, true, true);
-	} else if (g->n_mid) {
+	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, filter);
+	launch_class<W, 2>(c, a, g->d_small, g->n_small, filter);
+	if (g->n_mid) {
 		a.list = g->d_mid.as<uint32_t>();
 		a.nlist = g->n_mid;
 		const uint32_t grid = div_up((uint64_t)g->n_mid * 32, 128);
@@ -76,18 +72,13 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, boo
 		count_launch(c);
 	}
 	if (g->n_hub) {
-		if (parents) {
-			// ordered first-match needs a single consumer per vertex: one warp per hub
-			launch_class<W, C::G>(c, a, g->d_hub, g->n_hub, true, true);
-		} else {
-			a.list = g->d_hub.as<uint32_t>();
-			a.nlist = g->n_hub;
-			a.chunks = g->d_hubchunks.as<HubChunk>();
-			a.nchunks = g->n_hubchunks;
-			pull_hub_kernel<W><<<g->n_hubchunks, 256, 0, st>>>(a);
-			hub_finalize_kernel<W><<<div_up((uint64_t)g->n_hub * C::TPV, 256), 256, 0, st>>>(a);
-			count_launch(c, 2);
-		}
+		a.list = g->d_hub.as<uint32_t>();
+		a.nlist = g->n_hub;
+		a.chunks = g->d_hubchunks.as<HubChunk>();
+		a.nchunks = g->n_hubchunks;
+		pull_hub_kernel<W><<<g->n_hubchunks, 256, 0, st>>>(a);
+		hub_finalize_kernel<W><<<div_up((uint64_t)g->n_hub * C::TPV, 256), 256, 0, st>>>(a);
+		count_launch(c, 2);
 	}
 	frontier_stats_kernel<<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[fb[1]], b.fbit_words, (uint32_t)g->V,
 	                                                               g->d_off.as<int64_t>(), b.ctrl);
@@ -95,13 +86,12 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, boo
 	return PGQ_OK;
 }
 
-int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, const int *fb, bool parents, int iter,
-                   bool filter) {
+int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, const int *fb, int iter, bool filter) {
 	switch (W) {
-	case 64: return launch_level<64>(c, g, b, cur, fb, parents, iter, filter);
-	case 128: return launch_level<128>(c, g, b, cur, fb, parents, iter, filter);
-	case 256: return launch_level<256>(c, g, b, cur, fb, parents, iter, filter);
-	case 512: return launch_level<512>(c, g, b, cur, fb, parents, iter, filter);
+	case 64: return launch_level<64>(c, g, b, cur, fb, iter, filter);
+	case 128: return launch_level<128>(c, g, b, cur, fb, iter, filter);
+	case 256: return launch_level<256>(c, g, b, cur, fb, iter, filter);
+	case 512: return launch_level<512>(c, g, b, cur, fb, iter, filter);
 	}
 	set_error("unsupported lane width %d", W);
 	return PGQ_ERR_INVALID;
@@ -185,13 +175,12 @@ int read_ctrl(Ctx *c, const BatchBufs &b, BfsCtrl *h) {
 	return PGQ_OK;
 }
 
-int alloc_bufs(Ctx *c, Csr *g, int W, bool parents, BatchBufs *b) {
+int alloc_bufs(Ctx *c, Csr *g, int W, BatchBufs *b) {
 	const size_t bm = (size_t)(g->V > 0 ? g->V : 1) * (W / 8);
 	PGQ_TRY(c->bfs_seen.reserve(bm));
 	PGQ_TRY(c->bfs_visit[0].reserve(bm));
 	PGQ_TRY(c->bfs_visit[1].reserve(bm));
 	PGQ_TRY(c->bfs_ctrl.reserve(sizeof(BfsCtrl)));
-	if (parents) PGQ_TRY(c->bfs_parent.reserve((size_t)(g->V > 0 ? g->V : 1) * W * sizeof(uint32_t)));
 	const size_t hb = (size_t)(g->n_hub > 0 ? g->n_hub : 1) * (W / 8);
 	if (hb > c->bfs_hubacc.cap) {
 		PGQ_TRY(c->bfs_hubacc.reserve(hb));
@@ -201,7 +190,6 @@ int alloc_bufs(Ctx *c, Csr *g, int W, bool parents, BatchBufs *b) {
 	b->seen = c->bfs_seen.as<uint32_t>();
 	b->visit[0] = c->bfs_visit[0].as<uint32_t>();
 	b->visit[1] = c->bfs_visit[1].as<uint32_t>();
-	b->parent = parents ? c->bfs_parent.as<uint32_t>() : nullptr;
 	b->hubacc = c->bfs_hubacc.as<uint32_t>();
 	b->ctrl = c->bfs_ctrl.as<BfsCtrl>();
 	PGQ_TRY(c->bfs_alive.reserve((size_t)ALIVE_SLOTS * 16 * sizeof(uint32_t)));
@@ -221,12 +209,29 @@ int alloc_bufs(Ctx *c, Csr *g, int W, bool parents, BatchBufs *b) {
 	return PGQ_OK;
 }
 
+// A zeroed frontier buffer for level `k` of a batch that keeps its history (shortestpath).
+int hist_level(Ctx *c, size_t k, size_t bm, uint32_t **out) {
+	if (c->bfs_hist.size() <= k) c->bfs_hist.resize(k + 1);
+	PGQ_TRY(c->bfs_hist[k].reserve(bm ? bm : 16));
+	if (bm) PGQ_CUDA(cudaMemsetAsync(c->bfs_hist[k].p, 0, bm, c->stream));
+	*out = c->bfs_hist[k].as<uint32_t>();
+	return PGQ_OK;
+}
+
 // One batch of W lanes.  d_lane_src/dst/found point at this batch's W slots.
-int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uint32_t *d_lane_src,
-              const uint32_t *d_lane_dst, int32_t *d_found) {
+// keep_hist (shortestpath): level k's frontier stays in c->bfs_hist[k] instead of a ping-pong pair, so
+// the path kernel can apply the parent rule afterwards; *out_levels = levels run.
+int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, const uint32_t *d_lane_src,
+              const uint32_t *d_lane_dst, int32_t *d_found, int *out_levels = nullptr) {
 	cudaStream_t st = c->stream;
+	BatchBufs b = b_in;
 	const size_t bm = (size_t)g->V * (W / 8);
-	if (bm) {
+	if (keep_hist) {
+		if (bm) PGQ_CUDA(cudaMemsetAsync(b.seen, 0, bm, st));
+		PGQ_TRY(hist_level(c, 0, bm, &b.visit[0]));
+		b.visit[1] = nullptr; // set per level
+		c->bfs_dirty.valid = false;
+	} else if (bm) {
 		PGQ_CUDA(cudaMemsetAsync(b.seen, 0, bm, st));
 		// The frontier buffers must start all-zero (a top-down level ORs into them).  After a clean
 		// batch on the same buffers their only non-zero words are the ones the last two frontier
@@ -248,13 +253,18 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 	BfsCtrl h;
 	PGQ_TRY(read_ctrl(c, b, &h));
 	c->stats.batches++;
+	const uint64_t levels_at_start = c->stats.levels;
 	uint32_t active = h.n_active;
 	int cur = 0, q = 0;
 	int fb[3] = {0, 1, 2}; // bitmap of visit[cur] / being built for visit[cur^1] / of what visit[cur^1] holds
 	bool have_queue = true; // queue[q] describes visit[cur] and visit[cur^1] is all-zero
 	for (int iter = 1; active; iter++) {
 		// direction switch on frontier density: top-down while the frontier's out-edges are few
-		const bool push = !parents && c->opt.direction == 0 &&
+		if (keep_hist) { // fresh zeroed buffer for this level's output; the input stays where it is
+			b.visit[cur] = c->bfs_hist[(size_t)iter - 1].as<uint32_t>();
+			PGQ_TRY(hist_level(c, (size_t)iter, bm, &b.visit[cur ^ 1]));
+		}
+		const bool push = c->opt.direction == 0 &&
 		                  (unsigned long long)h.out_edges * (unsigned long long)c->opt.push_beta <=
 		                      (unsigned long long)g->E &&
 		                  (unsigned long long)h.out_verts * (unsigned long long)c->opt.push_vbeta <=
@@ -272,7 +282,7 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 			// the bitmap test is dead weight once the frontier holds most of the edges
 			const bool filter = (unsigned long long)h.out_edges * (unsigned long long)c->opt.filter_gamma <=
 			                    (unsigned long long)g->E;
-			PGQ_TRY(launch_level_w(c, g, b, W, cur, fb, parents, iter, filter));
+			PGQ_TRY(launch_level_w(c, g, b, W, cur, fb, iter, filter));
 			have_queue = false;
 		}
 		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
@@ -301,7 +311,8 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b, int W, bool parents, const uin
 		if (!h.change_out) break;
 		active = h.n_active;
 	}
-	if (bm) { // what the frontier buffers hold now, for the next batch's scrub
+	if (out_levels) *out_levels = (int)(c->stats.levels - levels_at_start);
+	if (bm && !keep_hist) { // what the frontier buffers hold now, for the next batch's scrub
 		BfsDirty &d = c->bfs_dirty;
 		d.valid = true;
 		d.W = W;
@@ -335,7 +346,7 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 	PGQ_TRY(csr_prepare(c, g));
 	const bool want_paths = paths != nullptr;
 	BatchBufs b{};
-	PGQ_TRY(alloc_bufs(c, g, W, want_paths, &b));
+	PGQ_TRY(alloc_bufs(c, g, W, &b));
 	cudaStream_t st = c->stream;
 	// lane tables: src | dst | found | lane_off(u64, paths only)
 	size_t lane_bytes = (size_t)nslots * (2 * sizeof(uint32_t) + sizeof(int32_t)) + (size_t)W * sizeof(uint64_t) + 64;
@@ -348,11 +359,12 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 	PGQ_CUDA(cudaMemcpyAsync(d_dst, lt.dst.data(), (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
 	c->stats.h2d_bytes += (uint64_t)nslots * 8;
 	const uint64_t levels_before = c->stats.levels;
-	TmpBuf d_out;
+	DevBuf &d_out = c->bfs_pathout; // persistent: a per-call buffer would cudaMalloc/cudaFree every batch
 	std::vector<uint64_t> lane_off((size_t)W);
 	uint64_t total = 0; // running list offset over all rows (paths)
 	for (int64_t bi = 0; bi < lt.nbatch; bi++) {
-		PGQ_TRY(run_batch(c, g, b, W, want_paths, d_src + bi * W, d_dst + bi * W, d_found + bi * W));
+		int nlev = 0;
+		PGQ_TRY(run_batch(c, g, b, W, want_paths, d_src + bi * W, d_dst + bi * W, d_found + bi * W, &nlev));
 		if (!want_paths) continue;
 		// ---- K8: reconstruct this batch's paths in ROW order (R9) ----
 		int32_t *hf = h_found + bi * W;
@@ -382,12 +394,20 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 		const uint64_t bt = total - base;
 		paths->vals.resize(total);
 		if (bt) {
-			PGQ_TRY(d_out.reserve(bt * sizeof(int64_t)));
+			if (bt * sizeof(int64_t) > d_out.cap) PGQ_TRY(d_out.reserve(bt * sizeof(int64_t) * 2));
 			PGQ_CUDA(cudaMemcpyAsync(d_lane_off, lane_off.data(), (size_t)W * 8, cudaMemcpyHostToDevice, st));
-			bfs_paths_kernel<<<div_up(W, 128), 128, 0, st>>>(
-			    b.parent, g->d_isrc.as<uint32_t>(), g->d_ipos.as<uint32_t>(),
+			// device table of the level buffers (they may have been reallocated by this batch)
+			std::vector<const uint32_t *> hp((size_t)nlev + 1);
+			for (int k = 0; k <= nlev; k++) hp[(size_t)k] = c->bfs_hist[(size_t)k].as<uint32_t>();
+			PGQ_TRY(c->bfs_hist_tab.reserve(hp.size() * sizeof(uint32_t *)));
+			PGQ_CUDA(cudaMemcpyAsync(c->bfs_hist_tab.p, hp.data(), hp.size() * sizeof(uint32_t *),
+			                         cudaMemcpyHostToDevice, st));
+			bfs_paths_hist_kernel<<<W, 256, 0, st>>>(
+			    c->bfs_hist_tab.as<const uint32_t *const>(), g->d_ioff.as<uint32_t>(), g->d_isrc.as<uint32_t>(),
+			    g->d_ipos.as<uint32_t>(),
 			    g->have_eid ? g->d_eid.as<int64_t>() : nullptr, g->keep_rows ? g->d_row.as<uint32_t>() : nullptr,
-			    d_dst + bi * W, d_found + bi * W, (const unsigned long long *)d_lane_off, W, paths->mode,
+			    d_src + bi * W, d_dst + bi * W, d_found + bi * W, (const unsigned long long *)d_lane_off, W,
+			    paths->mode,
 			    d_out.as<int64_t>());
 			count_launch(c);
 			PGQ_CUDA(cudaMemcpyAsync(paths->vals.data() + base, d_out.p, bt * sizeof(int64_t),
@@ -453,8 +473,8 @@ int launch_part_level(Ctx *c, Csr *g, const PartBufs &b, int cur, int iter) {
 		a.peer_next = b.peer_tab + (size_t)(cur ^ 1) * (G - 1);
 		a.npeers = (uint32_t)(G - 1);
 	}
-	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, false, true);
-	launch_class<W, 2>(c, a, g->d_small, g->n_small, false, true);
+	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, true);
+	launch_class<W, 2>(c, a, g->d_small, g->n_small, true);
 	if (g->n_mid) {
 		a.list = g->d_mid.as<uint32_t>();
 		a.nlist = g->n_mid;
@@ -651,7 +671,7 @@ int msbfs_run_device(Ctx *c, Csr *g, int64_t n, const int64_t *d_srcs, const int
 	const int64_t nbatch = (n + W - 1) / W, nslots = nbatch * W;
 	PGQ_TRY(csr_prepare(c, g));
 	BatchBufs b{};
-	PGQ_TRY(alloc_bufs(c, g, W, false, &b));
+	PGQ_TRY(alloc_bufs(c, g, W, &b));
 	cudaStream_t st = c->stream;
 	PGQ_TRY(c->bfs_lane.reserve((size_t)nslots * 12 + 64));
 	uint32_t *d_src = c->bfs_lane.as<uint32_t>() + 4; // [0] = error flag

@@ -9,6 +9,9 @@
 // Parent rule R7 falls out of the reverse CSR's order: the in-list of n is sorted by
 // (source id ascending, forward CSR offset ascending), so the FIRST in-edge whose source has
 // lane l in the frontier, at the level n is first reached by l, is the reference's parent.
+// shortestpath therefore runs the same level kernels as iterativelength and only KEEPS every
+// level's frontier; bfs_paths_hist_kernel finds parents by that rule while walking back from the
+// destination (no V x W parent array, no per-bit parent stores in the hot loop).
 //
 // Layout: bitmaps are uint32[V][W/32]; a thread owns a 128-bit slice (64-bit when W=64) of one
 // vertex word and moves it with one vector load/store.  HBM-bound: per level
@@ -74,7 +77,6 @@ struct PullArgs {
 	const uint32_t *visit;
 	uint32_t *next;
 	uint32_t *seen;
-	uint32_t *parent; // [V][W] in-edge index, PARENTS only
 	BfsCtrl *ctrl;
 	uint32_t V;
 	uint32_t small_max;
@@ -181,20 +183,6 @@ __device__ __forceinline__ Slice<SW> warp_or_groups(Slice<SW> s) {
 	return s;
 }
 
-// record parent = in-edge index j for every set bit of `bits` (lanes base..base+SW*32)
-template <int SW>
-__device__ __forceinline__ void store_parents(uint32_t *prow, const Slice<SW> &bits, uint32_t j) {
-#pragma unroll
-	for (int i = 0; i < SW; i++) {
-		uint32_t b = bits.w[i];
-		while (b) {
-			int k = __ffs(b) - 1;
-			b &= b - 1;
-			prow[i * 32 + k] = j;
-		}
-	}
-}
-
 __device__ __forceinline__ void flag_change(BfsCtrl *ctrl, bool anynew) {
 	if (__any_sync(0xffffffffu, anynew)) {
 		if ((threadIdx.x & 31) == 0) ctrl->change = 1u;
@@ -262,11 +250,7 @@ __device__ __forceinline__ bool group_any(bool x) {
 // frontier bit is clear before their word is touched (pays off unless the frontier holds most
 // edges).  Loops are warp-uniform (trip count = the slowest vertex of the warp) because the
 // reductions use full-mask shuffles.
-//
-// PARENTS (R7): in-edges are consumed in ascending index; a lane bit offered by several
-// sub-groups in the same step goes to the lowest sub-group (exclusive prefix-OR) = lowest in-edge
-// index = (smallest source id, then lowest forward CSR offset).
-template <int W, int GPV, bool PARENTS, bool FILTER>
+template <int W, int GPV, bool FILTER>
 __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
@@ -311,9 +295,8 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 		for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
 	}
 	bool open = slice_any<SW>(unseen); // identical in all sub-groups of the vertex (same t)
-	Slice<SW> acc = slice_zero<SW>();  // PARENTS: lanes claimed so far; else: this sub-group's OR
+	Slice<SW> acc = slice_zero<SW>();  // this sub-group's OR
 	Slice<SW> tot = slice_zero<SW>();
-	uint32_t *prow = PARENTS ? a.parent + (size_t)n * W + (size_t)t * (SW * 32) : nullptr;
 	uint32_t fm = 0; // bit u: edge u of the current round has its source in the frontier
 #pragma unroll
 	for (int u = 0; u < U; u++) {
@@ -340,51 +323,16 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 			if (FILTER && f) f = fbit_test(a.fcur, v1[u]);
 			fn |= (f ? 1u : 0u) << u;
 		}
-		if (!PARENTS) {
 #pragma unroll
-			for (int u = 0; u < U; u++) {
+		for (int u = 0; u < U; u++) {
 #pragma unroll
-				for (int i = 0; i < SW; i++) acc.w[i] |= w[u].w[i];
-			}
-			tot = acc;
+			for (int i = 0; i < SW; i++) acc.w[i] |= w[u].w[i];
+		}
+		tot = acc;
 #pragma unroll
-			for (int d = TPV; d < TPV * GPV; d <<= 1) {
+		for (int d = TPV; d < TPV * GPV; d <<= 1) {
 #pragma unroll
-				for (int i = 0; i < SW; i++) tot.w[i] |= __shfl_xor_sync(FULL, tot.w[i], d);
-			}
-		} else {
-#pragma unroll
-			for (int u = 0; u < U; u++) {
-				Slice<SW> cand;
-#pragma unroll
-				for (int i = 0; i < SW; i++) cand.w[i] = w[u].w[i] & unseen.w[i] & ~acc.w[i];
-				if (GPV == 1) {
-					store_parents<SW>(prow, cand, j + u * GPV);
-#pragma unroll
-					for (int i = 0; i < SW; i++) acc.w[i] |= cand.w[i];
-				} else if (__any_sync(FULL, slice_any<SW>(cand))) {
-					Slice<SW> incl = cand;
-#pragma unroll
-					for (int d = 1; d < GPV; d <<= 1) {
-#pragma unroll
-						for (int i = 0; i < SW; i++) {
-							const uint32_t y = __shfl_up_sync(FULL, incl.w[i], d * TPV);
-							if (sg >= (uint32_t)d) incl.w[i] |= y;
-						}
-					}
-					Slice<SW> take;
-#pragma unroll
-					for (int i = 0; i < SW; i++) {
-						const uint32_t y = __shfl_up_sync(FULL, incl.w[i], TPV);
-						const uint32_t excl = sg == 0 ? 0u : y;
-						const uint32_t all = __shfl_sync(FULL, incl.w[i], vslot * (GPV * TPV) + (GPV - 1) * TPV + t);
-						take.w[i] = cand.w[i] & ~excl;
-						acc.w[i] |= all;
-					}
-					store_parents<SW>(prow, take, j + u * GPV);
-				}
-			}
-			tot = acc;
+			for (int i = 0; i < SW; i++) tot.w[i] |= __shfl_xor_sync(FULL, tot.w[i], d);
 		}
 		open = open && !slice_covers<SW>(tot, unseen);
 		j = jn;
@@ -984,35 +932,79 @@ __global__ void bfs_check_part_kernel(const uint32_t *__restrict__ next, const u
 	}
 }
 
-// K8: one thread per lane walks dst -> parent in-edges -> src and writes the list back to front.
-// mode 0: [src,..,dst] (len L+1); mode 1: [src,e0,v1,..,dst] (len 2L+1).  R7/R8.
-__global__ void bfs_paths_kernel(const uint32_t *__restrict__ parent, const uint32_t *__restrict__ isrc,
-                                 const uint32_t *__restrict__ ipos, const int64_t *__restrict__ eid,
-                                 const uint32_t *__restrict__ row, const uint32_t *__restrict__ lane_dst,
-                                 const int32_t *__restrict__ found, const unsigned long long *__restrict__ lane_off,
-                                 int W, int mode, int64_t *__restrict__ out) {
-	const int lane = blockIdx.x * blockDim.x + threadIdx.x;
+// K8: path reconstruction from the per-level frontier history (R7/R8).  One BLOCK per lane walks
+// dst -> src.  The parent of `cur` (discovered at level k+1) is the FIRST in-edge, in reverse-CSR
+// order (source id, then forward offset), whose source holds this lane's bit in the frontier of
+// level k: the block tests 256 in-edges per step and takes the lowest hit (a hub's in-list can be
+// 10^5 entries long before the first hit).  Level 0's frontier is the source itself, found by
+// binary search in the id-sorted in-list.
+// mode 0: [src,..,dst] (len L+1); mode 1: [src,e0,v1,..,dst] (len 2L+1).
+__global__ void __launch_bounds__(256) bfs_paths_hist_kernel(const uint32_t *const *__restrict__ hist,
+                                                             const uint32_t *__restrict__ ioff,
+                                                             const uint32_t *__restrict__ isrc,
+                                                             const uint32_t *__restrict__ ipos,
+                                                             const int64_t *__restrict__ eid,
+                                                             const uint32_t *__restrict__ row,
+                                                             const uint32_t *__restrict__ lane_src,
+                                                             const uint32_t *__restrict__ lane_dst,
+                                                             const int32_t *__restrict__ found,
+                                                             const unsigned long long *__restrict__ lane_off, int W,
+                                                             int mode, int64_t *__restrict__ out) {
+	__shared__ uint32_t s_first;
+	const int lane = blockIdx.x; // BFS lane served by this block
+	const uint32_t tid = threadIdx.x;
 	if (lane >= W) return;
 	const int L = found[lane];
 	if (L < 0) return;
+	const int WPV = W / 32, wsel = lane >> 5;
+	const uint32_t bit = 1u << (lane & 31);
 	uint32_t cur = lane_dst[lane];
 	int64_t *o = out + lane_off[lane];
-	if (mode == 0) {
-		o[L] = (int64_t)cur;
-		for (int k = L - 1; k >= 0; k--) {
-			uint32_t q = parent[(size_t)cur * W + lane];
-			cur = isrc[q];
-			o[k] = (int64_t)cur;
+	if (tid == 0) o[mode == 0 ? L : 2 * L] = (int64_t)cur;
+	for (int k = L - 1; k >= 0; k--) {
+		const uint32_t lo = ioff[cur], hi = ioff[cur + 1];
+		uint32_t pq = 0xFFFFFFFFu;
+		if (k == 0) {
+			// frontier 0 = {src}: first in-edge from src = lower bound in the id-sorted in-list
+			const uint32_t s = lane_src[lane];
+			uint32_t a = lo, b = hi;
+			while (a < b) {
+				const uint32_t mid = a + ((b - a) >> 1);
+				if (isrc[mid] < s) a = mid + 1;
+				else b = mid;
+			}
+			if (a < hi && isrc[a] == s) pq = a;
+		} else {
+			const uint32_t *fr = hist[k];
+			for (uint32_t base = lo; base < hi; base += 256) {
+				if (tid == 0) s_first = 0xFFFFFFFFu;
+				__syncthreads();
+				const uint32_t j = base + tid;
+				bool ok = false;
+				if (j < hi) ok = (fr[(size_t)isrc[j] * WPV + wsel] & bit) != 0;
+				const unsigned m = __ballot_sync(0xffffffffu, ok);
+				if (m && (tid & 31) == 0) atomicMin(&s_first, base + (tid & ~31u) + (uint32_t)(__ffs(m) - 1));
+				__syncthreads();
+				pq = s_first;
+				__syncthreads(); // everyone has read s_first before the next step resets it
+				if (pq != 0xFFFFFFFFu) break;
+			}
 		}
-	} else {
-		o[2 * L] = (int64_t)cur;
-		for (int k = L - 1; k >= 0; k--) {
-			uint32_t q = parent[(size_t)cur * W + lane];
-			uint32_t p = ipos[q];
-			o[2 * k + 1] = eid ? eid[p] : (int64_t)row[p];
-			cur = isrc[q];
-			o[2 * k] = (int64_t)cur;
+		if (pq == 0xFFFFFFFFu) { // cannot happen for a found lane; leave a visible marker
+			if (tid == 0) o[mode == 0 ? k : 2 * k] = -1;
+			return;
 		}
+		const uint32_t pv = isrc[pq];
+		if (tid == 0) {
+			if (mode == 0) {
+				o[k] = (int64_t)pv;
+			} else {
+				const uint32_t p = ipos[pq];
+				o[2 * k + 1] = eid ? eid[p] : (int64_t)row[p];
+				o[2 * k] = (int64_t)pv;
+			}
+		}
+		cur = pv;
 	}
 }
 
