@@ -33,6 +33,23 @@ void launch_class(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool 
 	count_launch(c);
 }
 
+// tiny class: straight-line kernel when the class really is <= 4 in-edges, else the generic one
+template <int W>
+void launch_tiny(Ctx *c, PullArgs &a, Csr *g, bool filter) {
+	if (!g->n_tiny) return;
+	if (g->bins_tiny_max > 4) {
+		launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, filter);
+		return;
+	}
+	using C = LaneCfg<W>;
+	a.list = g->d_tiny.as<uint32_t>();
+	a.nlist = g->n_tiny;
+	const uint32_t grid = div_up((uint64_t)div_up(g->n_tiny, C::G) * 32, 128);
+	if (filter) pull_tiny_kernel<W, true><<<grid, 128, 0, c->stream>>>(a);
+	else pull_tiny_kernel<W, false><<<grid, 128, 0, c->stream>>>(a);
+	count_launch(c);
+}
+
 // One bottom-up level: frontier visit[cur]/fbit[cur] -> next visit[cur^1]/fbit[cur^1].
 template <int W>
 int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, int iter, bool filter) {
@@ -61,7 +78,7 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, int
 	a.fcur = b.fbit[fb[0]];
 	a.fnext = b.fbit[fb[1]];
 	a.alive_slots = b.alive_slots;
-	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, filter);
+	launch_tiny<W>(c, a, g, filter);
 	launch_class<W, 2>(c, a, g->d_small, g->n_small, filter);
 	if (g->n_mid) {
 		a.list = g->d_mid.as<uint32_t>();
@@ -473,7 +490,7 @@ int launch_part_level(Ctx *c, Csr *g, const PartBufs &b, int cur, int iter) {
 		a.peer_next = b.peer_tab + (size_t)(cur ^ 1) * (G - 1);
 		a.npeers = (uint32_t)(G - 1);
 	}
-	launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, true);
+	launch_tiny<W>(c, a, g, true);
 	launch_class<W, 2>(c, a, g->d_small, g->n_small, true);
 	if (g->n_mid) {
 		a.list = g->d_mid.as<uint32_t>();

@@ -364,6 +364,75 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	// no global counters here: frontier_stats_kernel derives them from fnext afterwards
 }
 
+// ---- K4 tiny: in-degree 1..4, straight-line ------------------------------------------------------
+// Same result as pull_list_kernel<W, 1, FILTER> for vertices with at most 4 in-edges, without the
+// round loop, the prefetch pipeline and the cross-group shuffles: this class is 25 % of an R-MAT's
+// vertices and 3 % of its edges, so its cost is instructions and dependent loads per VERTEX.
+template <int W, bool FILTER>
+__global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
+	using C = LaneCfg<W>;
+	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
+	constexpr uint32_t INV = 0xFFFFFFFFu, FULL = 0xffffffffu;
+	__shared__ uint32_t salive[16];
+	alive_init(salive, a.alive_slots);
+	const uint32_t wid = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+	if ((uint64_t)wid * G >= a.nlist) return; // warp-uniform
+	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
+	const uint64_t idx = (uint64_t)wid * G + g;
+	const bool listed = idx < a.nlist;
+	const uint32_t n = listed ? a.list[idx] : 0u;
+	uint32_t lo = 0, hi = 0;
+	if (listed) {
+		lo = a.ioff[n];
+		hi = a.ioff[n + 1];
+	}
+	uint32_t vs[U];
+#pragma unroll
+	for (int u = 0; u < U; u++) vs[u] = lo + u < hi ? a.isrc[lo + u] : INV;
+	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
+	Slice<SW> s = slice_zero<SW>(), unseen = slice_zero<SW>();
+	if (listed) {
+		s = ld_slice<SW>(a.seen + wo);
+		const Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
+#pragma unroll
+		for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
+	}
+	Slice<SW> acc = slice_zero<SW>();
+	if (slice_any<SW>(unseen)) {
+		Slice<SW> w[U];
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			bool f = vs[u] != INV;
+			if (FILTER && f) f = fbit_test(a.fcur, vs[u]);
+			w[u] = f ? ldg_slice<SW>(a.visit + (size_t)vs[u] * WPV + t * SW) : slice_zero<SW>();
+		}
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+#pragma unroll
+			for (int i = 0; i < SW; i++) acc.w[i] |= w[u].w[i];
+		}
+	}
+	Slice<SW> news;
+#pragma unroll
+	for (int i = 0; i < SW; i++) news.w[i] = acc.w[i] & unseen.w[i];
+	const bool mine = slice_any<SW>(news);
+	if (listed) {
+		st_slice<SW>(a.next + wo, news);
+		if (mine) {
+#pragma unroll
+			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
+			st_slice<SW>(a.seen + wo, s);
+			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
+		}
+	}
+	const unsigned bal = __ballot_sync(FULL, mine);
+	const bool vnew = ((bal >> (g * TPV)) & ((1u << TPV) - 1u)) != 0;
+	if (listed && vnew) {
+		if (t == 0) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+		if (a.npeers) st_peers<SW>(a, wo, news);
+	}
+}
+
 // ---- K4 mid (lengths): one warp per vertex, edge-parallel scan ------------------------------------
 // Each LANE owns one in-edge of a 32-edge round: one coalesced source load and one frontier-bit
 // test per edge (instead of once per thread of the group), a ballot, and then the G groups gather
