@@ -199,6 +199,7 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "timing")) c->opt.timing = value;
 	else if (!strcmp(key, "tiny_max")) c->opt.tiny_max = value < 0 ? 0 : value;
 	else if (!strcmp(key, "small_max")) c->opt.small_max = value < 0 ? 0 : value;
+	else if (!strcmp(key, "med_max")) c->opt.med_max = value < 0 ? 0 : value;
 	else if (!strcmp(key, "hub_min")) c->opt.hub_min = value < 1 ? 1 : value;
 	else if (!strcmp(key, "hub_chunk")) c->opt.hub_chunk = value < 256 ? 256 : value;
 	else if (!strcmp(key, "direction")) c->opt.direction = value;

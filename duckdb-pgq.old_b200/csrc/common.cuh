@@ -105,11 +105,12 @@ struct Csr {
 	// in-degree classes, each an ascending vertex list (in-degree 0 is in no list: never a target)
 	DevBuf d_tiny;  // 1 <= indeg <= tiny_max          one thread group per vertex, one round
 	DevBuf d_small; // tiny_max < indeg <= small_max   two thread groups per vertex
-	DevBuf d_mid;   // small_max < indeg <= hub_min    one warp per vertex
+	DevBuf d_med;   // small_max < indeg <= med_max    two groups per vertex on dense levels, a warp on filtered ones
+	DevBuf d_mid;   // med_max < indeg <= hub_min      one warp per vertex
 	DevBuf d_hub;   // indeg > hub_min                 one block per chunk of the in-list
 	DevBuf d_hubchunks; // HubChunk[]
-	uint32_t n_tiny = 0, n_small = 0, n_mid = 0, n_hub = 0, n_hubchunks = 0;
-	int64_t bins_tiny_max = -1, bins_small_max = -1, bins_hub_min = -1;
+	uint32_t n_tiny = 0, n_small = 0, n_med = 0, n_mid = 0, n_hub = 0, n_hubchunks = 0;
+	int64_t bins_tiny_max = -1, bins_small_max = -1, bins_med_max = -1, bins_hub_min = -1;
 	// 1-D partition (part.cu): this object then describes the slice of the reverse CSR owned by the
 	// rank — V = owned vertex count (local index space), E = local in-edges, d_isrc = GLOBAL sources
 	bool is_part = false;
@@ -125,7 +126,8 @@ struct Options {
 	int64_t stats = 0;
 	int64_t timing = 0;
 	int64_t tiny_max = 4;
-	int64_t small_max = 32;
+	int64_t small_max = 64;
+	int64_t med_max = 192;
 	int64_t hub_min = 4096;
 	int64_t hub_chunk = 4096;
 	int64_t direction = 0; // 0 auto (push when the frontier is sparse), 1 pull only

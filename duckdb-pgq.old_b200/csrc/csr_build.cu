@@ -200,6 +200,7 @@ int csr_prepare(Ctx *c, Csr *g) {
 	cudaStream_t st = c->stream;
 	const bool need_rev = !g->prepared;
 	const bool need_bins = need_rev || g->bins_tiny_max != c->opt.tiny_max || g->bins_small_max != c->opt.small_max ||
+	                       g->bins_med_max != c->opt.med_max ||
 	                       g->bins_hub_min != c->opt.hub_min;
 	if (!need_bins) return PGQ_OK;
 	PGQ_CUDA(cudaEventRecord(c->ev_a, st));
@@ -231,8 +232,10 @@ int csr_prepare(Ctx *c, Csr *g) {
 	{
 		uint32_t tiny_max = (uint32_t)c->opt.tiny_max, small_max = (uint32_t)c->opt.small_max;
 		uint32_t hub_min = (uint32_t)c->opt.hub_min, chunk = (uint32_t)c->opt.hub_chunk;
+		uint32_t med_max = (uint32_t)c->opt.med_max;
 		if (small_max < tiny_max) tiny_max = small_max;
-		if (hub_min < small_max) hub_min = small_max;
+		if (med_max < small_max) med_max = small_max;
+		if (hub_min < med_max) hub_min = med_max;
 		TmpBuf flag, tot;
 		PGQ_TRY(flag.reserve((size_t)(V + 1) * sizeof(uint32_t)));
 		PGQ_TRY(tot.reserve(16));
@@ -240,7 +243,8 @@ int csr_prepare(Ctx *c, Csr *g) {
 		uint64_t *dt = tot.as<uint64_t>();
 		PGQ_TRY(build_class(c, g, 1, tiny_max, f, dt, &g->d_tiny, &g->n_tiny));
 		PGQ_TRY(build_class(c, g, tiny_max + 1, small_max, f, dt, &g->d_small, &g->n_small));
-		PGQ_TRY(build_class(c, g, small_max + 1, hub_min, f, dt, &g->d_mid, &g->n_mid));
+		PGQ_TRY(build_class(c, g, small_max + 1, med_max, f, dt, &g->d_med, &g->n_med));
+		PGQ_TRY(build_class(c, g, med_max + 1, hub_min, f, dt, &g->d_mid, &g->n_mid));
 		PGQ_TRY(build_class(c, g, hub_min + 1, 0xFFFFFFFFu, f, dt, &g->d_hub, &g->n_hub));
 		g->n_hubchunks = 0;
 		if (g->n_hub) {
@@ -257,6 +261,7 @@ int csr_prepare(Ctx *c, Csr *g) {
 		PGQ_CUDA(cudaStreamSynchronize(st));
 		g->bins_tiny_max = c->opt.tiny_max;
 		g->bins_small_max = c->opt.small_max;
+		g->bins_med_max = c->opt.med_max;
 		g->bins_hub_min = c->opt.hub_min;
 	}
 	if (need_rev) {
@@ -276,7 +281,7 @@ void Csr::free_all() {
 	d_src64.release(); d_dst64.release(); d_eid64.release();
 	d_off.release(); d_tgt.release(); d_row.release(); d_eid.release(); d_fsrc.release();
 	d_ioff.release(); d_isrc.release(); d_ipos.release();
-	d_tiny.release(); d_small.release(); d_mid.release(); d_hub.release(); d_hubchunks.release();
+	d_tiny.release(); d_small.release(); d_med.release(); d_mid.release(); d_hub.release(); d_hubchunks.release();
 	d_ltgt.release(); d_lsrc.release();
 }
 

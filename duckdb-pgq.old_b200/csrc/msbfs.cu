@@ -33,6 +33,17 @@ void launch_class(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool 
 	count_launch(c);
 }
 
+template <int W>
+void launch_warp(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter) {
+	if (!nlist) return;
+	a.list = list.as<uint32_t>();
+	a.nlist = nlist;
+	const uint32_t grid = div_up((uint64_t)nlist * 32, 128);
+	if (filter) pull_warp_kernel<W, true><<<grid, 128, 0, c->stream>>>(a);
+	else pull_warp_kernel<W, false><<<grid, 128, 0, c->stream>>>(a);
+	count_launch(c);
+}
+
 // tiny class: straight-line kernel when the class really is <= 4 in-edges, else the generic one
 template <int W>
 void launch_tiny(Ctx *c, PullArgs &a, Csr *g, bool filter) {
@@ -52,7 +63,7 @@ void launch_tiny(Ctx *c, PullArgs &a, Csr *g, bool filter) {
 
 // One bottom-up level: frontier visit[cur]/fbit[cur] -> next visit[cur^1]/fbit[cur^1].
 template <int W>
-int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, int iter, bool filter) {
+int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, int iter, bool filter, bool early) {
 	using C = LaneCfg<W>;
 	cudaStream_t st = c->stream;
 	// fb[0] describes visit[cur], fb[1] is built for visit[cur^1], fb[2] describes what visit[cur^1]
@@ -80,14 +91,12 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, int
 	a.alive_slots = b.alive_slots;
 	launch_tiny<W>(c, a, g, filter);
 	launch_class<W, 2>(c, a, g->d_small, g->n_small, filter);
-	if (g->n_mid) {
-		a.list = g->d_mid.as<uint32_t>();
-		a.nlist = g->n_mid;
-		const uint32_t grid = div_up((uint64_t)g->n_mid * 32, 128);
-		if (filter) pull_warp_kernel<W, true><<<grid, 128, 0, st>>>(a);
-		else pull_warp_kernel<W, false><<<grid, 128, 0, st>>>(a);
-		count_launch(c);
-	}
+	// medium in-degrees: the edge-parallel warp scan wins while most vertices still scan their whole
+	// in-list against a sparse frontier (early levels); two thread groups per vertex win when every
+	// word is gathered anyway (dense levels) or most vertices have nothing left to find (tail)
+	if (filter && early) launch_warp<W>(c, a, g->d_med, g->n_med, true);
+	else launch_class<W, 2>(c, a, g->d_med, g->n_med, filter);
+	launch_warp<W>(c, a, g->d_mid, g->n_mid, filter);
 	if (g->n_hub) {
 		a.list = g->d_hub.as<uint32_t>();
 		a.nlist = g->n_hub;
@@ -103,12 +112,13 @@ int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, int
 	return PGQ_OK;
 }
 
-int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, const int *fb, int iter, bool filter) {
+int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, const int *fb, int iter, bool filter,
+                   bool early) {
 	switch (W) {
-	case 64: return launch_level<64>(c, g, b, cur, fb, iter, filter);
-	case 128: return launch_level<128>(c, g, b, cur, fb, iter, filter);
-	case 256: return launch_level<256>(c, g, b, cur, fb, iter, filter);
-	case 512: return launch_level<512>(c, g, b, cur, fb, iter, filter);
+	case 64: return launch_level<64>(c, g, b, cur, fb, iter, filter, early);
+	case 128: return launch_level<128>(c, g, b, cur, fb, iter, filter, early);
+	case 256: return launch_level<256>(c, g, b, cur, fb, iter, filter, early);
+	case 512: return launch_level<512>(c, g, b, cur, fb, iter, filter, early);
 	}
 	set_error("unsupported lane width %d", W);
 	return PGQ_ERR_INVALID;
@@ -273,6 +283,7 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 	const uint64_t levels_at_start = c->stats.levels;
 	uint32_t active = h.n_active;
 	int cur = 0, q = 0;
+	unsigned long long cum_verts = h.out_verts; // frontier vertices of all levels so far
 	int fb[3] = {0, 1, 2}; // bitmap of visit[cur] / being built for visit[cur^1] / of what visit[cur^1] holds
 	bool have_queue = true; // queue[q] describes visit[cur] and visit[cur^1] is all-zero
 	for (int iter = 1; active; iter++) {
@@ -299,7 +310,9 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 			// the bitmap test is dead weight once the frontier holds most of the edges
 			const bool filter = (unsigned long long)h.out_edges * (unsigned long long)c->opt.filter_gamma <=
 			                    (unsigned long long)g->E;
-			PGQ_TRY(launch_level_w(c, g, b, W, cur, fb, iter, filter));
+			// "early": fewer vertex discoveries so far than vertices that can be discovered at all
+			const bool early = cum_verts < (unsigned long long)g->n_tiny + g->n_small + g->n_med + g->n_mid + g->n_hub;
+			PGQ_TRY(launch_level_w(c, g, b, W, cur, fb, iter, filter, early));
 			have_queue = false;
 		}
 		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
@@ -327,6 +340,7 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 		}
 		if (!h.change_out) break;
 		active = h.n_active;
+		cum_verts += h.out_verts;
 	}
 	if (out_levels) *out_levels = (int)(c->stats.levels - levels_at_start);
 	if (bm && !keep_hist) { // what the frontier buffers hold now, for the next batch's scrub
@@ -492,12 +506,8 @@ int launch_part_level(Ctx *c, Csr *g, const PartBufs &b, int cur, int iter) {
 	}
 	launch_tiny<W>(c, a, g, true);
 	launch_class<W, 2>(c, a, g->d_small, g->n_small, true);
-	if (g->n_mid) {
-		a.list = g->d_mid.as<uint32_t>();
-		a.nlist = g->n_mid;
-		pull_warp_kernel<W, true><<<div_up((uint64_t)g->n_mid * 32, 128), 128, 0, st>>>(a);
-		count_launch(c);
-	}
+	launch_warp<W>(c, a, g->d_med, g->n_med, true);
+	launch_warp<W>(c, a, g->d_mid, g->n_mid, true);
 	if (g->n_hub) {
 		a.list = g->d_hub.as<uint32_t>();
 		a.nlist = g->n_hub;

@@ -151,11 +151,12 @@ def test_lengths_rmat_all_lane_widths(ctx, lanes):
     ctx.csr_delete(1)
 
 
-@pytest.mark.parametrize("bins", [(0, 0, 1), (1, 2, 8), (4, 32, 4096), (0, 32, 64), (1 << 30, 1 << 30, 1 << 30),
-                                  (2, 1 << 30, 1 << 30)])
+@pytest.mark.parametrize("bins", [(0, 0, 0, 1), (1, 2, 4, 8), (4, 32, 64, 4096), (0, 16, 32, 64),
+                                  (1 << 30, 1 << 30, 1 << 30, 1 << 30), (2, 1 << 30, 1 << 30, 1 << 30),
+                                  (2, 4, 1 << 30, 1 << 30)])
 @pytest.mark.parametrize("lanes", [64, 256, 512])
 def test_lengths_all_degree_bins(ctx, bins, lanes):
-    """Force every vertex through each in-degree class kernel (tiny / small / warp / hub), with and
+    """Force every vertex through each in-degree class kernel (tiny / small / medium / warp / hub), with and
     without the frontier-bitmap filter, at every threads-per-word layout."""
     V, E = 3000, 90000
     src, dst = orc.gen_knows(33, V, E)
@@ -166,7 +167,8 @@ def test_lengths_all_degree_bins(ctx, bins, lanes):
     ep = orc.shortestpath(V, v, e, eids, ps, pd, mode=1)
     ctx.set_option("tiny_max", bins[0])
     ctx.set_option("small_max", bins[1])
-    ctx.set_option("hub_min", bins[2])
+    ctx.set_option("med_max", bins[2])
+    ctx.set_option("hub_min", bins[3])
     ctx.set_option("hub_chunk", 256)
     ctx.set_option("lanes", lanes)
     try:
@@ -180,7 +182,8 @@ def test_lengths_all_degree_bins(ctx, bins, lanes):
         p = ctx.shortestpath(1, ps, pd, mode=1)
     finally:
         ctx.set_option("tiny_max", 4)
-        ctx.set_option("small_max", 32)
+        ctx.set_option("small_max", 64)
+        ctx.set_option("med_max", 192)
         ctx.set_option("hub_min", 4096)
         ctx.set_option("hub_chunk", 4096)
         ctx.set_option("lanes", 0)
