@@ -274,6 +274,71 @@ def bench_paths(ctx, V, E, npairs, steps, warmup):
                         "(e2e through the C ABI)" % (V, E, npairs), **out}
 
 
+def bench_c1(ctx, steps, warmup, with_cpu):
+    """BASELINE configs[0]: LDBC SNB SF1-shaped Person-knows-Person graph (10 k vertices, 180 k directed
+    edges): CSR build + iterativelength for 2048 pairs, everything from HOST buffers through the same
+    calls the DuckDB functions make.  This is the one config the CPU side can run in full, so the
+    oracle is timed on exactly the same work (rank 0, N=1 only)."""
+    import pgq_b200
+    V, E, npairs = 10000, 180000, 2048
+    mult, add = knows_params(V)
+    d_src, d_dst = ctx.dev_alloc(E * 8), ctx.dev_alloc(E * 8)
+    ctx.gen_knows_device(SEED_BASE + 1, V, E, mult, add, d_src, d_dst)
+    src = np.empty(E, dtype=np.int64)
+    dst = np.empty(E, dtype=np.int64)
+    ctx.d2h(src, d_src)
+    ctx.d2h(dst, d_dst)
+    ctx.dev_free(d_src)
+    ctx.dev_free(d_dst)
+    deg = np.bincount(src, minlength=V).astype(np.int64)
+    vid = np.arange(V, dtype=np.int64)
+    v_off = np.concatenate([[0], np.cumsum(deg), [E]]).astype(np.int64)
+    ps, pd = make_pairs(V, v_off, npairs, 77)
+
+    def gpu_once():
+        ctx.create_csr_vertex(300, V, vid, deg)
+        for lo in range(0, E, 1024):  # the engine hands the function 1024-row chunks
+            ctx.create_csr_edge(300, V, E, src[lo:lo + 1024], dst[lo:lo + 1024])
+        ctx.csr_finalize(300)
+        t1 = time.perf_counter()
+        outs = []
+        for lo in range(0, npairs, 1024):
+            outs.append(ctx.iterativelength(300, ps[lo:lo + 1024], pd[lo:lo + 1024]))
+        t2 = time.perf_counter()
+        ctx.csr_delete(300)
+        return t1, t2, outs
+
+    for _ in range(max(1, warmup)):
+        gpu_once()
+    tb, tq = [], []
+    for _ in range(max(1, steps)):
+        t0 = time.perf_counter()
+        t1, t2, outs = gpu_once()
+        tb.append(t1 - t0)
+        tq.append(t2 - t1)
+    res = {"workload": "BASELINE configs[0]: LDBC-SF1-shaped knows graph V=%d E=%d, CSR build from 1024-row "
+                       "chunks + iterativelength for %d pairs in 1024-row calls, host buffers" % (V, E, npairs),
+           "gpu": {"csr_build_ms": float(np.mean(tb)) * 1e3, "iterativelength_ms": float(np.mean(tq)) * 1e3,
+                   "pairs_per_s": npairs / float(np.mean(tq))}}
+    if with_cpu:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import orc
+        t0 = time.perf_counter()
+        v, e, _ = orc.csr_build(V, src, dst, want_eids=False)
+        t1 = time.perf_counter()
+        couts = []
+        for lo in range(0, npairs, 1024):
+            couts.append(orc.iterativelength(V, v, e, ps[lo:lo + 1024], pd[lo:lo + 1024]))
+        t2 = time.perf_counter()
+        same = all(np.array_equal(a[1], b[1]) and np.array_equal(np.where(b[1] == 1, a[0], -1),
+                                                                 np.where(b[1] == 1, b[0], -1))
+                   for a, b in zip(outs, couts))
+        res["cpu_oracle_1thread"] = {"csr_build_ms": (t1 - t0) * 1e3, "iterativelength_ms": (t2 - t1) * 1e3,
+                                     "pairs_per_s": npairs / (t2 - t1), "kind": "port",
+                                     "parity": "identical" if same else "MISMATCH"}
+    return res
+
+
 def main_ours(a):
     import pgq_b200
     rank, world, local, dist = dist_setup(a.gpus)
@@ -387,6 +452,8 @@ def main_ours(a):
     }
     if rank == 0 and world == 1 and not a.no_csr:
         line["csr_build"] = bench_csr(ctx, a.csr_scale, ef, a.steps, a.warmup, peak_gbs)
+    if rank == 0 and world == 1 and not a.no_paths:
+        line["config1"] = bench_c1(ctx, a.steps, a.warmup, not a.no_cpu_baseline)
     if rank == 0 and world == 1 and not a.no_paths:
         line["paths"] = bench_paths(ctx, 450000, 40000000, 16384, max(1, a.steps // 2), a.warmup)
     if rank == 0 and world == 1 and not a.no_cpu_baseline:

@@ -127,7 +127,7 @@ struct Options {
 	int64_t timing = 0;
 	int64_t tiny_max = 4;
 	int64_t small_max = 64;
-	int64_t med_max = 192;
+	int64_t med_max = 512;
 	int64_t hub_min = 4096;
 	int64_t hub_chunk = 4096;
 	int64_t direction = 0; // 0 auto (push when the frontier is sparse), 1 pull only

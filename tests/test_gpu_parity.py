@@ -183,7 +183,7 @@ def test_lengths_all_degree_bins(ctx, bins, lanes):
     finally:
         ctx.set_option("tiny_max", 4)
         ctx.set_option("small_max", 64)
-        ctx.set_option("med_max", 192)
+        ctx.set_option("med_max", 512)
         ctx.set_option("hub_min", 4096)
         ctx.set_option("hub_chunk", 4096)
         ctx.set_option("lanes", 0)
