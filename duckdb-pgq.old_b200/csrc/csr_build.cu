@@ -16,17 +16,30 @@ template <typename OutT>
 __global__ void __launch_bounds__(256) offsets_from_sorted_kernel(const uint32_t *__restrict__ key, uint32_t n,
                                                                   uint32_t nv, uint32_t tail,
                                                                   OutT *__restrict__ off) {
-	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-	if (p > n) return;
-	if (p == n) { // one extra thread closes the array
-		const uint32_t first = n ? key[n - 1] + 1 : 0;
-		for (uint32_t s = first; s < nv + tail; s++) off[s] = (OutT)n;
-		return;
+	// four consecutive keys per thread (one 16-byte load) + the key before them
+	const uint64_t p0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+	if (p0 > n) return;
+	uint32_t kk[4];
+	if (p0 + 4 <= n) {
+		const uint4 q = *reinterpret_cast<const uint4 *>(key + p0);
+		kk[0] = q.x; kk[1] = q.y; kk[2] = q.z; kk[3] = q.w;
+	} else {
+#pragma unroll
+		for (int j = 0; j < 4; j++) kk[j] = p0 + j < n ? key[p0 + j] : 0u;
 	}
-	const uint32_t k = key[p];
-	const uint32_t first = p ? key[p - 1] + 1 : 0; // keys (first .. k] start here (empty when k == key[p-1])
-	if (p && key[p - 1] == k) return;
-	for (uint32_t s = first; s <= k && s < nv; s++) off[s] = (OutT)p;
+	uint32_t first = p0 ? key[p0 - 1] + 1 : 0; // keys (first .. k] start at this position
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		const uint64_t p = p0 + j;
+		if (p > n) break;
+		if (p == n) { // closes the array
+			for (uint32_t s = first; s < nv + tail; s++) off[s] = (OutT)n;
+			break;
+		}
+		const uint32_t k = kk[j];
+		for (uint32_t s = first; s <= k && s < nv; s++) off[s] = (OutT)p;
+		first = k + 1;
+	}
 }
 
 // create_csr_vertex counts (host-provided, uploaded) must equal the histogram.
@@ -46,7 +59,7 @@ __global__ void __launch_bounds__(256) gather_eid_kernel(const int64_t *__restri
 }
 
 int part_offsets_u32(Ctx *c, const uint32_t *keys, uint32_t n, uint32_t nv, uint32_t *off) {
-	offsets_from_sorted_kernel<uint32_t><<<div_up((uint64_t)n + 1, 256), 256, 0, c->stream>>>(keys, n, nv, 1u, off);
+	offsets_from_sorted_kernel<uint32_t><<<div_up(div_up((uint64_t)n + 1, 4), 256), 256, 0, c->stream>>>(keys, n, nv, 1u, off);
 	count_launch(c);
 	PGQ_CUDA(cudaGetLastError());
 	return PGQ_OK;
@@ -92,7 +105,7 @@ int csr_device_build(Ctx *c, Csr *g) {
 		io.err = d_err;
 		PGQ_TRY(radix_sort_stable(c, io));
 	}
-	offsets_from_sorted_kernel<int64_t><<<div_up((uint64_t)E + 1, 256), 256, 0, st>>>(
+	offsets_from_sorted_kernel<int64_t><<<div_up(div_up((uint64_t)E + 1, 4), 256), 256, 0, st>>>(
 	    g->d_fsrc.as<uint32_t>(), (uint32_t)E, (uint32_t)V, 2u, g->d_off.as<int64_t>());
 	count_launch(c);
 	TmpBuf d_cnt;
@@ -221,7 +234,7 @@ int csr_prepare(Ctx *c, Csr *g) {
 			io.keys_scratch = &tkeys;
 			PGQ_TRY(radix_sort_stable(c, io));
 		}
-		offsets_from_sorted_kernel<uint32_t><<<div_up((uint64_t)E + 1, 256), 256, 0, st>>>(
+		offsets_from_sorted_kernel<uint32_t><<<div_up(div_up((uint64_t)E + 1, 4), 256), 256, 0, st>>>(
 		    tkeys, (uint32_t)E, (uint32_t)V, 1u, g->d_ioff.as<uint32_t>());
 		count_launch(c);
 		PGQ_CUDA(cudaStreamSynchronize(st));

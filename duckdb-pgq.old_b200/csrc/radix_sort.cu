@@ -46,6 +46,21 @@ __device__ __forceinline__ uint32_t rs_load_key(const RsArgs &a, uint32_t i) {
 	return a.kin[i];
 }
 
+// Lanes of the warp holding the same 8-bit digit, from 8 ballots (one per digit bit).  The
+// hardware MATCH.ANY costs one iteration per distinct value in the warp (measured: the digit pass
+// with 32 distinct digits per warp ran 1.3x slower than the skewed top-digit pass); the ballots
+// cost the same whatever the distribution.
+__device__ __forceinline__ unsigned rs_match8(uint32_t d, bool valid) {
+	unsigned peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+	for (int b = 0; b < 8; b++) {
+		const bool bit = (d >> b) & 1u;
+		const unsigned m = __ballot_sync(0xffffffffu, bit);
+		peers &= bit ? m : ~m;
+	}
+	return peers;
+}
+
 // Ranks the tile's keys. keys[r], rank[r] per round; leaves per-warp exclusive bases in cnt and
 // tile totals in tot.
 template <bool FIRST64, bool WANT_RANK>
@@ -56,21 +71,28 @@ __device__ __forceinline__ void rs_rank_tile(const RsArgs &a, uint32_t (*cnt)[25
 	for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&cnt[0][0])[i] = 0;
 	__syncthreads();
 	const uint64_t wbase = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)warp * (RS_ITEMS * 32);
+	// all loads first: 16 independent coalesced requests in flight per thread before any ranking
 #pragma unroll
 	for (int r = 0; r < RS_ITEMS; r++) {
-		uint64_t idx = wbase + (uint64_t)r * 32 + lane;
-		bool valid = idx < a.n;
-		uint32_t key = valid ? rs_load_key<FIRST64>(a, (uint32_t)idx) : 0u;
-		keys[r] = key;
-		uint32_t d = (key >> a.shift) & 0xFFu;
-		unsigned peers = __match_any_sync(0xffffffffu, valid ? d : 0xFFFFFFFFu);
-		unsigned lower = peers & lt_mask;
-		uint32_t base = 0;
-		if (valid) base = cnt[warp][d];
-		__syncwarp();
-		if (valid && lower == 0) cnt[warp][d] = base + __popc(peers);
-		__syncwarp();
-		if (WANT_RANK) rank[r] = base + __popc(lower);
+		const uint64_t idx = wbase + (uint64_t)r * 32 + lane;
+		keys[r] = idx < a.n ? rs_load_key<FIRST64>(a, (uint32_t)idx) : 0u;
+	}
+#pragma unroll
+	for (int r = 0; r < RS_ITEMS; r++) {
+		const bool valid = wbase + (uint64_t)r * 32 + lane < a.n;
+		const uint32_t d = (keys[r] >> a.shift) & 0xFFu;
+		if (WANT_RANK) {
+			const unsigned peers = rs_match8(d, valid);
+			const unsigned lower = peers & lt_mask;
+			uint32_t base = 0;
+			if (valid) base = cnt[warp][d];
+			__syncwarp();
+			if (valid && lower == 0) cnt[warp][d] = base + __popc(peers);
+			__syncwarp();
+			rank[r] = base + __popc(lower);
+		} else if (valid) {
+			atomicAdd(&cnt[warp][d], 1u); // counting only: order-free shared-memory reduction
+		}
 	}
 	__syncthreads();
 	// exclusive scan over warps, one digit per thread (RS_THREADS == 256)
@@ -97,33 +119,93 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(RsArgs a) {
 	a.hist[(uint64_t)threadIdx.x * a.ntiles + blockIdx.x] = tot[threadIdx.x];
 }
 
+// Scatter with a tile-local reorder: the ranked items are first placed at their position inside
+// the tile's own sorted order in shared memory, then written out by consecutive threads, so each
+// digit bucket receives contiguous runs (avg RS_TILE/256 items) instead of 32 unrelated 4-byte
+// stores per warp instruction.  Keys stay in shared memory (they give the digit, hence the global
+// position, of every sorted slot); payloads go through one 16 KB staging array, one at a time.
 template <bool FIRST64>
-__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(RsArgs a) {
+__global__ void __launch_bounds__(RS_THREADS, 4) rs_scatter_kernel(RsArgs a) {
 	__shared__ uint32_t cnt[RS_WARPS][256];
-	__shared__ uint32_t tot[256];
-	uint32_t keys[RS_ITEMS], rank[RS_ITEMS];
-	rs_rank_tile<FIRST64, true>(a, cnt, tot, keys, rank);
-	// global bucket base of this tile per digit (reuse tot[])
-	tot[threadIdx.x] = a.hist[(uint64_t)threadIdx.x * a.ntiles + blockIdx.x];
-	__syncthreads();
+	__shared__ uint32_t tot[256];    // tile totals, then (global bucket base - local bucket start)
+	__shared__ uint32_t lstart[256]; // local bucket start inside the tile's sorted order
+	__shared__ uint32_t wsum[RS_WARPS];
+	__shared__ uint32_t skey[RS_TILE];
+	__shared__ uint32_t sval[RS_TILE];
+	uint32_t keys[RS_ITEMS], lp[RS_ITEMS];
+	rs_rank_tile<FIRST64, true>(a, cnt, tot, keys, lp);
 	const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	const uint64_t wbase = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)warp * (RS_ITEMS * 32);
+	{ // exclusive scan of the tile totals over the 256 digits, one digit per thread
+		const uint32_t t = tot[threadIdx.x];
+		uint32_t inc = t;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+			if ((int)lane >= o) inc += y;
+		}
+		if (lane == 31) wsum[warp] = inc;
+		__syncthreads();
+		uint32_t wb = 0;
+#pragma unroll
+		for (int w = 0; w < RS_WARPS; w++) wb += (w < (int)warp) ? wsum[w] : 0u;
+		const uint32_t ls = wb + inc - t;
+		lstart[threadIdx.x] = ls;
+		tot[threadIdx.x] = a.hist[(uint64_t)threadIdx.x * a.ntiles + blockIdx.x] - ls;
+	}
+	__syncthreads();
+	const uint64_t tbase = (uint64_t)blockIdx.x * RS_TILE;
+	const uint64_t wbase = tbase + (uint64_t)warp * (RS_ITEMS * 32);
+	const uint32_t ntile = (uint32_t)((a.n - tbase) < (uint64_t)RS_TILE ? (a.n - tbase) : (uint64_t)RS_TILE);
 #pragma unroll
 	for (int r = 0; r < RS_ITEMS; r++) {
-		uint64_t idx = wbase + (uint64_t)r * 32 + lane;
+		const uint64_t idx = wbase + (uint64_t)r * 32 + lane;
 		if (idx < a.n) {
-			uint32_t i = (uint32_t)idx;
-			uint32_t d = (keys[r] >> a.shift) & 0xFFu;
-			uint32_t pos = tot[d] + cnt[warp][d] + rank[r];
-			if (a.kout) a.kout[pos] = keys[r];
+			const uint32_t d = (keys[r] >> a.shift) & 0xFFu;
+			lp[r] = lstart[d] + cnt[warp][d] + lp[r];
+			skey[lp[r]] = keys[r];
+		}
+	}
+	__syncthreads();
+#define RS_GPOS(j) (tot[(skey[j] >> a.shift) & 0xFFu] + (j))
+	if (a.kout) {
+#pragma unroll
+		for (int k = 0; k < RS_ITEMS; k++) {
+			const uint32_t j = threadIdx.x + k * RS_THREADS;
+			if (j < ntile) a.kout[RS_GPOS(j)] = skey[j];
+		}
+	}
+	// payload 0
+#pragma unroll
+	for (int r = 0; r < RS_ITEMS; r++) {
+		const uint64_t idx = wbase + (uint64_t)r * 32 + lane;
+		if (idx < a.n) {
 			if (FIRST64) {
-				const uint64_t pv = (uint64_t)a.p64[i];
+				const uint64_t pv = (uint64_t)a.p64[idx];
 				if (a.err && pv >= a.vmax) atomicOr(a.err, 1u);
-				a.p0out[pos] = (uint32_t)pv;
+				sval[lp[r]] = (uint32_t)pv;
 			} else {
-				a.p0out[pos] = a.p0in[i];
+				sval[lp[r]] = a.p0in[idx];
 			}
-			if (a.p1out) a.p1out[pos] = a.p1in ? a.p1in[i] : i;
+		}
+	}
+	__syncthreads();
+#pragma unroll
+	for (int k = 0; k < RS_ITEMS; k++) {
+		const uint32_t j = threadIdx.x + k * RS_THREADS;
+		if (j < ntile) a.p0out[RS_GPOS(j)] = sval[j];
+	}
+	if (a.p1out) {
+		__syncthreads();
+#pragma unroll
+		for (int r = 0; r < RS_ITEMS; r++) {
+			const uint64_t idx = wbase + (uint64_t)r * 32 + lane;
+			if (idx < a.n) sval[lp[r]] = a.p1in ? a.p1in[idx] : (uint32_t)idx;
+		}
+		__syncthreads();
+#pragma unroll
+		for (int k = 0; k < RS_ITEMS; k++) {
+			const uint32_t j = threadIdx.x + k * RS_THREADS;
+			if (j < ntile) a.p1out[RS_GPOS(j)] = sval[j];
 		}
 	}
 }
