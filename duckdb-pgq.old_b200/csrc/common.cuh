@@ -135,6 +135,7 @@ struct Options {
 	int64_t push_beta = 32; // push when frontier out-edges * push_beta <= E
 	int64_t push_vbeta = 16; // ... and frontier vertices * push_vbeta <= V (+ slack for tiny graphs)
 	int64_t filter_gamma = 2; // pull tests the frontier bitmap while frontier out-edges * gamma <= E
+	int64_t small_path = 1;   // whole-batch cooperative kernel for graphs that live in L2 (msbfs_small.cuh)
 };
 
 // What the two frontier buffers hold after the last completed batch (msbfs.cu run_batch).

@@ -3,6 +3,7 @@
 // run level steps while a lane is active and something changed, check destinations after each
 // level, retire found lanes.  One stream, one host sync per level (reads 16 bytes of control).
 #include "msbfs_kernels.cuh"
+#include "msbfs_small.cuh"
 #include "nccl_dl.cuh"
 
 namespace pgq {
@@ -245,6 +246,111 @@ int hist_level(Ctx *c, size_t k, size_t bm, uint32_t **out) {
 	return PGQ_OK;
 }
 
+// ---- small graphs: the whole batch in one cooperative launch (msbfs_small.cuh) ------------------
+static constexpr int SMALL_HIST_LEVELS = 48;      // level buffers kept for shortestpath
+static constexpr int PGQ_SMALL_OVERFLOW = 0x7001; // internal: history too short, use the general path
+
+bool small_eligible(const Ctx *c, const Csr *g, int W, bool keep_hist) {
+	if (!c->opt.small_path || c->opt.stats || g->V <= 0 || g->is_part) return false;
+	const uint64_t bm = (uint64_t)g->V * (W / 8), eb = (uint64_t)g->E * (W / 8);
+	if (keep_hist && bm > (2ull << 20)) return false; // 49 level buffers
+	return bm <= (8ull << 20) && eb <= (64ull << 20);
+}
+
+template <int W>
+int small_grid(Ctx *c, int *out) {
+	static int per_sm = -1; // per instantiation
+	if (per_sm < 0) {
+		int nb = 0;
+		PGQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, msbfs_small_kernel<W>, SMALL_THREADS, 0));
+		per_sm = nb;
+	}
+	*out = per_sm;
+	return PGQ_OK;
+}
+
+int run_batch_small(Ctx *c, Csr *g, const BatchBufs &b, int W, bool keep_hist, const uint32_t *d_lane_src,
+                    const uint32_t *d_lane_dst, int32_t *d_found, int *out_levels) {
+	cudaStream_t st = c->stream;
+	const size_t bm = (size_t)g->V * (W / 8);
+	SmallArgs a{};
+	a.ioff = g->d_ioff.as<uint32_t>();
+	a.isrc = g->d_isrc.as<uint32_t>();
+	a.V = (uint32_t)g->V;
+	a.team_threads = 256;
+	a.warp_max = (uint32_t)g->bins_small_max; // the lists below hold exactly the vertices above it
+	a.big[0] = g->d_med.as<uint32_t>();
+	a.nbig[0] = g->n_med;
+	a.big[1] = g->d_mid.as<uint32_t>();
+	a.nbig[1] = g->n_mid;
+	a.big[2] = g->d_hub.as<uint32_t>();
+	a.nbig[2] = g->n_hub;
+	a.seen = b.seen;
+	a.buf[0] = b.visit[0];
+	a.buf[1] = b.visit[1];
+	a.lane_src = d_lane_src;
+	a.lane_dst = d_lane_dst;
+	a.found = d_found;
+	a.ctrl = b.ctrl;
+	a.max_levels = 0x7fffffff;
+	if (keep_hist) {
+		if (c->bfs_hist.size() < (size_t)SMALL_HIST_LEVELS + 1) c->bfs_hist.resize((size_t)SMALL_HIST_LEVELS + 1);
+		std::vector<uint32_t *> hp((size_t)SMALL_HIST_LEVELS + 1);
+		for (int k = 0; k <= SMALL_HIST_LEVELS; k++) {
+			PGQ_TRY(c->bfs_hist[(size_t)k].reserve(bm));
+			hp[(size_t)k] = c->bfs_hist[(size_t)k].as<uint32_t>();
+		}
+		PGQ_TRY(c->bfs_hist_tab.reserve(hp.size() * sizeof(uint32_t *)));
+		PGQ_CUDA(cudaMemcpyAsync(c->bfs_hist_tab.p, hp.data(), hp.size() * sizeof(uint32_t *), cudaMemcpyHostToDevice,
+		                         st));
+		PGQ_CUDA(cudaStreamSynchronize(st)); // hp is a host temporary
+		a.hist = c->bfs_hist_tab.as<uint32_t *const>();
+		a.max_levels = SMALL_HIST_LEVELS;
+	}
+	c->bfs_dirty.valid = false; // the frontier pair is left in a state the scrub does not describe
+	int per_sm = 0;
+	switch (W) {
+	case 64: PGQ_TRY(small_grid<64>(c, &per_sm)); break;
+	case 128: PGQ_TRY(small_grid<128>(c, &per_sm)); break;
+	case 256: PGQ_TRY(small_grid<256>(c, &per_sm)); break;
+	default: PGQ_TRY(small_grid<512>(c, &per_sm)); break;
+	}
+	if (per_sm < 1) return PGQ_SMALL_OVERFLOW;
+	int grid = c->sm_count; // one 1024-thread block per SM: the grid barrier scales with the block count
+	const int want = (int)div_up((uint64_t)g->V, SMALL_THREADS / 32);
+	if (grid > want) grid = want;
+	if (grid < 1) grid = 1;
+	void *args[] = {&a};
+	const void *fn = nullptr;
+	switch (W) {
+	case 64: fn = (const void *)msbfs_small_kernel<64>; break;
+	case 128: fn = (const void *)msbfs_small_kernel<128>; break;
+	case 256: fn = (const void *)msbfs_small_kernel<256>; break;
+	default: fn = (const void *)msbfs_small_kernel<512>; break;
+	}
+	if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
+	PGQ_CUDA(cudaMemsetAsync(&b.ctrl->small_bar, 0, sizeof(BfsCtrl) - offsetof(BfsCtrl, small_bar), st));
+	PGQ_CUDA(cudaLaunchCooperativeKernel(fn, dim3((unsigned)grid), dim3(SMALL_THREADS), args, 0, st));
+	count_launch(c);
+	if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
+	BfsCtrl h;
+	PGQ_TRY(read_ctrl(c, b, &h));
+	if (h.small_overflow) return PGQ_SMALL_OVERFLOW;
+	c->stats.batches++;
+	c->stats.levels += h.small_levels;
+	if (c->opt.timing) {
+		float ms = 0;
+		PGQ_CUDA(cudaEventElapsedTime(&ms, c->ev_a, c->ev_b));
+		c->stats.level_kernel_ms += ms;
+		c->stats.level_kernel_launches += 1;
+		if (c->opt.trace)
+			fprintf(stderr, "[pgq] small-graph kernel: %u levels %.3f ms, grid %d x %d\n", h.small_levels, ms, grid,
+			        SMALL_THREADS);
+	}
+	if (out_levels) *out_levels = (int)h.small_levels;
+	return PGQ_OK;
+}
+
 // One batch of W lanes.  d_lane_src/dst/found point at this batch's W slots.
 // keep_hist (shortestpath): level k's frontier stays in c->bfs_hist[k] instead of a ping-pong pair, so
 // the path kernel can apply the parent rule afterwards; *out_levels = levels run.
@@ -253,6 +359,10 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 	cudaStream_t st = c->stream;
 	BatchBufs b = b_in;
 	const size_t bm = (size_t)g->V * (W / 8);
+	if (small_eligible(c, g, W, keep_hist)) {
+		const int rc = run_batch_small(c, g, b, W, keep_hist, d_lane_src, d_lane_dst, d_found, out_levels);
+		if (rc != PGQ_SMALL_OVERFLOW) return rc;
+	}
 	if (keep_hist) {
 		if (bm) PGQ_CUDA(cudaMemsetAsync(b.seen, 0, bm, st));
 		PGQ_TRY(hist_level(c, 0, bm, &b.visit[0]));

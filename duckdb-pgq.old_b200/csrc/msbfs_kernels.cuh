@@ -39,6 +39,12 @@ struct BfsCtrl {
 	unsigned long long out_edges;
 	uint32_t out_verts;
 	uint32_t out_items;
+	// whole-batch kernel for small graphs (msbfs_small_kernel)
+	uint32_t small_bar;      // grid barrier counter (zeroed by the host before the launch)
+	uint32_t small_levels;   // levels run
+	uint32_t small_overflow; // ran out of level buffers (shortestpath history): host falls back
+	uint32_t pad3;
+	uint32_t small_slots[3][20]; // per level (mod 3): alive lanes [0..15], change flag [16]
 };
 
 // Lanes that gained a frontier bit in the running level ("alive").  A lane with an empty frontier

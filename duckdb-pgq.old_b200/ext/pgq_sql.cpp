@@ -5,6 +5,8 @@
 // plugin and the host share one copy of DuckDB (SURVEY.md §8(b) caveat about the static shell).
 #include "duckdb.hpp"
 
+#include <chrono>
+#include <cstdlib>
 #include <iostream>
 #include <sstream>
 #include <string>
@@ -16,14 +18,19 @@ int main(int argc, char **argv) {
 	Connection con(db);
 	std::string line, stmt;
 	int n = 0, failed = 0;
+	const bool timing = std::getenv("PGQ_SQL_TIME") != nullptr;
 	while (std::getline(std::cin, line)) {
 		stmt += line;
 		stmt += "\n";
 		size_t end = line.find_last_not_of(" \t\r");
 		if (end == std::string::npos || line[end] != ';') continue;
+		auto t0 = std::chrono::steady_clock::now();
 		auto res = con.Query(stmt);
+		auto t1 = std::chrono::steady_clock::now();
 		stmt.clear();
 		n++;
+		if (timing) // PGQ_SQL_TIME=1: wall time of Connection::Query (parse + plan + execute + materialise)
+			std::cout << "-- time " << n << ": " << std::chrono::duration<double, std::milli>(t1 - t0).count() << " ms\n";
 		if (!res->success) {
 			std::cout << "-- error " << n << ": " << res->error << "\n";
 			failed++;

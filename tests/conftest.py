@@ -13,10 +13,13 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
 
 
-@pytest.fixture(scope="session")
-def ctx():
-    """One GPU context per test session (GPU tests only)."""
+@pytest.fixture(scope="session", params=[0, 1], ids=["general", "smallpath"])
+def ctx(request):
+    """One GPU context per test session (GPU tests only).  Every test runs twice: with the general
+    level-by-level path forced (small_path=0) and with the default dispatch, where graphs that live
+    in L2 take the whole-batch cooperative kernel (msbfs_small.cuh)."""
     import pgq_b200
     c = pgq_b200.Context(0)
+    c.set_option("small_path", request.param)
     yield c
     c.close()

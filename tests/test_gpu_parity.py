@@ -257,6 +257,26 @@ def test_shortestpath_bit_identical(ctx, graph, mode):
     ctx.csr_delete(1)
 
 
+@pytest.mark.parametrize("n", [30, 49, 50, 120])
+def test_long_chain_levels(ctx, n):
+    """A path graph needs n-1 levels: more than the small-graph kernel keeps level buffers for
+    (shortestpath falls back to the general path), and lengths must not care."""
+    src = np.arange(n - 1, dtype=np.int64)
+    dst = src + 1
+    v, e, eids = _build_both(ctx, n, src, dst)
+    qs = np.array([0, 0, 1, n - 1, 3], dtype=np.int64)
+    qd = np.array([n - 1, n // 2, n - 1, 0, 3], dtype=np.int64)
+    out, ov = ctx.iterativelength(1, qs, qd)
+    eo, ev = orc.iterativelength(n, v, e, qs, qd)
+    assert ov.tolist() == ev.tolist()
+    assert lengths_list(out, ov) == lengths_list(eo, ev)
+    for mode in (0, 1):
+        got = ctx.shortestpath(1, qs, qd, mode=mode)
+        exp = orc.shortestpath(n, v, e, eids, qs, qd, mode=mode)
+        assert_paths_equal(got, exp, "chain %d mode %d" % (n, mode))
+    ctx.csr_delete(1)
+
+
 def test_config1_ldbc_sf1_shape(ctx):
     """BASELINE config 1: LDBC-SF1-shaped knows graph, CSR build + iterativelength for 2048 pairs."""
     V, E = 10000, 180000
