@@ -179,7 +179,8 @@ struct Ctx {
 	DevBuf bfs_lane; // per-call lane tables
 	DevBuf bfs_ctrl; // device control block
 	DevBuf l2_flush;
-	void *h_ctrl = nullptr; // pinned host mirror of the control block
+	void *h_ctrl = nullptr; // pinned host mirror of the control block (4 KiB; upper half: small-path level counts)
+	int small_pending = 0;  // small-graph batches whose level count has not been folded into stats yet
 	cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_timer = nullptr, ev_timer2 = nullptr;
 	std::vector<cudaEvent_t> ev_pool; // level-kernel timing events
 	size_t ev_used = 0;

@@ -250,6 +250,18 @@ int hist_level(Ctx *c, size_t k, size_t bm, uint32_t **out) {
 static constexpr int SMALL_HIST_LEVELS = 48;      // level buffers kept for shortestpath
 static constexpr int PGQ_SMALL_OVERFLOW = 0x7001; // internal: history too short, use the general path
 
+static constexpr int SMALL_PENDING_MAX = 512;
+
+// Level counts of small-graph batches are copied back asynchronously; fold them into the stats.
+int small_flush(Ctx *c) {
+	if (!c->small_pending) return PGQ_OK;
+	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	const uint32_t *lv = reinterpret_cast<const uint32_t *>(static_cast<const char *>(c->h_ctrl) + 2048);
+	for (int i = 0; i < c->small_pending; i++) c->stats.levels += lv[i];
+	c->small_pending = 0;
+	return PGQ_OK;
+}
+
 bool small_eligible(const Ctx *c, const Csr *g, int W, bool keep_hist) {
 	if (!c->opt.small_path || c->opt.stats || g->V <= 0 || g->is_part) return false;
 	const uint64_t bm = (uint64_t)g->V * (W / 8), eb = (uint64_t)g->E * (W / 8);
@@ -333,6 +345,15 @@ int run_batch_small(Ctx *c, Csr *g, const BatchBufs &b, int W, bool keep_hist, c
 	PGQ_CUDA(cudaLaunchCooperativeKernel(fn, dim3((unsigned)grid), dim3(SMALL_THREADS), args, 0, st));
 	count_launch(c);
 	if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
+	if (!keep_hist && !c->opt.timing) {
+		// nothing the host needs before the results: the level count is fetched with them
+		if (c->small_pending == SMALL_PENDING_MAX) PGQ_TRY(small_flush(c));
+		uint32_t *slot = reinterpret_cast<uint32_t *>(static_cast<char *>(c->h_ctrl) + 2048) + c->small_pending++;
+		PGQ_CUDA(cudaMemcpyAsync(slot, &b.ctrl->small_levels, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+		c->stats.batches++;
+		if (out_levels) *out_levels = 0;
+		return PGQ_OK;
+	}
 	BfsCtrl h;
 	PGQ_TRY(read_ctrl(c, b, &h));
 	if (h.small_overflow) return PGQ_SMALL_OVERFLOW;
@@ -565,6 +586,7 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 		PGQ_CUDA(cudaStreamSynchronize(st));
 		c->stats.d2h_bytes += (uint64_t)nslots * 4;
 	}
+	PGQ_TRY(small_flush(c));
 	if (c->opt.stats)
 		c->stats.algo_bytes += (c->stats.levels - levels_before) * 4ull * (uint64_t)g->V * (uint64_t)(W / 8);
 	return PGQ_OK;
@@ -827,6 +849,7 @@ int msbfs_run_device(Ctx *c, Csr *g, int64_t n, const int64_t *d_srcs, const int
 	uint32_t h_err = 0;
 	PGQ_CUDA(cudaMemcpyAsync(&h_err, d_err, 4, cudaMemcpyDeviceToHost, st));
 	PGQ_CUDA(cudaStreamSynchronize(st));
+	PGQ_TRY(small_flush(c));
 	if (c->opt.stats)
 		c->stats.algo_bytes += (c->stats.levels - levels_before) * 4ull * (uint64_t)g->V * (uint64_t)(W / 8);
 	if (h_err) {

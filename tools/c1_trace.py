@@ -22,6 +22,11 @@ ctx.csr_build(1, V, src, dst)
 for k, val in (kv.split('=') for kv in args):
     ctx.set_option(k, int(val))
 ctx.iterativelength(1, ps[:1024], pd[:1024])
+for rows in (1024, 512, 64, 1):
+    t0 = time.perf_counter()
+    for _ in range(50):
+        ctx.iterativelength(1, ps[:rows], pd[:rows])
+    print("rows %d: %.1f us per call (timers off)" % (rows, (time.perf_counter() - t0) / 50 * 1e6))
 ctx.set_option("timing", 1); ctx.set_option("trace", 1)
 for rows in (1024, 512, 64, 1):
     ctx.reset_stats()
