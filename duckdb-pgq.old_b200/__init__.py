@@ -213,6 +213,47 @@ class Context:
                                                out.ctypes.data_as(I64P), ov.ctypes.data_as(U8P)))
         return out, ov
 
+    def csr_set_weights(self, csr_id, w, chunk=None):
+        """Edge weights per INPUT ROW (int64 or float64), optionally sent in chunks like the rows of
+        the 7-argument create_csr_edge would arrive (R10)."""
+        w = np.ascontiguousarray(w)
+        if w.dtype not in (np.int64, np.float64):
+            raise ValueError("weights must be int64 or float64")
+        wtype = 1 if w.dtype == np.int64 else 2
+        n = w.shape[0]
+        step = n if not chunk else int(chunk)
+        for lo in range(0, max(n, 1), max(step, 1)):
+            part = w[lo:lo + step]
+            self._chk(self.lib.pgq_csr_set_weights(self._ctx, C.c_int32(csr_id), C.c_int(wtype),
+                                                   C.c_void_p(part.ctypes.data), C.c_int64(lo),
+                                                   C.c_int64(part.shape[0])))
+
+    def csr_download_weights(self, csr_id):
+        """Weights in CSR slot order (dtype by the weight type)."""
+        wt = C.c_int(0)
+        self._chk(self.lib.pgq_csr_weight_type(self._ctx, C.c_int32(csr_id), C.byref(wt)))
+        if wt.value == 0:
+            raise PgqError(-3, "csr has no weights")
+        _, e_size = self.csr_info(csr_id)
+        out = np.empty(e_size, dtype=np.int64 if wt.value == 1 else np.float64)
+        self._chk(self.lib.pgq_csr_download_weights(self._ctx, C.c_int32(csr_id), C.c_void_p(out.ctypes.data)))
+        return out
+
+    def cheapest_path_length(self, csr_id, src, dst, src_valid=None, dst_valid=None):
+        """-> (length int64|float64 [n], valid uint8[n]); NULL for NULL inputs / unreachable (R10)."""
+        wt = C.c_int(0)
+        self._chk(self.lib.pgq_csr_weight_type(self._ctx, C.c_int32(csr_id), C.byref(wt)))
+        src, ps = _i64(src)
+        dst, pd = _i64(dst)
+        n = src.shape[0]
+        sv, psv = _u8(src_valid, n)
+        dv, pdv = _u8(dst_valid, n)
+        out = np.zeros(n, dtype=np.float64 if wt.value == 2 else np.int64)
+        ov = np.zeros(n, dtype=np.uint8)
+        self._chk(self.lib.pgq_cheapest_path_length(self._ctx, C.c_int32(csr_id), C.c_int64(n), ps, pd, psv, pdv,
+                                                    C.c_void_p(out.ctypes.data), ov.ctypes.data_as(U8P)))
+        return out, ov
+
     def reachability(self, csr_id, src, dst, src_valid=None, dst_valid=None):
         src, ps = _i64(src)
         dst, pd = _i64(dst)

@@ -5,6 +5,8 @@
 #include <string.h>
 
 #include "common.cuh"
+
+#include <cmath>
 #include "nccl_dl.cuh"
 
 namespace pgq {
@@ -171,7 +173,7 @@ int pgq_shutdown(pgq_ctx_t *ctx) {
 	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
 	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->bfs_seen, &c->bfs_visit[0],
 	                  &c->bfs_visit[1], &c->bfs_hist_tab, &c->bfs_pathout, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
-	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->part_visit[0], &c->part_visit[1], &c->part_peer_tab, &c->l2_flush};
+	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->part_visit[0], &c->part_visit[1], &c->part_peer_tab, &c->l2_flush, &c->sssp_dist, &c->sssp_chg};
 	for (DevBuf *b : bufs) b->release();
 	for (DevBuf &hb : c->bfs_hist) hb.release();
 	c->bfs_hist.clear();
@@ -498,7 +500,7 @@ int pgq_csr_prepare(pgq_ctx_t *ctx, int32_t id) {
 // Lane filling exactly like the reference's loop: rows are consumed in order;
 // NULL rows and src==dst rows are answered without a lane; every other row takes the next lane.
 static int build_lane_table(Ctx *c, Csr *g, int64_t n, const int64_t *src, const int64_t *dst,
-                            const uint8_t *sv, const uint8_t *dv, LaneTable *lt) {
+                            const uint8_t *sv, const uint8_t *dv, LaneTable *lt, int force_w = 0) {
 	lt->kind.assign((size_t)n, 0);
 	int64_t need = 0;
 	for (int64_t i = 0; i < n; i++) {
@@ -514,7 +516,7 @@ static int build_lane_table(Ctx *c, Csr *g, int64_t n, const int64_t *src, const
 			need++;
 		}
 	}
-	const int W = c->opt.lanes ? (int)c->opt.lanes : pick_lane_width(need);
+	const int W = force_w ? force_w : c->opt.lanes ? (int)c->opt.lanes : pick_lane_width(need);
 	lt->W = W;
 	int64_t started = 0;
 	while (started < n) {
@@ -583,6 +585,77 @@ static int query_lengths(Ctx *c, int32_t id, int64_t n, const int64_t *src, cons
 		} else { // reachability: false, not NULL (R6)
 			out_valid[r] = 1;
 			out_bool[r] = found[s] >= 0;
+		}
+	}
+	return PGQ_OK;
+}
+
+// ---- weighted next row (f4) ---------------------------------------------------------------------
+
+int pgq_csr_set_weights(pgq_ctx_t *ctx, int32_t id, int wtype, const void *w, int64_t row0, int64_t n) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (g->state != Csr::READY) {
+		set_error("csr %d not finalized", id);
+		return PGQ_ERR_STATE;
+	}
+	if (n > 0 && !w) {
+		set_error("null weights");
+		return PGQ_ERR_INVALID;
+	}
+	return csr_set_weights(c, g, wtype, w, row0, n);
+}
+
+int pgq_csr_download_weights(pgq_ctx_t *ctx, int32_t id, void *out) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	return csr_download_weights(c, g, out);
+}
+
+int pgq_csr_weight_type(pgq_ctx_t *ctx, int32_t id, int *wtype) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g || !wtype) return PGQ_ERR_INVALID;
+	*wtype = g->w_ready ? g->wtype : 0;
+	return PGQ_OK;
+}
+
+int pgq_cheapest_path_length(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                             const uint8_t *src_valid, const uint8_t *dst_valid, void *out, uint8_t *out_valid) {
+	LOCK(ctx);
+	Csr *g = find_csr(c, id);
+	if (!g) return PGQ_ERR_INVALID;
+	if (g->state != Csr::READY || !g->w_ready) {
+		set_error("csr %d has no weights (pgq_csr_set_weights after finalize)", id);
+		return PGQ_ERR_STATE;
+	}
+	if (n <= 0) return PGQ_OK;
+	LaneTable lt;
+	PGQ_TRY(build_lane_table(c, g, n, src, dst, src_valid, dst_valid, &lt, 64));
+	std::vector<uint64_t> d8((size_t)lt.nbatch * lt.W, 0);
+	PGQ_TRY(sssp_run(c, g, lt, d8.data()));
+	const bool f64 = g->wtype == PGQ_WEIGHT_F64;
+	int64_t *oi = static_cast<int64_t *>(out);
+	double *od = static_cast<double *>(out);
+	for (int64_t i = 0; i < n; i++) { // NULL rows and src == dst rows took no lane
+		out_valid[i] = lt.kind[i] == 1;
+		if (f64) od[i] = 0.0;
+		else oi[i] = 0;
+	}
+	for (size_t s = 0; s < d8.size(); s++) {
+		const int64_t r = lt.row[s];
+		if (r < 0) continue;
+		if (f64) {
+			double d;
+			memcpy(&d, &d8[s], 8);
+			out_valid[r] = !std::isinf(d);
+			od[r] = std::isinf(d) ? 0.0 : d;
+		} else {
+			const int64_t d = (int64_t)d8[s];
+			out_valid[r] = d < INT64_MAX / 2;
+			oi[r] = d < INT64_MAX / 2 ? d : 0;
 		}
 	}
 	return PGQ_OK;

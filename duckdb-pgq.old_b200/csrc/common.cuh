@@ -97,6 +97,13 @@ struct Csr {
 	DevBuf d_eid;  // int64[E] edge ids in CSR order (only when caller gave eids)
 	DevBuf d_fsrc; // uint32[E] source of each forward slot (sorted keys of the build; consumed by csr_prepare)
 	bool keep_rows = false;
+	// edge weights (sssp.cu): raw 8-byte values, int64 or double
+	int wtype = 0;          // 0 none, PGQ_WEIGHT_I64, PGQ_WEIGHT_F64
+	bool w_ready = false;
+	int64_t w_rows = 0;     // input rows received so far
+	DevBuf d_w_in;          // [E] input-row order while rows arrive
+	DevBuf d_w;             // [E] CSR slot order
+	DevBuf d_iw;            // [E] reverse-CSR order (lazy)
 	// reverse CSR (lazy)
 	bool prepared = false;
 	DevBuf d_ioff;  // uint32[V+1]
@@ -177,6 +184,7 @@ struct Ctx {
 	int64_t part_p2p_Vp = 0;
 	DevBuf bfs_alive; // per-block-slot alive lane masks (msbfs_kernels.cuh)
 	DevBuf bfs_lane; // per-call lane tables
+	DevBuf sssp_dist, sssp_chg; // cheapest_path_length: dist[V][64], two changed-bitmaps + flag
 	DevBuf bfs_ctrl; // device control block
 	DevBuf l2_flush;
 	void *h_ctrl = nullptr; // pinned host mirror of the control block (4 KiB; upper half: small-path level counts)
@@ -219,6 +227,8 @@ struct SortIO {
 int radix_sort_stable(Ctx *c, const SortIO &io);
 
 // ---- csr_build.cu ----
+int csr_set_weights(Ctx *c, Csr *g, int wtype, const void *w, int64_t row0, int64_t n); // sssp.cu
+int csr_download_weights(Ctx *c, Csr *g, void *out);
 int csr_device_build(Ctx *c, Csr *g);   // K1-K3 from d_src64/d_dst64/d_eid64
 int csr_prepare(Ctx *c, Csr *g);        // reverse CSR + degree bins
 
@@ -249,6 +259,8 @@ int msbfs_run_device(Ctx *c, Csr *g, int64_t n, const int64_t *d_src, const int6
                      uint8_t *d_out_valid);
 // partitioned variant (collective): g is the rank's slice
 int msbfs_part_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found);
+// cheapest_path_length batches (sssp.cu): h_out8[slot] = distance (int64 or double by g->wtype), +inf = unreached
+int sssp_run(Ctx *c, Csr *g, const LaneTable &lt, void *h_out8);
 
 // ---- part.cu ----
 int part_add_edges_device(Ctx *c, Csr *g, const int64_t *d_src, const int64_t *d_dst, int64_t n);

@@ -115,6 +115,25 @@ int pgq_shortestpath(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, 
                      uint64_t *out_total);
 void pgq_free(void *p);
 
+/* ---- weighted next row ------------------------------------------------------
+ * Replaces the 7-argument create_csr_edge(csr_id, v_size, num_edges, src, dst, edge_rowid, weight)
+ * and cheapest_path_length(csr_id, v_size, src, dst) of DuckPGQ ([RECALL], rule R10 in
+ * DESIGN.md section 5b; not present in /root/reference).  Weights are given per INPUT ROW
+ * (the order the rows went through pgq_csr_add_edges), in one or more consecutive chunks after
+ * pgq_csr_finalize; the CSR must track rows (edge ids given, or PGQ_CSR_KEEP_ROWS).  The library
+ * moves them into the edge's CSR slot.  wtype: BIGINT weights give BIGINT lengths, DOUBLE gives DOUBLE. */
+#define PGQ_WEIGHT_I64 1
+#define PGQ_WEIGHT_F64 2
+int pgq_csr_set_weights(pgq_ctx_t *ctx, int32_t id, int wtype, const void *w, int64_t row0, int64_t n);
+/* weights in CSR slot order (8 bytes each), and their type (0 = none) */
+int pgq_csr_download_weights(pgq_ctx_t *ctx, int32_t id, void *out);
+int pgq_csr_weight_type(pgq_ctx_t *ctx, int32_t id, int *wtype);
+/* Lane-batched Bellman-Ford (64 lanes per batch).  out: int64[n] or double[n] by the weight type;
+ * out_valid[i] = 0 (SQL NULL) for NULL inputs and unreachable destinations; src == dst gives 0.
+ * A negative cycle reachable from a source is an error (the reference would not terminate). */
+int pgq_cheapest_path_length(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                             const uint8_t *src_valid, const uint8_t *dst_valid, void *out, uint8_t *out_valid);
+
 /* DEVICE-resident variant (all rows valid): d_out int64[n] (-1 = no path), d_out_valid uint8[n]. */
 int pgq_iterativelength_device(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *d_src,
                                const int64_t *d_dst, int64_t *d_out, uint8_t *d_out_valid);

@@ -139,6 +139,49 @@ def shortestpath(V, v, e, eids, src, dst, src_valid=None, dst_valid=None, mode=0
     return off, ln, ov, values
 
 
+def csr_weights(V, v, src, w):
+    """Weights of the input rows in CSR slot order (R3 slot rule); dtype int64 or float64 kept."""
+    v, pv = _i64(v)
+    src, ps = _i64(src)
+    w = np.ascontiguousarray(w)
+    assert w.dtype in (np.int64, np.float64) and w.shape[0] == src.shape[0]
+    out = np.empty_like(w)
+    lib().orc_csr_weights(C.c_int64(V), C.c_int64(src.shape[0]), pv, ps, C.c_void_p(w.ctypes.data),
+                          C.c_void_p(out.ctypes.data))
+    return out
+
+
+def cheapest_path_length(V, v, e, w, src, dst, src_valid=None, dst_valid=None):
+    """R10 -> (out int64|float64 [n], valid uint8[n], rounds).  w in CSR slot order."""
+    v, pv = _i64(v)
+    e, pe = _i64(e)
+    src, ps = _i64(src)
+    dst, pd = _i64(dst)
+    n = src.shape[0]
+    sv, psv = _u8opt(src_valid, n)
+    dv, pdv = _u8opt(dst_valid, n)
+    w = np.ascontiguousarray(w)
+    out = np.zeros(n, dtype=w.dtype)
+    ov = np.zeros(n, dtype=np.uint8)
+    rounds = C.c_uint64(0)
+    fn = lib().orc_cheapest_path_length_i64 if w.dtype == np.int64 else lib().orc_cheapest_path_length_f64
+    fn.restype = C.c_int
+    rc = fn(C.c_int64(V), pv, pe, C.c_void_p(w.ctypes.data), C.c_int64(n), ps, pd, psv, pdv,
+            C.c_void_p(out.ctypes.data), ov.ctypes.data_as(U8P), C.byref(rounds))
+    if rc:
+        raise ValueError("negative cycle")
+    return out, ov, int(rounds.value)
+
+
+def dijkstra(V, v, e, w, source):
+    v, pv = _i64(v)
+    e, pe = _i64(e)
+    w, pw = _i64(w)
+    dist = np.empty(V, dtype=np.int64)
+    lib().orc_dijkstra_i64(C.c_int64(V), pv, pe, pw, C.c_int64(source), dist.ctypes.data_as(I64P))
+    return dist
+
+
 def bfs_simple(V, v, e, source):
     v, pv = _i64(v)
     e, pe = _i64(e)

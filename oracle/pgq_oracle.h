@@ -89,6 +89,20 @@ void orc_free(void *p);
 /* Textbook single-source queue BFS: dist[V] (-1 unreachable).  Independent of the bitset code. */
 void orc_bfs_simple(int64_t V, const int64_t *v, const int64_t *e, int64_t source, int32_t *dist);
 
+/* ---- weighted next row (R10; pgq_oracle_weighted.c) ------------------- */
+/* weights of the input rows -> CSR slot order (raw 8-byte values: int64 or double) */
+void orc_csr_weights(int64_t V, int64_t E, const int64_t *v, const int64_t *src, const void *w_in, void *w_out);
+/* cheapest_path_length: lane-batched Bellman-Ford; returns 1 if a negative cycle was met */
+int orc_cheapest_path_length_i64(int64_t V, const int64_t *v, const int64_t *e, const int64_t *w, int64_t n,
+                                 const int64_t *src, const int64_t *dst, const uint8_t *src_valid,
+                                 const uint8_t *dst_valid, int64_t *out, uint8_t *out_valid, uint64_t *rounds);
+int orc_cheapest_path_length_f64(int64_t V, const int64_t *v, const int64_t *e, const double *w, int64_t n,
+                                 const int64_t *src, const int64_t *dst, const uint8_t *src_valid,
+                                 const uint8_t *dst_valid, double *out, uint8_t *out_valid, uint64_t *rounds);
+/* independent check: binary-heap Dijkstra, non-negative int64 weights; INT64_MAX/2 = unreachable */
+void orc_dijkstra_i64(int64_t V, const int64_t *v, const int64_t *e, const int64_t *w, int64_t source,
+                      int64_t *dist);
+
 /* ---- multi-threaded driver = the reference's execution shape ----------------------- */
 /* Splits the n rows into ORC_CHUNK-row calls handed to nthreads workers (dynamic assignment),
  * like DuckDB's PhysicalProjection under PRAGMA threads (src/parallel/pipeline.cpp:104-123).

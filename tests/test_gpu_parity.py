@@ -443,3 +443,77 @@ def test_partitioned_path_world1(ctx, lanes):
     ctx.dev_free(d_src)
     ctx.dev_free(d_dst)
     ctx.csr_delete(7)
+
+
+# ---- weighted next row (rule R10) -----------------------------------------------
+
+def _weighted_case(ctx, V, src, dst, w, n_pairs, seed):
+    v, e, eids = _build_both(ctx, V, src, dst)
+    wc = orc.csr_weights(V, v, src, w)
+    ctx.csr_set_weights(1, w, chunk=1024)  # chunks as the engine would hand them over
+    _cmp_arr("weights in CSR order", ctx.csr_download_weights(1), wc)
+    ps, pd = orc.gen_pairs(seed, V, v, n_pairs)
+    rng = np.random.default_rng(seed)
+    sv = (rng.random(n_pairs) > 0.03).astype(np.uint8)
+    dv = (rng.random(n_pairs) > 0.03).astype(np.uint8)
+    ps[::41] = pd[::41]
+    got, gv = ctx.cheapest_path_length(1, ps, pd, sv, dv)
+    exp, ev, _ = orc.cheapest_path_length(V, v, e, wc, ps, pd, sv, dv)
+    _cmp_arr("cheapest_path_length validity", gv, ev)
+    assert got.dtype == exp.dtype
+    assert got.tobytes() == exp.tobytes(), "cheapest_path_length values differ (bit-exact expected)"
+    return v, e, wc, ps, pd, got, gv
+
+
+@pytest.mark.parametrize("graph", ["rmat12", "knows"])
+def test_cheapest_path_length_int64(ctx, graph):
+    if graph == "rmat12":
+        V = 1 << 12
+        src, dst = orc.gen_rmat(0x5eed0000 + 12, 12)
+    else:
+        V = 3000
+        src, dst = orc.gen_knows(0x1dbc, V, 50000)
+    w = np.random.default_rng(11).integers(1, 1000, size=len(src)).astype(np.int64)
+    v, e, wc, ps, pd, got, gv = _weighted_case(ctx, V, src, dst, w, 200, 5)
+    for i in range(0, 200, 23):  # independent check: binary-heap Dijkstra
+        if ps[i] == pd[i]:
+            continue
+        d = orc.dijkstra(V, v, e, wc, int(ps[i]))[pd[i]]
+        if gv[i]:
+            assert got[i] == d
+    ctx.csr_delete(1)
+
+
+def test_cheapest_path_length_double_and_negative(ctx):
+    V = 1 << 11
+    src, dst = orc.gen_rmat(0x5eed0000 + 11, 11)
+    w = np.random.default_rng(12).random(len(src)) * 10.0 + 0.001
+    _weighted_case(ctx, V, src, dst, w, 150, 6)
+    ctx.csr_delete(1)
+    # negative weights on a DAG (edges only from lower to higher ids): no cycle, Bellman-Ford is exact
+    lo, hi = np.minimum(src, dst), np.maximum(src, dst)
+    keep = lo != hi
+    lo, hi = lo[keep], hi[keep]
+    w = np.random.default_rng(13).integers(-50, 100, size=len(lo)).astype(np.int64)
+    _weighted_case(ctx, V, lo, hi, w, 150, 7)
+    ctx.csr_delete(1)
+
+
+def test_cheapest_path_length_errors(ctx):
+    src = np.array([0, 1, 2], dtype=np.int64)
+    dst = np.array([1, 2, 0], dtype=np.int64)
+    ctx.csr_build(1, 3, src, dst, rowids=True)
+    import pgq_b200
+    with pytest.raises(pgq_b200.PgqError):  # no weights yet
+        ctx.cheapest_path_length(1, [0], [2])
+    ctx.csr_set_weights(1, np.array([1, -5, 1], dtype=np.int64))
+    with pytest.raises(pgq_b200.PgqError, match="negative cycle"):
+        ctx.cheapest_path_length(1, [0], [2])
+    ctx.csr_set_weights(1, np.array([1.5, 2.25, 1.0]))
+    out, ov = ctx.cheapest_path_length(1, [0, 2, 1], [2, 1, 1])
+    assert ov.tolist() == [1, 1, 1] and out.tolist() == [3.75, 2.5, 0.0]
+    ctx.csr_delete(1)
+    ctx.csr_build(1, 3, src, dst)  # no row tracking
+    with pytest.raises(pgq_b200.PgqError, match="row tracking"):
+        ctx.csr_set_weights(1, np.array([1, 1, 1], dtype=np.int64))
+    ctx.csr_delete(1)
