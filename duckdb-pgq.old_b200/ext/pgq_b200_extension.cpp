@@ -39,6 +39,9 @@ struct PgqCsrSlot {
 	bool edge_started = false;   // CsrInitializeEdge done (first create_csr_edge row seen)
 	bool finalized = false;
 	int64_t num_edges = 0, rows_added = 0;
+	// 7-argument create_csr_edge: weights of the rows seen so far (raw 8-byte values, input-row order)
+	int wtype = 0;
+	std::vector<uint64_t> weights;
 };
 
 struct PgqState {
@@ -57,6 +60,17 @@ struct PgqState {
 	}
 	static void Check(const char *what, int rc) {
 		if (rc != PGQ_OK) Fail(what, rc);
+	}
+	// caller holds mu: K1-K3 run now; weights (if the rows carried any) go into the CSR slots
+	void Finish(PgqCsrSlot &s) {
+		Check("csr finalize", pgq_csr_finalize(Ctx(), s.dev_id));
+		s.finalized = true;
+		if (s.wtype) {
+			Check("csr weights", pgq_csr_set_weights(Ctx(), s.dev_id, s.wtype, s.weights.data(), 0,
+			                                         (int64_t)s.weights.size()));
+			s.weights.clear();
+			s.weights.shrink_to_fit();
+		}
 	}
 	// caller holds mu
 	pgq_ctx_t *Ctx() {
@@ -85,8 +99,7 @@ struct PgqState {
 		}
 		PgqCsrSlot &s = it->second;
 		if (!s.finalized) {
-			Check("csr finalize", pgq_csr_finalize(Ctx(), s.dev_id));
-			s.finalized = true;
+			Finish(s);
 		}
 		return s;
 	}
@@ -207,13 +220,15 @@ static void CreateCsrEdgeFunction(DataChunk &args, ExpressionState &state, Vecto
 	const int32_t csr_id = FirstInt(args, 0);
 	const int64_t v_size = FirstBigint(args, 1);
 	const int64_t num_edges = FirstBigint(args, 2);
-	const bool with_eid = args.ColumnCount() == 6;
-	DenseCol src, dst, eid;
+	const bool with_eid = args.ColumnCount() >= 6;
+	const bool with_w = args.ColumnCount() == 7; // later DuckPGQ: ..., edge_rowid, weight BIGINT|DOUBLE (R10)
+	DenseCol src, dst, eid, wcol;
 	src.Load(args.data[3], count);
 	dst.Load(args.data[4], count);
 	if (with_eid) eid.Load(args.data[5], count);
-	if (!src.all_valid || !dst.all_valid || (with_eid && !eid.all_valid)) {
-		throw InvalidInputException("pgq_b200: create_csr_edge got a NULL src / dst / edge id");
+	if (with_w) wcol.Load(args.data[6], count); // BIGINT and DOUBLE are both 8-byte columns: raw copy
+	if (!src.all_valid || !dst.all_valid || (with_eid && !eid.all_valid) || (with_w && !wcol.all_valid)) {
+		throw InvalidInputException("pgq_b200: create_csr_edge got a NULL src / dst / edge id / weight");
 	}
 	auto out = FlatVector::GetData<int32_t>(result);
 	for (idx_t i = 0; i < count; i++) out[i] = 1;
@@ -227,6 +242,14 @@ static void CreateCsrEdgeFunction(DataChunk &args, ExpressionState &state, Vecto
 		slot.finalized = false;
 		slot.rows_added = 0;
 	}
+	if (slot.rows_added == 0) {
+		slot.weights.clear();
+		slot.wtype = !with_w ? 0 : args.data[6].GetType().id() == LogicalTypeId::DOUBLE ? PGQ_WEIGHT_F64 : PGQ_WEIGHT_I64;
+	}
+	if (with_w) {
+		const uint64_t *raw = reinterpret_cast<const uint64_t *>(wcol.val.data());
+		slot.weights.insert(slot.weights.end(), raw, raw + count);
+	}
 	if (!slot.edge_started) { // first row: CsrInitializeEdge
 		PgqState::Check("create_csr_edge", pgq_csr_begin_edges(pctx, slot.dev_id, num_edges));
 		slot.edge_started = true;
@@ -236,10 +259,7 @@ static void CreateCsrEdgeFunction(DataChunk &args, ExpressionState &state, Vecto
 	PgqState::Check("create_csr_edge", pgq_csr_add_edges(pctx, slot.dev_id, src.val.data(), dst.val.data(),
 	                                                     with_eid ? eid.val.data() : nullptr, (int64_t)count));
 	slot.rows_added += (int64_t)count;
-	if (slot.rows_added == slot.num_edges) { // last row: K1-K3 run now
-		PgqState::Check("create_csr_edge", pgq_csr_finalize(pctx, slot.dev_id));
-		slot.finalized = true;
-	}
+	if (slot.rows_added == slot.num_edges) st.Finish(slot); // last row
 }
 
 // ---- iterativelength / reachability (R4-R6) ----------------------------------------------------------
@@ -278,6 +298,41 @@ static void LengthFunction(DataChunk &args, ExpressionState &state, Vector &resu
 		for (idx_t i = 0; i < count; i++) {
 			if (!ov[i]) validity.SetInvalid(i);
 		}
+	}
+}
+
+// ---- cheapest_path_length -> BIGINT / DOUBLE (R10) --------------------------------------------------
+// The result type of a scalar function is fixed at bind time, before the CSR (and its weight type)
+// exists, so the two weight types get two names: cheapest_path_length (BIGINT weights) and
+// cheapest_path_length_double (DOUBLE weights).
+template <bool F64>
+static void CheapestPathLengthFunction(DataChunk &args, ExpressionState &state, Vector &result) {
+	const idx_t count = args.size();
+	result.SetVectorType(VectorType::FLAT_VECTOR);
+	if (count == 0) return;
+	auto &st = State();
+	const int32_t csr_id = FirstInt(args, 0);
+	DenseCol src, dst;
+	src.Load(args.data[2], count);
+	dst.Load(args.data[3], count);
+	std::vector<uint8_t> ov(count);
+	auto &validity = FlatVector::Validity(result);
+	std::lock_guard<std::mutex> lock(st.mu);
+	auto *pctx = st.Ctx();
+	auto &slot = st.ReadySlot(ContextOf(state), csr_id);
+	int wtype = 0;
+	PgqState::Check("cheapest_path_length", pgq_csr_weight_type(pctx, slot.dev_id, &wtype));
+	if (wtype != (F64 ? PGQ_WEIGHT_F64 : PGQ_WEIGHT_I64)) {
+		throw InvalidInputException(wtype == 0 ? "pgq_b200: this CSR has no weights (7-argument create_csr_edge)"
+		                            : F64      ? "pgq_b200: BIGINT weights: use cheapest_path_length"
+		                                       : "pgq_b200: DOUBLE weights: use cheapest_path_length_double");
+	}
+	void *out = F64 ? (void *)FlatVector::GetData<double>(result) : (void *)FlatVector::GetData<int64_t>(result);
+	PgqState::Check("cheapest_path_length",
+	                pgq_cheapest_path_length(pctx, slot.dev_id, (int64_t)count, src.val.data(), dst.val.data(),
+	                                         src.valid.data(), dst.valid.data(), out, ov.data()));
+	for (idx_t i = 0; i < count; i++) {
+		if (!ov[i]) validity.SetInvalid(i);
 	}
 }
 
@@ -361,6 +416,10 @@ DUCKDB_EXTENSION_API void pgq_b200_init(duckdb::DatabaseInstance &db) {
 		ScalarFunctionSet set("create_csr_edge");
 		set.AddFunction(ScalarFunction({I, B, B, B, B}, I, CreateCsrEdgeFunction, true, PgqBind));
 		set.AddFunction(ScalarFunction({I, B, B, B, B, B}, I, CreateCsrEdgeFunction, true, PgqBind));
+		// with an edge weight (later DuckPGQ, rule R10)
+		set.AddFunction(ScalarFunction({I, B, B, B, B, B, B}, I, CreateCsrEdgeFunction, true, PgqBind));
+		set.AddFunction(ScalarFunction({I, B, B, B, B, B, LogicalType::DOUBLE}, I, CreateCsrEdgeFunction, true,
+		                               PgqBind));
 		CreateScalarFunctionInfo info(set);
 		catalog.CreateFunction(context, &info);
 	}
@@ -376,6 +435,9 @@ DUCKDB_EXTENSION_API void pgq_b200_init(duckdb::DatabaseInstance &db) {
 	// later DuckPGQ behaviour: [v, e, v, ..., v] with edge row ids interleaved
 	Register(context, catalog, "shortestpath_with_edges", {I, B, B, B}, LogicalType::LIST(B),
 	         ShortestPathFunction<1>);
+	Register(context, catalog, "cheapest_path_length", {I, B, B, B}, B, CheapestPathLengthFunction<false>);
+	Register(context, catalog, "cheapest_path_length_double", {I, B, B, B}, LogicalType::DOUBLE,
+	         CheapestPathLengthFunction<true>);
 	Register(context, catalog, "delete_csr", {I}, BO, DeleteCsrFunction);
 	con.Commit();
 }

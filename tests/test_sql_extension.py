@@ -45,11 +45,12 @@ def test_extension_loads_and_fails_loudly_without_gpu():
     sql = "LOAD '%s';\n" % EXT
     sql += "SELECT name FROM pragma_functions() WHERE name IN ('create_csr_vertex'," \
            "'create_csr_edge','iterativelength','reachability','shortestpath','shortestpath_with_edges'," \
-           "'delete_csr') GROUP BY name ORDER BY name;\n"
+           "'delete_csr','cheapest_path_length','cheapest_path_length_double') GROUP BY name ORDER BY name;\n"
     sql += "SELECT iterativelength(0, CAST(10 AS BIGINT), CAST(1 AS BIGINT), CAST(2 AS BIGINT));\n"
     r = run_sql(sql)
     assert r[0][0] == "result"
-    assert r[1] == ("result", ["create_csr_edge", "create_csr_vertex", "delete_csr", "iterativelength",
+    assert r[1] == ("result", ["cheapest_path_length", "cheapest_path_length_double", "create_csr_edge",
+                               "create_csr_vertex", "delete_csr", "iterativelength",
                                "reachability", "shortestpath", "shortestpath_with_edges"])
     assert r[2][0] == "error"
     if not torch.cuda.is_available():
@@ -159,3 +160,54 @@ SELECT i, shortestpath_with_edges(3, CAST(%d AS BIGINT), s, d) FROM pairs ORDER 
     got = [_parse_list(row.split(",", 1)[1]) for row in r[7][1]]
     exp = [None if not pv[i] else [int(x) for x in vals[int(off[i]):int(off[i]) + int(ln[i])]] for i in range(n)]
     assert got == exp
+
+
+@pytest.mark.gpu
+@needs_host
+def test_sql_cheapest_path_length(tmp_path):
+    """7-argument create_csr_edge (edge rowid + weight) and cheapest_path_length through SQL, BIGINT and
+    DOUBLE weights, against the oracle's Bellman-Ford (rule R10).  The distance does not depend on
+    the neighbour order, so no ORDER BY / threads=1 subtleties apply to the values."""
+    scale = 10
+    V = 1 << scale
+    src, dst = orc.gen_rmat(0x5eed0000 + scale, scale)
+    E = len(src)
+    v, e, _ = orc.csr_build(V, src, dst, want_eids=False)
+    wi = np.random.default_rng(21).integers(1, 500, size=E).astype(np.int64)
+    n = 300
+    ps, pd = orc.gen_pairs(10, V, v, n)
+    ps = ps.astype(object)
+    for i in range(0, n, 37):
+        ps[i] = None
+    sv = np.array([x is not None for x in ps], dtype=np.uint8)
+    ps_i = np.array([0 if x is None else x for x in ps], dtype=np.int64)
+    _write_csv(tmp_path / "e.csv", [src, dst, wi])
+    _write_csv(tmp_path / "pairs.csv", [np.arange(n), ps, pd])
+    sql = """LOAD '%s';
+PRAGMA threads=1;
+CREATE TABLE e(s BIGINT, d BIGINT, w BIGINT);
+CREATE TABLE pairs(i BIGINT, s BIGINT, d BIGINT);
+COPY e FROM '%s';
+COPY pairs FROM '%s';
+SELECT sum(create_csr_edge(4, CAST(%d AS BIGINT), CAST(%d AS BIGINT), s, d, rowid, w)) FROM e;
+SELECT i, cheapest_path_length(4, CAST(%d AS BIGINT), s, d) FROM pairs ORDER BY i;
+SELECT cheapest_path_length_double(4, CAST(%d AS BIGINT), s, d) FROM pairs LIMIT 1;
+SELECT sum(create_csr_edge(5, CAST(%d AS BIGINT), CAST(%d AS BIGINT), s, d, rowid, CAST(w AS DOUBLE) / 4)) FROM e;
+SELECT i, cheapest_path_length_double(5, CAST(%d AS BIGINT), s, d) FROM pairs ORDER BY i;
+SELECT iterativelength(5, CAST(%d AS BIGINT), s, d) FROM pairs WHERE i = 1;
+""" % (EXT, tmp_path / "e.csv", tmp_path / "pairs.csv", V, E, V, V, V, E, V, V)
+    r = run_sql(sql)
+    assert [k for k, _ in r[:8]] == ["result"] * 8, r[:8]
+    assert r[6] == ("result", [str(E)])
+    wc = orc.csr_weights(V, v, src, wi)
+    eo, ev, _ = orc.cheapest_path_length(V, v, e, wc, ps_i, pd, src_valid=sv)
+    got = [row.split(",", 1)[1] for row in r[7][1]]
+    assert got == ["NULL" if not ev[i] else str(int(eo[i])) for i in range(n)]
+    assert r[8][0] == "error" and "BIGINT weights" in r[8][1]
+    assert r[9] == ("result", [str(E)])
+    wcd = orc.csr_weights(V, v, src, wi.astype(np.float64) / 4)
+    do, dv, _ = orc.cheapest_path_length(V, v, e, wcd, ps_i, pd, src_valid=sv)
+    got = [row.split(",", 1)[1] for row in r[10][1]]
+    assert [g == "NULL" for g in got] == [not dv[i] for i in range(n)]
+    assert [float(g) for i, g in enumerate(got) if dv[i]] == [float(do[i]) for i in range(n) if dv[i]]
+    assert r[11][0] == "result"  # the unweighted functions work on a weighted CSR too
