@@ -269,6 +269,22 @@ def bench_paths(ctx, V, E, npairs, steps, warmup):
             off, ln, valid, vals = res
             out[name]["found"] = int(np.sum(valid))
             out[name]["path_values"] = int(len(vals))
+    # next row f4 on the same graph: cheapest_path_length, BIGINT weights 1..100 per knows row
+    try:
+        w = np.random.default_rng(4243).integers(1, 101, size=E).astype(np.int64)
+        ctx.csr_set_weights(200, w)
+        nw = min(npairs, 1024)
+        ctx.cheapest_path_length(200, src[:nw], dst[:nw])
+        ctx.reset_stats()
+        t0 = time.perf_counter()
+        res = ctx.cheapest_path_length(200, src[:nw], dst[:nw])
+        secs = time.perf_counter() - t0
+        st = ctx.stats()
+        out["cheapest_path_length"] = {"pairs": nw, "pairs_per_s": nw / secs, "ms": secs * 1e3,
+                                       "batches": int(st["batches"]), "rounds": int(st["levels"]),
+                                       "found": int(np.sum(res[1])), "weights": "int64 uniform 1..100"}
+    except Exception as ex:  # reported, never fatal for the headline
+        out["cheapest_path_length"] = {"error": str(ex)[:200]}
     ctx.csr_delete(200)
     return {"workload": "BASELINE configs[3]: LDBC-SF100-shaped knows graph V=%d E=%d, %d pairs, host buffers "
                         "(e2e through the C ABI)" % (V, E, npairs), **out}

@@ -118,6 +118,7 @@ struct Csr {
 	DevBuf d_hubchunks; // HubChunk[]
 	uint32_t n_tiny = 0, n_small = 0, n_med = 0, n_mid = 0, n_hub = 0, n_hubchunks = 0;
 	int64_t bins_tiny_max = -1, bins_small_max = -1, bins_med_max = -1, bins_hub_min = -1;
+	uint32_t eff_med_max = 0; // med_max after clamping to >= small_max
 	// 1-D partition (part.cu): this object then describes the slice of the reverse CSR owned by the
 	// rank — V = owned vertex count (local index space), E = local in-edges, d_isrc = GLOBAL sources
 	bool is_part = false;

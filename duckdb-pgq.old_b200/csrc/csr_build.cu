@@ -242,12 +242,14 @@ int csr_prepare(Ctx *c, Csr *g) {
 		g->prepared = true;
 	}
 	// in-degree classes
+	uint32_t med_max_eff = 0;
 	{
 		uint32_t tiny_max = (uint32_t)c->opt.tiny_max, small_max = (uint32_t)c->opt.small_max;
 		uint32_t hub_min = (uint32_t)c->opt.hub_min, chunk = (uint32_t)c->opt.hub_chunk;
 		uint32_t med_max = (uint32_t)c->opt.med_max;
 		if (small_max < tiny_max) tiny_max = small_max;
 		if (med_max < small_max) med_max = small_max;
+		med_max_eff = med_max;
 		if (hub_min < med_max) hub_min = med_max;
 		TmpBuf flag, tot;
 		PGQ_TRY(flag.reserve((size_t)(V + 1) * sizeof(uint32_t)));
@@ -275,6 +277,7 @@ int csr_prepare(Ctx *c, Csr *g) {
 		g->bins_tiny_max = c->opt.tiny_max;
 		g->bins_small_max = c->opt.small_max;
 		g->bins_med_max = c->opt.med_max;
+		g->eff_med_max = med_max_eff; // clamped: d_mid and d_hub hold exactly the vertices above it
 		g->bins_hub_min = c->opt.hub_min;
 	}
 	if (need_rev) {

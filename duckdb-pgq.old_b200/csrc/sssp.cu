@@ -58,21 +58,14 @@ __global__ void sssp_seed_kernel(const uint32_t *__restrict__ lane_src, T *__res
 	atomicOr(&chg[s >> 5], 1u << (s & 31));
 }
 
+// min over the in-edges base0, base0+step, ... (32 consecutive edges per visit) of dist[src] + w, for
+// lanes `lane` and `lane + 32`; only sources whose bit is set in chg_prev are read.
 template <typename T>
-__global__ void __launch_bounds__(256) sssp_relax_kernel(const uint32_t *__restrict__ ioff,
-                                                         const uint32_t *__restrict__ isrc, const T *__restrict__ iw,
-                                                         T *dist, const uint32_t *__restrict__ chg_prev,
-                                                         uint32_t *__restrict__ chg_next, uint32_t *__restrict__ flag,
-                                                         uint32_t V) {
-	const uint32_t n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-	const unsigned lane = threadIdx.x & 31;
-	if (n >= V) return;
-	const uint32_t lo = ioff[n], hi = ioff[n + 1];
-	if (lo == hi) return;
-	T *row = dist + (size_t)n * SSSP_LANES;
-	const T cur0 = row[lane], cur1 = row[lane + 32];
-	T best0 = cur0, best1 = cur1;
-	for (uint32_t base = lo; base < hi; base += 32) {
+__device__ __forceinline__ bool sssp_scan(const uint32_t *__restrict__ isrc, const T *__restrict__ iw, const T *dist,
+                                          const uint32_t *__restrict__ chg_prev, uint32_t base0, uint32_t hi,
+                                          uint32_t step, unsigned lane, T &best0, T &best1) {
+	bool touched = false;
+	for (uint32_t base = base0; base < hi; base += step) {
 		const uint32_t j = base + lane;
 		uint32_t v = 0;
 		T w = (T)0;
@@ -83,25 +76,59 @@ __global__ void __launch_bounds__(256) sssp_relax_kernel(const uint32_t *__restr
 			if (hot) w = iw[j];
 		}
 		unsigned m = __ballot_sync(0xffffffffu, hot);
-		while (m) {
-			const int k = __ffs(m) - 1;
-			m &= m - 1;
-			const uint32_t sv = __shfl_sync(0xffffffffu, v, k);
-			const T sw = __shfl_sync(0xffffffffu, w, k);
-			const T *srow = dist + (size_t)sv * SSSP_LANES;
-			// volatile: rows are updated in place by other warps; never cache them in registers
-			const T d0 = *reinterpret_cast<const volatile T *>(srow + lane);
-			const T d1 = *reinterpret_cast<const volatile T *>(srow + lane + 32);
-			if (!WInf<T>::is_inf(d0)) {
-				const T c0 = d0 + sw;
-				if (c0 < best0) best0 = c0;
+		touched |= m != 0;
+		while (m) { // four source rows (8 loads per thread) in flight per step
+			uint32_t sv[4];
+			T sw[4], d0[4], d1[4];
+			bool on[4];
+#pragma unroll
+			for (int u = 0; u < 4; u++) {
+				on[u] = m != 0;
+				const int k = on[u] ? __ffs(m) - 1 : 0;
+				m &= m - 1; // 0 stays 0
+				sv[u] = __shfl_sync(0xffffffffu, v, k);
+				sw[u] = __shfl_sync(0xffffffffu, w, k);
 			}
-			if (!WInf<T>::is_inf(d1)) {
-				const T c1 = d1 + sw;
-				if (c1 < best1) best1 = c1;
+#pragma unroll
+			for (int u = 0; u < 4; u++) {
+				// volatile: rows are updated in place by other warps; never cache them in registers
+				const T *srow = dist + (size_t)sv[u] * SSSP_LANES;
+				d0[u] = on[u] ? *reinterpret_cast<const volatile T *>(srow + lane) : WInf<T>::value();
+				d1[u] = on[u] ? *reinterpret_cast<const volatile T *>(srow + lane + 32) : WInf<T>::value();
+			}
+#pragma unroll
+			for (int u = 0; u < 4; u++) {
+				if (!WInf<T>::is_inf(d0[u])) {
+					const T c0 = d0[u] + sw[u];
+					if (c0 < best0) best0 = c0;
+				}
+				if (!WInf<T>::is_inf(d1[u])) {
+					const T c1 = d1[u] + sw[u];
+					if (c1 < best1) best1 = c1;
+				}
 			}
 		}
 	}
+	return touched;
+}
+
+// one warp per vertex with at most warp_max in-edges
+template <typename T>
+__global__ void __launch_bounds__(256) sssp_relax_kernel(const uint32_t *__restrict__ ioff,
+                                                         const uint32_t *__restrict__ isrc, const T *__restrict__ iw,
+                                                         T *dist, const uint32_t *__restrict__ chg_prev,
+                                                         uint32_t *__restrict__ chg_next, uint32_t *__restrict__ flag,
+                                                         uint32_t V, uint32_t warp_max) {
+	const uint32_t n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const unsigned lane = threadIdx.x & 31;
+	if (n >= V) return;
+	const uint32_t lo = ioff[n], hi = ioff[n + 1];
+	if (lo == hi || hi - lo > warp_max) return;
+	T *row = dist + (size_t)n * SSSP_LANES;
+	T best0 = WInf<T>::value(), best1 = WInf<T>::value();
+	// the vertex's own row is only read when some in-neighbour changed
+	if (!sssp_scan<T>(isrc, iw, dist, chg_prev, lo, hi, 32, lane, best0, best1)) return; // warp-uniform
+	const T cur0 = row[lane], cur1 = row[lane + 32];
 	bool ch = false;
 	if (best0 < cur0) {
 		row[lane] = best0;
@@ -111,6 +138,44 @@ __global__ void __launch_bounds__(256) sssp_relax_kernel(const uint32_t *__restr
 		row[lane + 32] = best1;
 		ch = true;
 	}
+	if (__any_sync(0xffffffffu, ch) && lane == 0) {
+		atomicOr(&chg_next[n >> 5], 1u << (n & 31));
+		*flag = 1u;
+	}
+}
+
+// one block (8 warps) per vertex of a high in-degree class list; warps take alternate 32-edge groups
+template <typename T>
+__global__ void __launch_bounds__(256) sssp_relax_big_kernel(const uint32_t *__restrict__ list,
+                                                             const uint32_t *__restrict__ ioff,
+                                                             const uint32_t *__restrict__ isrc,
+                                                             const T *__restrict__ iw, T *dist,
+                                                             const uint32_t *__restrict__ chg_prev,
+                                                             uint32_t *__restrict__ chg_next,
+                                                             uint32_t *__restrict__ flag) {
+	__shared__ T part[8][SSSP_LANES];
+	__shared__ int s_touched;
+	const uint32_t n = list[blockIdx.x];
+	const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const uint32_t lo = ioff[n], hi = ioff[n + 1];
+	if (threadIdx.x == 0) s_touched = 0;
+	__syncthreads();
+	T best0 = WInf<T>::value(), best1 = WInf<T>::value();
+	const bool touched = sssp_scan<T>(isrc, iw, dist, chg_prev, lo + warp * 32, hi, 8 * 32, lane, best0, best1);
+	part[warp][lane] = best0;
+	part[warp][lane + 32] = best1;
+	if (touched && lane == 0) s_touched = 1;
+	__syncthreads();
+	if (!s_touched || threadIdx.x >= SSSP_LANES) return;
+	T best = part[0][threadIdx.x];
+#pragma unroll
+	for (int k = 1; k < 8; k++) {
+		const T x = part[k][threadIdx.x];
+		if (x < best) best = x;
+	}
+	T *row = dist + (size_t)n * SSSP_LANES;
+	const bool ch = best < row[threadIdx.x];
+	if (ch) row[threadIdx.x] = best;
 	if (__any_sync(0xffffffffu, ch) && lane == 0) {
 		atomicOr(&chg_next[n >> 5], 1u << (n & 31));
 		*flag = 1u;
@@ -221,8 +286,22 @@ static int sssp_batches(Ctx *c, Csr *g, const LaneTable &lt, T *h_out) {
 			PGQ_CUDA(cudaMemsetAsync(chg[cur ^ 1], 0, (size_t)cw * 4, st));
 			PGQ_CUDA(cudaMemsetAsync(d_flag, 0, 4, st));
 			sssp_relax_kernel<T><<<div_up((uint64_t)V * 32, 256), 256, 0, st>>>(
-			    g->d_ioff.as<uint32_t>(), g->d_isrc.as<uint32_t>(), iw, dist, chg[cur], chg[cur ^ 1], d_flag, V);
+			    g->d_ioff.as<uint32_t>(), g->d_isrc.as<uint32_t>(), iw, dist, chg[cur], chg[cur ^ 1], d_flag, V,
+			    g->eff_med_max);
 			count_launch(c);
+			// in-degree above med_max: exactly the `mid` and `hub` class lists of csr_prepare
+			if (g->n_mid) {
+				sssp_relax_big_kernel<T><<<g->n_mid, 256, 0, st>>>(g->d_mid.as<uint32_t>(), g->d_ioff.as<uint32_t>(),
+				                                                 g->d_isrc.as<uint32_t>(), iw, dist, chg[cur],
+				                                                 chg[cur ^ 1], d_flag);
+				count_launch(c);
+			}
+			if (g->n_hub) {
+				sssp_relax_big_kernel<T><<<g->n_hub, 256, 0, st>>>(g->d_hub.as<uint32_t>(), g->d_ioff.as<uint32_t>(),
+				                                                 g->d_isrc.as<uint32_t>(), iw, dist, chg[cur],
+				                                                 chg[cur ^ 1], d_flag);
+				count_launch(c);
+			}
 			PGQ_CUDA(cudaMemcpyAsync(h_flag, d_flag, 4, cudaMemcpyDeviceToHost, st));
 			PGQ_CUDA(cudaStreamSynchronize(st));
 			c->stats.levels++;

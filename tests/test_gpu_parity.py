@@ -475,6 +475,16 @@ def test_cheapest_path_length_int64(ctx, graph):
         src, dst = orc.gen_knows(0x1dbc, V, 50000)
     w = np.random.default_rng(11).integers(1, 1000, size=len(src)).astype(np.int64)
     v, e, wc, ps, pd, got, gv = _weighted_case(ctx, V, src, dst, w, 200, 5)
+    # same answers when almost every vertex goes through the block-per-vertex kernel
+    ctx.set_option("small_max", 2)
+    ctx.set_option("med_max", 1)  # clamped to small_max internally
+    try:
+        again, av = ctx.cheapest_path_length(1, ps, pd)
+        ref, rv, _ = orc.cheapest_path_length(V, v, e, wc, ps, pd)
+        assert av.tolist() == rv.tolist() and again.tobytes() == ref.tobytes()
+    finally:
+        ctx.set_option("small_max", 64)
+        ctx.set_option("med_max", 512)
     for i in range(0, 200, 23):  # independent check: binary-heap Dijkstra
         if ps[i] == pd[i]:
             continue
