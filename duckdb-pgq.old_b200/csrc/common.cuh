@@ -312,26 +312,6 @@ __host__ __device__ static inline uint32_t part_newid(uint64_t v, const PartMap 
 int part_add_edges_device(Ctx *c, Csr *g, const int64_t *d_src, const int64_t *d_dst, int64_t n);
 int part_finalize(Ctx *c, Csr *g);
 int part_offsets_u32(Ctx *c, const uint32_t *keys, uint32_t n, uint32_t nv, uint32_t *off); // csr_build.cu
-// Ownership is block-cyclic over 32-vertex blocks (one frontier-bitmap word): vertex v belongs to
-// rank (v/32) % G.  Contiguous ranges would put all R-MAT hubs on rank 0.  Internally vertices are
-// renumbered rank-major, new(v) = owner*Vp + local(v), so every rank's slice of the replicated
-// frontier structures is contiguous (in-place allgather) and sources index them directly.
-static constexpr int PART_BLOCK_LOG2 = 5;
-static inline int64_t part_slice(int64_t V, int world) {
-	const int64_t nblk = (V + 31) / 32;
-	const int64_t vp = (nblk + world - 1) / world * 32;
-	return (vp + 255) / 256 * 256;
-}
-__host__ __device__ static inline uint32_t part_owner(uint64_t v, uint32_t G) {
-	return (uint32_t)((v >> PART_BLOCK_LOG2) % G);
-}
-__host__ __device__ static inline uint32_t part_local(uint64_t v, uint32_t G) {
-	return (uint32_t)((((v >> PART_BLOCK_LOG2) / G) << PART_BLOCK_LOG2) | (v & 31u));
-}
-__host__ __device__ static inline uint32_t part_newid(uint64_t v, uint32_t G, uint64_t Vp) {
-	return (uint32_t)(part_owner(v, G) * Vp + part_local(v, G));
-}
-
 // ---- gen.cu ----
 int gen_rmat_device(Ctx *c, uint64_t seed, int scale, int64_t E, int64_t *d_src, int64_t *d_dst);
 int gen_rmat_rows_device(Ctx *c, uint64_t seed, int scale, int64_t row0, int64_t n, int64_t *d_src, int64_t *d_dst);

@@ -189,12 +189,6 @@ __device__ __forceinline__ Slice<SW> warp_or_groups(Slice<SW> s) {
 	return s;
 }
 
-__device__ __forceinline__ void flag_change(BfsCtrl *ctrl, bool anynew) {
-	if (__any_sync(0xffffffffu, anynew)) {
-		if ((threadIdx.x & 31) == 0) ctrl->change = 1u;
-	}
-}
-
 __device__ __forceinline__ void snapshot_frontier(BfsCtrl *ctrl) {
 	ctrl->out_edges = ctrl->next_edges;
 	ctrl->out_verts = ctrl->next_verts;
@@ -204,39 +198,8 @@ __device__ __forceinline__ void snapshot_frontier(BfsCtrl *ctrl) {
 	ctrl->next_items = 0;
 }
 
-// Frontier statistics for the direction switch: vertices with a non-empty `next` word and the sum
-// of their out-degrees.  `leader_new` is true in exactly one thread per such vertex.
-__device__ __forceinline__ void count_frontier(BfsCtrl *ctrl, const int64_t *off, uint32_t n, bool leader_new) {
-	unsigned long long deg = 0;
-	if (leader_new) deg = (unsigned long long)(off[n + 1] - off[n]);
-	const unsigned m = __ballot_sync(0xffffffffu, leader_new);
-	if (m == 0) return;
-#pragma unroll
-	for (int d = 16; d > 0; d >>= 1) deg += __shfl_xor_sync(0xffffffffu, deg, d);
-	if ((threadIdx.x & 31) == 0) {
-		atomicAdd(&ctrl->next_edges, deg);
-		atomicAdd(&ctrl->next_verts, (uint32_t)__popc(m));
-	}
-}
-
 __device__ __forceinline__ bool fbit_test(const uint32_t *f, uint32_t v) {
 	return (__ldg(f + (v >> 5)) >> (v & 31)) & 1u;
-}
-
-// pull_small: the warp owns G = 32/TPV consecutive vertices; lane 0 stores their frontier bits as one
-// naturally aligned G-bit unit (plain store: the small kernel runs first and owns every unit; the
-// mid/hub kernels add their vertices afterwards with atomicOr).
-template <int TPV>
-__device__ __forceinline__ void store_group_bits(uint32_t *fnext, uint64_t first_vertex, unsigned ballot) {
-	constexpr int G = 32 / TPV;
-	uint32_t b = 0;
-#pragma unroll
-	for (int k = 0; k < G; k++) b |= ((ballot >> (k * TPV)) & 1u) << k;
-	if ((threadIdx.x & 31) == 0) {
-		if (G == 32) fnext[first_vertex >> 5] = b;
-		else if (G == 16) reinterpret_cast<uint16_t *>(fnext)[first_vertex >> 4] = (uint16_t)b;
-		else reinterpret_cast<uint8_t *>(fnext)[first_vertex >> 3] = (uint8_t)b;
-	}
 }
 
 template <int TPV>
