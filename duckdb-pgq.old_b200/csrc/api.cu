@@ -210,6 +210,7 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "filter_gamma")) c->opt.filter_gamma = value < 0 ? 0 : value;
 	else if (!strcmp(key, "push_beta")) c->opt.push_beta = value < 1 ? 1 : value;
 	else if (!strcmp(key, "small_path")) c->opt.small_path = value;
+	else if (!strcmp(key, "small_edge_mb")) c->opt.small_edge_mb = value < 0 ? 0 : value;
 	else {
 		set_error("unknown option '%s'", key);
 		return PGQ_ERR_INVALID;

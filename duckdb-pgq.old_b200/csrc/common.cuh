@@ -143,6 +143,7 @@ struct Options {
 	int64_t push_beta = 32; // push when frontier out-edges * push_beta <= E
 	int64_t push_vbeta = 16; // ... and frontier vertices * push_vbeta <= V (+ slack for tiny graphs)
 	int64_t filter_gamma = 2; // pull tests the frontier bitmap while frontier out-edges * gamma <= E
+	int64_t small_edge_mb = 256; // ... while E * W/8 stays below this many MiB (one level's gather volume)
 	int64_t small_path = 1;   // whole-batch cooperative kernel for graphs that live in L2 (msbfs_small.cuh)
 };
 

@@ -266,7 +266,7 @@ bool small_eligible(const Ctx *c, const Csr *g, int W, bool keep_hist) {
 	if (!c->opt.small_path || c->opt.stats || g->V <= 0 || g->is_part) return false;
 	const uint64_t bm = (uint64_t)g->V * (W / 8), eb = (uint64_t)g->E * (W / 8);
 	if (keep_hist && bm > (2ull << 20)) return false; // 49 level buffers
-	return bm <= (8ull << 20) && eb <= (64ull << 20);
+	return bm <= (8ull << 20) && eb <= ((uint64_t)c->opt.small_edge_mb << 20);
 }
 
 template <int W>
