@@ -97,6 +97,53 @@ static int finalize(Ctx *c, Csr *g) {
 
 } // namespace pgq
 
+
+namespace pgq {
+
+const char *last_error_str() {
+	return g_err;
+}
+
+int ctx_init_resources(Ctx *c) {
+	PGQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+	PGQ_CUDA(cudaEventCreate(&c->ev_a));
+	PGQ_CUDA(cudaEventCreate(&c->ev_b));
+	PGQ_CUDA(cudaEventCreate(&c->ev_c));
+	PGQ_CUDA(cudaEventCreate(&c->ev_timer));
+	PGQ_CUDA(cudaEventCreate(&c->ev_timer2));
+	PGQ_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+	PGQ_CUDA(cudaHostAlloc(&c->h_ctrl, 4096, cudaHostAllocDefault));
+	return PGQ_OK;
+}
+
+void ctx_release_resources(Ctx *c) {
+	for (Ctx *h : c->helpers) {
+		if (h->stream) cudaStreamSynchronize(h->stream);
+		ctx_release_resources(h);
+		delete h;
+	}
+	c->helpers.clear();
+	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
+	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->bfs_seen, &c->bfs_visit[0],
+	                  &c->bfs_visit[1], &c->bfs_hist_tab, &c->bfs_pathout, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
+	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->part_visit[0], &c->part_visit[1], &c->part_peer_tab, &c->l2_flush, &c->sssp_dist, &c->sssp_chg};
+	for (DevBuf *b : bufs) b->release();
+	for (DevBuf &hb : c->bfs_hist) hb.release();
+	c->bfs_hist.clear();
+	if (c->h_ctrl) cudaFreeHost(c->h_ctrl);
+	c->h_ctrl = nullptr;
+	if (c->ev_a) cudaEventDestroy(c->ev_a);
+	if (c->ev_b) cudaEventDestroy(c->ev_b);
+	if (c->ev_c) cudaEventDestroy(c->ev_c);
+	if (c->ev_timer) cudaEventDestroy(c->ev_timer);
+	if (c->ev_timer2) cudaEventDestroy(c->ev_timer2);
+	if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+	if (c->stream) cudaStreamDestroy(c->stream);
+	c->stream = nullptr;
+}
+
+} // namespace pgq
+
 using namespace pgq;
 
 #define LOCK(ctx)                                   \
@@ -142,13 +189,12 @@ int pgq_init(int device, pgq_ctx_t **out_ctx) {
 	Ctx *c = &ctx->c;
 	c->device = device;
 	c->sm_count = prop.multiProcessorCount;
-	PGQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-	PGQ_CUDA(cudaEventCreate(&c->ev_a));
-	PGQ_CUDA(cudaEventCreate(&c->ev_b));
-	PGQ_CUDA(cudaEventCreate(&c->ev_c));
-	PGQ_CUDA(cudaEventCreate(&c->ev_timer));
-	PGQ_CUDA(cudaEventCreate(&c->ev_timer2));
-	PGQ_CUDA(cudaHostAlloc(&c->h_ctrl, 4096, cudaHostAllocDefault));
+	int rc = ctx_init_resources(c);
+	if (rc != PGQ_OK) {
+		ctx_release_resources(c);
+		delete ctx;
+		return rc;
+	}
 	*out_ctx = ctx;
 	return PGQ_OK;
 }
@@ -170,20 +216,7 @@ int pgq_shutdown(pgq_ctx_t *ctx) {
 		if (nc) nc->CommDestroy((ncclComm_t)c->nccl_comm);
 		c->nccl_comm = nullptr;
 	}
-	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
-	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->bfs_seen, &c->bfs_visit[0],
-	                  &c->bfs_visit[1], &c->bfs_hist_tab, &c->bfs_pathout, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
-	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->part_visit[0], &c->part_visit[1], &c->part_peer_tab, &c->l2_flush, &c->sssp_dist, &c->sssp_chg};
-	for (DevBuf *b : bufs) b->release();
-	for (DevBuf &hb : c->bfs_hist) hb.release();
-	c->bfs_hist.clear();
-	if (c->h_ctrl) cudaFreeHost(c->h_ctrl);
-	cudaEventDestroy(c->ev_a);
-	cudaEventDestroy(c->ev_b);
-	cudaEventDestroy(c->ev_c);
-	cudaEventDestroy(c->ev_timer);
-	cudaEventDestroy(c->ev_timer2);
-	cudaStreamDestroy(c->stream);
+	ctx_release_resources(c);
 	delete ctx;
 	return PGQ_OK;
 }
@@ -211,6 +244,7 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "push_beta")) c->opt.push_beta = value < 1 ? 1 : value;
 	else if (!strcmp(key, "small_path")) c->opt.small_path = value;
 	else if (!strcmp(key, "small_edge_mb")) c->opt.small_edge_mb = value < 0 ? 0 : value;
+	else if (!strcmp(key, "streams")) c->opt.streams = value < 1 ? 1 : value > 8 ? 8 : value;
 	else {
 		set_error("unknown option '%s'", key);
 		return PGQ_ERR_INVALID;

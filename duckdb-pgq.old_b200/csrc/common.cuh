@@ -145,6 +145,7 @@ struct Options {
 	int64_t filter_gamma = 2; // pull tests the frontier bitmap while frontier out-edges * gamma <= E
 	int64_t small_edge_mb = 256; // ... while E * W/8 stays below this many MiB (one level's gather volume)
 	int64_t small_path = 1;   // whole-batch cooperative kernel for graphs that live in L2 (msbfs_small.cuh)
+	int64_t streams = 4;      // general path: batches of one call in flight at once (own stream + buffers each)
 };
 
 // What the two frontier buffers hold after the last completed batch (msbfs.cu run_batch).
@@ -194,7 +195,15 @@ struct Ctx {
 	cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_timer = nullptr, ev_timer2 = nullptr;
 	std::vector<cudaEvent_t> ev_pool; // level-kernel timing events
 	size_t ev_used = 0;
+	// batch-level concurrency (msbfs.cu run_batches): helper contexts with their own stream, control
+	// block and frontier buffers; they share the caller's CSRs read-only and hold none of their own
+	std::vector<Ctx *> helpers;
+	cudaEvent_t ev_fork = nullptr;
 };
+
+int ctx_init_resources(Ctx *c);    // stream, events, pinned control mirror (api.cu)
+void ctx_release_resources(Ctx *c); // everything a Ctx owns except its CSRs (api.cu)
+const char *last_error_str();
 
 inline void count_launch(Ctx *c, uint64_t n = 1) {
 	c->stats.kernel_launches += n;

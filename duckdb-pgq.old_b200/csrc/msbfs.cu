@@ -6,6 +6,10 @@
 #include "msbfs_small.cuh"
 #include "nccl_dl.cuh"
 
+#include <atomic>
+#include <functional>
+#include <thread>
+
 namespace pgq {
 
 namespace {
@@ -496,6 +500,97 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 	return PGQ_OK;
 }
 
+// All batches of one call (lengths / reachability).  A batch on the general path meets the host once
+// per level and leaves the GPU idle across launch gaps, memsets and kernel tails (about 12 % of a
+// batch on R-MAT s24, most of it on mid-sized graphs), and batches are independent: so up to
+// `streams` of them are in flight at once, each on a helper context with its own stream, control
+// block and frontier buffers, driven by its own host thread.  The CSR is shared read-only.
+using BatchFn = std::function<int(Ctx *, const BatchBufs &, int64_t)>; // (worker context, its buffers, batch index)
+
+int run_batches(Ctx *c, Csr *g, const BatchBufs &b0, int W, int64_t nbatch, bool keep_hist, const BatchFn &fn) {
+	int nw = (int)std::min<int64_t>(c->opt.streams, nbatch);
+	if (nw < 2 || c->opt.timing || c->opt.stats || c->opt.trace || g->is_part || small_eligible(c, g, W, keep_hist)) {
+		for (int64_t bi = 0; bi < nbatch; bi++) PGQ_TRY(fn(c, b0, bi));
+		return PGQ_OK;
+	}
+	while ((int)c->helpers.size() < nw - 1) {
+		Ctx *h = new Ctx();
+		h->device = c->device;
+		h->sm_count = c->sm_count;
+		const int rc = ctx_init_resources(h);
+		if (rc != PGQ_OK) {
+			ctx_release_resources(h);
+			delete h;
+			return rc;
+		}
+		c->helpers.push_back(h);
+	}
+	PGQ_CUDA(cudaEventRecord(c->ev_fork, c->stream)); // the lane tables are in place after this point
+	struct Res {
+		int rc = PGQ_OK;
+		std::string err;
+	};
+	std::vector<Res> res((size_t)nw);
+	std::atomic<int64_t> next_batch{0};
+	std::atomic<int> failed{0};
+	auto drain = [&](Ctx *w, const BatchBufs &bw, Res &r) {
+		while (!failed.load(std::memory_order_relaxed)) {
+			const int64_t bi = next_batch.fetch_add(1);
+			if (bi >= nbatch) break;
+			const int rc = fn(w, bw, bi);
+			if (rc != PGQ_OK) {
+				r.rc = rc;
+				r.err = last_error_str();
+				failed.store(1);
+				break;
+			}
+		}
+	};
+	std::vector<std::thread> threads;
+	for (int i = 1; i < nw; i++) {
+		threads.emplace_back([&, i] {
+			Ctx *w = c->helpers[(size_t)i - 1];
+			Res &r = res[(size_t)i];
+			auto fail = [&](int rc) {
+				r.rc = rc;
+				r.err = last_error_str();
+				failed.store(1);
+			};
+			if (cudaSetDevice(w->device) != cudaSuccess || cudaStreamWaitEvent(w->stream, c->ev_fork, 0) != cudaSuccess) {
+				set_error("helper stream setup failed");
+				return fail(PGQ_ERR_CUDA);
+			}
+			w->opt = c->opt;
+			BatchBufs bw{};
+			const int rc = alloc_bufs(w, g, W, &bw);
+			if (rc == PGQ_ERR_OOM) return; // no room for a second set of bitmaps: the other workers take every batch
+			if (rc != PGQ_OK) return fail(rc);
+			drain(w, bw, r);
+			if (cudaStreamSynchronize(w->stream) != cudaSuccess) {
+				set_error("helper stream failed");
+				fail(PGQ_ERR_CUDA);
+			}
+		});
+	}
+	drain(c, b0, res[0]);
+	for (std::thread &t : threads) t.join();
+	for (Ctx *h : c->helpers) {
+		c->stats.kernel_launches += h->stats.kernel_launches;
+		c->stats.batches += h->stats.batches;
+		c->stats.levels += h->stats.levels;
+		c->stats.push_levels += h->stats.push_levels;
+		c->stats.h2d_bytes += h->stats.h2d_bytes;
+		c->stats.d2h_bytes += h->stats.d2h_bytes;
+		h->stats = pgq_stats_t{};
+	}
+	for (const Res &r : res)
+		if (r.rc != PGQ_OK) {
+			set_error("%s", r.err.c_str());
+			return r.rc;
+		}
+	return PGQ_OK;
+}
+
 } // namespace
 
 // found[slot] for all lane slots of all batches (host).  Path output per batch when `paths`.
@@ -521,64 +616,83 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 	PGQ_CUDA(cudaMemcpyAsync(d_dst, lt.dst.data(), (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
 	c->stats.h2d_bytes += (uint64_t)nslots * 8;
 	const uint64_t levels_before = c->stats.levels;
-	DevBuf &d_out = c->bfs_pathout; // persistent: a per-call buffer would cudaMalloc/cudaFree every batch
-	std::vector<uint64_t> lane_off((size_t)W);
-	uint64_t total = 0; // running list offset over all rows (paths)
-	for (int64_t bi = 0; bi < lt.nbatch; bi++) {
-		int nlev = 0;
-		PGQ_TRY(run_batch(c, g, b, W, want_paths, d_src + bi * W, d_dst + bi * W, d_found + bi * W, &nlev));
-		if (!want_paths) continue;
-		// ---- K8: reconstruct this batch's paths in ROW order (R9) ----
-		int32_t *hf = h_found + bi * W;
-		PGQ_CUDA(cudaMemcpyAsync(hf, d_found + bi * W, (size_t)W * 4, cudaMemcpyDeviceToHost, st));
-		PGQ_CUDA(cudaStreamSynchronize(st));
-		c->stats.d2h_bytes += (uint64_t)W * 4;
-		const int64_t r0 = lt.batch_row_begin[bi], r1 = lt.batch_row_end[bi];
-		const uint64_t base = total;
-		int lane = 0;
-		for (int64_t r = r0; r < r1; r++) {
-			const uint8_t kind = lt.kind[r];
-			uint64_t len = 0;
-			if (kind == 1) {
-				len = 1;
-			} else if (kind == 2) {
-				while (lane < W && lt.row[bi * W + lane] != r) lane++;
-				if (lane < W && hf[lane] >= 0) {
-					len = paths->mode == 0 ? (uint64_t)hf[lane] + 1 : 2ull * (uint64_t)hf[lane] + 1;
-					lane_off[lane] = total - base;
+	if (!want_paths) {
+		PGQ_TRY(run_batches(c, g, b, W, lt.nbatch, false, [&](Ctx *w, const BatchBufs &bw, int64_t bi) {
+			return run_batch(w, g, bw, W, false, d_src + bi * W, d_dst + bi * W, d_found + bi * W);
+		}));
+	} else {
+		// ---- K8: each batch reconstructs its paths in ROW order (R9) with batch-local list offsets;
+		// the batches (possibly finished out of order on different streams) are stitched afterwards.
+		std::vector<std::vector<int64_t>> batch_vals((size_t)lt.nbatch);
+		PGQ_TRY(run_batches(c, g, b, W, lt.nbatch, true, [&](Ctx *w, const BatchBufs &bw, int64_t bi) {
+			cudaStream_t ws = w->stream;
+			int nlev = 0;
+			PGQ_TRY(run_batch(w, g, bw, W, true, d_src + bi * W, d_dst + bi * W, d_found + bi * W, &nlev));
+			int32_t *hf = h_found + bi * W;
+			PGQ_CUDA(cudaMemcpyAsync(hf, d_found + bi * W, (size_t)W * 4, cudaMemcpyDeviceToHost, ws));
+			PGQ_CUDA(cudaStreamSynchronize(ws));
+			w->stats.d2h_bytes += (uint64_t)W * 4;
+			const int64_t r0 = lt.batch_row_begin[bi], r1 = lt.batch_row_end[bi];
+			std::vector<uint64_t> lane_off((size_t)W);
+			uint64_t bt = 0; // values of this batch so far
+			int lane = 0;
+			for (int64_t r = r0; r < r1; r++) {
+				const uint8_t kind = lt.kind[r];
+				uint64_t len = 0;
+				if (kind == 1) {
+					len = 1;
+				} else if (kind == 2) {
+					while (lane < W && lt.row[bi * W + lane] != r) lane++;
+					if (lane < W && hf[lane] >= 0) {
+						len = paths->mode == 0 ? (uint64_t)hf[lane] + 1 : 2ull * (uint64_t)hf[lane] + 1;
+						lane_off[lane] = bt;
+					}
 				}
+				paths->entries[r].offset = bt; // batch-local until stitched
+				paths->entries[r].length = len;
+				paths->valid[r] = len ? 1 : 0;
+				bt += len;
 			}
-			paths->entries[r].offset = total;
-			paths->entries[r].length = len;
-			paths->valid[r] = len ? 1 : 0;
-			total += len;
-		}
-		const uint64_t bt = total - base;
-		paths->vals.resize(total);
-		if (bt) {
+			std::vector<int64_t> &vals = batch_vals[(size_t)bi];
+			vals.resize(bt);
+			if (!bt) return (int)PGQ_OK;
+			DevBuf &d_out = w->bfs_pathout; // persistent: a per-call buffer would cudaMalloc/cudaFree every batch
 			if (bt * sizeof(int64_t) > d_out.cap) PGQ_TRY(d_out.reserve(bt * sizeof(int64_t) * 2));
-			PGQ_CUDA(cudaMemcpyAsync(d_lane_off, lane_off.data(), (size_t)W * 8, cudaMemcpyHostToDevice, st));
+			uint64_t *d_lo = d_lane_off;
+			if (w != c) { // helpers keep their own lane-offset table
+				PGQ_TRY(w->bfs_lane.reserve((size_t)W * sizeof(uint64_t) + 64));
+				d_lo = w->bfs_lane.as<uint64_t>();
+			}
+			PGQ_CUDA(cudaMemcpyAsync(d_lo, lane_off.data(), (size_t)W * 8, cudaMemcpyHostToDevice, ws));
 			// device table of the level buffers (they may have been reallocated by this batch)
 			std::vector<const uint32_t *> hp((size_t)nlev + 1);
-			for (int k = 0; k <= nlev; k++) hp[(size_t)k] = c->bfs_hist[(size_t)k].as<uint32_t>();
-			PGQ_TRY(c->bfs_hist_tab.reserve(hp.size() * sizeof(uint32_t *)));
-			PGQ_CUDA(cudaMemcpyAsync(c->bfs_hist_tab.p, hp.data(), hp.size() * sizeof(uint32_t *),
-			                         cudaMemcpyHostToDevice, st));
-			bfs_paths_hist_kernel<<<W, 256, 0, st>>>(
-			    c->bfs_hist_tab.as<const uint32_t *const>(), g->d_ioff.as<uint32_t>(), g->d_isrc.as<uint32_t>(),
-			    g->d_ipos.as<uint32_t>(),
-			    g->have_eid ? g->d_eid.as<int64_t>() : nullptr, g->keep_rows ? g->d_row.as<uint32_t>() : nullptr,
-			    d_src + bi * W, d_dst + bi * W, d_found + bi * W, (const unsigned long long *)d_lane_off, W,
-			    paths->mode,
-			    d_out.as<int64_t>());
-			count_launch(c);
-			PGQ_CUDA(cudaMemcpyAsync(paths->vals.data() + base, d_out.p, bt * sizeof(int64_t),
-			                         cudaMemcpyDeviceToHost, st));
-			PGQ_CUDA(cudaStreamSynchronize(st));
-			c->stats.d2h_bytes += bt * 8;
+			for (int k = 0; k <= nlev; k++) hp[(size_t)k] = w->bfs_hist[(size_t)k].as<uint32_t>();
+			PGQ_TRY(w->bfs_hist_tab.reserve(hp.size() * sizeof(uint32_t *)));
+			PGQ_CUDA(cudaMemcpyAsync(w->bfs_hist_tab.p, hp.data(), hp.size() * sizeof(uint32_t *),
+			                         cudaMemcpyHostToDevice, ws));
+			bfs_paths_hist_kernel<<<W, 256, 0, ws>>>(
+			    w->bfs_hist_tab.as<const uint32_t *const>(), g->d_ioff.as<uint32_t>(), g->d_isrc.as<uint32_t>(),
+			    g->d_ipos.as<uint32_t>(), g->have_eid ? g->d_eid.as<int64_t>() : nullptr,
+			    g->keep_rows ? g->d_row.as<uint32_t>() : nullptr, d_src + bi * W, d_dst + bi * W, d_found + bi * W,
+			    (const unsigned long long *)d_lo, W, paths->mode, d_out.as<int64_t>());
+			count_launch(w);
+			PGQ_CUDA(cudaMemcpyAsync(vals.data(), d_out.p, bt * sizeof(int64_t), cudaMemcpyDeviceToHost, ws));
+			PGQ_CUDA(cudaStreamSynchronize(ws));
+			w->stats.d2h_bytes += bt * 8;
 			// trivial rows: [src]
 			for (int64_t r = r0; r < r1; r++)
-				if (lt.kind[r] == 1) paths->vals[paths->entries[r].offset] = row_src[r];
+				if (lt.kind[r] == 1) vals[paths->entries[r].offset] = row_src[r];
+			return (int)PGQ_OK;
+		}));
+		uint64_t total = 0; // running list offset over all rows
+		for (int64_t bi = 0; bi < lt.nbatch; bi++) total += batch_vals[(size_t)bi].size();
+		paths->vals.resize(total);
+		total = 0;
+		for (int64_t bi = 0; bi < lt.nbatch; bi++) {
+			const std::vector<int64_t> &vals = batch_vals[(size_t)bi];
+			for (int64_t r = lt.batch_row_begin[bi]; r < lt.batch_row_end[bi]; r++) paths->entries[r].offset += total;
+			if (!vals.empty()) memcpy(paths->vals.data() + total, vals.data(), vals.size() * sizeof(int64_t));
+			total += vals.size();
 		}
 	}
 	if (!want_paths) {
@@ -842,8 +956,9 @@ int msbfs_run_device(Ctx *c, Csr *g, int64_t n, const int64_t *d_srcs, const int
 	                                                            d_dst, d_err);
 	count_launch(c);
 	const uint64_t levels_before = c->stats.levels;
-	for (int64_t bi = 0; bi < nbatch; bi++)
-		PGQ_TRY(run_batch(c, g, b, W, false, d_src + bi * W, d_dst + bi * W, d_found + bi * W));
+	PGQ_TRY(run_batches(c, g, b, W, nbatch, false, [&](Ctx *w, const BatchBufs &bw, int64_t bi) {
+		return run_batch(w, g, bw, W, false, d_src + bi * W, d_dst + bi * W, d_found + bi * W);
+	}));
 	rows_from_lanes_kernel<<<div_up(n, 256), 256, 0, st>>>(d_srcs, d_dsts, n, d_found, d_out, d_out_valid);
 	count_launch(c);
 	uint32_t h_err = 0;

@@ -527,3 +527,33 @@ def test_cheapest_path_length_errors(ctx):
     with pytest.raises(pgq_b200.PgqError, match="row tracking"):
         ctx.csr_set_weights(1, np.array([1, 1, 1], dtype=np.int64))
     ctx.csr_delete(1)
+
+
+@pytest.mark.parametrize("streams", [1, 3, 8])
+def test_batches_in_flight(ctx, streams):
+    """Batches of one call run concurrently on helper streams (option `streams`); lengths,
+    reachability and paths (stitched in row order, R9) must not depend on it."""
+    scale = 13
+    V = 1 << scale
+    src, dst = orc.gen_rmat(0x5eed0000 + scale, scale)
+    v, e, eids = _build_both(ctx, V, src, dst)
+    n = 1024
+    ps, pd = orc.gen_pairs(11, V, v, n)
+    sv = (np.random.default_rng(3).random(n) > 0.02).astype(np.uint8)
+    ps[::41] = pd[::41]
+    ctx.set_option("lanes", 64)  # 16 batches per call
+    ctx.set_option("streams", streams)
+    try:
+        out, ov = ctx.iterativelength(1, ps, pd, sv, None)
+        got = ctx.shortestpath(1, ps, pd, sv, None, mode=1)
+        st = ctx.stats()
+    finally:
+        ctx.set_option("lanes", 0)
+        ctx.set_option("streams", 4)
+    eo, ev = orc.iterativelength(V, v, e, ps, pd, sv, None)
+    _cmp_arr("valid", ov, ev)
+    _cmp_arr("length", out, eo)
+    exp = orc.shortestpath(V, v, e, eids, ps, pd, sv, None, mode=1)
+    assert_paths_equal(got, exp, "streams %d" % streams)
+    assert st["batches"] >= 16
+    ctx.csr_delete(1)
