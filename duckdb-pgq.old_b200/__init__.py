@@ -213,6 +213,21 @@ class Context:
                                                out.ctypes.data_as(I64P), ov.ctypes.data_as(U8P)))
         return out, ov
 
+    def iterativelength_bounded(self, csr_id, src, dst, lower, upper, src_valid=None, dst_valid=None):
+        """6-argument iterativelength (R11): at most `upper` levels (negative = unbounded); a shortest
+        length below `lower` is NULL."""
+        src, ps = _i64(src)
+        dst, pd = _i64(dst)
+        n = src.shape[0]
+        sv, psv = _u8(src_valid, n)
+        dv, pdv = _u8(dst_valid, n)
+        out = np.full(n, -1, dtype=np.int64)
+        ov = np.zeros(n, dtype=np.uint8)
+        self._chk(self.lib.pgq_iterativelength_bounded(self._ctx, C.c_int32(csr_id), C.c_int64(n), ps, pd, psv, pdv,
+                                                       C.c_int64(lower), C.c_int64(upper),
+                                                       out.ctypes.data_as(I64P), ov.ctypes.data_as(U8P)))
+        return out, ov
+
     def csr_set_weights(self, csr_id, w, chunk=None):
         """Edge weights per INPUT ROW (int64 or float64), optionally sent in chunks like the rows of
         the 7-argument create_csr_edge would arrive (R10)."""

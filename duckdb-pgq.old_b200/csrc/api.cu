@@ -578,7 +578,8 @@ static int build_lane_table(Ctx *c, Csr *g, int64_t n, const int64_t *src, const
 }
 
 static int query_lengths(Ctx *c, int32_t id, int64_t n, const int64_t *src, const int64_t *dst, const uint8_t *sv,
-                         const uint8_t *dv, int64_t *out_len, uint8_t *out_bool, uint8_t *out_valid) {
+                         const uint8_t *dv, int64_t *out_len, uint8_t *out_bool, uint8_t *out_valid,
+                         int64_t lower = 0, int64_t upper = -1) {
 	Csr *g = find_csr(c, id);
 	if (!g) return PGQ_ERR_INVALID;
 	if (g->state != Csr::READY) {
@@ -597,26 +598,37 @@ static int query_lengths(Ctx *c, int32_t id, int64_t n, const int64_t *src, cons
 			lt.src[k] = part_newid(lt.src[k], pm);
 			lt.dst[k] = part_newid(lt.dst[k], pm);
 		}
+		if (upper >= 0) {
+			set_error("csr %d is vertex-partitioned: bounded iterativelength is not available on that path", id);
+			return PGQ_ERR_STATE;
+		}
 		PGQ_TRY(msbfs_part_run(c, g, lt, found.data()));
+	} else if (upper != 0) { // upper == 0: no level runs, every lane stays unfound
+		// the level loops (host loop and whole-batch kernel) read the cap from the options the helper
+		// contexts copy; it is reset before anything else can run (the context lock is held)
+		c->opt.level_cap = upper < 0 || upper > 0x7fffffff ? 0x7fffffff : upper;
+		const int rc = msbfs_run(c, g, lt, found.data(), nullptr, src, n);
+		c->opt.level_cap = 0x7fffffff;
+		PGQ_TRY(rc);
 	}
-	else PGQ_TRY(msbfs_run(c, g, lt, found.data(), nullptr, src, n));
 	for (int64_t i = 0; i < n; i++) {
 		if (lt.kind[i] == 0) {
 			out_valid[i] = 0;
 			if (out_len) out_len[i] = -1;
 			if (out_bool) out_bool[i] = 0;
-		} else if (lt.kind[i] == 1) {
-			out_valid[i] = 1;
-			if (out_len) out_len[i] = 0;
+		} else if (lt.kind[i] == 1) { // src == dst: a length-0 path, in bounds only when lower <= 0 (R11)
+			out_valid[i] = lower <= 0;
+			if (out_len) out_len[i] = lower <= 0 ? 0 : -1;
 			if (out_bool) out_bool[i] = 1;
 		}
 	}
 	for (size_t s = 0; s < found.size(); s++) {
 		int64_t r = lt.row[s];
 		if (r < 0) continue;
-		if (out_len) { // iterativelength: NULL when no path
-			out_valid[r] = found[s] >= 0;
-			out_len[r] = found[s] >= 0 ? found[s] : -1;
+		if (out_len) { // iterativelength: NULL when no path (or a shortest length below the lower bound, R11)
+			const bool ok = found[s] >= 0 && found[s] >= lower;
+			out_valid[r] = ok;
+			out_len[r] = ok ? found[s] : -1;
 		} else { // reachability: false, not NULL (R6)
 			out_valid[r] = 1;
 			out_bool[r] = found[s] >= 0;
@@ -700,6 +712,13 @@ int pgq_iterativelength(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *sr
                         const uint8_t *src_valid, const uint8_t *dst_valid, int64_t *out, uint8_t *out_valid) {
 	LOCK(ctx);
 	return query_lengths(c, id, n, src, dst, src_valid, dst_valid, out, nullptr, out_valid);
+}
+
+int pgq_iterativelength_bounded(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                                const uint8_t *src_valid, const uint8_t *dst_valid, int64_t lower, int64_t upper,
+                                int64_t *out, uint8_t *out_valid) {
+	LOCK(ctx);
+	return query_lengths(c, id, n, src, dst, src_valid, dst_valid, out, nullptr, out_valid, lower, upper);
 }
 
 int pgq_reachability(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,

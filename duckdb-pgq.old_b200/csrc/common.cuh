@@ -146,6 +146,7 @@ struct Options {
 	int64_t small_edge_mb = 256; // ... while E * W/8 stays below this many MiB (one level's gather volume)
 	int64_t small_path = 1;   // whole-batch cooperative kernel for graphs that live in L2 (msbfs_small.cuh)
 	int64_t streams = 4;      // general path: batches of one call in flight at once (own stream + buffers each)
+	int64_t level_cap = 0x7fffffff; // per call, not user-settable: iterativelength's upper bound (R11)
 };
 
 // What the two frontier buffers hold after the last completed batch (msbfs.cu run_batch).

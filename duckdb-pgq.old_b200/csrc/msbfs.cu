@@ -309,6 +309,7 @@ int run_batch_small(Ctx *c, Csr *g, const BatchBufs &b, int W, bool keep_hist, c
 	a.found = d_found;
 	a.ctrl = b.ctrl;
 	a.max_levels = 0x7fffffff;
+	a.level_cap = (int)c->opt.level_cap;
 	if (keep_hist) {
 		if (c->bfs_hist.size() < (size_t)SMALL_HIST_LEVELS + 1) c->bfs_hist.resize((size_t)SMALL_HIST_LEVELS + 1);
 		std::vector<uint32_t *> hp((size_t)SMALL_HIST_LEVELS + 1);
@@ -421,7 +422,7 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 	unsigned long long cum_verts = h.out_verts; // frontier vertices of all levels so far
 	int fb[3] = {0, 1, 2}; // bitmap of visit[cur] / being built for visit[cur^1] / of what visit[cur^1] holds
 	bool have_queue = true; // queue[q] describes visit[cur] and visit[cur^1] is all-zero
-	for (int iter = 1; active; iter++) {
+	for (int iter = 1; active && iter <= (int)c->opt.level_cap; iter++) {
 		// direction switch on frontier density: top-down while the frontier's out-edges are few
 		if (keep_hist) { // fresh zeroed buffer for this level's output; the input stays where it is
 			b.visit[cur] = c->bfs_hist[(size_t)iter - 1].as<uint32_t>();

@@ -32,6 +32,7 @@ struct SmallArgs {
 	uint32_t *buf[2];      // frontier ping-pong (hist == nullptr)
 	uint32_t *const *hist; // level buffers 0..max_levels (shortestpath keeps every frontier)
 	int max_levels;
+	int level_cap; // stop after this many levels whatever is still open (iterativelength upper bound, R11)
 	const uint32_t *lane_src;
 	const uint32_t *lane_dst;
 	int32_t *found;
@@ -250,7 +251,7 @@ __global__ void __launch_bounds__(SMALL_THREADS) msbfs_small_kernel(SmallArgs a)
 			}
 		}
 		__syncthreads();
-		bool cont = __ldcg(&slot[16]) != 0 && s_cnt > 0;
+		bool cont = __ldcg(&slot[16]) != 0 && s_cnt > 0 && iter < a.level_cap;
 		bool overflow = false;
 		if (cont && a.hist && iter >= a.max_levels) { // no buffer for another level
 			cont = false;

@@ -292,6 +292,17 @@ static void LengthFunction(DataChunk &args, ExpressionState &state, Vector &resu
 		}
 	} else {
 		auto out = FlatVector::GetData<int64_t>(result);
+		if (args.ColumnCount() == 6) {
+			// iterativelength(csr_id, v_size, src, dst, lower, upper) of the later DuckPGQ code (R11): the
+			// bounds are per-query constants, read from row 0 like csr_id / v_size
+			const int64_t lower = FirstBigint(args, 4), upper = FirstBigint(args, 5);
+			if (lower < 0 || upper < 0)
+				throw InvalidInputException("pgq_b200: iterativelength bounds must be non-negative");
+			PgqState::Check("iterativelength",
+			                pgq_iterativelength_bounded(pctx, slot.dev_id, (int64_t)count, src.val.data(),
+			                                            dst.val.data(), src.valid.data(), dst.valid.data(), lower,
+			                                            upper, out, ov.data()));
+		} else
 		PgqState::Check("iterativelength", pgq_iterativelength(pctx, slot.dev_id, (int64_t)count, src.val.data(),
 		                                                       dst.val.data(), src.valid.data(), dst.valid.data(),
 		                                                       out, ov.data()));
@@ -423,7 +434,14 @@ DUCKDB_EXTENSION_API void pgq_b200_init(duckdb::DatabaseInstance &db) {
 		CreateScalarFunctionInfo info(set);
 		catalog.CreateFunction(context, &info);
 	}
-	Register(context, catalog, "iterativelength", {I, B, B, B}, B, LengthFunction<false>);
+	{
+		// 4 arguments, and the later 6-argument form with lower / upper length bounds (f1, rule R11)
+		ScalarFunctionSet set("iterativelength");
+		set.AddFunction(ScalarFunction({I, B, B, B}, B, LengthFunction<false>, true, PgqBind));
+		set.AddFunction(ScalarFunction({I, B, B, B, B, B}, B, LengthFunction<false>, true, PgqBind));
+		CreateScalarFunctionInfo info(set);
+		catalog.CreateFunction(context, &info);
+	}
 	{
 		ScalarFunctionSet set("reachability");
 		set.AddFunction(ScalarFunction({I, B, B, B}, BO, LengthFunction<true>, true, PgqBind));

@@ -105,6 +105,13 @@ int pgq_csr_prepare(pgq_ctx_t *ctx, int32_t id);
 int pgq_iterativelength(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
                         const uint8_t *src_valid, const uint8_t *dst_valid, int64_t *out,
                         uint8_t *out_valid);
+/* 6-argument iterativelength(csr_id, v_size, src, dst, lower, upper) of the later DuckPGQ code (SURVEY.md
+ * §8(f) f1; rule R11 in DESIGN.md §4, [RECALL] -- not present in /root/reference): the search stops after
+ * `upper` levels (negative = unbounded); a pair whose shortest length is below `lower` gives NULL;
+ * src == dst gives 0 when lower <= 0, else NULL.  Not available on a vertex-partitioned csr. */
+int pgq_iterativelength_bounded(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                                const uint8_t *src_valid, const uint8_t *dst_valid, int64_t lower, int64_t upper,
+                                int64_t *out, uint8_t *out_valid);
 int pgq_reachability(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
                      const uint8_t *src_valid, const uint8_t *dst_valid, uint8_t *out, uint8_t *out_valid);
 /* mode 0: [src,...,dst]; mode 1: [src,e0,v1,e1,...,dst].  *out_vals is allocated by the

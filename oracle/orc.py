@@ -95,6 +95,23 @@ def iterativelength(V, v, e, src, dst, src_valid=None, dst_valid=None, stats=Fal
     return (out, ov, st.as_dict()) if stats else (out, ov)
 
 
+def iterativelength_bounded(V, v, e, src, dst, lower, upper, src_valid=None, dst_valid=None):
+    """R11: at most `upper` levels (negative = unbounded); a shortest length below `lower` is NULL."""
+    v, pv = _i64(v)
+    e, pe = _i64(e)
+    src, ps = _i64(src)
+    dst, pd = _i64(dst)
+    n = src.shape[0]
+    sv, psv = _u8opt(src_valid, n)
+    dv, pdv = _u8opt(dst_valid, n)
+    out = np.full(n, -1, dtype=np.int64)
+    ov = np.zeros(n, dtype=np.uint8)
+    lib().orc_iterativelength_bounded(C.c_int64(V), pv, pe, C.c_int64(n), ps, pd, psv, pdv,
+                                      C.c_int64(lower), C.c_int64(upper),
+                                      out.ctypes.data_as(I64P), ov.ctypes.data_as(U8P), None)
+    return out, ov
+
+
 def reachability(V, v, e, src, dst, src_valid=None, dst_valid=None):
     v, pv = _i64(v)
     e, pe = _i64(e)

@@ -109,7 +109,7 @@ static int level_step(int64_t V, const int64_t *v, const int64_t *e, bs512 *seen
 static void msbfs_lengths(int kind, int64_t V, const int64_t *v, const int64_t *e, int64_t n,
                           const int64_t *src, const int64_t *dst, const uint8_t *src_valid,
                           const uint8_t *dst_valid, int64_t *out_len, uint8_t *out_bool, uint8_t *out_valid,
-                          orc_stats_t *st) {
+                          orc_stats_t *st, int64_t lower, int64_t upper) {
 	size_t vv = (size_t)(V > 0 ? V : 1);
 	bs512 *seen = (bs512 *)malloc(vv * sizeof(bs512));
 	bs512 *visit1 = (bs512 *)malloc(vv * sizeof(bs512));
@@ -135,8 +135,8 @@ static void msbfs_lengths(int kind, int64_t V, const int64_t *v, const int64_t *
 					if (out_len) out_len[row] = -1;
 					if (out_bool) out_bool[row] = 0;
 				} else if (src[row] == dst[row]) {
-					out_valid[row] = 1;
-					if (out_len) out_len[row] = 0; /* length-0 path needs no search */
+					out_valid[row] = lower <= 0; /* R11: a length-0 path is in bounds only when lower <= 0 */
+					if (out_len) out_len[row] = lower <= 0 ? 0 : -1; /* length-0 path needs no search */
 					if (out_bool) out_bool[row] = 1;
 				} else {
 					bs_set(&visit1[src[row]], lane);
@@ -148,15 +148,15 @@ static void msbfs_lengths(int kind, int64_t V, const int64_t *v, const int64_t *
 			}
 		}
 		if (st) st->batches++;
-		for (int64_t iter = 1; active; iter++) {
+		for (int64_t iter = 1; active && iter <= upper; iter++) { /* R11: at most `upper` levels */
 			bs512 *vis = (iter & 1) ? visit1 : visit2;
 			bs512 *nxt = (iter & 1) ? visit2 : visit1;
 			if (!level_step(V, v, e, seen, vis, nxt, &active_mask, st)) break;
 			for (int lane = 0; lane < ORC_LANE_LIMIT; lane++) {
 				int64_t row = lane_to_num[lane];
 				if (row >= 0 && bs_test(&seen[dst[row]], lane)) {
-					out_valid[row] = 1;
-					if (out_len) out_len[row] = iter; /* found at iter => path length */
+					out_valid[row] = iter >= lower; /* R11: shortest length below the lower bound -> NULL */
+					if (out_len) out_len[row] = iter >= lower ? iter : -1; /* found at iter => path length */
 					if (out_bool) out_bool[row] = 1;
 					lane_to_num[lane] = -1; /* retired, NOT refilled until the batch ends (R5) */
 					active_mask.w[lane >> 6] &= ~(1ull << (lane & 63));
@@ -187,11 +187,24 @@ static void msbfs_lengths(int kind, int64_t V, const int64_t *v, const int64_t *
 void orc_iterativelength(int64_t V, const int64_t *v, const int64_t *e, int64_t n, const int64_t *src,
                          const int64_t *dst, const uint8_t *src_valid, const uint8_t *dst_valid,
                          int64_t *out, uint8_t *out_valid, orc_stats_t *stats) {
-	msbfs_lengths(0, V, v, e, n, src, dst, src_valid, dst_valid, out, NULL, out_valid, stats);
+	msbfs_lengths(0, V, v, e, n, src, dst, src_valid, dst_valid, out, NULL, out_valid, stats, 0, INT64_MAX);
+}
+
+/* R11 [RECALL, low confidence; frozen here]: iterativelength(csr_id, v_size, src, dst, lower, upper) of the
+ * later DuckPGQ code.  The level loop stops after `upper` levels; a destination first seen at level L
+ * gives L when lower <= L (<= upper by construction), otherwise NULL -- the search is a BFS with a `seen`
+ * set, so L is the only length it can report for the pair.  src == dst gives 0 when lower <= 0, else NULL.
+ * A negative upper bound means "unbounded" (what the 4-argument form does). */
+void orc_iterativelength_bounded(int64_t V, const int64_t *v, const int64_t *e, int64_t n, const int64_t *src,
+                                 const int64_t *dst, const uint8_t *src_valid, const uint8_t *dst_valid,
+                                 int64_t lower, int64_t upper, int64_t *out, uint8_t *out_valid,
+                                 orc_stats_t *stats) {
+	msbfs_lengths(0, V, v, e, n, src, dst, src_valid, dst_valid, out, NULL, out_valid, stats, lower,
+	              upper < 0 ? INT64_MAX : upper);
 }
 
 void orc_reachability(int64_t V, const int64_t *v, const int64_t *e, int64_t n, const int64_t *src,
                       const int64_t *dst, const uint8_t *src_valid, const uint8_t *dst_valid, uint8_t *out,
                       uint8_t *out_valid, orc_stats_t *stats) {
-	msbfs_lengths(1, V, v, e, n, src, dst, src_valid, dst_valid, NULL, out, out_valid, stats);
+	msbfs_lengths(1, V, v, e, n, src, dst, src_valid, dst_valid, NULL, out, out_valid, stats, 0, INT64_MAX);
 }

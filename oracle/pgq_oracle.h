@@ -63,6 +63,13 @@ void orc_iterativelength(int64_t V, const int64_t *v, const int64_t *e, int64_t 
                          const int64_t *dst, const uint8_t *src_valid, const uint8_t *dst_valid,
                          int64_t *out, uint8_t *out_valid, orc_stats_t *stats);
 
+/* iterativelength with lower/upper bounds (R11): at most `upper` levels (negative =
+ * unbounded); a shortest length below `lower` is NULL. */
+void orc_iterativelength_bounded(int64_t V, const int64_t *v, const int64_t *e, int64_t n, const int64_t *src,
+                                 const int64_t *dst, const uint8_t *src_valid, const uint8_t *dst_valid,
+                                 int64_t lower, int64_t upper, int64_t *out, uint8_t *out_valid,
+                                 orc_stats_t *stats);
+
 /* reachability (R6): out[i] in {0,1}; NULL only for NULL inputs. */
 void orc_reachability(int64_t V, const int64_t *v, const int64_t *e, int64_t n, const int64_t *src,
                       const int64_t *dst, const uint8_t *src_valid, const uint8_t *dst_valid, uint8_t *out,

@@ -151,6 +151,43 @@ def test_lengths_rmat_all_lane_widths(ctx, lanes):
     ctx.csr_delete(1)
 
 
+@pytest.mark.parametrize("small_path", [1, 0])
+@pytest.mark.parametrize("graph", ["rmat13", "knows", "chain"])
+def test_bounded_lengths(ctx, graph, small_path):
+    """6-argument iterativelength (R11) on the whole-batch kernel and on the general level loop."""
+    if graph == "rmat13":
+        V = 1 << 13
+        src, dst = orc.gen_rmat(0x5eed0000 + 13, 13)
+    elif graph == "knows":
+        V = 3000
+        src, dst = orc.gen_knows(31, V, 30000)
+    else:  # long levels: the cap has to stop the loop mid-way
+        V = 200
+        src, dst = np.arange(V - 1), np.arange(1, V)
+    v, e, _ = _build_both(ctx, V, src, dst)
+    n = 1400
+    ps, pd = orc.gen_pairs(17, V, v, n)
+    if graph == "chain":
+        ps, pd = np.minimum(ps, pd), np.maximum(ps, pd)
+    ps[::61] = pd[::61]
+    sv = (np.arange(n) % 37 != 0).astype(np.uint8)
+    ctx.set_option("small_path", small_path)
+    try:
+        for lo, hi in [(0, 0), (0, 1), (0, 2), (1, 3), (2, 4), (3, 3), (0, 60), (4, 1), (0, -1)]:
+            out, ov = ctx.iterativelength_bounded(1, ps, pd, lo, hi, sv)
+            eo, ev = orc.iterativelength_bounded(V, v, e, ps, pd, lo, hi, sv)
+            _cmp_arr("valid %d..%d" % (lo, hi), ov, ev)
+            _cmp_arr("length %d..%d" % (lo, hi), out, eo)
+        # the cap is per call: the unbounded function afterwards sees the whole search again
+        out, ov = ctx.iterativelength(1, ps, pd, sv)
+        eo, ev = orc.iterativelength(V, v, e, ps, pd, sv)
+        _cmp_arr("valid after", ov, ev)
+        _cmp_arr("length after", out, eo)
+    finally:
+        ctx.set_option("small_path", 1)
+    ctx.csr_delete(1)
+
+
 @pytest.mark.parametrize("bins", [(0, 0, 0, 1), (1, 2, 4, 8), (4, 32, 64, 4096), (0, 16, 32, 64),
                                   (1 << 30, 1 << 30, 1 << 30, 1 << 30), (2, 1 << 30, 1 << 30, 1 << 30),
                                   (2, 4, 1 << 30, 1 << 30)])

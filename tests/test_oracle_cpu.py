@@ -51,6 +51,32 @@ def test_null_rows_G8():
     assert p == [[0, 1, 2, 3], None, None, [2]]
 
 
+def test_bounded_lengths_R11():
+    """6-argument iterativelength: hand-checked on the path graph, then the defining property on R-MAT:
+    bounded(l, u) = full where l <= full <= u, NULL elsewhere."""
+    c = CASES["G1_path"]  # 0 -> 1 -> 2 -> 3
+    v, e, _ = orc.csr_build(4, [a for a, _ in c["edges"]], [b for _, b in c["edges"]])
+    qs, qd = [0, 0, 0, 1, 2, 3], [3, 2, 1, 3, 2, 0]
+    assert lengths_list(*orc.iterativelength_bounded(4, v, e, qs, qd, 0, 2)) == [None, 2, 1, 2, 0, None]
+    assert lengths_list(*orc.iterativelength_bounded(4, v, e, qs, qd, 0, 3)) == [3, 2, 1, 2, 0, None]
+    assert lengths_list(*orc.iterativelength_bounded(4, v, e, qs, qd, 2, 3)) == [3, 2, None, 2, None, None]
+    assert lengths_list(*orc.iterativelength_bounded(4, v, e, qs, qd, 1, 1)) == [None, None, 1, None, None, None]
+    assert lengths_list(*orc.iterativelength_bounded(4, v, e, qs, qd, 0, 0)) == [None, None, None, None, 0, None]
+    assert lengths_list(*orc.iterativelength_bounded(4, v, e, qs, qd, 0, -1)) == [3, 2, 1, 2, 0, None]
+    s, d = orc.gen_rmat(21, 11)
+    V = 1 << 11
+    v, e, _ = orc.csr_build(V, s, d)
+    ps, pd = orc.gen_pairs(9, V, v, 1300)
+    ps[::53] = pd[::53]
+    sv = (np.arange(1300) % 41 != 0).astype(np.uint8)
+    full, fv = orc.iterativelength(V, v, e, ps, pd, sv)
+    for lo, hi in [(0, 1), (0, 3), (2, 4), (3, 3), (1, 100), (5, 2)]:
+        out, ov = orc.iterativelength_bounded(V, v, e, ps, pd, lo, hi, sv)
+        ok = (fv == 1) & (full >= lo) & (full <= hi)
+        assert np.array_equal(ov, ok.astype(np.uint8)), (lo, hi)
+        assert np.array_equal(out, np.where(ok, full, -1)), (lo, hi)
+
+
 def test_batches_G9_G10():
     """> 512 and > 1024 rows (lane reuse), duplicate pairs inside one batch."""
     s, d = orc.gen_rmat(11, 10)

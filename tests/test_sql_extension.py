@@ -109,6 +109,7 @@ SELECT sum(create_csr_edge(0, (SELECT count(*) FROM person),
 SELECT i, iterativelength(0, (SELECT count(*) FROM person), s, d) FROM pairs ORDER BY i;
 SELECT i, reachability(0, (SELECT count(*) FROM person), s, d) FROM pairs ORDER BY i;
 SELECT i, shortestpath(0, (SELECT count(*) FROM person), s, d) FROM pairs ORDER BY i;
+SELECT i, iterativelength(0, (SELECT count(*) FROM person), s, d, CAST(2 AS BIGINT), CAST(3 AS BIGINT)) FROM pairs ORDER BY i;
 SELECT delete_csr(0);
 SELECT iterativelength(0, CAST(5 AS BIGINT), CAST(1 AS BIGINT), CAST(2 AS BIGINT));
 """ % (EXT, tmp_path / "person.csv", tmp_path / "knows.csv", tmp_path / "pairs.csv")
@@ -126,8 +127,11 @@ SELECT iterativelength(0, CAST(5 AS BIGINT), CAST(1 AS BIGINT), CAST(2 AS BIGINT
     got = [_parse_list(row.split(",", 1)[1]) for row in r[11][1]]
     exp = [None if not pv[i] else [int(x) for x in vals[int(off[i]):int(off[i]) + int(ln[i])]] for i in range(n)]
     assert got == exp
-    assert r[12] == ("result", ["True"])
-    assert r[13][0] == "error" and "does not exist" in r[13][1]
+    bo, bv = orc.iterativelength_bounded(V, v, e, ps_i, pd_i, 2, 3, src_valid=sv)  # 6-argument form (R11)
+    got = [row.split(",", 1)[1] for row in r[12][1]]
+    assert got == ["NULL" if not bv[i] else str(int(bo[i])) for i in range(n)]
+    assert r[13] == ("result", ["True"])
+    assert r[14][0] == "error" and "does not exist" in r[14][1]
 
 
 @pytest.mark.gpu
