@@ -124,7 +124,7 @@ void ctx_release_resources(Ctx *c) {
 	}
 	c->helpers.clear();
 	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
-	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->bfs_seen, &c->bfs_visit[0],
+	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->sort_pack, &c->bfs_seen, &c->bfs_visit[0],
 	                  &c->bfs_visit[1], &c->bfs_hist_tab, &c->bfs_pathout, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
 	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->part_visit[0], &c->part_visit[1], &c->part_peer_tab, &c->l2_flush, &c->sssp_dist, &c->sssp_chg};
 	for (DevBuf *b : bufs) b->release();
@@ -244,6 +244,8 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "push_beta")) c->opt.push_beta = value < 1 ? 1 : value;
 	else if (!strcmp(key, "small_path")) c->opt.small_path = value;
 	else if (!strcmp(key, "small_edge_mb")) c->opt.small_edge_mb = value < 0 ? 0 : value;
+	else if (!strcmp(key, "sort_wide")) c->opt.sort_wide = value;
+	else if (!strcmp(key, "sort_wide_min")) c->opt.sort_wide_min = value < 0 ? 0 : value;
 	else if (!strcmp(key, "streams")) c->opt.streams = value < 1 ? 1 : value > 8 ? 8 : value;
 	else {
 		set_error("unknown option '%s'", key);

@@ -146,6 +146,8 @@ struct Options {
 	int64_t small_edge_mb = 256; // ... while E * W/8 stays below this many MiB (one level's gather volume)
 	int64_t small_path = 1;   // whole-batch cooperative kernel for graphs that live in L2 (msbfs_small.cuh)
 	int64_t streams = 4;      // general path: batches of one call in flight at once (own stream + buffers each)
+	int64_t sort_wide = 1;    // keys of <= 22 bits: two 11-bit passes (radix_sort_wide.cu) instead of 8-bit ones
+	int64_t sort_wide_min = 32768; // ... from this many keys on
 	int64_t level_cap = 0x7fffffff; // per call, not user-settable: iterativelength's upper bound (R11)
 };
 
@@ -168,7 +170,7 @@ struct Ctx {
 	pgq_stats_t stats{};
 	// scratch reused across calls
 	DevBuf scan_tmp;
-	DevBuf sort_keys[2], sort_p0[2], sort_p1[2], sort_hist;
+	DevBuf sort_keys[2], sort_p0[2], sort_p1[2], sort_hist, sort_pack;
 	DevBuf bfs_seen, bfs_visit[2], bfs_hubacc;
 	std::vector<DevBuf> bfs_hist; // shortestpath: one frontier buffer per level of the running batch
 	DevBuf bfs_hist_tab;          // device pointer table of bfs_hist
@@ -237,6 +239,9 @@ struct SortIO {
 };
 
 int radix_sort_stable(Ctx *c, const SortIO &io);
+// radix_sort_wide.cu: the same sort in two passes of <= 11-bit digits (keys of at most 22 bits)
+bool radix_sort_wide_eligible(const Ctx *c, const SortIO &io);
+int radix_sort_wide(Ctx *c, const SortIO &io);
 
 // ---- csr_build.cu ----
 int csr_set_weights(Ctx *c, Csr *g, int wtype, const void *w, int64_t row0, int64_t n); // sssp.cu

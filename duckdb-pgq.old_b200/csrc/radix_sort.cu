@@ -212,6 +212,7 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_scatter_kernel(RsArgs a) {
 
 int radix_sort_stable(Ctx *c, const SortIO &io) {
 	if (io.n == 0) return PGQ_OK;
+	if (radix_sort_wide_eligible(c, io)) return radix_sort_wide(c, io);
 	int passes = (io.key_bits + 7) / 8;
 	if (passes < 1) passes = 1;
 	const uint32_t ntiles = div_up(io.n, RS_TILE);

@@ -71,6 +71,44 @@ def test_csr_bit_identical_rmat(ctx, scale, ef):
     ctx.csr_delete(1)
 
 
+@pytest.mark.parametrize("wide", [1, 2, 0])
+@pytest.mark.parametrize("V,E", [(2000, 40000), ((1 << 11) + 1, 50000), ((1 << 17) - 5, 300000),
+                                 ((1 << 22) - 3, 250000), ((1 << 22) + 9, 100000), (3, 70000)])
+def test_csr_both_sort_cores(ctx, V, E, wide):
+    """The two-pass 11-bit sort (keys <= 22 bits) and the 8-bit sort give the same, oracle-identical CSR:
+    digit splits 6+5 / 6+6 / 9+8 / 11+11, one pass (<= 11 bits), > 22 bits (always the 8-bit core), ragged
+    last tiles, heavy duplicates (V = 3), forward arrays + edge ids and the reverse CSR (checked through
+    a query)."""
+    rng = np.random.default_rng(V + E)
+    src = rng.integers(0, V, E, dtype=np.int64)
+    dst = rng.integers(0, V, E, dtype=np.int64)
+    hot = rng.integers(0, V, 8)
+    src[::5] = hot[rng.integers(0, 8, len(src[::5]))]  # a few very long neighbour lists
+    eid = rng.permutation(E).astype(np.int64) * 3 + 1
+    v, e, eids = orc.csr_build(V, src, dst, eid)
+    ctx.set_option("sort_wide", wide)
+    ctx.set_option("sort_wide_min", 0)
+    try:
+        ctx.csr_build(2, V, src, dst, eid=eid)
+        gv, ge, geid = ctx.csr_download(2, want_eid=True)
+        _cmp_arr("v", gv, v)
+        _cmp_arr("e", ge, e)
+        _cmp_arr("eid", geid, eids)
+        big = V > (1 << 20)  # V x 64-byte bitmaps per level: keep the query small there
+        ps, pd = orc.gen_pairs(3, V, v, 40 if big else 300)
+        got = ctx.iterativelength(2, ps, pd) if big else ctx.shortestpath(2, ps, pd, mode=1)
+    finally:
+        ctx.set_option("sort_wide", 1)
+        ctx.set_option("sort_wide_min", 32768)
+    if big:
+        eo, ev = orc.iterativelength(V, v, e, ps, pd)
+        _cmp_arr("valid", got[1], ev)
+        _cmp_arr("length", got[0], eo)
+    else:
+        assert_paths_equal(got, orc.shortestpath(V, v, e, eids, ps, pd, mode=1), "paths after sort core %d" % wide)
+    ctx.csr_delete(2)
+
+
 def test_csr_with_explicit_edge_ids_and_chunked_rows(ctx):
     """create_csr_vertex + create_csr_edge fed in 1024-row chunks like DuckDB does (R2/R3)."""
     V, E = 5000, 60000
@@ -151,10 +189,10 @@ def test_lengths_rmat_all_lane_widths(ctx, lanes):
     ctx.csr_delete(1)
 
 
-@pytest.mark.parametrize("small_path", [1, 0])
 @pytest.mark.parametrize("graph", ["rmat13", "knows", "chain"])
-def test_bounded_lengths(ctx, graph, small_path):
-    """6-argument iterativelength (R11) on the whole-batch kernel and on the general level loop."""
+def test_bounded_lengths(ctx, graph):
+    """6-argument iterativelength (R11); the ctx fixture runs it on the whole-batch kernel and on the
+    general level loop."""
     if graph == "rmat13":
         V = 1 << 13
         src, dst = orc.gen_rmat(0x5eed0000 + 13, 13)
@@ -171,20 +209,16 @@ def test_bounded_lengths(ctx, graph, small_path):
         ps, pd = np.minimum(ps, pd), np.maximum(ps, pd)
     ps[::61] = pd[::61]
     sv = (np.arange(n) % 37 != 0).astype(np.uint8)
-    ctx.set_option("small_path", small_path)
-    try:
-        for lo, hi in [(0, 0), (0, 1), (0, 2), (1, 3), (2, 4), (3, 3), (0, 60), (4, 1), (0, -1)]:
-            out, ov = ctx.iterativelength_bounded(1, ps, pd, lo, hi, sv)
-            eo, ev = orc.iterativelength_bounded(V, v, e, ps, pd, lo, hi, sv)
-            _cmp_arr("valid %d..%d" % (lo, hi), ov, ev)
-            _cmp_arr("length %d..%d" % (lo, hi), out, eo)
-        # the cap is per call: the unbounded function afterwards sees the whole search again
-        out, ov = ctx.iterativelength(1, ps, pd, sv)
-        eo, ev = orc.iterativelength(V, v, e, ps, pd, sv)
-        _cmp_arr("valid after", ov, ev)
-        _cmp_arr("length after", out, eo)
-    finally:
-        ctx.set_option("small_path", 1)
+    for lo, hi in [(0, 0), (0, 1), (0, 2), (1, 3), (2, 4), (3, 3), (0, 60), (4, 1), (0, -1)]:
+        out, ov = ctx.iterativelength_bounded(1, ps, pd, lo, hi, sv)
+        eo, ev = orc.iterativelength_bounded(V, v, e, ps, pd, lo, hi, sv)
+        _cmp_arr("valid %d..%d" % (lo, hi), ov, ev)
+        _cmp_arr("length %d..%d" % (lo, hi), out, eo)
+    # the cap is per call: the unbounded function afterwards sees the whole search again
+    out, ov = ctx.iterativelength(1, ps, pd, sv)
+    eo, ev = orc.iterativelength(V, v, e, ps, pd, sv)
+    _cmp_arr("valid after", ov, ev)
+    _cmp_arr("length after", out, eo)
     ctx.csr_delete(1)
 
 

@@ -6,6 +6,9 @@ from bench import SEED_BASE
 scale = int(sys.argv[1]) if len(sys.argv) > 1 else 22
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 ctx = pgq_b200.Context(0)
+for kv in sys.argv[3:]:  # option=value ...
+    k, val = kv.split("=")
+    ctx.set_option(k, int(val))
 V, E = 1 << scale, 16 << scale
 d_src, d_dst = ctx.dev_alloc(E * 8), ctx.dev_alloc(E * 8)
 ctx.gen_rmat_device(SEED_BASE + scale, scale, E, d_src, d_dst)
