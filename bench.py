@@ -236,7 +236,7 @@ def bench_csr(ctx, scale, ef, steps, warmup, peak_gbs):
                     "ms": float(np.mean(e2e_ms)), "h2d_bytes_per_step": 16 * E, "d2h_bytes_per_step": 0},
             "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak_gbs, "unit": "GB/s",
                          "frac": algo / (ms * 1e-3) / 1e9 / peak_gbs, "traffic": None,
-                         "algo_bytes": algo, "kernels": "stable radix sort by source (hist + scan + tile-reordered scatter per pass) + offsets from sorted keys (whole build)"}}
+                         "algo_bytes": algo, "kernels": "stable radix sort by source: global bucket histogram + two 11-bit passes (tile-reordered scatter, decoupled look-back) + offsets from sorted keys (whole build)"}}
 
 
 def knows_params(V):

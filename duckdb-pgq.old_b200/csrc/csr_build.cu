@@ -141,6 +141,10 @@ int csr_device_build(Ctx *c, Csr *g) {
 		set_error("create_csr_vertex counts disagree with the edge rows");
 		return PGQ_ERR_MISMATCH;
 	}
+	if (h_err & 4u) {
+		set_error("csr build: radix sort look-back watchdog fired (a tile never published its bucket totals)");
+		return PGQ_ERR_CUDA;
+	}
 	return PGQ_OK;
 }
 

@@ -39,6 +39,10 @@ struct RwArgs {
 	uint32_t *p0out;      //                    payload0
 	uint32_t *p1out;      // payload1 (nullptr = not carried)
 	uint32_t *hist;       // [1 << nbits][ntiles] bin-major: tile counts, then (after the scan) tile bases
+	// decoupled look-back instead of the histogram pre-pass (status != nullptr):
+	uint32_t *status;      // [ntiles][RW_NB] tile-major, zeroed: (flag << 30) | count, flag 1 = tile total, 2 = inclusive prefix
+	uint32_t *ticket;      // zeroed: tiles are numbered in the order their blocks start
+	const uint32_t *gdig;  // [RW_NB] global start of every bucket of this pass
 	uint32_t n;
 	uint32_t ntiles;
 	int shift;
@@ -94,9 +98,86 @@ __global__ void __launch_bounds__(RW_THREADS) rw_hist_kernel(RwArgs a) {
 	for (uint32_t d = threadIdx.x; d < nb; d += RW_THREADS) a.hist[(uint64_t)d * a.ntiles + blockIdx.x] = h[d];
 }
 
+// ---- look-back variant: one read of the first-pass keys gives the GLOBAL bucket sizes of both passes ----
+template <int IN>
+__global__ void __launch_bounds__(RW_THREADS) rw_global_hist_kernel(RwArgs a, int bits0, int bits1, uint32_t *gh) {
+	__shared__ uint32_t h[2 * RW_NB];
+	for (int i = threadIdx.x; i < 2 * RW_NB; i += RW_THREADS) h[i] = 0;
+	__syncthreads();
+	const uint32_t m0 = (1u << bits0) - 1u, m1 = (1u << bits1) - 1u; // bits1 == 0: m1 = 0, everything in bucket 0
+	for (uint32_t tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+		const uint32_t tbase = tile * (uint32_t)RW_TILE;
+		if (a.n - tbase >= (uint32_t)RW_TILE) {
+			uint32_t keys[RW_ITEMS];
+#pragma unroll
+			for (int r = 0; r < RW_ITEMS; r++) keys[r] = rw_load_key<IN>(a, tbase + r * RW_THREADS + threadIdx.x);
+#pragma unroll
+			for (int r = 0; r < RW_ITEMS; r++) {
+				atomicAdd(&h[keys[r] & m0], 1u);
+				atomicAdd(&h[RW_NB + ((keys[r] >> bits0) & m1)], 1u);
+			}
+		} else {
+			for (uint32_t idx = tbase + threadIdx.x; idx < a.n; idx += RW_THREADS) {
+				const uint32_t k = rw_load_key<IN>(a, idx);
+				atomicAdd(&h[k & m0], 1u);
+				atomicAdd(&h[RW_NB + ((k >> bits0) & m1)], 1u);
+			}
+		}
+	}
+	__syncthreads();
+	for (int i = threadIdx.x; i < 2 * RW_NB; i += RW_THREADS)
+		if (h[i]) atomicAdd(&gh[i], h[i]);
+}
+
+// exclusive scan of each pass's RW_NB bucket sizes, in place (one 1024-thread block per pass)
+__global__ void __launch_bounds__(1024) rw_gdig_scan_kernel(uint32_t *gh) {
+	__shared__ uint32_t wsum[32];
+	uint32_t *g = gh + blockIdx.x * RW_NB;
+	const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const uint32_t x0 = g[2 * threadIdx.x], x1 = g[2 * threadIdx.x + 1];
+	uint32_t inc = x0 + x1;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+		if ((int)lane >= o) inc += y;
+	}
+	if (lane == 31) wsum[warp] = inc;
+	__syncthreads();
+	uint32_t ex = inc - x0 - x1;
+	for (int w = 0; w < (int)warp; w++) ex += wsum[w];
+	g[2 * threadIdx.x] = ex;
+	g[2 * threadIdx.x + 1] = ex + x0;
+}
+
+static constexpr uint32_t RW_FLAG_A = 1u << 30, RW_FLAG_P = 2u << 30, RW_VMASK = (1u << 30) - 1u;
+
+// DPT consecutive status words of one tile, read / written past L1 (they are polled)
+template <int DPT>
+__device__ __forceinline__ void rw_status_load(const uint32_t *p, uint32_t (&w)[DPT]) {
+	if (DPT == 8) {
+		asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+		             : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p) : "memory");
+		asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+		             : "=r"(w[4 % DPT]), "=r"(w[5 % DPT]), "=r"(w[6 % DPT]), "=r"(w[7 % DPT]) : "l"(p + 4) : "memory");
+	} else {
+		asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(w[0]), "=r"(w[1]) : "l"(p) : "memory");
+	}
+}
+template <int DPT>
+__device__ __forceinline__ void rw_status_store(uint32_t *p, const uint32_t (&w)[DPT]) {
+	if (DPT == 8) {
+		asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};"
+		             :: "l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+		asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};"
+		             :: "l"(p + 4), "r"(w[4 % DPT]), "r"(w[5 % DPT]), "r"(w[6 % DPT]), "r"(w[7 % DPT]) : "memory");
+	} else {
+		asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" :: "l"(p), "r"(w[0]), "r"(w[1]) : "memory");
+	}
+}
+
 // Scatter kernel configuration: THREADS x ITEMS = RW_TILE keys per block.
-//   <256, 32>: two blocks per SM (16 warps), long per-warp rank chains;
-//   <1024, 8>: one block per SM (32 warps), per-warp counters take 128 KB of the SM's shared memory.
+//   <256, 32>: two blocks per SM (16 warps), long per-warp rank chains (default: 2.11 ms at R-MAT s22);
+//   <1024, 8>: one block per SM (32 warps), per-warp counters take 128 KB of shared memory (2.74 ms; option sort_wide=2).
 template <int THREADS>
 struct RwCfg {
 	static constexpr int WARPS = THREADS / 32;
@@ -104,8 +185,7 @@ struct RwCfg {
 	static constexpr int DPT = RW_NB / THREADS; // digits per thread in the block scans (8 or 2)
 	static constexpr size_t OFF_STAGE = 0;                                     // uint2[RW_TILE]
 	static constexpr size_t OFF_GBASE = OFF_STAGE + (size_t)RW_TILE * 8;       // uint32[RW_NB]
-	static constexpr size_t OFF_LSTART = OFF_GBASE + (size_t)RW_NB * 4;        // uint16[RW_NB]
-	static constexpr size_t OFF_CNT = OFF_LSTART + (size_t)RW_NB * 2;          // uint16[WARPS][RW_NB]
+	static constexpr size_t OFF_CNT = OFF_GBASE + (size_t)RW_NB * 4;           // uint16[WARPS][RW_NB]
 	static constexpr size_t OFF_WSUM = OFF_CNT + (size_t)WARPS * RW_NB * 2;    // uint32[WARPS]
 	static constexpr size_t SMEM = OFF_WSUM + (size_t)WARPS * 4 + 32;
 	static_assert((size_t)WARPS * RW_NB * 2 >= (size_t)RW_TILE * 4, "payload1 staging reuses the counter area");
@@ -120,7 +200,6 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 	extern __shared__ __align__(16) unsigned char rw_smem[];
 	uint2 *stage = reinterpret_cast<uint2 *>(rw_smem + C::OFF_STAGE);
 	uint32_t *gbase = reinterpret_cast<uint32_t *>(rw_smem + C::OFF_GBASE); // global bucket base - local start
-	uint16_t *lstart = reinterpret_cast<uint16_t *>(rw_smem + C::OFF_LSTART);
 	uint16_t *cnt = reinterpret_cast<uint16_t *>(rw_smem + C::OFF_CNT);
 	uint32_t *wsum = reinterpret_cast<uint32_t *>(rw_smem + C::OFF_WSUM);
 	const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -131,8 +210,14 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 #pragma unroll
 		for (int i = 0; i < WARPS * RW_NB * 2 / 16 / THREADS; i++) z[i * THREADS + threadIdx.x] = make_uint4(0u, 0u, 0u, 0u);
 	}
+	// Look-back variant: tiles are numbered in the order their blocks START, so every predecessor a tile
+	// waits for is already running (forward progress whatever order the hardware schedules blocks in).
+	__shared__ uint32_t s_tile;
+	if (a.status && threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
+	if (a.status) __syncthreads();
+	const uint32_t tile = a.status ? s_tile : blockIdx.x;
 	// Each warp owns a contiguous run of the tile and walks it 32 keys at a time (stability).
-	const uint32_t tbase = blockIdx.x * (uint32_t)RW_TILE;
+	const uint32_t tbase = tile * (uint32_t)RW_TILE;
 	const uint32_t wbase = tbase + warp * (uint32_t)(ITEMS * 32) + lane;
 	uint32_t keys[ITEMS], vals[ITEMS];
 	bool bad = false;
@@ -220,6 +305,47 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 			tot[1 % DPT] += x >> 16;
 		}
 	}
+	// Look-back: publish this tile's bucket totals, then add up the predecessors' until one of them
+	// already knows its inclusive prefix (per bucket).
+	uint32_t pre[DPT];
+#pragma unroll
+	for (int k = 0; k < DPT; k++) pre[k] = 0;
+	if (a.status) {
+		uint32_t *mine = a.status + (size_t)tile * RW_NB + threadIdx.x * DPT;
+		uint32_t w[DPT];
+		if (tile != 0) {
+#pragma unroll
+			for (int k = 0; k < DPT; k++) w[k] = tot[k] | RW_FLAG_A;
+			rw_status_store<DPT>(mine, w);
+			uint32_t open = (1u << DPT) - 1u; // buckets still looking back
+			uint32_t spins = 0;
+			for (uint32_t t = tile - 1; open;) {
+				rw_status_load<DPT>(a.status + (size_t)t * RW_NB + threadIdx.x * DPT, w);
+				bool ready = true;
+#pragma unroll
+				for (int k = 0; k < DPT; k++) ready &= (w[k] >> 30) != 0u;
+				if (!ready) {
+					if (++spins > (1u << 22)) { // never expected; do not hang the GPU
+						if (a.err) atomicOr(a.err, 4u);
+						break;
+					}
+					__nanosleep(20);
+					continue;
+				}
+#pragma unroll
+				for (int k = 0; k < DPT; k++) {
+					if ((open >> k) & 1u) {
+						pre[k] += w[k] & RW_VMASK;
+						if ((w[k] >> 30) == 2u) open &= ~(1u << k);
+					}
+				}
+				t--; // tile 0 always publishes inclusive prefixes, so t never passes it with `open` set
+			}
+		}
+#pragma unroll
+		for (int k = 0; k < DPT; k++) w[k] = ((pre[k] + tot[k]) & RW_VMASK) | RW_FLAG_P;
+		rw_status_store<DPT>(mine, w);
+	}
 	// Exclusive scan of the tile totals over the digits.
 	{
 		uint32_t tsum = 0;
@@ -237,12 +363,31 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 #pragma unroll 8
 		for (int w = 0; w < WARPS; w++) ex += (w < (int)warp) ? wsum[w] : 0u;
 		const uint32_t nb = 1u << a.nbits;
+		uint32_t ls[DPT]; // local start of each of my buckets inside the tile's sorted order
 #pragma unroll
 		for (int k = 0; k < DPT; k++) {
 			const uint32_t d = threadIdx.x * DPT + k;
-			lstart[d] = (uint16_t)ex;
-			gbase[d] = (d < nb ? a.hist[(uint64_t)d * a.ntiles + blockIdx.x] : 0u) - ex;
+			ls[k] = ex;
+			if (a.status) gbase[d] = a.gdig[d] + pre[k] - ex;
+			else gbase[d] = (d < nb ? a.hist[(uint64_t)d * a.ntiles + tile] : 0u) - ex;
 			ex += tot[k];
+		}
+		// fold the bucket start into every warp's exclusive base: one random shared-memory read per key
+		// (instead of two) when the items are placed; all values stay below RW_TILE <= 65535
+#pragma unroll 8
+		for (int w = 0; w < WARPS; w++) {
+			if (DPT == 8) {
+				uint4 *row = reinterpret_cast<uint4 *>(cnt + w * RW_NB) + threadIdx.x;
+				uint4 q = *row;
+				q.x += ls[0] | (ls[1 % DPT] << 16);
+				q.y += ls[2 % DPT] | (ls[3 % DPT] << 16);
+				q.z += ls[4 % DPT] | (ls[5 % DPT] << 16);
+				q.w += ls[6 % DPT] | (ls[7 % DPT] << 16);
+				*row = q;
+			} else {
+				uint32_t *row = reinterpret_cast<uint32_t *>(cnt + w * RW_NB) + threadIdx.x;
+				*row += ls[0] | (ls[1 % DPT] << 16);
+			}
 		}
 	}
 	__syncthreads();
@@ -254,7 +399,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 		const uint32_t rank = (r & 1) ? (lp[r >> 1] >> 16) : (lp[r >> 1] & 0xFFFFu);
 		uint32_t p = 0;
 		if (valid) {
-			p = (uint32_t)lstart[d] + (uint32_t)mycnt[d] + rank;
+			p = (uint32_t)mycnt[d] + rank;
 			stage[p] = make_uint2(keys[r], vals[r]);
 		}
 		if (r & 1) lp[r >> 1] = (lp[r >> 1] & 0xFFFFu) | (p << 16);
@@ -343,7 +488,29 @@ int radix_sort_wide(Ctx *c, const SortIO &io) {
 		keys_out = c->sort_keys[0].as<uint32_t>();
 		*io.keys_scratch = keys_out;
 	}
-	PGQ_TRY(c->sort_hist.reserve(((size_t)ntiles << bits0) * sizeof(uint32_t)));
+	// look-back variant (option sort_lookback, counts must fit 30 bits): no per-tile histogram pre-pass and no
+	// device-wide scan; one extra read of the first-pass keys gives the global bucket sizes of both passes
+	const bool lookback = c->opt.sort_lookback != 0 && io.n < (1u << 30);
+	const size_t status_bytes = (size_t)ntiles * RW_NB * sizeof(uint32_t);
+	uint32_t *d_gdig = nullptr, *d_ticket = nullptr;
+	if (lookback) {
+		PGQ_TRY(c->sort_hist.reserve(status_bytes + 2 * RW_NB * sizeof(uint32_t) + 256));
+		d_gdig = reinterpret_cast<uint32_t *>(static_cast<char *>(c->sort_hist.p) + status_bytes);
+		d_ticket = d_gdig + 2 * RW_NB;
+		PGQ_CUDA(cudaMemsetAsync(d_gdig, 0, 2 * RW_NB * sizeof(uint32_t) + 256, c->stream));
+		RwArgs a{};
+		a.k64 = io.k64;
+		a.k32 = io.k32;
+		a.n = io.n;
+		a.ntiles = ntiles;
+		const unsigned grid = ntiles < (unsigned)c->sm_count * 8u ? ntiles : (unsigned)c->sm_count * 8u;
+		if (io.k64) rw_global_hist_kernel<RW_IN_64><<<grid, RW_THREADS, 0, c->stream>>>(a, bits0, bits1, d_gdig);
+		else rw_global_hist_kernel<RW_IN_32><<<grid, RW_THREADS, 0, c->stream>>>(a, bits0, bits1, d_gdig);
+		rw_gdig_scan_kernel<<<2, 1024, 0, c->stream>>>(d_gdig);
+		count_launch(c, 2);
+	} else {
+		PGQ_TRY(c->sort_hist.reserve(((size_t)ntiles << bits0) * sizeof(uint32_t)));
+	}
 	for (int p = 0; p < passes; p++) {
 		RwArgs a{};
 		const bool first = p == 0, last = p == passes - 1;
@@ -353,11 +520,11 @@ int radix_sort_wide(Ctx *c, const SortIO &io) {
 			a.k32 = io.k32;
 			a.p32 = io.p32;
 			a.vmax = io.vmax;
-			a.err = io.k64 ? io.err : nullptr;
 		} else {
 			a.pin = c->sort_pack.as<uint2>();
 			a.p1in = want_p1 ? c->sort_p1[0].as<uint32_t>() : nullptr;
 		}
+		a.err = io.err; // may be nullptr: out-of-range ids (64-bit form) and the look-back watchdog report here
 		if (last) {
 			a.kout = keys_out;
 			a.p0out = io.out_p0;
@@ -372,13 +539,20 @@ int radix_sort_wide(Ctx *c, const SortIO &io) {
 		a.shift = first ? 0 : bits0;
 		a.nbits = first ? bits0 : bits1;
 		const int form = !first ? RW_IN_PACKED : io.k64 ? RW_IN_64 : RW_IN_32;
-		if (form == RW_IN_64) rw_hist_kernel<RW_IN_64><<<ntiles, RW_THREADS, 0, c->stream>>>(a);
-		else if (form == RW_IN_32) rw_hist_kernel<RW_IN_32><<<ntiles, RW_THREADS, 0, c->stream>>>(a);
-		else rw_hist_kernel<RW_IN_PACKED><<<ntiles, RW_THREADS, 0, c->stream>>>(a);
-		count_launch(c);
-		PGQ_TRY(exclusive_scan_u32(c, a.hist, a.hist, (uint64_t)ntiles << a.nbits, nullptr));
-		if (c->opt.sort_wide == 2) PGQ_TRY(rw_launch_scatter<256>(c, form, a));
-		else PGQ_TRY(rw_launch_scatter<1024>(c, form, a));
+		if (lookback) {
+			a.status = c->sort_hist.as<uint32_t>();
+			a.ticket = d_ticket + p;
+			a.gdig = d_gdig + p * RW_NB;
+			PGQ_CUDA(cudaMemsetAsync(a.status, 0, status_bytes, c->stream));
+		} else {
+			if (form == RW_IN_64) rw_hist_kernel<RW_IN_64><<<ntiles, RW_THREADS, 0, c->stream>>>(a);
+			else if (form == RW_IN_32) rw_hist_kernel<RW_IN_32><<<ntiles, RW_THREADS, 0, c->stream>>>(a);
+			else rw_hist_kernel<RW_IN_PACKED><<<ntiles, RW_THREADS, 0, c->stream>>>(a);
+			count_launch(c);
+			PGQ_TRY(exclusive_scan_u32(c, a.hist, a.hist, (uint64_t)ntiles << a.nbits, nullptr));
+		}
+		if (c->opt.sort_wide == 2) PGQ_TRY(rw_launch_scatter<1024>(c, form, a));
+		else PGQ_TRY(rw_launch_scatter<256>(c, form, a));
 		PGQ_CUDA(cudaGetLastError());
 	}
 	return PGQ_OK;

@@ -71,11 +71,12 @@ def test_csr_bit_identical_rmat(ctx, scale, ef):
     ctx.csr_delete(1)
 
 
-@pytest.mark.parametrize("wide", [1, 2, 0])
+@pytest.mark.parametrize("wide,lookback", [(1, 1), (1, 0), (2, 1), (0, 0)])
 @pytest.mark.parametrize("V,E", [(2000, 40000), ((1 << 11) + 1, 50000), ((1 << 17) - 5, 300000),
                                  ((1 << 22) - 3, 250000), ((1 << 22) + 9, 100000), (3, 70000)])
-def test_csr_both_sort_cores(ctx, V, E, wide):
-    """The two-pass 11-bit sort (keys <= 22 bits) and the 8-bit sort give the same, oracle-identical CSR:
+def test_csr_both_sort_cores(ctx, V, E, wide, lookback):
+    """The two-pass 11-bit sort (keys <= 22 bits; both block shapes; tile bases by decoupled look-back or by
+    histogram pre-pass + scan) and the 8-bit sort give the same, oracle-identical CSR:
     digit splits 6+5 / 6+6 / 9+8 / 11+11, one pass (<= 11 bits), > 22 bits (always the 8-bit core), ragged
     last tiles, heavy duplicates (V = 3), forward arrays + edge ids and the reverse CSR (checked through
     a query)."""
@@ -87,6 +88,7 @@ def test_csr_both_sort_cores(ctx, V, E, wide):
     eid = rng.permutation(E).astype(np.int64) * 3 + 1
     v, e, eids = orc.csr_build(V, src, dst, eid)
     ctx.set_option("sort_wide", wide)
+    ctx.set_option("sort_lookback", lookback)
     ctx.set_option("sort_wide_min", 0)
     try:
         ctx.csr_build(2, V, src, dst, eid=eid)
@@ -99,6 +101,7 @@ def test_csr_both_sort_cores(ctx, V, E, wide):
         got = ctx.iterativelength(2, ps, pd) if big else ctx.shortestpath(2, ps, pd, mode=1)
     finally:
         ctx.set_option("sort_wide", 1)
+        ctx.set_option("sort_lookback", 1)
         ctx.set_option("sort_wide_min", 32768)
     if big:
         eo, ev = orc.iterativelength(V, v, e, ps, pd)
