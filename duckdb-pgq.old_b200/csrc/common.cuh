@@ -146,6 +146,7 @@ struct Options {
 	int64_t small_edge_mb = 256; // ... while E * W/8 stays below this many MiB (one level's gather volume)
 	int64_t small_path = 1;   // whole-batch cooperative kernel for graphs that live in L2 (msbfs_small.cuh)
 	int64_t streams = 4;      // general path: batches of one call in flight at once (own stream + buffers each)
+	int64_t seg_small = 1;    // filtered levels: small in-degree class through pull_seg_kernel (0 = pull_list_kernel)
 	int64_t sort_wide = 1;    // keys of <= 22 bits: two 11-bit passes (radix_sort_wide.cu) instead of 8-bit ones
 	int64_t sort_lookback = 1; // two-pass sort: decoupled look-back instead of histogram pre-pass + scan
 	int64_t sort_wide_min = 32768; // ... from this many keys on

@@ -477,6 +477,115 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 	if (a.npeers && wany && g == 0) st_peers<SW>(a, wo, news);
 }
 
+// ---- K4 small class, filtered levels: SEG lanes per vertex, edge-parallel frontier test ----------------
+// On a filtered level most in-edges fail the frontier-bit test and nothing is gathered for them, so the
+// cost of pull_list_kernel<W, GPV, true> is the test itself, which every one of the TPV threads of a
+// word repeats for every edge (issue-bound: profiles/r01_ncu_iter2_filtered.txt).  Here the SEG lanes that
+// serve a vertex each own ONE in-edge of a SEG-edge round (one source load + one bit test per edge), a
+// ballot collects the hits of every segment, and the segment's SEG/TPV word groups gather only those,
+// source ids handed over by shuffle.  pull_warp_kernel is the SEG = 32 case of the same idea; this one
+// packs 32/SEG vertices into a warp for in-degrees far below 32.  Rounds are pipelined two deep.
+template <int W, int SEG>
+__global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
+	using C = LaneCfg<W>;
+	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
+	constexpr int VPW = 32 / SEG;  // vertices per warp
+	constexpr int GPS = SEG / TPV; // word groups per segment
+	static_assert(SEG >= TPV && SEG <= 32 && (SEG & (SEG - 1)) == 0, "segment shape");
+	constexpr uint32_t INV = 0xFFFFFFFFu, FULL = 0xffffffffu;
+	constexpr uint32_t SEGMASK = SEG == 32 ? 0xffffffffu : ((1u << SEG) - 1u);
+	__shared__ uint32_t salive[16];
+	alive_init(salive, a.alive_slots);
+	const uint32_t wid = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+	if ((uint64_t)wid * VPW >= a.nlist) return; // warp-uniform
+	const uint32_t lane = threadIdx.x & 31, seg = lane / SEG, sl = lane % SEG;
+	const uint32_t g = sl / TPV, t = sl % TPV; // word group inside the segment, slice inside the word
+	const uint64_t idx = (uint64_t)wid * VPW + seg;
+	const bool valid = idx < a.nlist;
+	const uint32_t n = valid ? a.list[idx] : 0u;
+	uint32_t lo = 0, hi = 0;
+	if (valid) {
+		lo = a.ioff[n];
+		hi = a.ioff[n + 1];
+	}
+	uint32_t v0 = lo + sl < hi ? a.isrc[lo + sl] : INV;
+	uint32_t v1 = lo + SEG + sl < hi ? a.isrc[lo + SEG + sl] : INV;
+	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
+	Slice<SW> s = slice_zero<SW>(), unseen = slice_zero<SW>();
+	if (valid) {
+		s = ld_slice<SW>(a.seen + wo);
+		const Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
+#pragma unroll
+		for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
+	}
+	// a vertex is scanned while ANY of its slices still misses lanes (the edge tests are shared by the
+	// whole segment); a covered slice just stops gathering
+	bool mine_open = slice_any<SW>(unseen);
+	bool vopen = (__ballot_sync(FULL, mine_open) >> (seg * SEG)) & SEGMASK;
+	Slice<SW> acc = slice_zero<SW>();
+	bool p0 = vopen && v0 != INV && fbit_test(a.fcur, v0);
+	uint32_t base = lo;
+	while (__any_sync(FULL, vopen && base < hi)) {
+		const unsigned bal = __ballot_sync(FULL, p0);
+		// sources of the round after next, frontier bits of the next round: in flight during the gathers
+		const uint32_t j2 = base + 2 * SEG + sl;
+		const uint32_t v2 = (vopen && j2 < hi) ? a.isrc[j2] : INV;
+		const bool p1 = vopen && v1 != INV && fbit_test(a.fcur, v1);
+		unsigned m = (bal >> (seg * SEG)) & SEGMASK; // hits of my vertex in this round
+		while (__any_sync(FULL, m != 0u)) {
+			unsigned mm = m; // my group takes the g-th lowest hit
+#pragma unroll
+			for (int k = 0; k < GPS - 1; k++)
+				if (k < (int)g) mm &= mm - 1u;
+			const uint32_t src = __shfl_sync(FULL, v0, (int)(seg * SEG) + (mm ? __ffs((int)mm) - 1 : 0));
+			if (mm && mine_open) {
+				const Slice<SW> w = ldg_slice<SW>(a.visit + (size_t)src * WPV + t * SW);
+#pragma unroll
+				for (int i = 0; i < SW; i++) acc.w[i] |= w.w[i];
+			}
+#pragma unroll
+			for (int k = 0; k < GPS; k++) m &= m - 1u;
+		}
+		if (bal) { // something was gathered somewhere in the warp: early-exit test per vertex
+			Slice<SW> tot = acc;
+#pragma unroll
+			for (int d = TPV; d < SEG; d <<= 1) {
+#pragma unroll
+				for (int i = 0; i < SW; i++) tot.w[i] |= __shfl_xor_sync(FULL, tot.w[i], d);
+			}
+			mine_open = mine_open && !slice_covers<SW>(tot, unseen);
+			vopen = (__ballot_sync(FULL, mine_open) >> (seg * SEG)) & SEGMASK;
+		}
+		v0 = v1;
+		v1 = v2;
+		p0 = p1 && vopen;
+		base += SEG;
+	}
+	Slice<SW> tot = acc;
+#pragma unroll
+	for (int d = TPV; d < SEG; d <<= 1) {
+#pragma unroll
+		for (int i = 0; i < SW; i++) tot.w[i] |= __shfl_xor_sync(FULL, tot.w[i], d);
+	}
+	Slice<SW> news;
+#pragma unroll
+	for (int i = 0; i < SW; i++) news.w[i] = tot.w[i] & unseen.w[i];
+	const bool writer = valid && g == 0;
+	if (writer) {
+		st_slice<SW>(a.next + wo, news);
+		if (slice_any<SW>(news)) {
+#pragma unroll
+			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
+			st_slice<SW>(a.seen + wo, s);
+			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
+		}
+	}
+	const unsigned nb = __ballot_sync(FULL, writer && slice_any<SW>(news));
+	const bool vnew = ((nb >> (seg * SEG)) & SEGMASK) != 0u;
+	if (writer && t == 0 && vnew) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+	if (a.npeers && writer && vnew) st_peers<SW>(a, wo, news); // whole word, zero slices included
+}
+
 // ---- K4 hubs: one block per chunk of a hub's in-list, partial ORs merged with atomicOr ---------
 template <int W>
 __global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
