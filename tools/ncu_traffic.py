@@ -8,7 +8,7 @@ import csv
 import json
 import sys
 
-LEVEL = ("pull_list_kernel", "pull_warp_kernel", "pull_hub_kernel", "hub_finalize_kernel", "push_kernel",
+LEVEL = ("pull_list_kernel", "pull_seg_kernel", "pull_tiny_kernel", "pull_warp_kernel", "pull_hub_kernel", "hub_finalize_kernel", "push_kernel",
          "clear_by_bitmap_kernel", "compact_bitmap_kernel", "frontier_stats_kernel")
 
 
