@@ -370,6 +370,9 @@ def bench_c1(ctx, steps, warmup, with_cpu):
     return res
 
 
+W_BITS = 512  # lanes per vertex word on the timed path
+
+
 def main_ours(a):
     import pgq_b200
     rank, world, local, dist = dist_setup(a.gpus)
@@ -501,6 +504,18 @@ def main_ours(a):
         "setup": {"csr_build_ms": build_ms, "reverse_csr_ms": transpose_ms},
         "clocks": clocks,
     }
+    if rank == 0 and W_BITS == 512:
+        # what the memory system gives for the dense level's access pattern (random 64-byte word gathers, no
+        # arithmetic): beyond L2 it is a fraction of the sequential-copy peak, whatever the kernel does
+        try:
+            g_l2, _ = ctx.probe_gather(int(0.245e9) // 64, 1 << 26, 4)
+            g_far, _ = ctx.probe_gather((1 << 30) // 64, 1 << 26, 4)
+            line["roofline"]["random_gather_gbs"] = {
+                "table_245MB_(one_dense_frontier)": g_l2, "table_1GB_(whole_visit_array)": g_far,
+                "what": "measured live: random 64-byte gathers, 4 threads x 16 B per word, 4 in flight per "
+                        "thread, indices streamed; GB/s counts 68 B per gather"}
+        except Exception as ex:  # a probe must not cost the bench line
+            line["roofline"]["random_gather_gbs"] = {"error": str(ex)}
     if rank == 0 and world == 1 and not a.no_csr:
         line["csr_build"] = bench_csr(ctx, a.csr_scale, ef, a.steps, a.warmup, peak_gbs)
     if rank == 0 and world == 1 and not a.no_paths:

@@ -386,6 +386,14 @@ class Context:
         self._chk(self.lib.pgq_gen_rmat_device(self._ctx, C.c_uint64(seed), C.c_int(scale), C.c_int64(e_size),
                                                C.c_void_p(d_src), C.c_void_p(d_dst)))
 
+    def probe_gather(self, nwords, ngathers, unroll=4):
+        """-> (GB/s, ms) of random 64-byte gathers from a table of nwords words (measurement probe)."""
+        g = C.c_double(0)
+        ms = C.c_double(0)
+        self._chk(self.lib.pgq_probe_gather(self._ctx, C.c_int64(nwords), C.c_int64(ngathers), C.c_int(unroll),
+                                            C.byref(g), C.byref(ms)))
+        return g.value, ms.value
+
     def gen_knows_device(self, seed, v_size, e_size, mult, add, d_src, d_dst):
         self._chk(self.lib.pgq_gen_knows_device(self._ctx, C.c_uint64(seed), C.c_int64(v_size), C.c_int64(e_size),
                                                 C.c_uint64(mult), C.c_uint64(add), C.c_void_p(d_src),

@@ -1041,6 +1041,11 @@ int pgq_gen_knows_device(pgq_ctx_t *ctx, uint64_t seed, int64_t v_size, int64_t 
 	return PGQ_OK;
 }
 
+int pgq_probe_gather(pgq_ctx_t *ctx, int64_t nwords, int64_t ngathers, int unroll, double *out_gbs, double *out_ms) {
+	LOCK(ctx);
+	return probe_gather(c, nwords, ngathers, unroll, out_gbs, out_ms);
+}
+
 int pgq_flush_l2(pgq_ctx_t *ctx) {
 	LOCK(ctx);
 	const size_t bytes = (size_t)256 << 20; // > 126 MB L2

@@ -333,6 +333,7 @@ int part_offsets_u32(Ctx *c, const uint32_t *keys, uint32_t n, uint32_t nv, uint
 // ---- gen.cu ----
 int gen_rmat_device(Ctx *c, uint64_t seed, int scale, int64_t E, int64_t *d_src, int64_t *d_dst);
 int gen_rmat_rows_device(Ctx *c, uint64_t seed, int scale, int64_t row0, int64_t n, int64_t *d_src, int64_t *d_dst);
+int probe_gather(Ctx *c, int64_t nwords, int64_t ngathers, int unroll, double *out_gbs, double *out_ms);
 int gen_knows_device(Ctx *c, uint64_t seed, int64_t V, int64_t E, uint64_t mult, uint64_t add, int64_t *d_src,
                      int64_t *d_dst);
 

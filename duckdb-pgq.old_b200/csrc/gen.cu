@@ -67,4 +67,80 @@ int gen_knows_device(Ctx *c, uint64_t seed, int64_t V, int64_t E, uint64_t mult,
 	return PGQ_OK;
 }
 
+// ---- measurement probe: what the memory system gives for the dense level's access pattern --------------
+// 64-byte words gathered at random from a table of `nwords` words, four threads per word (16 bytes each),
+// `U` independent gathers in flight per thread, indices streamed from a sequential array: the shape of the
+// dense bottom-up level without any of its arithmetic.  bench.py quotes the result beside the level
+// kernels' DRAM rate (a random 64-byte gather does not reach the sequential-copy peak).
+__global__ void __launch_bounds__(256) probe_fill_idx_kernel(uint32_t *idx, uint64_t n, uint32_t nwords,
+                                                             uint64_t seed) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+		uint64_t z = seed + (i + 1) * 0x9E3779B97F4A7C15ull; // splitmix64
+		z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+		z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+		z ^= z >> 31;
+		idx[i] = (uint32_t)(z % nwords);
+	}
+}
+
+template <int U>
+__global__ void __launch_bounds__(256) probe_gather_kernel(const uint4 *__restrict__ table,
+                                                           const uint32_t *__restrict__ idx, uint64_t n,
+                                                           uint4 *__restrict__ sink) {
+	const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	const uint64_t grp = tid >> 2, ngrp = ((uint64_t)gridDim.x * blockDim.x) >> 2;
+	const uint32_t t = (uint32_t)(tid & 3);
+	uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+	for (uint64_t i = grp * U; i + U <= n; i += ngrp * U) {
+		uint32_t v[U];
+#pragma unroll
+		for (int u = 0; u < U; u++) v[u] = idx[i + u];
+		uint4 w[U];
+#pragma unroll
+		for (int u = 0; u < U; u++) w[u] = __ldg(table + (size_t)v[u] * 4 + t);
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			acc.x |= w[u].x;
+			acc.y |= w[u].y;
+			acc.z |= w[u].z;
+			acc.w |= w[u].w;
+		}
+	}
+	if (acc.x == 0x12345678u && acc.y == 0x9abcdef0u) sink[tid & 1023] = acc; // keeps the loads alive
+}
+
+int probe_gather(Ctx *c, int64_t nwords, int64_t ngathers, int unroll, double *out_gbs, double *out_ms) {
+	if (nwords < 1 || ngathers < 1024 || nwords > 0xFFFFFFFFll) {
+		set_error("probe_gather: bad sizes");
+		return PGQ_ERR_INVALID;
+	}
+	TmpBuf table, idx, sink;
+	PGQ_TRY(table.reserve((size_t)nwords * 64));
+	PGQ_TRY(idx.reserve((size_t)ngathers * 4));
+	PGQ_TRY(sink.reserve(1024 * 16));
+	cudaStream_t st = c->stream;
+	PGQ_CUDA(cudaMemsetAsync(table.p, 0x11, (size_t)nwords * 64, st));
+	probe_fill_idx_kernel<<<c->sm_count * 16, 256, 0, st>>>(idx.as<uint32_t>(), (uint64_t)ngathers, (uint32_t)nwords,
+	                                                        0x5eedULL);
+	const unsigned grid = (unsigned)c->sm_count * 8u;
+	float best = 0;
+	for (int rep = 0; rep < 3; rep++) { // first repetition warms up; report the faster of the other two
+		PGQ_CUDA(cudaEventRecord(c->ev_a, st));
+		if (unroll >= 8) probe_gather_kernel<8><<<grid, 256, 0, st>>>(table.as<uint4>(), idx.as<uint32_t>(), (uint64_t)ngathers, sink.as<uint4>());
+		else if (unroll >= 4) probe_gather_kernel<4><<<grid, 256, 0, st>>>(table.as<uint4>(), idx.as<uint32_t>(), (uint64_t)ngathers, sink.as<uint4>());
+		else probe_gather_kernel<2><<<grid, 256, 0, st>>>(table.as<uint4>(), idx.as<uint32_t>(), (uint64_t)ngathers, sink.as<uint4>());
+		PGQ_CUDA(cudaEventRecord(c->ev_b, st));
+		PGQ_CUDA(cudaEventSynchronize(c->ev_b));
+		float ms = 0;
+		PGQ_CUDA(cudaEventElapsedTime(&ms, c->ev_a, c->ev_b));
+		if (rep && (best == 0 || ms < best)) best = ms;
+	}
+	count_launch(c, 4);
+	PGQ_CUDA(cudaGetLastError());
+	if (out_ms) *out_ms = best;
+	if (out_gbs) *out_gbs = (double)ngathers * 68.0 / (best * 1e-3) / 1e9; // 64-byte word + its 4-byte index
+	return PGQ_OK;
+}
+
 } // namespace pgq

@@ -195,6 +195,10 @@ int pgq_gen_rmat_rows_device(pgq_ctx_t *ctx, uint64_t seed, int scale, int64_t r
 int pgq_gen_knows_device(pgq_ctx_t *ctx, uint64_t seed, int64_t v_size, int64_t e_size, uint64_t mult,
                          uint64_t add, int64_t *d_src, int64_t *d_dst);
 /* write >L2-sized scratch so the next timed step starts with a cold L2 */
+/* Measurement probe (bench only): `ngathers` random 64-byte gathers (4 threads x 16 bytes, `unroll` in flight
+ * per thread, indices streamed) from a table of `nwords` words -- the dense bottom-up level's access pattern
+ * without its arithmetic.  *out_gbs counts 68 bytes per gather (word + index). */
+int pgq_probe_gather(pgq_ctx_t *ctx, int64_t nwords, int64_t ngathers, int unroll, double *out_gbs, double *out_ms);
 int pgq_flush_l2(pgq_ctx_t *ctx);
 /* CUDA-event stopwatch on the library's stream */
 int pgq_timer_start(pgq_ctx_t *ctx);
