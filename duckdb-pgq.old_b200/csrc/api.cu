@@ -6,6 +6,11 @@
 
 #include "common.cuh"
 
+#include <map>
+#include <mutex>
+#include <utility>
+#include <vector>
+
 #include <cmath>
 #include "nccl_dl.cuh"
 
@@ -86,9 +91,9 @@ static int finalize(Ctx *c, Csr *g) {
 	g->d_src64.release();
 	g->d_dst64.release();
 	g->d_eid64.release();
-	if (g->h_src) cudaFreeHost(g->h_src);
-	if (g->h_dst) cudaFreeHost(g->h_dst);
-	if (g->h_eid) cudaFreeHost(g->h_eid);
+	pinned_release(g->h_src, g->h_bytes);
+	pinned_release(g->h_dst, g->h_bytes);
+	pinned_release(g->h_eid, g->h_bytes);
 	g->h_src = g->h_dst = g->h_eid = nullptr;
 	g->staged_cap = 0;
 	g->state = Csr::READY;
@@ -99,6 +104,140 @@ static int finalize(Ctx *c, Csr *g) {
 
 
 namespace pgq {
+
+// ---- small-block caches (see common.cuh) ---------------------------------------------------------------
+namespace {
+constexpr size_t CACHE_MAX_BLOCK = (size_t)16 << 20;
+constexpr size_t CACHE_MAX_TOTAL = (size_t)512 << 20;
+constexpr size_t PINNED_MAX_BLOCK = (size_t)32 << 20;
+constexpr size_t PINNED_MAX_TOTAL = (size_t)256 << 20;
+std::mutex g_cache_mu;
+struct DevCache {
+	std::vector<void *> free_list[32]; // by log2(size)
+	size_t total = 0;
+};
+std::map<int, DevCache> g_devcache; // per device
+std::vector<std::pair<void *, size_t>> g_pinned;
+size_t g_pinned_total = 0;
+
+inline int size_class(size_t bytes, size_t *rounded) {
+	int k = 8; // 256 B
+	while (((size_t)1 << k) < bytes) k++;
+	*rounded = (size_t)1 << k;
+	return k;
+}
+} // namespace
+
+void *devcache_alloc(size_t bytes, size_t *actual) {
+	void *p = nullptr;
+	if (bytes <= CACHE_MAX_BLOCK) {
+		size_t rounded;
+		const int k = size_class(bytes, &rounded);
+		int dev = 0;
+		cudaGetDevice(&dev);
+		{
+			std::lock_guard<std::mutex> lk(g_cache_mu);
+			DevCache &dc = g_devcache[dev];
+			if (!dc.free_list[k].empty()) {
+				p = dc.free_list[k].back();
+				dc.free_list[k].pop_back();
+				dc.total -= rounded;
+			}
+		}
+		bytes = rounded;
+	}
+	if (!p) {
+		cudaError_t e = cudaMalloc(&p, bytes);
+		if (e != cudaSuccess) { // give the cached blocks back and try once more
+			(void)cudaGetLastError();
+			devcache_trim();
+			e = cudaMalloc(&p, bytes);
+		}
+		if (e != cudaSuccess) {
+			set_error("cudaMalloc(%zu) -> %s", bytes, cudaGetErrorString(e));
+			(void)cudaGetLastError();
+			*actual = 0;
+			return nullptr;
+		}
+	}
+	*actual = bytes;
+	return p;
+}
+
+void devcache_free(void *p, size_t actual) {
+	if (!p) return;
+	if (actual <= CACHE_MAX_BLOCK && actual >= 256 && (actual & (actual - 1)) == 0) {
+		int dev = 0;
+		cudaGetDevice(&dev);
+		cudaDeviceSynchronize(); // what cudaFree guaranteed: nothing in flight still uses the block
+		size_t rounded;
+		const int k = size_class(actual, &rounded);
+		std::lock_guard<std::mutex> lk(g_cache_mu);
+		DevCache &dc = g_devcache[dev];
+		if (dc.total + rounded <= CACHE_MAX_TOTAL) {
+			dc.free_list[k].push_back(p);
+			dc.total += rounded;
+			return;
+		}
+	}
+	cudaFree(p);
+}
+
+void devcache_trim() {
+	int dev = 0;
+	cudaGetDevice(&dev);
+	std::vector<void *> victims;
+	{
+		std::lock_guard<std::mutex> lk(g_cache_mu);
+		DevCache &dc = g_devcache[dev];
+		for (auto &fl : dc.free_list) {
+			victims.insert(victims.end(), fl.begin(), fl.end());
+			fl.clear();
+		}
+		dc.total = 0;
+	}
+	for (void *p : victims) cudaFree(p);
+}
+
+void *pinned_acquire(size_t bytes, size_t *actual) {
+	if (bytes <= PINNED_MAX_BLOCK) {
+		size_t rounded;
+		size_class(bytes, &rounded);
+		bytes = rounded;
+		std::lock_guard<std::mutex> lk(g_cache_mu);
+		for (size_t i = 0; i < g_pinned.size(); i++) {
+			if (g_pinned[i].second == bytes) {
+				void *p = g_pinned[i].first;
+				g_pinned.erase(g_pinned.begin() + (long)i);
+				g_pinned_total -= bytes;
+				*actual = bytes;
+				return p;
+			}
+		}
+	}
+	void *p = nullptr;
+	if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+		set_error("cudaHostAlloc(%zu) failed", bytes);
+		(void)cudaGetLastError();
+		*actual = 0;
+		return nullptr;
+	}
+	*actual = bytes;
+	return p;
+}
+
+void pinned_release(void *p, size_t actual) {
+	if (!p) return;
+	if (actual <= PINNED_MAX_BLOCK) {
+		std::lock_guard<std::mutex> lk(g_cache_mu);
+		if (g_pinned_total + actual <= PINNED_MAX_TOTAL) {
+			g_pinned.emplace_back(p, actual);
+			g_pinned_total += actual;
+			return;
+		}
+	}
+	cudaFreeHost(p);
+}
 
 const char *last_error_str() {
 	return g_err;
@@ -217,6 +356,7 @@ int pgq_shutdown(pgq_ctx_t *ctx) {
 		c->nccl_comm = nullptr;
 	}
 	ctx_release_resources(c);
+	devcache_trim(); // cached blocks of this device go back to the driver with the context
 	delete ctx;
 	return PGQ_OK;
 }
@@ -352,9 +492,10 @@ int pgq_csr_add_edges(pgq_ctx_t *ctx, int32_t id, const int64_t *src, const int6
 	if (!g->h_src) {
 		g->staged_cap = g->E < STAGE_ROWS ? (g->E > 0 ? g->E : 1) : STAGE_ROWS;
 		size_t bytes = (size_t)g->staged_cap * sizeof(int64_t);
-		PGQ_CUDA(cudaHostAlloc((void **)&g->h_src, bytes, cudaHostAllocDefault));
-		PGQ_CUDA(cudaHostAlloc((void **)&g->h_dst, bytes, cudaHostAllocDefault));
-		if (g->have_eid) PGQ_CUDA(cudaHostAlloc((void **)&g->h_eid, bytes, cudaHostAllocDefault));
+		g->h_src = static_cast<int64_t *>(pinned_acquire(bytes, &g->h_bytes));
+		g->h_dst = static_cast<int64_t *>(pinned_acquire(bytes, &g->h_bytes));
+		if (g->have_eid) g->h_eid = static_cast<int64_t *>(pinned_acquire(bytes, &g->h_bytes));
+		if (!g->h_src || !g->h_dst || (g->have_eid && !g->h_eid)) return PGQ_ERR_OOM;
 	}
 	int64_t done = 0;
 	while (done < n) {

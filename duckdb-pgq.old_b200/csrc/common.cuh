@@ -29,28 +29,34 @@ void set_error(const char *fmt, ...);
 		if (_rc != PGQ_OK) return _rc; \
 	} while (0)
 
+// Small-block cache behind DevBuf (api.cu).  A config-1 sized CSR build (180 k edges) spends 0.1 ms in
+// kernels and, without this, 3.5 ms in a dozen cudaMalloc / cudaFree / cudaHostAlloc calls.  Blocks of at
+// most 16 MiB are rounded up to a power of two and kept per device when released (up to 512 MiB);
+// releasing synchronises the device first, which is what cudaFree did for the callers before.
+void *devcache_alloc(size_t bytes, size_t *actual); // nullptr: out of memory (error text set)
+void devcache_free(void *p, size_t actual);
+void devcache_trim();                               // cudaFree everything cached (context shutdown)
+void *pinned_acquire(size_t bytes, size_t *actual); // pinned host staging blocks, same idea
+void pinned_release(void *p, size_t actual);
+
 // Owning device buffer (grows, never shrinks unless released).
 struct DevBuf {
 	void *p = nullptr;
 	size_t cap = 0;
+	size_t actual = 0; // bytes behind p (>= cap: cached blocks are rounded up)
 	int reserve(size_t bytes) {
 		if (bytes <= cap) return PGQ_OK;
-		if (p) cudaFree(p);
-		p = nullptr;
-		cap = 0;
-		cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
-		if (e != cudaSuccess) {
-			set_error("cudaMalloc(%zu) -> %s", bytes, cudaGetErrorString(e));
-			(void)cudaGetLastError();
-			return PGQ_ERR_OOM;
-		}
+		release();
+		p = devcache_alloc(bytes ? bytes : 16, &actual);
+		if (!p) return PGQ_ERR_OOM;
 		cap = bytes;
 		return PGQ_OK;
 	}
 	void release() {
-		if (p) cudaFree(p);
+		if (p) devcache_free(p, actual);
 		p = nullptr;
 		cap = 0;
+		actual = 0;
 	}
 	template <class T>
 	T *as() const {
@@ -83,6 +89,7 @@ struct Csr {
 	bool have_cnt = false;
 	// create_csr_edge rows staged in pinned host memory until finalize
 	int64_t *h_src = nullptr, *h_dst = nullptr, *h_eid = nullptr;
+	size_t h_bytes = 0; // size of each pinned staging block (pinned_acquire)
 	int64_t staged = 0, staged_cap = 0;
 	bool have_eid = false;
 	bool pending_begin = false; // begin_edges deferred until the first row batch tells whether eids exist

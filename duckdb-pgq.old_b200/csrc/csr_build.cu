@@ -294,9 +294,9 @@ int csr_prepare(Ctx *c, Csr *g) {
 }
 
 void Csr::free_all() {
-	if (h_src) cudaFreeHost(h_src);
-	if (h_dst) cudaFreeHost(h_dst);
-	if (h_eid) cudaFreeHost(h_eid);
+	pinned_release(h_src, h_bytes);
+	pinned_release(h_dst, h_bytes);
+	pinned_release(h_eid, h_bytes);
 	h_src = h_dst = h_eid = nullptr;
 	d_src64.release(); d_dst64.release(); d_eid64.release();
 	d_off.release(); d_tgt.release(); d_row.release(); d_eid.release(); d_fsrc.release();
