@@ -524,7 +524,9 @@ int radix_sort_wide(Ctx *c, const SortIO &io) {
 			a.pin = c->sort_pack.as<uint2>();
 			a.p1in = want_p1 ? c->sort_p1[0].as<uint32_t>() : nullptr;
 		}
-		a.err = io.err; // may be nullptr: out-of-range ids (64-bit form) and the look-back watchdog report here
+		// out-of-range ids (64-bit form) and the look-back watchdog report here; without a caller's flag the
+		// watchdog gets a private one, checked below
+		a.err = io.err ? io.err : (lookback ? d_ticket + 8 : nullptr);
 		if (last) {
 			a.kout = keys_out;
 			a.p0out = io.out_p0;
@@ -554,6 +556,15 @@ int radix_sort_wide(Ctx *c, const SortIO &io) {
 		if (c->opt.sort_wide == 2) PGQ_TRY(rw_launch_scatter<1024>(c, form, a));
 		else PGQ_TRY(rw_launch_scatter<256>(c, form, a));
 		PGQ_CUDA(cudaGetLastError());
+	}
+	if (lookback && !io.err) {
+		uint32_t h = 0;
+		PGQ_CUDA(cudaMemcpyAsync(&h, d_ticket + 8, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+		PGQ_CUDA(cudaStreamSynchronize(c->stream));
+		if (h & 4u) {
+			set_error("radix sort look-back watchdog fired (a tile never published its bucket totals)");
+			return PGQ_ERR_CUDA;
+		}
 	}
 	return PGQ_OK;
 }
