@@ -384,6 +384,7 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "push_beta")) c->opt.push_beta = value < 1 ? 1 : value;
 	else if (!strcmp(key, "small_path")) c->opt.small_path = value;
 	else if (!strcmp(key, "small_edge_mb")) c->opt.small_edge_mb = value < 0 ? 0 : value;
+	else if (!strcmp(key, "trim_cache")) devcache_trim(); // give cached small blocks back to the driver now
 	else if (!strcmp(key, "seg_small")) c->opt.seg_small = value;
 	else if (!strcmp(key, "sort_wide")) c->opt.sort_wide = value;
 	else if (!strcmp(key, "sort_lookback")) c->opt.sort_lookback = value;

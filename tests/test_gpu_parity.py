@@ -112,6 +112,36 @@ def test_csr_both_sort_cores(ctx, V, E, wide, lookback):
     ctx.csr_delete(2)
 
 
+def test_small_block_cache_reuse(ctx):
+    """CSRs built, queried and deleted back to back run on recycled device / pinned blocks (api.cu small-block
+    cache): recycled memory is not zero like a fresh cudaMalloc often is, so every array must be fully written."""
+    rng = np.random.default_rng(4)
+    for rep in range(6):
+        V = int(rng.integers(50, 6000))
+        E = int(rng.integers(1, 40000))
+        src = rng.integers(0, V, E, dtype=np.int64)
+        dst = rng.integers(0, V, E, dtype=np.int64)
+        v, e, eids = orc.csr_build(V, src, dst)
+        deg = np.bincount(src, minlength=V).astype(np.int64)
+        ctx.create_csr_vertex(9, V, np.arange(V), deg)
+        for lo in range(0, E, 1024):
+            ctx.create_csr_edge(9, V, E, src[lo:lo + 1024], dst[lo:lo + 1024])
+        ctx.csr_finalize(9)
+        gv, ge, _ = ctx.csr_download(9)
+        _cmp_arr("v", gv, v)
+        _cmp_arr("e", ge, e)
+        ps, pd = orc.gen_pairs(rep, V, v, 700)
+        out, ov = ctx.iterativelength(9, ps, pd)
+        eo, ev = orc.iterativelength(V, v, e, ps, pd)
+        _cmp_arr("valid", ov, ev)
+        _cmp_arr("length", out, eo)
+        assert_paths_equal(ctx.shortestpath(9, ps[:200], pd[:200], mode=0),
+                           orc.shortestpath(V, v, e, eids, ps[:200], pd[:200], mode=0), "paths rep %d" % rep)
+        ctx.csr_delete(9)
+        if rep == 3:
+            ctx.set_option("trim_cache", 1)
+
+
 def test_csr_with_explicit_edge_ids_and_chunked_rows(ctx):
     """create_csr_vertex + create_csr_edge fed in 1024-row chunks like DuckDB does (R2/R3)."""
     V, E = 5000, 60000
