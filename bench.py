@@ -425,7 +425,7 @@ def main_ours(a):
     ctx.set_option("timing", 0)
     # batches in flight per call: each has a host thread that spin-waits on its stream once per level, so
     # keep ranks x streams within the host's cores
-    streams = a.streams if a.streams else max(1, min(4, host_cores() // max(1, world)))
+    streams = a.streams if a.streams else max(1, min(8, host_cores() // max(1, world)))
     ctx.set_option("streams", streams)
     # ---- device-resident timed region ----
     for _ in range(a.warmup):
