@@ -52,7 +52,7 @@ struct BfsCtrl {
 // kernels' early exit.  Producers OR their new words into a block-shared mask and flush it once
 // per block into slot blockIdx % ALIVE_SLOTS (spread addresses: no hot atomics); the check kernel
 // folds the slots into BfsCtrl::alive.
-static constexpr uint32_t ALIVE_SLOTS = 1024;
+static constexpr uint32_t ALIVE_SLOTS = 128;
 
 // Producers keep a block-shared copy of their slot (blockIdx % ALIVE_SLOTS), preloaded from the
 // slot so knowledge carries over between blocks, and touch the global slot only for bits the copy
