@@ -51,6 +51,21 @@ def test_golden_cases(ctx, name):
     ctx.csr_delete(7)
 
 
+def test_cte_golden_upper_bound(ctx):
+    """The reference DuckDB's own (recursive-CTE) answers with an upper bound on the path length."""
+    g = json.load(open(os.path.join(GOLD, "cte_knows_bounded.json")))
+    ctx.csr_build(8, g["V"], g["src"], g["dst"])
+    top = str(max(g["uppers"]))
+    out, ov = ctx.iterativelength(8, g["q_src"], g["q_dst"])
+    assert lengths_list(out, ov) == g["expected"][top]
+    r, rv = ctx.reachability(8, g["q_src"], g["q_dst"])
+    assert r.tolist() == [int(x is not None) for x in g["expected"][top]]
+    for u in g["uppers"]:
+        out, ov = ctx.iterativelength_bounded(8, g["q_src"], g["q_dst"], 0, u)
+        assert lengths_list(out, ov) == g["expected"][str(u)], u
+    ctx.csr_delete(8)
+
+
 def test_cte_golden(ctx):
     g = json.load(open(os.path.join(GOLD, "cte_lengths.json")))
     ctx.csr_build(8, g["V"], g["src"], g["dst"])

@@ -51,6 +51,21 @@ def test_null_rows_G8():
     assert p == [[0, 1, 2, 3], None, None, [2]]
 
 
+def test_cte_golden_upper_bound():
+    """Upper-bounded hop distances produced by the reference DuckDB's recursive CTE (tests/golden/
+    make_cte_golden2.py) on a knows-shaped graph: pins iterativelength, reachability and the upper bound of R11."""
+    g = json.load(open(os.path.join(GOLD, "cte_knows_bounded.json")))
+    v, e, _ = orc.csr_build(g["V"], g["src"], g["dst"])
+    top = str(max(g["uppers"]))
+    out, ov = orc.iterativelength(g["V"], v, e, g["q_src"], g["q_dst"])
+    assert lengths_list(out, ov) == g["expected"][top]
+    r, rv = orc.reachability(g["V"], v, e, g["q_src"], g["q_dst"])
+    assert r.tolist() == [int(x is not None) for x in g["expected"][top]]
+    for u in g["uppers"]:
+        out, ov = orc.iterativelength_bounded(g["V"], v, e, g["q_src"], g["q_dst"], 0, u)
+        assert lengths_list(out, ov) == g["expected"][str(u)], u
+
+
 def test_bounded_lengths_R11():
     """6-argument iterativelength: hand-checked on the path graph, then the defining property on R-MAT:
     bounded(l, u) = full where l <= full <= u, NULL elsewhere."""
