@@ -322,3 +322,28 @@ SELECT count(*), sum(CASE WHEN %s THEN 0 ELSE 1 END)
     assert all(k == "result" for k, _ in r), [x for x in r if x[0] != "result"][:2]
     verdicts = [rows for _, rows in r if rows and "," in rows[0]]
     assert verdicts == [["%d,0" % n]] * nq, verdicts
+
+
+@needs_host
+def test_oracle_csr_against_engine_sql(tmp_path):
+    """CPU: rule R3 (neighbour order inside a vertex = arrival order of the rows) restated in SQL and run by the
+    reference DuckDB: `e` = targets ordered by (source, rowid), `v` = running count of the sources."""
+    V, E = 300, 4000
+    rng = np.random.default_rng(8)
+    src = rng.integers(0, V, E)
+    dst = rng.integers(0, V, E)
+    src[::7] = 5  # a long neighbour list with many duplicates
+    v, e, _ = orc.csr_build(V, src, dst)
+    _write_csv(tmp_path / "knows.csv", [src, dst])
+    sql = "PRAGMA threads=1;\nCREATE TABLE knows(p1 BIGINT, p2 BIGINT);\nCOPY knows FROM '%s';\n" % (tmp_path / "knows.csv")
+    sql += "SELECT p2 FROM knows ORDER BY p1, rowid;\n"
+    sql += "SELECT p1, count(*) FROM knows GROUP BY p1 ORDER BY p1;\n"
+    r = run_sql(sql)
+    assert all(k == "result" for k, _ in r), r
+    assert [int(x) for x in r[3][1]] == e.tolist()
+    deg = np.zeros(V, dtype=np.int64)
+    for row in r[4][1]:
+        a, b = row.split(",")
+        deg[int(a)] = int(b)
+    expect_v = np.concatenate([[0], np.cumsum(deg), [E]])
+    assert expect_v.tolist() == v.tolist()
