@@ -36,3 +36,27 @@ def test_reference_arm_other_ranks_stay_silent():
     assert _run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}, "--gpus", "2") == []
     lines = _run({"RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0"}, "--gpus", "2")
     assert len(lines) == 1 and json.loads(lines[0])["n_gpus"] == 2
+
+
+import pytest  # noqa: E402
+
+
+@pytest.mark.gpu
+def test_own_arm_contract_on_a_small_graph():
+    """GPU: the product arm at a small scale carries every key the measurement contract names."""
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--scale", "15", "--csr-scale", "15",
+                          "--pairs", "4096", "--steps", "1", "--warmup", "3", "--cpu-threads", "2", "--no-paths"],
+                         capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-1500:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    need = (KEYS - {"impl"}) | {"gpu_launches", "roofline", "clocks", "csr_build"}
+    assert need <= set(d), need - set(d)
+    assert d["n_gpus"] == 1 and d["gpu_launches"] > 0 and d["value"] > 0 and d["e2e"]["value"] > 0
+    assert d["e2e"]["h2d_bytes_per_step"] > 0 and d["e2e"]["d2h_bytes_per_step"] > 0
+    r = d["roofline"]
+    assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
+    c = d["cpu_baseline"]
+    assert c["kind"] == "port" and c["cores"] >= 1 and c["value"] > 0 and "identical" in c["parity"]
+    assert d["csr_build"]["unit"] == "GE/s" and d["csr_build"]["value"] > 0
