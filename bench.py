@@ -425,7 +425,8 @@ def main_ours(a):
     ctx.set_option("timing", 0)
     # batches in flight per call: each has a host thread that spin-waits on its stream once per level, so
     # keep ranks x streams within the host's cores
-    streams = a.streams if a.streams else max(1, min(8, host_cores() // max(1, world)))
+    cores_per_rank = host_cores() // max(1, world)
+    streams = a.streams if a.streams else (8 if cores_per_rank >= 16 else max(1, min(4, cores_per_rank)))
     ctx.set_option("streams", streams)
     # ---- device-resident timed region ----
     for _ in range(a.warmup):
