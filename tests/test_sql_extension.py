@@ -47,6 +47,11 @@ def test_extension_loads_and_fails_loudly_without_gpu():
            "'create_csr_edge','iterativelength','reachability','shortestpath','shortestpath_with_edges'," \
            "'delete_csr','cheapest_path_length','cheapest_path_length_double') GROUP BY name ORDER BY name;\n"
     sql += "SELECT iterativelength(0, CAST(10 AS BIGINT), CAST(1 AS BIGINT), CAST(2 AS BIGINT));\n"
+    # every overload binds (the error, if any, comes from the call, not from the binder)
+    sql += "SELECT iterativelength(0, CAST(10 AS BIGINT), CAST(1 AS BIGINT), CAST(2 AS BIGINT), CAST(0 AS BIGINT), CAST(3 AS BIGINT));\n"
+    sql += "SELECT reachability(0, TRUE, CAST(10 AS BIGINT), CAST(1 AS BIGINT), CAST(2 AS BIGINT));\n"
+    sql += "SELECT create_csr_edge(0, CAST(10 AS BIGINT), CAST(1 AS BIGINT), CAST(1 AS BIGINT), CAST(2 AS BIGINT), CAST(0 AS BIGINT), CAST(1.5 AS DOUBLE));\n"
+    sql += "SELECT iterativelength(0, CAST(10 AS BIGINT), CAST(1 AS BIGINT));\n"  # no such overload
     r = run_sql(sql)
     assert r[0][0] == "result"
     assert r[1] == ("result", ["cheapest_path_length", "cheapest_path_length_double", "create_csr_edge",
@@ -57,6 +62,9 @@ def test_extension_loads_and_fails_loudly_without_gpu():
         assert "no CPU fallback" in r[2][1] or "CUDA" in r[2][1]
     else:
         assert "does not exist" in r[2][1]
+    for k in (3, 4, 5):  # on a GPU box the weighted create_csr_edge simply succeeds
+        assert r[k][0] == "result" or ("No function matches" not in r[k][1] and "Binder" not in r[k][1]), r[k]
+    assert r[6][0] == "error" and ("No function matches" in r[6][1] or "Binder" in r[6][1]), r[6]
 
 
 def _write_csv(path, cols):
