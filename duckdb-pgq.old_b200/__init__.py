@@ -33,7 +33,11 @@ class Stats(C.Structure):
                 ("level_kernel_ms", C.c_double), ("level_kernel_launches", C.c_uint64),
                 ("csr_build_ms", C.c_double), ("transpose_ms", C.c_double),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
-                ("coll_bytes", C.c_uint64), ("coll_ms", C.c_double)]
+                ("coll_bytes", C.c_uint64), ("coll_ms", C.c_double),
+                ("model_bytes", C.c_uint64), ("k_listed", C.c_uint64), ("k_open", C.c_uint64), ("k_new", C.c_uint64),
+                ("k_scanned", C.c_uint64), ("k_gathered", C.c_uint64), ("kp_items", C.c_uint64),
+                ("kp_edges", C.c_uint64), ("kp_seen", C.c_uint64), ("kp_next", C.c_uint64),
+                ("host_syncs", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -87,13 +91,23 @@ class Context:
     """One GPU context (one per process/rank).  Holds the csr_id -> CSR map like the reference's
     per-connection state."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, devices=None):
+        """device: the GPU of a one-device context.  devices=[d0, d1, ...]: a multi-GPU context of ONE
+        process (pgq_init_devices): CSRs are built on d0 and replicated on first use, every query deals
+        its batches over all of them."""
         self.lib = load_library()
         self._ctx = C.c_void_p()
-        rc = self.lib.pgq_init(C.c_int(device), C.byref(self._ctx))
+        if devices is not None:
+            devices = [int(d) for d in devices]
+            arr = (C.c_int * len(devices))(*devices)
+            rc = self.lib.pgq_init_devices(arr, C.c_int(len(devices)), C.byref(self._ctx))
+            device = devices[0] if devices else 0
+        else:
+            rc = self.lib.pgq_init(C.c_int(device), C.byref(self._ctx))
         if rc != 0:
             raise PgqError(rc, self.lib.pgq_last_error().decode())
         self.device = device
+        self.devices = devices if devices is not None else [device]
 
     def _chk(self, rc):
         if rc != 0:

@@ -1,7 +1,11 @@
 // C ABI of pgq_b200 (include/pgq_b200.h): context, CSR lifecycle, queries, helpers.
 // Thread-safety: every entry point takes the context mutex (DuckDB may enter a scalar function
 // from several worker threads at once: /root/reference/src/parallel/pipeline.cpp:79-123).
+#include <execinfo.h>
+#include <signal.h>
 #include <stdarg.h>
+#include <stdlib.h>
+#include <unistd.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -257,11 +261,20 @@ int ctx_init_resources(Ctx *c) {
 
 void ctx_release_resources(Ctx *c) {
 	for (Ctx *h : c->helpers) {
+		cudaSetDevice(h->device);
 		if (h->stream) cudaStreamSynchronize(h->stream);
 		ctx_release_resources(h);
+		if (h->device != c->device) devcache_trim();
 		delete h;
 	}
 	c->helpers.clear();
+	cudaSetDevice(c->device);
+	for (LoopGraph &lg : c->loop_graph) lg.destroy();
+	if (c->h_found) cudaFreeHost(c->h_found);
+	c->h_found = nullptr;
+	c->h_found_cap = 0;
+	c->bfs_done.release();
+	c->hist_bytes = 0;
 	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
 	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->sort_pack, &c->bfs_seen, &c->bfs_visit[0],
 	                  &c->bfs_visit[1], &c->bfs_hist_tab, &c->bfs_pathout, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
@@ -303,7 +316,23 @@ const char *pgq_last_error(void) {
 	return g_err;
 }
 
-int pgq_init(int device, pgq_ctx_t **out_ctx) {
+// PGQ_B200_BACKTRACE=1: frames of a crashing thread on stderr (addresses resolve with addr2line -e libpgq_b200.so)
+static void crash_handler(int sig) {
+	void *frames[64];
+	const int n = backtrace(frames, 64);
+	const char msg[] = "[pgq_b200] fatal signal, backtrace:\n";
+	if (write(2, msg, sizeof(msg) - 1) < 0) {
+	}
+	backtrace_symbols_fd(frames, n, 2);
+	signal(sig, SIG_DFL);
+	raise(sig);
+}
+
+static int init_one(int device, pgq_ctx_t **out_ctx) {
+	if (getenv("PGQ_B200_BACKTRACE")) {
+		signal(SIGSEGV, crash_handler);
+		signal(SIGABRT, crash_handler);
+	}
 	if (!out_ctx) return PGQ_ERR_INVALID;
 	*out_ctx = nullptr;
 	int ndev = 0;
@@ -334,7 +363,56 @@ int pgq_init(int device, pgq_ctx_t **out_ctx) {
 		delete ctx;
 		return rc;
 	}
+	c->devices.assign(1, device);
+	c->devices_all = c->devices;
 	*out_ctx = ctx;
+	return PGQ_OK;
+}
+
+int pgq_init(int device, pgq_ctx_t **out_ctx) {
+	return init_one(device, out_ctx);
+}
+
+int pgq_init_devices(const int *devices, int n, pgq_ctx_t **out_ctx) {
+	if (!out_ctx || !devices || n < 1) {
+		set_error("pgq_init_devices: need at least one device");
+		return PGQ_ERR_INVALID;
+	}
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0) {
+		set_error("no CUDA device: %s (pgq_b200 has no CPU fallback)", cudaGetErrorString(e));
+		(void)cudaGetLastError();
+		*out_ctx = nullptr;
+		return PGQ_ERR_CUDA;
+	}
+	for (int i = 0; i < n; i++) {
+		if (devices[i] < 0 || devices[i] >= ndev) {
+			set_error("device %d out of range (%d devices)", devices[i], ndev);
+			return PGQ_ERR_INVALID;
+		}
+		for (int j = 0; j < i; j++)
+			if (devices[j] == devices[i]) {
+				set_error("device %d listed twice", devices[i]);
+				return PGQ_ERR_INVALID;
+			}
+		cudaDeviceProp prop;
+		PGQ_CUDA(cudaGetDeviceProperties(&prop, devices[i]));
+		if (prop.major < 10) {
+			set_error("device %d is sm_%d%d; pgq_b200 is built for sm_100a only", devices[i], prop.major, prop.minor);
+			return PGQ_ERR_CUDA;
+		}
+	}
+	PGQ_TRY(init_one(devices[0], out_ctx));
+	Ctx *c = &(*out_ctx)->c;
+	c->devices.assign(devices, devices + n);
+	c->devices_all = c->devices;
+	return PGQ_OK;
+}
+
+int pgq_device_count(pgq_ctx_t *ctx, int *out_n) {
+	if (!ctx || !out_n) return PGQ_ERR_INVALID;
+	*out_n = (int)ctx->c.devices.size();
 	return PGQ_OK;
 }
 
@@ -389,7 +467,19 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "sort_wide")) c->opt.sort_wide = value;
 	else if (!strcmp(key, "sort_lookback")) c->opt.sort_lookback = value;
 	else if (!strcmp(key, "sort_wide_min")) c->opt.sort_wide_min = value < 0 ? 0 : value;
-	else if (!strcmp(key, "streams")) c->opt.streams = value < 1 ? 1 : value > 8 ? 8 : value;
+	else if (!strcmp(key, "streams")) c->opt.streams = value < 1 ? 1 : value > 16 ? 16 : value;
+	else if (!strcmp(key, "loop")) c->opt.loop = value;
+	else if (!strcmp(key, "done_bitmap")) c->opt.done_bitmap = value < 0 ? 0 : value > 2 ? 2 : value;
+	else if (!strcmp(key, "dense_store")) c->opt.dense_store = value ? 1 : 0;
+	else if (!strcmp(key, "l2_persist")) c->opt.l2_persist = value;
+	else if (!strcmp(key, "hist_budget_mb")) c->opt.hist_budget_mb = value < 0 ? 0 : value;
+	else if (!strcmp(key, "devices_used")) { // at most this many devices of a multi-GPU context take batches
+		if (value < 1 || value > (int64_t)c->devices_all.size()) {
+			set_error("devices_used must be in [1, %zu]", c->devices_all.size());
+			return PGQ_ERR_INVALID;
+		}
+		c->devices.assign(c->devices_all.begin(), c->devices_all.begin() + value);
+	}
 	else {
 		set_error("unknown option '%s'", key);
 		return PGQ_ERR_INVALID;
@@ -429,6 +519,7 @@ int pgq_csr_create(pgq_ctx_t *ctx, int32_t id, int64_t v_size) {
 	}
 	Csr *g = new Csr();
 	g->V = v_size;
+	g->device = c->device;
 	c->csrs[id] = g;
 	return PGQ_OK;
 }
@@ -537,6 +628,7 @@ static int build_common(Ctx *c, int32_t id, int64_t v_size, int64_t e_size, cons
 	}
 	Csr *g = new Csr();
 	g->V = v_size;
+	g->device = c->device;
 	c->csrs[id] = g;
 	g->keep_rows = (flags & PGQ_CSR_ROWIDS) != 0;
 	if (device_ptrs) { // inputs already resident: no staging copy of the edge table
@@ -997,6 +1089,7 @@ int pgq_part_csr_create(pgq_ctx_t *ctx, int32_t id, int64_t v_size) {
 		c->csrs.erase(it);
 	}
 	Csr *g = new Csr();
+	g->device = c->device;
 	g->is_part = true;
 	g->gV = v_size;
 	g->V = (int64_t)part_map(v_size, c->part_world).Vp;

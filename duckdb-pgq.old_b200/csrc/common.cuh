@@ -128,6 +128,13 @@ struct Csr {
 	uint32_t eff_med_max = 0; // med_max after clamping to >= small_max
 	// 1-D partition (part.cu): this object then describes the slice of the reverse CSR owned by the
 	// rank — V = owned vertex count (local index space), E = local in-edges, d_isrc = GLOBAL sources
+	// identity of the device arrays: bumped whenever they are (re)built, so cached level-loop graphs
+	// (msbfs.cu) notice a CSR that was rebuilt under the same id / address
+	uint64_t gen = 0;
+	int device = 0; // the GPU the arrays live on
+	// multi-GPU contexts (pgq_init_devices): read-only copies of the query-side arrays on the other
+	// devices, made on first use by a multi-device query (msbfs.cu csr_replica)
+	std::map<int, Csr *> replicas;
 	bool is_part = false;
 	int64_t gV = 0;         // global vertex count
 	int64_t part_base = 0;  // first owned vertex
@@ -158,6 +165,11 @@ struct Options {
 	int64_t sort_lookback = 1; // two-pass sort: decoupled look-back instead of histogram pre-pass + scan
 	int64_t sort_wide_min = 32768; // ... from this many keys on
 	int64_t level_cap = 0x7fffffff; // per call, not user-settable: iterativelength's upper bound (R11)
+	int64_t loop = 1;          // 1: device-side level loop (CUDA graph WHILE/SWITCH nodes), 0: host loop, one sync per level
+	int64_t done_bitmap = 1;   // skip vertices whose `seen` already holds every active lane: 1 = tested on tail levels, 2 = on every level
+	int64_t dense_store = 1;   // unfiltered levels write every listed vertex's `next` word (0: sparse stores + scrub everywhere)
+	int64_t l2_persist = 0;    // access-policy window (persisting L2) on `seen` for the batch streams
+	int64_t hist_budget_mb = 0; // shortestpath level history per worker: 0 = a quarter of the free HBM
 };
 
 // What the two frontier buffers hold after the last completed batch (msbfs.cu run_batch).
@@ -166,7 +178,28 @@ struct BfsDirty {
 	int W = 0;
 	int64_t V = 0;
 	const void *visit0 = nullptr, *fbit0 = nullptr;
-	int map[2] = {0, 0}; // bitmap index describing visit[0] / visit[1]
+	// which bitmaps name the non-zero words is in the worker's device control block (BfsCtrl::L)
+};
+
+// The level loop of one worker as an instantiated CUDA graph (msbfs.cu): loop_begin -> WHILE { SWITCH(mode)
+// { push | pull | pull filtered early | pull filtered late } -> check }.  Valid for one (CSR, lane width,
+// buffers) combination; rebuilt when any of them changes.
+struct LoopGraph {
+	cudaGraph_t graph = nullptr;
+	cudaGraphExec_t exec = nullptr;
+	const void *g = nullptr;
+	uint64_t gen = 0;
+	int W = 0;
+	bool keep_hist = false;
+	const void *seen = nullptr, *ctrl = nullptr, *done = nullptr;
+	int64_t seg_small = -1;
+	void destroy() {
+		if (exec) cudaGraphExecDestroy(exec);
+		if (graph) cudaGraphDestroy(graph);
+		exec = nullptr;
+		graph = nullptr;
+		g = nullptr;
+	}
 };
 
 struct Ctx {
@@ -211,6 +244,21 @@ struct Ctx {
 	// block and frontier buffers; they share the caller's CSRs read-only and hold none of their own
 	std::vector<Ctx *> helpers;
 	cudaEvent_t ev_fork = nullptr;
+	// multi-GPU context (pgq_init_devices): devices[0] == device; queries spread their batches over all
+	// of them (CSR replicated), everything else runs on the primary
+	std::vector<int> devices;
+	std::vector<int> devices_all; // as given to pgq_init_devices (option "devices_used" narrows `devices`)
+	DevBuf bfs_done;        // 1 bit per vertex: seen holds every active lane (msbfs_kernels.cuh)
+	LoopGraph loop_graph[2]; // [keep_hist]
+	bool loop_unsupported = false; // conditional graph nodes refused by the driver: host loop from then on
+	uint64_t tot_seen[3] = {0, 0, 0}; // device-side running totals already folded into stats (levels, push, launches)
+	bool ctrl_fresh = true;  // the control block has not been zeroed since it was allocated
+	void *h_found = nullptr; // pinned staging of the per-call found[] table
+	size_t h_found_cap = 0;
+	size_t hist_bytes = 0;   // bytes behind bfs_hist
+	uint32_t loop_nk[2][8] = {}; // kernels per level of each mode in loop_graph[i]
+	int l2_window_on = -1;   // access-policy window currently set on the stream (-1 unknown)
+	const void *l2_window_ptr = nullptr;
 };
 
 int ctx_init_resources(Ctx *c);    // stream, events, pinned control mirror (api.cu)

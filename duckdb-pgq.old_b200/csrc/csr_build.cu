@@ -6,6 +6,8 @@
 // and the reverse CSR used by the pull-direction MS-BFS (same kernels, key = target).
 #include "common.cuh"
 
+#include <atomic>
+
 namespace pgq {
 
 // ---- K1+K2 ----------------------------------------------------------------------------------
@@ -71,8 +73,11 @@ static int key_bits_for(int64_t V) {
 	return b;
 }
 
+static std::atomic<uint64_t> g_csr_gen{1};
+
 int csr_device_build(Ctx *c, Csr *g) {
 	const int64_t V = g->V, E = g->E;
+	g->gen = g_csr_gen.fetch_add(1);
 	if (V >= ((int64_t)1 << 32) - 2 || E >= ((int64_t)1 << 32) - 1) {
 		set_error("csr too large for one GPU slice (V=%lld E=%lld; 32-bit device ids)", (long long)V,
 		          (long long)E);
@@ -220,6 +225,7 @@ int csr_prepare(Ctx *c, Csr *g) {
 	                       g->bins_med_max != c->opt.med_max ||
 	                       g->bins_hub_min != c->opt.hub_min;
 	if (!need_bins) return PGQ_OK;
+	g->gen = g_csr_gen.fetch_add(1); // cached loop graphs and replicas of the old arrays are stale
 	PGQ_CUDA(cudaEventRecord(c->ev_a, st));
 	if (need_rev) {
 		const uint32_t *tkeys = nullptr; // sorted targets, left in the sort's scratch
@@ -294,6 +300,17 @@ int csr_prepare(Ctx *c, Csr *g) {
 }
 
 void Csr::free_all() {
+	if (!replicas.empty()) {
+		int cur = 0;
+		cudaGetDevice(&cur);
+		for (auto &kv : replicas) {
+			cudaSetDevice(kv.first);
+			kv.second->free_all();
+			delete kv.second;
+		}
+		replicas.clear();
+		cudaSetDevice(cur);
+	}
 	pinned_release(h_src, h_bytes);
 	pinned_release(h_dst, h_bytes);
 	pinned_release(h_eid, h_bytes);

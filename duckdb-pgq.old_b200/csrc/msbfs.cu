@@ -1,7 +1,16 @@
 // Host driver of the bitset MS-BFS (iterativelength / reachability / shortestpath batches).
 // Mirrors the reference's batch loop: clear seen/visit, seed the lanes,
 // run level steps while a lane is active and something changed, check destinations after each
-// level, retire found lanes.  One stream, one host sync per level (reads 16 bytes of control).
+// level, retire found lanes.
+//
+// The level loop itself lives on the device (msbfs_kernels.cuh LoopState): the check kernel that ends
+// a level rotates the frontier views and picks the direction of the next one, and the whole loop is
+// one CUDA graph -- loop_begin -> WHILE { SWITCH(mode) { push | pull | pull filtered early | pull
+// filtered late } -> check } -- launched once per batch.  Between the init kernel and the result
+// copy the host does nothing: batches of a call are enqueued back to back on several streams (and,
+// in a multi-GPU context, several devices) by ONE host thread.  The host-driven loop of round 1 is
+// kept for the instrumented passes (options "stats", "timing", "trace") and as "loop"=0; it launches
+// the same level bodies from the mode it reads back after every level.
 #include "msbfs_kernels.cuh"
 #include "msbfs_small.cuh"
 #include "nccl_dl.cuh"
@@ -21,11 +30,14 @@ struct BatchBufs {
 	size_t fbit_bytes;
 	uint32_t fbit_words;
 	uint32_t *alive_slots; // [ALIVE_SLOTS][16], all-zero between levels
+	uint32_t *done;        // 1 bit per vertex (same geometry as fbit), or nullptr
 	BfsCtrl *ctrl;
 };
 
-template <int W, int GPV>
-void launch_class(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter) {
+// ---- launchers of the in-degree class kernels.  *nk counts the kernels issued (a capture counts the
+// nodes of the body it records); STATS picks the instrumented instantiation of the untimed pass. ----
+template <int W, int GPV, bool STATS = false>
+void launch_class(PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter, cudaStream_t st, uint32_t *nk) {
 	if (!nlist) return;
 	using C = LaneCfg<W>;
 	constexpr int VPW = C::G / GPV;
@@ -33,183 +45,178 @@ void launch_class(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool 
 	a.nlist = nlist;
 	const uint32_t warps = div_up(nlist, VPW);
 	const uint32_t grid = div_up((uint64_t)warps * 32, 128);
-	if (filter) pull_list_kernel<W, GPV, true><<<grid, 128, 0, c->stream>>>(a);
-	else pull_list_kernel<W, GPV, false><<<grid, 128, 0, c->stream>>>(a);
-	count_launch(c);
+	if (filter) pull_list_kernel<W, GPV, true, STATS><<<grid, 128, 0, st>>>(a);
+	else pull_list_kernel<W, GPV, false, STATS><<<grid, 128, 0, st>>>(a);
+	++*nk;
 }
 
 // filtered levels, small in-degrees: SEG lanes per vertex, edge-parallel frontier test
-template <int W, int SEG>
-void launch_seg(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist) {
+template <int W, int SEG, bool STATS = false>
+void launch_seg(PullArgs &a, const DevBuf &list, uint32_t nlist, cudaStream_t st, uint32_t *nk) {
 	if (!nlist) return;
 	a.list = list.as<uint32_t>();
 	a.nlist = nlist;
 	const uint32_t warps = div_up(nlist, 32 / SEG);
-	pull_seg_kernel<W, SEG><<<div_up((uint64_t)warps * 32, 128), 128, 0, c->stream>>>(a);
-	count_launch(c);
+	pull_seg_kernel<W, SEG, STATS><<<div_up((uint64_t)warps * 32, 128), 128, 0, st>>>(a);
+	++*nk;
 }
 
-template <int W>
-void launch_warp(Ctx *c, PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter) {
+template <int W, bool STATS = false>
+void launch_warp(PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter, cudaStream_t st, uint32_t *nk) {
 	if (!nlist) return;
 	a.list = list.as<uint32_t>();
 	a.nlist = nlist;
 	const uint32_t grid = div_up((uint64_t)nlist * 32, 128);
-	if (filter) pull_warp_kernel<W, true><<<grid, 128, 0, c->stream>>>(a);
-	else pull_warp_kernel<W, false><<<grid, 128, 0, c->stream>>>(a);
-	count_launch(c);
+	if (filter) pull_warp_kernel<W, true, STATS><<<grid, 128, 0, st>>>(a);
+	else pull_warp_kernel<W, false, STATS><<<grid, 128, 0, st>>>(a);
+	++*nk;
 }
 
 // tiny class: straight-line kernel when the class really is <= 4 in-edges, else the generic one
-template <int W>
-void launch_tiny(Ctx *c, PullArgs &a, Csr *g, bool filter) {
+template <int W, bool STATS = false>
+void launch_tiny(PullArgs &a, Csr *g, bool filter, cudaStream_t st, uint32_t *nk) {
 	if (!g->n_tiny) return;
 	if (g->bins_tiny_max > 4) {
-		launch_class<W, 1>(c, a, g->d_tiny, g->n_tiny, filter);
+		launch_class<W, 1, STATS>(a, g->d_tiny, g->n_tiny, filter, st, nk);
 		return;
 	}
 	using C = LaneCfg<W>;
 	a.list = g->d_tiny.as<uint32_t>();
 	a.nlist = g->n_tiny;
 	const uint32_t grid = div_up((uint64_t)div_up(g->n_tiny, C::G) * 32, 128);
-	if (filter) pull_tiny_kernel<W, true><<<grid, 128, 0, c->stream>>>(a);
-	else pull_tiny_kernel<W, false><<<grid, 128, 0, c->stream>>>(a);
-	count_launch(c);
+	if (filter) pull_tiny_kernel<W, true, STATS><<<grid, 128, 0, st>>>(a);
+	else pull_tiny_kernel<W, false, STATS><<<grid, 128, 0, st>>>(a);
+	++*nk;
 }
 
-// One bottom-up level: frontier visit[cur]/fbit[cur] -> next visit[cur^1]/fbit[cur^1].
-template <int W>
-int launch_level(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, int iter, bool filter, bool early) {
+template <int W, bool STATS = false>
+void launch_hubs(PullArgs &a, Csr *g, cudaStream_t st, uint32_t *nk) {
+	if (!g->n_hub) return;
 	using C = LaneCfg<W>;
-	cudaStream_t st = c->stream;
-	// fb[0] describes visit[cur], fb[1] is built for visit[cur^1], fb[2] describes what visit[cur^1]
-	// still holds (the frontier of two levels ago).
-	// fnext is built with atomicOr: start from zero.  At level 2 `next` still holds the source words
-	// (level-0 frontier), some at in-degree-0 vertices that no class rewrites: clear them by bitmap.
-	PGQ_CUDA(cudaMemsetAsync(b.fbit[fb[1]], 0, b.fbit_bytes, st));
-	if (iter == 2) {
-		clear_by_bitmap_kernel<W><<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[fb[2]], b.fbit_words,
-		                                                                    b.visit[cur ^ 1]);
-		count_launch(c);
+	a.list = g->d_hub.as<uint32_t>();
+	a.nlist = g->n_hub;
+	a.chunks = g->d_hubchunks.as<HubChunk>();
+	a.nchunks = g->n_hubchunks;
+	pull_hub_kernel<W, STATS><<<g->n_hubchunks, 256, 0, st>>>(a);
+	hub_finalize_kernel<W><<<div_up((uint64_t)g->n_hub * C::TPV, 256), 256, 0, st>>>(a);
+	*nk += 2;
+}
+
+// One level of `mode` on stream st: the body of one SWITCH case of the loop graph (recorded by a stream
+// capture) and, identically, what the host loop launches.  Everything that changes from level to level
+// (frontier buffers, bitmaps, queues) is read from ctrl->L by the kernels.
+template <int W, bool STATS>
+int launch_body(Ctx *c, Csr *g, const BatchBufs &b, uint32_t mode, bool keep_hist, cudaStream_t st, uint32_t *nk) {
+	const uint32_t cgrid = div_up(b.fbit_words, 256);
+	const size_t bm = (size_t)g->V * (W / 8);
+	// `next` becomes all-zero: scrub the words its bitmap names (ping-pong pair) or zero the fresh level
+	// buffer (shortestpath); either way the bitmap two levels old is zeroed -- it is the one the level after
+	// this builds
+	// unfiltered bottom-up levels store densely (most vertices gain bits there: measured 3.1 vs 3.7 ms on the
+	// dense level of an s24 batch), every other level sparsely after a scrub of what `next` still holds
+	const bool dense = mode == MODE_PULL && c->opt.dense_store;
+	level_clear_kernel<W><<<cgrid, 256, 0, st>>>(b.ctrl, b.fbit_words, keep_hist ? 0 : dense ? 2 : 1);
+	++*nk;
+	if (keep_hist && bm) {
+		zero_next_kernel<<<(uint32_t)c->sm_count * 4, 256, 0, st>>>(b.ctrl, bm / 16);
+		++*nk;
 	}
-	PullArgs a{};
-	a.ioff = g->d_ioff.as<uint32_t>();
-	a.isrc = g->d_isrc.as<uint32_t>();
-	a.visit = b.visit[cur];
-	a.next = b.visit[cur ^ 1];
-	a.seen = b.seen;
-	a.ctrl = b.ctrl;
-	a.V = (uint32_t)g->V;
-	a.hubacc = b.hubacc;
-	a.off = g->d_off.as<int64_t>();
-	a.fcur = b.fbit[fb[0]];
-	a.fnext = b.fbit[fb[1]];
-	a.alive_slots = b.alive_slots;
-	launch_tiny<W>(c, a, g, filter);
-	// measured on the filtered levels of R-MAT s24 (levels 2 / 6): pull_list 2.23 / 0.62 ms, 8 lanes per
-	// vertex 2.08 / 0.56 ms, 16 lanes 2.31 / 0.73 ms; the same kernel for the tiny class: no change
-	if (filter && c->opt.seg_small) launch_seg<W, 8>(c, a, g->d_small, g->n_small);
-	else launch_class<W, 2>(c, a, g->d_small, g->n_small, filter);
-	// medium in-degrees: the edge-parallel warp scan wins while most vertices still scan their whole
-	// in-list against a sparse frontier (early levels); two thread groups per vertex win when every
-	// word is gathered anyway (dense levels) or most vertices have nothing left to find (tail)
-	if (filter && early) launch_warp<W>(c, a, g->d_med, g->n_med, true);
-	else launch_class<W, 2>(c, a, g->d_med, g->n_med, filter);
-	launch_warp<W>(c, a, g->d_mid, g->n_mid, filter);
-	if (g->n_hub) {
-		a.list = g->d_hub.as<uint32_t>();
-		a.nlist = g->n_hub;
-		a.chunks = g->d_hubchunks.as<HubChunk>();
-		a.nchunks = g->n_hubchunks;
-		pull_hub_kernel<W><<<g->n_hubchunks, 256, 0, st>>>(a);
-		hub_finalize_kernel<W><<<div_up((uint64_t)g->n_hub * C::TPV, 256), 256, 0, st>>>(a);
-		count_launch(c, 2);
+	if (mode == MODE_PUSH) {
+		// pull -> push transition: the queue is rebuilt from the frontier bitmap (both kernels return at once
+		// when the previous level left a queue)
+		compact_bitmap_kernel<<<cgrid, 256, 0, st>>>(b.fbit_words, (uint32_t)g->V, g->d_off.as<int64_t>(), b.ctrl);
+		bfs_snapshot_items_kernel<<<1, 1, 0, st>>>(b.ctrl);
+		PushArgs pa{};
+		pa.off = g->d_off.as<int64_t>();
+		pa.tgt = g->d_tgt.as<uint32_t>();
+		pa.seen = b.seen;
+		pa.ctrl = b.ctrl;
+		pa.alive_slots = b.alive_slots;
+		push_kernel<W, STATS><<<(uint32_t)c->sm_count * 8, 256, 0, st>>>(pa);
+		*nk += 3;
+	} else {
+		const bool filter = mode != MODE_PULL, early = mode == MODE_PULL_F_EARLY;
+		PullArgs a{};
+		a.ioff = g->d_ioff.as<uint32_t>();
+		a.isrc = g->d_isrc.as<uint32_t>();
+		a.seen = b.seen;
+		a.ctrl = b.ctrl;
+		a.V = (uint32_t)g->V;
+		a.hubacc = b.hubacc;
+		a.off = g->d_off.as<int64_t>();
+		a.alive_slots = b.alive_slots;
+		a.done = b.done;
+		a.dyn = 1;
+		a.dense = dense ? 1u : 0u;
+		a.use_done = (b.done && (mode == MODE_PULL_F_LATE || c->opt.done_bitmap == 2)) ? 1u : 0u;
+		launch_tiny<W, STATS>(a, g, filter, st, nk);
+		// measured on the filtered levels of R-MAT s24 (levels 2 / 6): pull_list 2.23 / 0.62 ms, 8 lanes per
+		// vertex 2.08 / 0.56 ms, 16 lanes 2.31 / 0.73 ms; the same kernel for the tiny class: no change
+		if (filter && c->opt.seg_small) launch_seg<W, 8, STATS>(a, g->d_small, g->n_small, st, nk);
+		else launch_class<W, 2, STATS>(a, g->d_small, g->n_small, filter, st, nk);
+		// medium in-degrees: the edge-parallel warp scan wins while most vertices still scan their whole
+		// in-list against a sparse frontier (early levels); two thread groups per vertex win when every
+		// word is gathered anyway (dense levels) or most vertices have nothing left to find (tail)
+		if (filter && early) launch_warp<W, STATS>(a, g->d_med, g->n_med, true, st, nk);
+		else launch_class<W, 2, STATS>(a, g->d_med, g->n_med, filter, st, nk);
+		launch_warp<W, STATS>(a, g->d_mid, g->n_mid, filter, st, nk);
+		launch_hubs<W, STATS>(a, g, st, nk);
+		frontier_stats_kernel<<<cgrid, 256, 0, st>>>(b.fbit_words, (uint32_t)g->V, g->d_off.as<int64_t>(), b.ctrl);
+		++*nk;
 	}
-	frontier_stats_kernel<<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[fb[1]], b.fbit_words, (uint32_t)g->V,
-	                                                               g->d_off.as<int64_t>(), b.ctrl);
-	count_launch(c);
+	PGQ_CUDA(cudaGetLastError());
 	return PGQ_OK;
 }
 
-int launch_level_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, const int *fb, int iter, bool filter,
-                   bool early) {
-	switch (W) {
-	case 64: return launch_level<64>(c, g, b, cur, fb, iter, filter, early);
-	case 128: return launch_level<128>(c, g, b, cur, fb, iter, filter, early);
-	case 256: return launch_level<256>(c, g, b, cur, fb, iter, filter, early);
-	case 512: return launch_level<512>(c, g, b, cur, fb, iter, filter, early);
+int launch_body_w(Ctx *c, Csr *g, const BatchBufs &b, int W, bool stats, uint32_t mode, bool keep_hist,
+                  cudaStream_t st, uint32_t *nk) {
+	if (stats) {
+		switch (W) {
+		case 64: return launch_body<64, true>(c, g, b, mode, keep_hist, st, nk);
+		case 128: return launch_body<128, true>(c, g, b, mode, keep_hist, st, nk);
+		case 256: return launch_body<256, true>(c, g, b, mode, keep_hist, st, nk);
+		case 512: return launch_body<512, true>(c, g, b, mode, keep_hist, st, nk);
+		}
+	} else {
+		switch (W) {
+		case 64: return launch_body<64, false>(c, g, b, mode, keep_hist, st, nk);
+		case 128: return launch_body<128, false>(c, g, b, mode, keep_hist, st, nk);
+		case 256: return launch_body<256, false>(c, g, b, mode, keep_hist, st, nk);
+		case 512: return launch_body<512, false>(c, g, b, mode, keep_hist, st, nk);
+		}
 	}
 	set_error("unsupported lane width %d", W);
 	return PGQ_ERR_INVALID;
 }
 
-// One top-down level over queue[q] (frontier in visit[cur]); builds queue[q^1] and fbit[cur^1].
-template <int W>
-int launch_push(Ctx *c, Csr *g, const BatchBufs &b, int cur, const int *fb, int q) {
-	PushArgs a{};
-	a.off = g->d_off.as<int64_t>();
-	a.tgt = g->d_tgt.as<uint32_t>();
-	a.visit = b.visit[cur];
-	a.next = b.visit[cur ^ 1];
-	a.seen = b.seen;
-	a.ctrl = b.ctrl;
-	a.queue = b.queue[q];
-	a.queue_next = b.queue[q ^ 1];
-	a.fnext = b.fbit[fb[1]];
-	// `next` still holds the frontier of two levels ago, described by fb[2]: zero exactly those words
-	PGQ_CUDA(cudaMemsetAsync(b.fbit[fb[1]], 0, b.fbit_bytes, c->stream));
-	clear_by_bitmap_kernel<W><<<div_up(b.fbit_words, 256), 256, 0, c->stream>>>(b.fbit[fb[2]], b.fbit_words,
-	                                                                           b.visit[cur ^ 1]);
-	const uint32_t grid = (uint32_t)c->sm_count * 8;
-	a.alive_slots = b.alive_slots;
-	push_kernel<W><<<grid, 256, 0, c->stream>>>(a);
-	count_launch(c, 2);
-	return PGQ_OK;
+void launch_check(const BatchBufs &b, int W, cudaStream_t st, int use_handles, cudaGraphConditionalHandle hw,
+                  cudaGraphConditionalHandle hs) {
+	bfs_check_kernel<<<1, W, 0, st>>>(b.seen, W, b.ctrl, b.alive_slots, use_handles, hw, hs);
 }
 
-int launch_push_w(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur, const int *fb, int q) {
-	switch (W) {
-	case 64: return launch_push<64>(c, g, b, cur, fb, q);
-	case 128: return launch_push<128>(c, g, b, cur, fb, q);
-	case 256: return launch_push<256>(c, g, b, cur, fb, q);
-	case 512: return launch_push<512>(c, g, b, cur, fb, q);
-	}
-	return PGQ_ERR_INVALID;
-}
-
-// zero the words of visit[which] named by bitmap fbit[bi] (and the bitmap)
-int launch_clear_w(Ctx *c, const BatchBufs &b, int W, int bi, int which) {
+// zero the words of the previous batch's last two frontiers (see scrub_kernel)
+int launch_scrub_w(Ctx *c, const BatchBufs &b, int W, int which) {
 	const uint32_t grid = div_up(b.fbit_words, 256);
 	switch (W) {
-	case 64: clear_by_bitmap_kernel<64><<<grid, 256, 0, c->stream>>>(b.fbit[bi], b.fbit_words, b.visit[which]); break;
-	case 128: clear_by_bitmap_kernel<128><<<grid, 256, 0, c->stream>>>(b.fbit[bi], b.fbit_words, b.visit[which]); break;
-	case 256: clear_by_bitmap_kernel<256><<<grid, 256, 0, c->stream>>>(b.fbit[bi], b.fbit_words, b.visit[which]); break;
-	case 512: clear_by_bitmap_kernel<512><<<grid, 256, 0, c->stream>>>(b.fbit[bi], b.fbit_words, b.visit[which]); break;
+	case 64: scrub_kernel<64><<<grid, 256, 0, c->stream>>>(b.ctrl, b.fbit_words, which); break;
+	case 128: scrub_kernel<128><<<grid, 256, 0, c->stream>>>(b.ctrl, b.fbit_words, which); break;
+	case 256: scrub_kernel<256><<<grid, 256, 0, c->stream>>>(b.ctrl, b.fbit_words, which); break;
+	case 512: scrub_kernel<512><<<grid, 256, 0, c->stream>>>(b.ctrl, b.fbit_words, which); break;
 	default: return PGQ_ERR_INVALID;
 	}
 	count_launch(c);
 	return PGQ_OK;
 }
 
-// pull -> push transition: queue[q] from the frontier bitmap fbit[cur].
-int launch_compact(Ctx *c, Csr *g, const BatchBufs &b, const int *fb, int q) {
-	cudaStream_t st = c->stream;
-	compact_bitmap_kernel<<<div_up(b.fbit_words, 256), 256, 0, st>>>(b.fbit[fb[0]], b.fbit_words, (uint32_t)g->V,
-	                                                                 g->d_off.as<int64_t>(), b.queue[q], b.ctrl);
-	bfs_snapshot_items_kernel<<<1, 1, 0, st>>>(b.ctrl);
-	count_launch(c, 2);
-	return PGQ_OK;
-}
-
-void launch_count(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur) {
+void launch_count(Ctx *c, Csr *g, const BatchBufs &b, int W, const uint32_t *visit) {
 	uint32_t grid = div_up(g->V, 256);
 	if (!grid) return;
 	const int64_t *off = g->d_off.as<int64_t>();
 	switch (W) {
-	case 64: bfs_count_kernel<64><<<grid, 256, 0, c->stream>>>(b.visit[cur], off, (uint32_t)g->V, b.ctrl); break;
-	case 128: bfs_count_kernel<128><<<grid, 256, 0, c->stream>>>(b.visit[cur], off, (uint32_t)g->V, b.ctrl); break;
-	case 256: bfs_count_kernel<256><<<grid, 256, 0, c->stream>>>(b.visit[cur], off, (uint32_t)g->V, b.ctrl); break;
-	case 512: bfs_count_kernel<512><<<grid, 256, 0, c->stream>>>(b.visit[cur], off, (uint32_t)g->V, b.ctrl); break;
+	case 64: bfs_count_kernel<64><<<grid, 256, 0, c->stream>>>(visit, off, (uint32_t)g->V, b.ctrl); break;
+	case 128: bfs_count_kernel<128><<<grid, 256, 0, c->stream>>>(visit, off, (uint32_t)g->V, b.ctrl); break;
+	case 256: bfs_count_kernel<256><<<grid, 256, 0, c->stream>>>(visit, off, (uint32_t)g->V, b.ctrl); break;
+	case 512: bfs_count_kernel<512><<<grid, 256, 0, c->stream>>>(visit, off, (uint32_t)g->V, b.ctrl); break;
 	}
 	count_launch(c);
 }
@@ -217,8 +224,38 @@ void launch_count(Ctx *c, Csr *g, const BatchBufs &b, int W, int cur) {
 int read_ctrl(Ctx *c, const BatchBufs &b, BfsCtrl *h) {
 	PGQ_CUDA(cudaMemcpyAsync(c->h_ctrl, b.ctrl, sizeof(BfsCtrl), cudaMemcpyDeviceToHost, c->stream));
 	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	c->stats.host_syncs++;
 	*h = *reinterpret_cast<BfsCtrl *>(c->h_ctrl);
 	return PGQ_OK;
+}
+
+// levels / launches the device counted since the last fold (the loop runs without the host)
+void fold_totals(Ctx *c, const BfsCtrl &h) {
+	c->stats.levels += h.tot_levels - c->tot_seen[0];
+	c->stats.push_levels += h.tot_push_levels - c->tot_seen[1];
+	c->stats.kernel_launches += h.tot_launches - c->tot_seen[2];
+	c->tot_seen[0] = h.tot_levels;
+	c->tot_seen[1] = h.tot_push_levels;
+	c->tot_seen[2] = h.tot_launches;
+}
+
+// Bytes THIS implementation must move for the levels one batch ran, from what its kernels touched
+// (instrumented pass).  No credit for cache hits: a gathered word counts W/8 bytes
+// wherever it was served from.
+uint64_t model_bytes_of(const BfsCtrl &h, const Csr *g, int W, size_t fbit_bytes, bool keep_hist) {
+	const uint64_t wb = (uint64_t)(W / 8), bm = (uint64_t)g->V * wb;
+	uint64_t m = 0;
+	// bottom-up: list entry + two in-offsets per listed vertex, `seen` per open vertex, `next` + `seen` stores
+	// per vertex that gained bits, a source id per scanned in-edge, a frontier word per gather
+	m += h.k_listed * 12ull + h.k_open * wb + h.k_new * 2ull * wb + h.k_scanned * 4ull + h.k_gathered * wb;
+	// top-down: queue item + frontier word + two out-offsets per item, a target id per edge, a 4-byte
+	// read-modify-write per atomic
+	m += h.kp_items * (8ull + wb + 16ull) + h.kp_edges * 4ull + (h.kp_seen + h.kp_next) * 8ull;
+	// per level: the old bitmap read + zeroed, the new one read for the statistics (+ a fresh level buffer)
+	m += (uint64_t)h.L.levels_run * (3ull * fbit_bytes + (keep_hist ? bm : 0ull));
+	// per batch: `seen` zeroed, the bitmaps zeroed; every frontier word is scrubbed once before its buffer is reused
+	m += bm + 4ull * fbit_bytes + (keep_hist ? 0ull : h.L.cum_verts * wb);
+	return m;
 }
 
 int alloc_bufs(Ctx *c, Csr *g, int W, BatchBufs *b) {
@@ -226,7 +263,14 @@ int alloc_bufs(Ctx *c, Csr *g, int W, BatchBufs *b) {
 	PGQ_TRY(c->bfs_seen.reserve(bm));
 	PGQ_TRY(c->bfs_visit[0].reserve(bm));
 	PGQ_TRY(c->bfs_visit[1].reserve(bm));
+	if (!c->bfs_ctrl.p) c->ctrl_fresh = true;
 	PGQ_TRY(c->bfs_ctrl.reserve(sizeof(BfsCtrl)));
+	if (c->ctrl_fresh) { // running totals start at zero
+		PGQ_CUDA(cudaMemsetAsync(c->bfs_ctrl.p, 0, sizeof(BfsCtrl), c->stream));
+		c->tot_seen[0] = c->tot_seen[1] = c->tot_seen[2] = 0;
+		c->ctrl_fresh = false;
+		c->bfs_dirty.valid = false;
+	}
 	const size_t hb = (size_t)(g->n_hub > 0 ? g->n_hub : 1) * (W / 8);
 	if (hb > c->bfs_hubacc.cap) {
 		PGQ_TRY(c->bfs_hubacc.reserve(hb));
@@ -252,16 +296,58 @@ int alloc_bufs(Ctx *c, Csr *g, int W, BatchBufs *b) {
 	// three frontier bitmaps in one allocation
 	PGQ_TRY(c->bfs_inq[0].reserve(3 * b->fbit_bytes));
 	for (int i = 0; i < 3; i++) b->fbit[i] = c->bfs_inq[0].as<uint32_t>() + (size_t)i * b->fbit_words;
+	b->done = nullptr;
+	if (c->opt.done_bitmap) {
+		PGQ_TRY(c->bfs_done.reserve(b->fbit_bytes));
+		b->done = c->bfs_done.as<uint32_t>();
+	}
 	return PGQ_OK;
 }
 
-// A zeroed frontier buffer for level `k` of a batch that keeps its history (shortestpath).
-int hist_level(Ctx *c, size_t k, size_t bm, uint32_t **out) {
-	if (c->bfs_hist.size() <= k) c->bfs_hist.resize(k + 1);
-	PGQ_TRY(c->bfs_hist[k].reserve(bm ? bm : 16));
-	if (bm) PGQ_CUDA(cudaMemsetAsync(c->bfs_hist[k].p, 0, bm, c->stream));
-	*out = c->bfs_hist[k].as<uint32_t>();
+// ---- shortestpath: per-level frontier history -----------------------------------------------------------
+static constexpr int PGQ_HIST_OVER = 0x7002; // internal: the level history would exceed its budget
+
+size_t hist_budget(Ctx *c) {
+	if (c->opt.hist_budget_mb > 0) return (size_t)c->opt.hist_budget_mb << 20;
+	size_t fr = 0, tot = 0;
+	if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) {
+		(void)cudaGetLastError();
+		return (size_t)4 << 30;
+	}
+	return (fr + c->hist_bytes) / 4; // a quarter of what is free once the history itself is not counted
+}
+
+// Level buffers 0..levels-1 of bm bytes each (grown, never zeroed here) and their device pointer table.
+int hist_reserve(Ctx *c, size_t levels, size_t bm) {
+	if (levels * (bm ? bm : 16) > hist_budget(c)) return PGQ_HIST_OVER;
+	if (c->bfs_hist.size() < levels) c->bfs_hist.resize(levels);
+	bool changed = false;
+	for (size_t k = 0; k < levels; k++) {
+		DevBuf &hb = c->bfs_hist[k];
+		if (hb.cap < (bm ? bm : 16)) {
+			c->hist_bytes -= hb.actual;
+			PGQ_TRY(hb.reserve(bm ? bm : 16));
+			c->hist_bytes += hb.actual;
+			changed = true;
+		}
+	}
+	if (changed || c->bfs_hist_tab.cap < c->bfs_hist.size() * sizeof(uint32_t *)) {
+		std::vector<uint32_t *> hp(c->bfs_hist.size());
+		for (size_t k = 0; k < hp.size(); k++) hp[k] = c->bfs_hist[k].as<uint32_t>();
+		PGQ_CUDA(cudaStreamSynchronize(c->stream)); // nothing in flight reads the old table
+		PGQ_TRY(c->bfs_hist_tab.reserve(hp.size() * sizeof(uint32_t *)));
+		PGQ_CUDA(cudaMemcpyAsync(c->bfs_hist_tab.p, hp.data(), hp.size() * sizeof(uint32_t *), cudaMemcpyHostToDevice,
+		                         c->stream));
+		PGQ_CUDA(cudaStreamSynchronize(c->stream)); // hp is a host temporary
+	}
 	return PGQ_OK;
+}
+
+void hist_trim(Ctx *c) {
+	for (DevBuf &hb : c->bfs_hist) hb.release();
+	c->bfs_hist.clear();
+	c->bfs_hist_tab.release();
+	c->hist_bytes = 0;
 }
 
 // ---- small graphs: the whole batch in one cooperative launch (msbfs_small.cuh) ------------------
@@ -325,16 +411,9 @@ int run_batch_small(Ctx *c, Csr *g, const BatchBufs &b, int W, bool keep_hist, c
 	a.max_levels = 0x7fffffff;
 	a.level_cap = (int)c->opt.level_cap;
 	if (keep_hist) {
-		if (c->bfs_hist.size() < (size_t)SMALL_HIST_LEVELS + 1) c->bfs_hist.resize((size_t)SMALL_HIST_LEVELS + 1);
-		std::vector<uint32_t *> hp((size_t)SMALL_HIST_LEVELS + 1);
-		for (int k = 0; k <= SMALL_HIST_LEVELS; k++) {
-			PGQ_TRY(c->bfs_hist[(size_t)k].reserve(bm));
-			hp[(size_t)k] = c->bfs_hist[(size_t)k].as<uint32_t>();
-		}
-		PGQ_TRY(c->bfs_hist_tab.reserve(hp.size() * sizeof(uint32_t *)));
-		PGQ_CUDA(cudaMemcpyAsync(c->bfs_hist_tab.p, hp.data(), hp.size() * sizeof(uint32_t *), cudaMemcpyHostToDevice,
-		                         st));
-		PGQ_CUDA(cudaStreamSynchronize(st)); // hp is a host temporary
+		const int rc = hist_reserve(c, (size_t)SMALL_HIST_LEVELS + 1, bm);
+		if (rc == PGQ_HIST_OVER) return PGQ_SMALL_OVERFLOW;
+		PGQ_TRY(rc);
 		a.hist = c->bfs_hist_tab.as<uint32_t *const>();
 		a.max_levels = SMALL_HIST_LEVELS;
 	}
@@ -360,7 +439,7 @@ int run_batch_small(Ctx *c, Csr *g, const BatchBufs &b, int W, bool keep_hist, c
 	default: fn = (const void *)msbfs_small_kernel<512>; break;
 	}
 	if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
-	PGQ_CUDA(cudaMemsetAsync(&b.ctrl->small_bar, 0, sizeof(BfsCtrl) - offsetof(BfsCtrl, small_bar), st));
+	PGQ_CUDA(cudaMemsetAsync(&b.ctrl->small_bar, 0, offsetof(BfsCtrl, k_listed) - offsetof(BfsCtrl, small_bar), st));
 	PGQ_CUDA(cudaLaunchCooperativeKernel(fn, dim3((unsigned)grid), dim3(SMALL_THREADS), args, 0, st));
 	count_launch(c);
 	if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
@@ -391,9 +470,127 @@ int run_batch_small(Ctx *c, Csr *g, const BatchBufs &b, int W, bool keep_hist, c
 	return PGQ_OK;
 }
 
+// ---- the level loop as a CUDA graph ---------------------------------------------------------------------
+// loop_begin -> WHILE(h_while) { SWITCH(h_switch) { body(mode 1..4) } -> check }.  The bodies are recorded
+// by stream capture of launch_body; the conditional handles are set by the check kernel
+// (cudaGraphSetConditional).  One graph per worker and (CSR, W, keep_hist): it embeds the worker's buffers.
+int loop_graph_build(Ctx *c, Csr *g, const BatchBufs &b, int W, bool keep_hist, LoopGraph *lg, uint32_t *nk_out) {
+	lg->destroy();
+	cudaGraph_t G = nullptr;
+	PGQ_CUDA(cudaGraphCreate(&G, 0));
+	lg->graph = G;
+	cudaGraphConditionalHandle hw, hs;
+	PGQ_CUDA(cudaGraphConditionalHandleCreate(&hw, G, 0, 0));
+	PGQ_CUDA(cudaGraphConditionalHandleCreate(&hs, G, 0, 0));
+	BfsCtrl *ctrl = b.ctrl;
+	cudaGraphNode_t n_begin, n_while, n_switch, n_check;
+	{
+		void *args[] = {&ctrl, &hw, &hs};
+		cudaKernelNodeParams kp{};
+		kp.func = (void *)loop_begin_kernel;
+		kp.gridDim = dim3(1);
+		kp.blockDim = dim3(1);
+		kp.kernelParams = args;
+		PGQ_CUDA(cudaGraphAddKernelNode(&n_begin, G, nullptr, 0, &kp));
+	}
+	cudaGraphNodeParams wp{};
+	wp.type = cudaGraphNodeTypeConditional;
+	wp.conditional.handle = hw;
+	wp.conditional.type = cudaGraphCondTypeWhile;
+	wp.conditional.size = 1;
+	PGQ_CUDA(cudaGraphAddNode(&n_while, G, &n_begin, 1, &wp));
+	cudaGraph_t body = wp.conditional.phGraph_out[0];
+	cudaGraphNodeParams sp{};
+	sp.type = cudaGraphNodeTypeConditional;
+	sp.conditional.handle = hs;
+	sp.conditional.type = cudaGraphCondTypeSwitch;
+	sp.conditional.size = MODE_COUNT - 1;
+	PGQ_CUDA(cudaGraphAddNode(&n_switch, body, nullptr, 0, &sp));
+	for (uint32_t m = MODE_PUSH; m < MODE_COUNT; m++) {
+		cudaGraph_t bg = sp.conditional.phGraph_out[m - 1];
+		PGQ_CUDA(cudaStreamBeginCaptureToGraph(c->stream, bg, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+		uint32_t nk = 0;
+		const int rc = launch_body_w(c, g, b, W, false, m, keep_hist, c->stream, &nk);
+		cudaGraph_t got = nullptr;
+		const cudaError_t e = cudaStreamEndCapture(c->stream, &got);
+		if (rc != PGQ_OK) return rc;
+		PGQ_CUDA(e);
+		nk_out[m] = nk;
+	}
+	nk_out[MODE_STOP] = 0;
+	{
+		const uint32_t *seen = b.seen;
+		uint32_t *alive = b.alive_slots;
+		int use = 1;
+		int w = W;
+		void *args[] = {&seen, &w, &ctrl, &alive, &use, &hw, &hs};
+		cudaKernelNodeParams kp{};
+		kp.func = (void *)bfs_check_kernel;
+		kp.gridDim = dim3(1);
+		kp.blockDim = dim3((unsigned)W);
+		kp.kernelParams = args;
+		PGQ_CUDA(cudaGraphAddKernelNode(&n_check, body, &n_switch, 1, &kp));
+	}
+	PGQ_CUDA(cudaGraphInstantiate(&lg->exec, G, 0));
+	lg->g = g;
+	lg->gen = g->gen;
+	lg->W = W;
+	lg->keep_hist = keep_hist;
+	lg->seen = b.seen;
+	lg->ctrl = b.ctrl;
+	lg->done = b.done;
+	lg->seg_small = c->opt.seg_small * 16 + c->opt.dense_store * 4 + c->opt.done_bitmap;
+	return PGQ_OK;
+}
+
+// the worker's loop graph for this batch shape (built on first use, reused by every later batch)
+int loop_graph_get(Ctx *c, Csr *g, const BatchBufs &b, int W, bool keep_hist, LoopGraph **out, uint32_t *nk) {
+	LoopGraph *lg = &c->loop_graph[keep_hist ? 1 : 0];
+	const bool hit = lg->exec && lg->g == g && lg->gen == g->gen && lg->W == W && lg->keep_hist == keep_hist &&
+	                 lg->seen == b.seen && lg->ctrl == b.ctrl && lg->done == b.done &&
+	                 lg->seg_small == c->opt.seg_small * 16 + c->opt.dense_store * 4 + c->opt.done_bitmap;
+	if (!hit) {
+		uint32_t fresh[MODE_COUNT] = {0, 0, 0, 0, 0};
+		static std::mutex build_mu; // graph construction + capture: one worker thread at a time
+		std::lock_guard<std::mutex> lk(build_mu);
+		const int rc = loop_graph_build(c, g, b, W, keep_hist, lg, fresh);
+		if (rc != PGQ_OK) {
+			lg->destroy();
+			return rc;
+		}
+		for (int i = 0; i < (int)MODE_COUNT; i++) c->loop_nk[keep_hist ? 1 : 0][i] = fresh[i];
+	}
+	for (int i = 0; i < (int)MODE_COUNT; i++) nk[i] = c->loop_nk[keep_hist ? 1 : 0][i];
+	*out = lg;
+	return PGQ_OK;
+}
+
+// persisting-L2 window on `seen` for the worker's stream (north-star item; measured)
+void apply_l2_window(Ctx *c, const BatchBufs &b, size_t bm) {
+	const int want = c->opt.l2_persist ? 1 : 0;
+	if (c->l2_window_on == want && (!want || c->l2_window_ptr == (const void *)b.seen)) return;
+	cudaStreamAttrValue v{};
+	if (want) {
+		int maxw = 0;
+		cudaDeviceGetAttribute(&maxw, cudaDevAttrMaxAccessPolicyWindowSize, c->device);
+		v.accessPolicyWindow.base_ptr = b.seen;
+		v.accessPolicyWindow.num_bytes = bm < (size_t)maxw ? bm : (size_t)maxw;
+		v.accessPolicyWindow.hitRatio = 1.0f;
+		v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+		v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+	} else {
+		v.accessPolicyWindow.num_bytes = 0;
+	}
+	if (cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &v) != cudaSuccess)
+		(void)cudaGetLastError();
+	c->l2_window_on = want;
+	c->l2_window_ptr = b.seen;
+}
+
 // One batch of W lanes.  d_lane_src/dst/found point at this batch's W slots.
 // keep_hist (shortestpath): level k's frontier stays in c->bfs_hist[k] instead of a ping-pong pair, so
-// the path kernel can apply the parent rule afterwards; *out_levels = levels run.
+// the path kernel can apply the parent rule afterwards; the batch is then complete when this returns and
+// *out_levels = levels run.  Otherwise (device loop) the batch is only ENQUEUED: nothing is waited for.
 int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, const uint32_t *d_lane_src,
               const uint32_t *d_lane_dst, int32_t *d_found, int *out_levels = nullptr) {
 	cudaStream_t st = c->stream;
@@ -403,206 +600,566 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 		const int rc = run_batch_small(c, g, b, W, keep_hist, d_lane_src, d_lane_dst, d_found, out_levels);
 		if (rc != PGQ_SMALL_OVERFLOW) return rc;
 	}
+	const bool host_loop = !c->opt.loop || c->opt.stats || c->opt.timing || c->opt.trace || c->loop_unsupported;
+	apply_l2_window(c, b, bm);
+	size_t hist_cap = 0;
 	if (keep_hist) {
-		if (bm) PGQ_CUDA(cudaMemsetAsync(b.seen, 0, bm, st));
-		PGQ_TRY(hist_level(c, 0, bm, &b.visit[0]));
-		b.visit[1] = nullptr; // set per level
+		hist_cap = c->bfs_hist.size() >= 16 ? c->bfs_hist.size() : 16;
+		int rc = hist_reserve(c, hist_cap, bm);
+		if (rc == PGQ_HIST_OVER && hist_cap > 2) {
+			hist_cap = 2;
+			rc = hist_reserve(c, hist_cap, bm);
+		}
+		if (rc != PGQ_OK) return rc; // PGQ_HIST_OVER: the caller narrows the lane words
+		if (bm) {
+			PGQ_CUDA(cudaMemsetAsync(b.seen, 0, bm, st));
+			PGQ_CUDA(cudaMemsetAsync(c->bfs_hist[0].p, 0, bm, st));
+		}
 		c->bfs_dirty.valid = false;
 	} else if (bm) {
 		PGQ_CUDA(cudaMemsetAsync(b.seen, 0, bm, st));
-		// The frontier buffers must start all-zero (a top-down level ORs into them).  After a clean
-		// batch on the same buffers their only non-zero words are the ones the last two frontier
-		// bitmaps name: scrub those instead of streaming 2 x V x W/8 bytes of zeros.
+		// The frontier buffers must start all-zero.  After a clean batch on the same buffers their only
+		// non-zero words are the ones its last two frontier bitmaps name (ctrl->L still describes them):
+		// scrub those instead of streaming 2 x V x W/8 bytes of zeros.
 		BfsDirty &d = c->bfs_dirty;
 		if (d.valid && d.W == W && d.V == g->V && d.visit0 == b.visit[0] && d.fbit0 == b.fbit[0]) {
-			PGQ_TRY(launch_clear_w(c, b, W, d.map[0], 0));
-			PGQ_TRY(launch_clear_w(c, b, W, d.map[1], 1));
+			PGQ_TRY(launch_scrub_w(c, b, W, 0));
+			PGQ_TRY(launch_scrub_w(c, b, W, 1));
 		} else {
 			PGQ_CUDA(cudaMemsetAsync(b.visit[0], 0, bm, st));
 			PGQ_CUDA(cudaMemsetAsync(b.visit[1], 0, bm, st));
 		}
-		d.valid = false; // until this batch completes
+		d.valid = false; // until this batch is enqueued completely
 	}
 	PGQ_CUDA(cudaMemsetAsync(b.fbit[0], 0, 3 * b.fbit_bytes, st)); // all three frontier bitmaps
-	bfs_init_kernel<<<1, W, 0, st>>>(d_lane_src, W, b.visit[0], d_found, b.ctrl, g->d_off.as<int64_t>(), b.queue[0],
-	                                 b.fbit[0]);
-	count_launch(c);
-	BfsCtrl h;
-	PGQ_TRY(read_ctrl(c, b, &h));
-	c->stats.batches++;
-	const uint64_t levels_at_start = c->stats.levels;
-	uint32_t active = h.n_active;
-	int cur = 0, q = 0;
-	unsigned long long cum_verts = h.out_verts; // frontier vertices of all levels so far
-	int fb[3] = {0, 1, 2}; // bitmap of visit[cur] / being built for visit[cur^1] / of what visit[cur^1] holds
-	bool have_queue = true; // queue[q] describes visit[cur] and visit[cur^1] is all-zero
-	for (int iter = 1; active && iter <= (int)c->opt.level_cap; iter++) {
-		// direction switch on frontier density: top-down while the frontier's out-edges are few
-		if (keep_hist) { // fresh zeroed buffer for this level's output; the input stays where it is
-			b.visit[cur] = c->bfs_hist[(size_t)iter - 1].as<uint32_t>();
-			PGQ_TRY(hist_level(c, (size_t)iter, bm, &b.visit[cur ^ 1]));
+	if (b.done) PGQ_CUDA(cudaMemsetAsync(b.done, 0, b.fbit_bytes, st));
+	LoopInit li{};
+	li.visit[0] = b.visit[0];
+	li.visit[1] = b.visit[1];
+	for (int i = 0; i < 3; i++) li.fbit[i] = b.fbit[i];
+	li.queue[0] = b.queue[0];
+	li.queue[1] = b.queue[1];
+	li.hist = keep_hist ? c->bfs_hist_tab.as<uint32_t *const>() : nullptr;
+	li.hist_cap = (uint32_t)hist_cap;
+	li.level_cap = (uint32_t)(c->opt.level_cap > 0x7fffffff ? 0x7fffffff : c->opt.level_cap);
+	li.direction = (uint32_t)c->opt.direction;
+	li.push_beta = (uint32_t)c->opt.push_beta;
+	li.push_vbeta = (uint32_t)c->opt.push_vbeta;
+	li.filter_gamma = (uint32_t)c->opt.filter_gamma;
+	li.E = (unsigned long long)g->E;
+	li.V = (unsigned long long)g->V;
+	li.n_listed = (unsigned long long)g->n_tiny + g->n_small + g->n_med + g->n_mid + g->n_hub;
+	li.lane_dst = d_lane_dst;
+	LoopGraph *lg = nullptr;
+	if (!host_loop) {
+		const int rc = loop_graph_get(c, g, b, W, keep_hist, &lg, li.nk);
+		if (rc != PGQ_OK) {
+			// a driver that refuses conditional nodes: remember it and fall through to the host loop
+			c->loop_unsupported = true;
+			(void)cudaGetLastError();
+			fprintf(stderr, "[pgq_b200] level-loop graph unavailable (%s): falling back to the host-driven loop\n",
+			        last_error_str());
+			lg = nullptr;
 		}
-		const bool push = c->opt.direction == 0 &&
-		                  (unsigned long long)h.out_edges * (unsigned long long)c->opt.push_beta <=
-		                      (unsigned long long)g->E &&
-		                  (unsigned long long)h.out_verts * (unsigned long long)c->opt.push_vbeta <=
-		                      (unsigned long long)g->V + (unsigned long long)c->opt.push_vbeta * 1024ull;
-		if (c->opt.stats) launch_count(c, g, b, W, cur);
-		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
-		uint64_t before = c->stats.kernel_launches;
-		if (push) {
-			if (!have_queue) PGQ_TRY(launch_compact(c, g, b, fb, q));
-			PGQ_TRY(launch_push_w(c, g, b, W, cur, fb, q));
-			have_queue = true;
-			q ^= 1;
-			c->stats.push_levels++;
-		} else {
-			// the bitmap test is dead weight once the frontier holds most of the edges
-			const bool filter = (unsigned long long)h.out_edges * (unsigned long long)c->opt.filter_gamma <=
-			                    (unsigned long long)g->E;
-			// "early": fewer vertex discoveries so far than vertices that can be discovered at all
-			const bool early = cum_verts < (unsigned long long)g->n_tiny + g->n_small + g->n_med + g->n_mid + g->n_hub;
-			PGQ_TRY(launch_level_w(c, g, b, W, cur, fb, iter, filter, early));
-			have_queue = false;
-		}
-		if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
-		bfs_check_kernel<<<1, W, 0, st>>>(b.seen, d_lane_dst, W, d_found, b.ctrl, iter, b.alive_slots);
-		count_launch(c);
-		PGQ_TRY(read_ctrl(c, b, &h));
-		c->stats.levels++;
-		if (c->opt.timing) {
-			float ms = 0;
-			PGQ_CUDA(cudaEventElapsedTime(&ms, c->ev_a, c->ev_b));
-			c->stats.level_kernel_ms += ms;
-			c->stats.level_kernel_launches += c->stats.kernel_launches - 1 - before;
-			if (c->opt.trace)
-				fprintf(stderr, "[pgq] iter %d %s %.3f ms  next: verts %u edges %llu items %u  active %u change %u\n",
-				        iter, push ? "push" : "pull", ms, h.out_verts, (unsigned long long)h.out_edges, h.out_items,
-				        h.n_active, h.change_out);
-		}
-		// the level's output becomes the current frontier
-		cur ^= 1;
-		{
-			const int t = fb[0];
-			fb[0] = fb[1];
-			fb[1] = fb[2];
-			fb[2] = t;
-		}
-		if (!h.change_out) break;
-		active = h.n_active;
-		cum_verts += h.out_verts;
 	}
-	if (out_levels) *out_levels = (int)(c->stats.levels - levels_at_start);
-	if (bm && !keep_hist) { // what the frontier buffers hold now, for the next batch's scrub
+	bfs_init_kernel<<<1, W, 0, st>>>(d_lane_src, W, d_found, b.ctrl, g->d_off.as<int64_t>(), li);
+	count_launch(c);
+	c->stats.batches++;
+	BfsCtrl h;
+	if (lg) {
+		// ---- device loop: one graph launch per batch, re-launched only when the level history ran out ----
+		for (;;) {
+			PGQ_CUDA(cudaGraphLaunch(lg->exec, st));
+			if (!keep_hist) break;
+			PGQ_TRY(read_ctrl(c, b, &h)); // shortestpath sizes its output on the host anyway
+			if (h.L.stop_reason != 2) break;
+			const size_t want = hist_cap * 2;
+			int rc = hist_reserve(c, want, bm);
+			if (rc == PGQ_HIST_OVER) rc = hist_reserve(c, hist_cap + 1, bm) == PGQ_OK ? PGQ_OK : PGQ_HIST_OVER;
+			if (rc != PGQ_OK) return rc;
+			hist_cap = c->bfs_hist.size();
+			loop_resume_kernel<<<1, 1, 0, st>>>(b.ctrl, c->bfs_hist_tab.as<uint32_t *const>(), (uint32_t)hist_cap);
+			count_launch(c);
+		}
+		if (keep_hist) {
+			fold_totals(c, h);
+			if (out_levels) *out_levels = (int)h.L.levels_run;
+		}
+	} else {
+		// ---- host loop: the mode the device picked is read back after every level ----
+		PGQ_TRY(read_ctrl(c, b, &h));
+		while (h.L.mode != MODE_STOP || h.L.stop_reason == 2) {
+			if (h.L.stop_reason == 2) { // level history full
+				int rc = hist_reserve(c, hist_cap * 2, bm);
+				if (rc == PGQ_HIST_OVER) rc = hist_reserve(c, hist_cap + 1, bm) == PGQ_OK ? PGQ_OK : PGQ_HIST_OVER;
+				if (rc != PGQ_OK) return rc;
+				hist_cap = c->bfs_hist.size();
+				loop_resume_kernel<<<1, 1, 0, st>>>(b.ctrl, c->bfs_hist_tab.as<uint32_t *const>(), (uint32_t)hist_cap);
+				count_launch(c);
+				PGQ_TRY(read_ctrl(c, b, &h));
+				continue;
+			}
+			if (c->opt.stats) launch_count(c, g, b, W, h.L.cur_visit);
+			if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
+			uint32_t nk = 0;
+			const uint32_t mode = h.L.mode;
+			PGQ_TRY(launch_body_w(c, g, b, W, c->opt.stats != 0, mode, keep_hist, st, &nk));
+			count_launch(c, nk);
+			if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
+			launch_check(b, W, st, 0, 0, 0);
+			const uint32_t iter = h.L.iter;
+			PGQ_TRY(read_ctrl(c, b, &h));
+			if (c->opt.timing) {
+				float ms = 0;
+				PGQ_CUDA(cudaEventElapsedTime(&ms, c->ev_a, c->ev_b));
+				c->stats.level_kernel_ms += ms;
+				c->stats.level_kernel_launches += nk;
+				if (c->opt.trace)
+					fprintf(stderr, "[pgq] iter %u %s %.3f ms  next: verts %u edges %llu items %u  active %u change %u\n",
+					        iter, mode == MODE_PUSH ? "push" : mode == MODE_PULL ? "pull" : mode == MODE_PULL_F_EARLY ? "pull-fe" : "pull-fl",
+					        ms, h.out_verts, (unsigned long long)h.out_edges, h.out_items, h.n_active, h.change_out);
+			}
+		}
+		fold_totals(c, h);
+		if (out_levels) *out_levels = (int)h.L.levels_run;
+		if (c->opt.stats) {
+			// counters accumulate in the control block over the batch (reset by the init kernel)
+			c->stats.edges_lane += h.edges_lane;
+			c->stats.edges_unique += h.edges_unique;
+			// SURVEY.md §8(d), the REFERENCE algorithm's bytes: 4*V*(W/8) per level + E_act*(4 + W/8) + 8*V_act
+			c->stats.algo_bytes += h.edges_unique * (uint64_t)(4 + W / 8) + 8ull * h.verts_active +
+			                       (uint64_t)h.L.levels_run * 4ull * (uint64_t)g->V * (uint64_t)(W / 8);
+			// what THIS implementation touched
+			const uint64_t wb = (uint64_t)(W / 8);
+			c->stats.k_listed += h.k_listed;
+			c->stats.k_open += h.k_open;
+			c->stats.k_new += h.k_new;
+			c->stats.k_scanned += h.k_scanned;
+			c->stats.k_gathered += h.k_gathered;
+			c->stats.kp_items += h.kp_items;
+			c->stats.kp_edges += h.kp_edges;
+			c->stats.kp_seen += h.kp_seen;
+			c->stats.kp_next += h.kp_next;
+			c->stats.model_bytes += model_bytes_of(h, g, W, b.fbit_bytes, keep_hist);
+			(void)wb;
+		}
+	}
+	if (bm && !keep_hist) { // what the frontier buffers hold once this batch is through, for the next batch's scrub
 		BfsDirty &d = c->bfs_dirty;
 		d.valid = true;
 		d.W = W;
 		d.V = g->V;
 		d.visit0 = b.visit[0];
 		d.fbit0 = b.fbit[0];
-		d.map[cur] = fb[0];
-		d.map[cur ^ 1] = fb[2];
-	}
-	if (c->opt.stats) {
-		// counters accumulate in the control block over the batch (reset by the init kernel)
-		PGQ_TRY(read_ctrl(c, b, &h));
-		c->stats.edges_lane += h.edges_lane;
-		c->stats.edges_unique += h.edges_unique;
-		// 4*V*(W/8) per level + E_act*(4 + W/8) + 8*V_act
-		c->stats.algo_bytes += h.edges_unique * (uint64_t)(4 + W / 8) + 8ull * h.verts_active;
 	}
 	PGQ_CUDA(cudaGetLastError());
 	return PGQ_OK;
 }
 
-// All batches of one call (lengths / reachability).  A batch on the general path meets the host once
-// per level and leaves the GPU idle across launch gaps, memsets and kernel tails (about 12 % of a
-// batch on R-MAT s24, most of it on mid-sized graphs), and batches are independent: so up to
-// `streams` of them are in flight at once, each on a helper context with its own stream, control
-// block and frontier buffers, driven by its own host thread.  The CSR is shared read-only.
-using BatchFn = std::function<int(Ctx *, const BatchBufs &, int64_t)>; // (worker context, its buffers, batch index)
+// ---- workers: one (device, stream, buffer set) each ----------------------------------------------------
+struct Worker {
+	Ctx *w = nullptr;
+	Csr *g = nullptr; // the CSR (replica) on the worker's device
+	BatchBufs b{};
+	uint32_t *d_src = nullptr, *d_dst = nullptr; // this device's copy of the call's lane tables
+	int32_t *d_found = nullptr;
+};
 
-int run_batches(Ctx *c, Csr *g, const BatchBufs &b0, int W, int64_t nbatch, bool keep_hist, const BatchFn &fn) {
-	int nw = (int)std::min<int64_t>(c->opt.streams, nbatch);
-	if (nw < 2 || c->opt.timing || c->opt.stats || c->opt.trace || g->is_part || small_eligible(c, g, W, keep_hist)) {
-		for (int64_t bi = 0; bi < nbatch; bi++) PGQ_TRY(fn(c, b0, bi));
+// Read-only copy of the query-side arrays of g on device `dev` (multi-GPU contexts), made on first use.
+#define PGQ_REPL(field)                                                                                   \
+	do {                                                                                                  \
+		if (g->field.p && g->field.cap) {                                                                 \
+			PGQ_TRY(r->field.reserve(g->field.cap));                                                      \
+			PGQ_CUDA(cudaMemcpyPeerAsync(r->field.p, dev, g->field.p, c->device, g->field.cap, c->stream)); \
+		}                                                                                                 \
+	} while (0)
+
+int csr_replica(Ctx *c, Csr *g, int dev, Csr **out) {
+	auto it = g->replicas.find(dev);
+	if (it != g->replicas.end() && it->second->gen == g->gen) {
+		*out = it->second;
 		return PGQ_OK;
 	}
-	while ((int)c->helpers.size() < nw - 1) {
-		Ctx *h = new Ctx();
-		h->device = c->device;
-		h->sm_count = c->sm_count;
-		const int rc = ctx_init_resources(h);
+	if (it != g->replicas.end()) {
+		PGQ_CUDA(cudaSetDevice(dev));
+		it->second->free_all();
+		delete it->second;
+		g->replicas.erase(it);
+	}
+	PGQ_CUDA(cudaSetDevice(c->device));
+	int can = 0;
+	cudaDeviceCanAccessPeer(&can, c->device, dev);
+	if (can && cudaDeviceEnablePeerAccess(dev, 0) != cudaSuccess) (void)cudaGetLastError(); // already enabled
+	PGQ_CUDA(cudaSetDevice(dev));
+	cudaDeviceCanAccessPeer(&can, dev, c->device);
+	if (can && cudaDeviceEnablePeerAccess(c->device, 0) != cudaSuccess) (void)cudaGetLastError();
+	Csr *r = new Csr();
+	r->device = dev;
+	r->V = g->V;
+	r->E = g->E;
+	r->state = g->state;
+	r->have_eid = g->have_eid;
+	r->keep_rows = g->keep_rows;
+	r->prepared = g->prepared;
+	r->n_tiny = g->n_tiny; r->n_small = g->n_small; r->n_med = g->n_med; r->n_mid = g->n_mid; r->n_hub = g->n_hub;
+	r->n_hubchunks = g->n_hubchunks;
+	r->bins_tiny_max = g->bins_tiny_max; r->bins_small_max = g->bins_small_max; r->bins_med_max = g->bins_med_max;
+	r->bins_hub_min = g->bins_hub_min; r->eff_med_max = g->eff_med_max;
+	r->gen = g->gen;
+	g->replicas[dev] = r;
+	PGQ_REPL(d_off);
+	PGQ_REPL(d_tgt);
+	PGQ_REPL(d_row);
+	PGQ_REPL(d_eid);
+	PGQ_REPL(d_ioff);
+	PGQ_REPL(d_isrc);
+	PGQ_REPL(d_ipos);
+	PGQ_REPL(d_tiny);
+	PGQ_REPL(d_small);
+	PGQ_REPL(d_med);
+	PGQ_REPL(d_mid);
+	PGQ_REPL(d_hub);
+	PGQ_REPL(d_hubchunks);
+	PGQ_CUDA(cudaSetDevice(c->device));
+	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	*out = r;
+	return PGQ_OK;
+}
+#undef PGQ_REPL
+
+// helper context number `idx` of device `dev` (created on first use; lives until pgq_shutdown)
+int get_helper(Ctx *c, int dev, int idx, Ctx **out) {
+	int seen = 0;
+	for (Ctx *h : c->helpers)
+		if (h->device == dev && seen++ == idx) {
+			*out = h;
+			return PGQ_OK;
+		}
+	PGQ_CUDA(cudaSetDevice(dev));
+	Ctx *h = new Ctx();
+	h->device = dev;
+	h->sm_count = c->sm_count;
+	const int rc = ctx_init_resources(h);
+	if (rc != PGQ_OK) {
+		ctx_release_resources(h);
+		delete h;
+		cudaSetDevice(c->device);
+		return rc;
+	}
+	c->helpers.push_back(h);
+	*out = h;
+	return PGQ_OK;
+}
+
+// The workers of one call: `streams` per device, over as many devices of the context as the call has
+// batches to keep busy (a 1024-row call = 2 batches stays on the primary).  Lane tables (already on the
+// primary, written on c->stream) are copied to every other device; all worker streams wait for them.
+int make_workers(Ctx *c, Csr *g, const BatchBufs &b0, int W, int64_t nbatch, bool keep_hist, uint32_t *d_src,
+                 uint32_t *d_dst, int32_t *d_found, int64_t nslots, std::vector<Worker> *out) {
+	out->clear();
+	Worker w0;
+	w0.w = c;
+	w0.g = g;
+	w0.b = b0;
+	w0.d_src = d_src;
+	w0.d_dst = d_dst;
+	w0.d_found = d_found;
+	out->push_back(w0);
+	const bool single = c->opt.timing || c->opt.stats || c->opt.trace || g->is_part || small_eligible(c, g, W, keep_hist);
+	if (single || nbatch < 2) return PGQ_OK;
+	int ndev = (int)c->devices.size();
+	if (ndev < 1) ndev = 1;
+	if ((int64_t)ndev > nbatch / 2) ndev = (int)(nbatch / 2 > 0 ? nbatch / 2 : 1);
+	const int streams = (int)c->opt.streams;
+	int64_t want = (int64_t)ndev * streams;
+	if (want > nbatch) want = nbatch;
+	PGQ_CUDA(cudaEventRecord(c->ev_fork, c->stream)); // the lane tables are in place after this point
+	// stream-major order: worker k sits on device k % ndev, so consecutive batches go to different GPUs
+	for (int64_t k = 1; k < want; k++) {
+		const int di = (int)(k % ndev), si = (int)(k / ndev);
+		const int dev = ndev > 1 ? c->devices[(size_t)di] : c->device;
+		Ctx *h = nullptr;
+		// the primary's own stream is its worker 0
+		int rc = get_helper(c, dev, dev == c->device ? si - 1 : si, &h);
+		if (rc != PGQ_OK) return rc;
+		Worker wk;
+		wk.w = h;
+		wk.g = g;
+		h->opt = c->opt;
+		PGQ_CUDA(cudaSetDevice(dev));
+		if (dev != c->device) {
+			rc = csr_replica(c, g, dev, &wk.g);
+			if (rc != PGQ_OK) {
+				cudaSetDevice(c->device);
+				return rc;
+			}
+			PGQ_CUDA(cudaSetDevice(dev));
+		}
+		rc = alloc_bufs(h, wk.g, W, &wk.b);
+		if (rc == PGQ_ERR_OOM) { // no room for another set of bitmaps: the other workers take every batch
+			(void)cudaGetLastError();
+			continue;
+		}
 		if (rc != PGQ_OK) {
-			ctx_release_resources(h);
-			delete h;
+			cudaSetDevice(c->device);
 			return rc;
 		}
-		c->helpers.push_back(h);
-	}
-	PGQ_CUDA(cudaEventRecord(c->ev_fork, c->stream)); // the lane tables are in place after this point
-	struct Res {
-		int rc = PGQ_OK;
-		std::string err;
-	};
-	std::vector<Res> res((size_t)nw);
-	std::atomic<int64_t> next_batch{0};
-	std::atomic<int> failed{0};
-	auto drain = [&](Ctx *w, const BatchBufs &bw, Res &r) {
-		while (!failed.load(std::memory_order_relaxed)) {
-			const int64_t bi = next_batch.fetch_add(1);
-			if (bi >= nbatch) break;
-			const int rc = fn(w, bw, bi);
-			if (rc != PGQ_OK) {
-				r.rc = rc;
-				r.err = last_error_str();
-				failed.store(1);
-				break;
+		if (dev == c->device) {
+			wk.d_src = d_src;
+			wk.d_dst = d_dst;
+			wk.d_found = d_found;
+			PGQ_CUDA(cudaStreamWaitEvent(h->stream, c->ev_fork, 0));
+		} else {
+			// the first worker of a device holds the device's lane tables; later ones share them
+			Worker *first = nullptr;
+			for (Worker &o : *out)
+				if (o.w->device == dev) {
+					first = &o;
+					break;
+				}
+			if (first) {
+				wk.d_src = first->d_src;
+				wk.d_dst = first->d_dst;
+				wk.d_found = first->d_found;
+				PGQ_CUDA(cudaStreamWaitEvent(h->stream, first->w->ev_fork, 0));
+			} else {
+				PGQ_TRY(h->bfs_lane.reserve((size_t)nslots * 12 + 64));
+				wk.d_src = h->bfs_lane.as<uint32_t>();
+				wk.d_dst = wk.d_src + nslots;
+				wk.d_found = reinterpret_cast<int32_t *>(wk.d_dst + nslots);
+				PGQ_CUDA(cudaStreamWaitEvent(h->stream, c->ev_fork, 0));
+				PGQ_CUDA(cudaMemcpyPeerAsync(wk.d_src, dev, d_src, c->device, (size_t)nslots * 4, h->stream));
+				PGQ_CUDA(cudaMemcpyPeerAsync(wk.d_dst, dev, d_dst, c->device, (size_t)nslots * 4, h->stream));
+				PGQ_CUDA(cudaEventRecord(h->ev_fork, h->stream));
 			}
 		}
-	};
-	std::vector<std::thread> threads;
-	for (int i = 1; i < nw; i++) {
-		threads.emplace_back([&, i] {
-			Ctx *w = c->helpers[(size_t)i - 1];
-			Res &r = res[(size_t)i];
-			auto fail = [&](int rc) {
-				r.rc = rc;
-				r.err = last_error_str();
-				failed.store(1);
-			};
-			if (cudaSetDevice(w->device) != cudaSuccess || cudaStreamWaitEvent(w->stream, c->ev_fork, 0) != cudaSuccess) {
-				set_error("helper stream setup failed");
-				return fail(PGQ_ERR_CUDA);
-			}
-			w->opt = c->opt;
-			BatchBufs bw{};
-			const int rc = alloc_bufs(w, g, W, &bw);
-			if (rc == PGQ_ERR_OOM) return; // no room for a second set of bitmaps: the other workers take every batch
-			if (rc != PGQ_OK) return fail(rc);
-			drain(w, bw, r);
-			if (cudaStreamSynchronize(w->stream) != cudaSuccess) {
-				set_error("helper stream failed");
-				fail(PGQ_ERR_CUDA);
-			}
-		});
+		out->push_back(wk);
 	}
-	drain(c, b0, res[0]);
-	for (std::thread &t : threads) t.join();
-	for (Ctx *h : c->helpers) {
+	PGQ_CUDA(cudaSetDevice(c->device));
+	return PGQ_OK;
+}
+
+using BatchFn = std::function<int(Worker &, int64_t)>; // (worker, batch index)
+
+// All batches of one call over the workers.  With the device-side level loop a lengths batch is a handful
+// of asynchronous launches, so ONE host thread deals them round-robin and nothing waits until the end.
+// Batches that meet the host (shortestpath, host loop) get a thread per worker and are handed out dynamically.
+int run_batches(Ctx *c, std::vector<Worker> &ws, int64_t nbatch, bool threaded, const BatchFn &fn) {
+	const int nw = (int)ws.size();
+	int rc_all = PGQ_OK;
+	std::string err_all;
+	if (nw == 1 || !threaded) {
+		for (int64_t bi = 0; bi < nbatch && rc_all == PGQ_OK; bi++) {
+			Worker &wk = ws[(size_t)(bi % nw)];
+			if (nw > 1 && cudaSetDevice(wk.w->device) != cudaSuccess) {
+				set_error("cudaSetDevice(%d) failed", wk.w->device);
+				rc_all = PGQ_ERR_CUDA;
+				break;
+			}
+			rc_all = fn(wk, bi);
+		}
+		for (int i = 1; i < nw; i++) {
+			cudaSetDevice(ws[(size_t)i].w->device);
+			if (cudaStreamSynchronize(ws[(size_t)i].w->stream) != cudaSuccess && rc_all == PGQ_OK) {
+				set_error("worker stream failed: %s", cudaGetErrorString(cudaGetLastError()));
+				rc_all = PGQ_ERR_CUDA;
+			}
+		}
+		cudaSetDevice(c->device);
+		if (rc_all != PGQ_OK) err_all = last_error_str();
+	} else {
+		struct Res {
+			int rc = PGQ_OK;
+			std::string err;
+		};
+		std::vector<Res> res((size_t)nw);
+		std::atomic<int64_t> next_batch{0};
+		std::atomic<int> failed{0};
+		auto drain = [&](Worker &wk, Res &r) {
+			while (!failed.load(std::memory_order_relaxed)) {
+				const int64_t bi = next_batch.fetch_add(1);
+				if (bi >= nbatch) break;
+				const int rc = fn(wk, bi);
+				if (rc != PGQ_OK) {
+					r.rc = rc;
+					r.err = last_error_str();
+					failed.store(1);
+					break;
+				}
+			}
+		};
+		std::vector<std::thread> threads;
+		for (int i = 1; i < nw; i++) {
+			threads.emplace_back([&, i] {
+				Worker &wk = ws[(size_t)i];
+				Res &r = res[(size_t)i];
+				if (cudaSetDevice(wk.w->device) != cudaSuccess) {
+					set_error("helper thread: cudaSetDevice(%d) failed", wk.w->device);
+					r.rc = PGQ_ERR_CUDA;
+					r.err = last_error_str();
+					failed.store(1);
+					return;
+				}
+				drain(wk, r);
+				if (cudaStreamSynchronize(wk.w->stream) != cudaSuccess && r.rc == PGQ_OK) {
+					set_error("helper stream failed");
+					r.rc = PGQ_ERR_CUDA;
+					r.err = last_error_str();
+					failed.store(1);
+				}
+			});
+		}
+		drain(ws[0], res[0]);
+		for (std::thread &t : threads) t.join();
+		for (const Res &r : res)
+			if (r.rc != PGQ_OK && rc_all == PGQ_OK) {
+				rc_all = r.rc;
+				err_all = r.err;
+			}
+	}
+	// the device-side running totals of every worker, then the helpers' host-side counters
+	for (int i = 0; i < nw && rc_all == PGQ_OK; i++) {
+		Worker &wk = ws[(size_t)i];
+		cudaSetDevice(wk.w->device);
+		BfsCtrl h;
+		const int rc = read_ctrl(wk.w, wk.b, &h);
+		wk.w->stats.host_syncs--; // end-of-call bookkeeping, not part of a batch
+		if (rc != PGQ_OK) {
+			rc_all = rc;
+			err_all = last_error_str();
+			break;
+		}
+		fold_totals(wk.w, h);
+	}
+	cudaSetDevice(c->device);
+	for (int i = 1; i < nw; i++) {
+		Ctx *h = ws[(size_t)i].w;
 		c->stats.kernel_launches += h->stats.kernel_launches;
 		c->stats.batches += h->stats.batches;
 		c->stats.levels += h->stats.levels;
 		c->stats.push_levels += h->stats.push_levels;
 		c->stats.h2d_bytes += h->stats.h2d_bytes;
 		c->stats.d2h_bytes += h->stats.d2h_bytes;
+		c->stats.host_syncs += h->stats.host_syncs;
 		h->stats = pgq_stats_t{};
 	}
-	for (const Res &r : res)
-		if (r.rc != PGQ_OK) {
-			set_error("%s", r.err.c_str());
-			return r.rc;
+	if (rc_all != PGQ_OK) {
+		set_error("%s", err_all.c_str());
+		return rc_all;
+	}
+	return PGQ_OK;
+}
+
+int pinned_found(Ctx *c, size_t bytes, int32_t **out) {
+	if (bytes > c->h_found_cap) {
+		if (c->h_found) cudaFreeHost(c->h_found);
+		c->h_found = nullptr;
+		c->h_found_cap = 0;
+		size_t cap = 4096;
+		while (cap < bytes) cap <<= 1;
+		PGQ_CUDA(cudaHostAlloc(&c->h_found, cap, cudaHostAllocPortable));
+		c->h_found_cap = cap;
+	}
+	*out = static_cast<int32_t *>(c->h_found);
+	return PGQ_OK;
+}
+
+// ---- K8: one shortestpath batch: BFS with level history, then the paths of its rows in ROW order (R9) --
+struct PathSeg {
+	int64_t r0 = 0, r1 = 0;     // rows [r0, r1)
+	std::vector<int64_t> vals;  // their list values, offsets in paths->entries are segment-local until stitched
+};
+
+// lanes [0, W) at d_src/d_dst/d_found (device) serve the rows lane_row[0..W) (host, -1 = unused) within
+// [r0, r1).  When the level history of a W-lane batch would not fit its budget the batch is redone as
+// W/64 batches of 64 lanes over slices of the same lane arrays (lanes are independent: same results).
+int path_batch(Worker &wk, int W, const uint32_t *d_src, const uint32_t *d_dst, int32_t *d_found,
+               const int64_t *lane_row, int64_t r0, int64_t r1, const uint8_t *kind, PathOut *paths,
+               const int64_t *row_src, std::vector<PathSeg> *segs) {
+	Ctx *w = wk.w;
+	Csr *g = wk.g;
+	cudaStream_t ws = w->stream;
+	int nlev = 0;
+	BatchBufs bw{};
+	PGQ_TRY(alloc_bufs(w, g, W, &bw));
+	int rc = run_batch(w, g, bw, W, true, d_src, d_dst, d_found, &nlev);
+	if (rc == PGQ_HIST_OVER) {
+		if (W <= 64) {
+			set_error("shortestpath: the level history of one 64-lane batch (%d+ levels x %zu bytes) exceeds its budget "
+			          "of %zu MiB; raise option hist_budget_mb", nlev, (size_t)g->V * 8, hist_budget(w) >> 20);
+			return PGQ_ERR_OOM;
 		}
+		for (int k = 0; k < W / 64; k++) {
+			// rows of this 64-lane group: from its first lane's row (group 0: from r0) up to the next group's
+			int64_t a = r0, b = r1;
+			if (k > 0) {
+				a = -1;
+				for (int l = k * 64; l < W && a < 0; l++) a = lane_row[l];
+				if (a < 0) break; // no lanes left: the rows before were taken by the previous group
+			}
+			{
+				int64_t nb = -1;
+				for (int l = (k + 1) * 64; l < W && nb < 0; l++) nb = lane_row[l];
+				if (nb >= 0) b = nb;
+			}
+			PGQ_TRY(path_batch(wk, 64, d_src + k * 64, d_dst + k * 64, d_found + k * 64, lane_row + k * 64, a, b, kind,
+			                   paths, row_src, segs));
+			if (b == r1) break;
+		}
+		return PGQ_OK;
+	}
+	PGQ_TRY(rc);
+	std::vector<int32_t> hf((size_t)W);
+	PGQ_CUDA(cudaMemcpyAsync(hf.data(), d_found, (size_t)W * 4, cudaMemcpyDeviceToHost, ws));
+	PGQ_CUDA(cudaStreamSynchronize(ws));
+	w->stats.host_syncs++;
+	w->stats.d2h_bytes += (uint64_t)W * 4;
+	std::vector<uint64_t> lane_off((size_t)W, 0);
+	uint64_t bt = 0; // values of this segment so far
+	int lane = 0;
+	for (int64_t r = r0; r < r1; r++) {
+		const uint8_t kd = kind[r];
+		uint64_t len = 0;
+		if (kd == 1) {
+			len = 1;
+		} else if (kd == 2) {
+			while (lane < W && lane_row[lane] != r) lane++;
+			if (lane < W && hf[(size_t)lane] >= 0) {
+				len = paths->mode == 0 ? (uint64_t)hf[(size_t)lane] + 1 : 2ull * (uint64_t)hf[(size_t)lane] + 1;
+				lane_off[(size_t)lane] = bt;
+			}
+		}
+		paths->entries[r].offset = bt; // segment-local until stitched
+		paths->entries[r].length = len;
+		paths->valid[r] = len ? 1 : 0;
+		bt += len;
+	}
+	segs->emplace_back();
+	PathSeg &seg = segs->back();
+	seg.r0 = r0;
+	seg.r1 = r1;
+	seg.vals.resize(bt);
+	if (!bt) return PGQ_OK;
+	// per-worker output buffer: [W lane offsets][values]; persistent, a per-call buffer would cudaMalloc every batch
+	DevBuf &d_out = w->bfs_pathout;
+	const size_t need = (size_t)W * 8 + bt * sizeof(int64_t);
+	if (need > d_out.cap) PGQ_TRY(d_out.reserve(need * 2));
+	unsigned long long *d_lo = d_out.as<unsigned long long>();
+	int64_t *d_vals = reinterpret_cast<int64_t *>(d_lo + W);
+	PGQ_CUDA(cudaMemcpyAsync(d_lo, lane_off.data(), (size_t)W * 8, cudaMemcpyHostToDevice, ws));
+	bfs_paths_hist_kernel<<<W, 256, 0, ws>>>(w->bfs_hist_tab.as<const uint32_t *const>(), g->d_ioff.as<uint32_t>(),
+	                                         g->d_isrc.as<uint32_t>(), g->d_ipos.as<uint32_t>(),
+	                                         g->have_eid ? g->d_eid.as<int64_t>() : nullptr,
+	                                         g->keep_rows ? g->d_row.as<uint32_t>() : nullptr, d_src, d_dst, d_found, d_lo,
+	                                         W, paths->mode, d_vals);
+	count_launch(w);
+	PGQ_CUDA(cudaMemcpyAsync(seg.vals.data(), d_vals, bt * sizeof(int64_t), cudaMemcpyDeviceToHost, ws));
+	PGQ_CUDA(cudaStreamSynchronize(ws));
+	w->stats.host_syncs++;
+	w->stats.d2h_bytes += bt * 8;
+	// trivial rows: [src]
+	for (int64_t r = r0; r < r1; r++)
+		if (kind[r] == 1) seg.vals[paths->entries[r].offset] = row_src[r];
 	return PGQ_OK;
 }
 
@@ -620,104 +1177,60 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 	BatchBufs b{};
 	PGQ_TRY(alloc_bufs(c, g, W, &b));
 	cudaStream_t st = c->stream;
-	// lane tables: src | dst | found | lane_off(u64, paths only)
-	size_t lane_bytes = (size_t)nslots * (2 * sizeof(uint32_t) + sizeof(int32_t)) + (size_t)W * sizeof(uint64_t) + 64;
-	PGQ_TRY(c->bfs_lane.reserve(lane_bytes));
-	uint64_t *d_lane_off = c->bfs_lane.as<uint64_t>(); // first, 8 B aligned
-	uint32_t *d_src = reinterpret_cast<uint32_t *>(d_lane_off + W);
+	// lane tables: src | dst | found
+	PGQ_TRY(c->bfs_lane.reserve((size_t)nslots * 12 + 64));
+	uint32_t *d_src = c->bfs_lane.as<uint32_t>();
 	uint32_t *d_dst = d_src + nslots;
 	int32_t *d_found = reinterpret_cast<int32_t *>(d_dst + nslots);
 	PGQ_CUDA(cudaMemcpyAsync(d_src, lt.src.data(), (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
 	PGQ_CUDA(cudaMemcpyAsync(d_dst, lt.dst.data(), (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
 	c->stats.h2d_bytes += (uint64_t)nslots * 8;
-	const uint64_t levels_before = c->stats.levels;
+	std::vector<Worker> ws;
+	PGQ_TRY(make_workers(c, g, b, W, lt.nbatch, want_paths, d_src, d_dst, d_found, nslots, &ws));
+	const bool host_loop = !c->opt.loop || c->opt.stats || c->opt.timing || c->opt.trace || c->loop_unsupported;
 	if (!want_paths) {
-		PGQ_TRY(run_batches(c, g, b, W, lt.nbatch, false, [&](Ctx *w, const BatchBufs &bw, int64_t bi) {
-			return run_batch(w, g, bw, W, false, d_src + bi * W, d_dst + bi * W, d_found + bi * W);
-		}));
-	} else {
-		// ---- K8: each batch reconstructs its paths in ROW order (R9) with batch-local list offsets;
-		// the batches (possibly finished out of order on different streams) are stitched afterwards.
-		std::vector<std::vector<int64_t>> batch_vals((size_t)lt.nbatch);
-		PGQ_TRY(run_batches(c, g, b, W, lt.nbatch, true, [&](Ctx *w, const BatchBufs &bw, int64_t bi) {
-			cudaStream_t ws = w->stream;
-			int nlev = 0;
-			PGQ_TRY(run_batch(w, g, bw, W, true, d_src + bi * W, d_dst + bi * W, d_found + bi * W, &nlev));
-			int32_t *hf = h_found + bi * W;
-			PGQ_CUDA(cudaMemcpyAsync(hf, d_found + bi * W, (size_t)W * 4, cudaMemcpyDeviceToHost, ws));
-			PGQ_CUDA(cudaStreamSynchronize(ws));
-			w->stats.d2h_bytes += (uint64_t)W * 4;
-			const int64_t r0 = lt.batch_row_begin[bi], r1 = lt.batch_row_end[bi];
-			std::vector<uint64_t> lane_off((size_t)W);
-			uint64_t bt = 0; // values of this batch so far
-			int lane = 0;
-			for (int64_t r = r0; r < r1; r++) {
-				const uint8_t kind = lt.kind[r];
-				uint64_t len = 0;
-				if (kind == 1) {
-					len = 1;
-				} else if (kind == 2) {
-					while (lane < W && lt.row[bi * W + lane] != r) lane++;
-					if (lane < W && hf[lane] >= 0) {
-						len = paths->mode == 0 ? (uint64_t)hf[lane] + 1 : 2ull * (uint64_t)hf[lane] + 1;
-						lane_off[lane] = bt;
-					}
-				}
-				paths->entries[r].offset = bt; // batch-local until stitched
-				paths->entries[r].length = len;
-				paths->valid[r] = len ? 1 : 0;
-				bt += len;
-			}
-			std::vector<int64_t> &vals = batch_vals[(size_t)bi];
-			vals.resize(bt);
-			if (!bt) return (int)PGQ_OK;
-			DevBuf &d_out = w->bfs_pathout; // persistent: a per-call buffer would cudaMalloc/cudaFree every batch
-			if (bt * sizeof(int64_t) > d_out.cap) PGQ_TRY(d_out.reserve(bt * sizeof(int64_t) * 2));
-			uint64_t *d_lo = d_lane_off;
-			if (w != c) { // helpers keep their own lane-offset table
-				PGQ_TRY(w->bfs_lane.reserve((size_t)W * sizeof(uint64_t) + 64));
-				d_lo = w->bfs_lane.as<uint64_t>();
-			}
-			PGQ_CUDA(cudaMemcpyAsync(d_lo, lane_off.data(), (size_t)W * 8, cudaMemcpyHostToDevice, ws));
-			// device table of the level buffers (they may have been reallocated by this batch)
-			std::vector<const uint32_t *> hp((size_t)nlev + 1);
-			for (int k = 0; k <= nlev; k++) hp[(size_t)k] = w->bfs_hist[(size_t)k].as<uint32_t>();
-			PGQ_TRY(w->bfs_hist_tab.reserve(hp.size() * sizeof(uint32_t *)));
-			PGQ_CUDA(cudaMemcpyAsync(w->bfs_hist_tab.p, hp.data(), hp.size() * sizeof(uint32_t *),
-			                         cudaMemcpyHostToDevice, ws));
-			bfs_paths_hist_kernel<<<W, 256, 0, ws>>>(
-			    w->bfs_hist_tab.as<const uint32_t *const>(), g->d_ioff.as<uint32_t>(), g->d_isrc.as<uint32_t>(),
-			    g->d_ipos.as<uint32_t>(), g->have_eid ? g->d_eid.as<int64_t>() : nullptr,
-			    g->keep_rows ? g->d_row.as<uint32_t>() : nullptr, d_src + bi * W, d_dst + bi * W, d_found + bi * W,
-			    (const unsigned long long *)d_lo, W, paths->mode, d_out.as<int64_t>());
-			count_launch(w);
-			PGQ_CUDA(cudaMemcpyAsync(vals.data(), d_out.p, bt * sizeof(int64_t), cudaMemcpyDeviceToHost, ws));
-			PGQ_CUDA(cudaStreamSynchronize(ws));
-			w->stats.d2h_bytes += bt * 8;
-			// trivial rows: [src]
-			for (int64_t r = r0; r < r1; r++)
-				if (lt.kind[r] == 1) vals[paths->entries[r].offset] = row_src[r];
+		int32_t *stage = nullptr;
+		PGQ_TRY(pinned_found(c, (size_t)nslots * 4, &stage));
+		PGQ_TRY(run_batches(c, ws, lt.nbatch, host_loop && ws.size() > 1, [&](Worker &wk, int64_t bi) {
+			PGQ_TRY(run_batch(wk.w, wk.g, wk.b, W, false, wk.d_src + bi * W, wk.d_dst + bi * W, wk.d_found + bi * W));
+			PGQ_CUDA(cudaMemcpyAsync(stage + bi * W, wk.d_found + bi * W, (size_t)W * 4, cudaMemcpyDeviceToHost,
+			                         wk.w->stream));
 			return (int)PGQ_OK;
 		}));
+		PGQ_CUDA(cudaStreamSynchronize(st));
+		memcpy(h_found, stage, (size_t)nslots * 4);
+		c->stats.d2h_bytes += (uint64_t)nslots * 4;
+	} else {
+		// each batch reconstructs its paths in row order with segment-local list offsets; the segments
+		// (possibly finished out of order on different streams / devices) are stitched afterwards
+		std::vector<std::vector<PathSeg>> segs((size_t)lt.nbatch);
+		const int rc = run_batches(c, ws, lt.nbatch, ws.size() > 1, [&](Worker &wk, int64_t bi) {
+			return path_batch(wk, W, wk.d_src + bi * W, wk.d_dst + bi * W, wk.d_found + bi * W, lt.row.data() + bi * W,
+			                  lt.batch_row_begin[bi], lt.batch_row_end[bi], lt.kind.data(), paths, row_src,
+			                  &segs[(size_t)bi]);
+		});
+		// level buffers beyond a working set are given back (a long-chain query must not pin HBM for good)
+		for (Worker &wk : ws)
+			if (wk.w->hist_bytes > ((size_t)2 << 30)) {
+				cudaSetDevice(wk.w->device);
+				cudaStreamSynchronize(wk.w->stream);
+				hist_trim(wk.w);
+			}
+		cudaSetDevice(c->device);
+		PGQ_TRY(rc);
 		uint64_t total = 0; // running list offset over all rows
-		for (int64_t bi = 0; bi < lt.nbatch; bi++) total += batch_vals[(size_t)bi].size();
+		for (auto &bs : segs)
+			for (PathSeg &s : bs) total += s.vals.size();
 		paths->vals.resize(total);
 		total = 0;
-		for (int64_t bi = 0; bi < lt.nbatch; bi++) {
-			const std::vector<int64_t> &vals = batch_vals[(size_t)bi];
-			for (int64_t r = lt.batch_row_begin[bi]; r < lt.batch_row_end[bi]; r++) paths->entries[r].offset += total;
-			if (!vals.empty()) memcpy(paths->vals.data() + total, vals.data(), vals.size() * sizeof(int64_t));
-			total += vals.size();
-		}
-	}
-	if (!want_paths) {
-		PGQ_CUDA(cudaMemcpyAsync(h_found, d_found, (size_t)nslots * 4, cudaMemcpyDeviceToHost, st));
-		PGQ_CUDA(cudaStreamSynchronize(st));
-		c->stats.d2h_bytes += (uint64_t)nslots * 4;
+		for (auto &bs : segs)
+			for (PathSeg &s : bs) {
+				for (int64_t r = s.r0; r < s.r1; r++) paths->entries[r].offset += total;
+				if (!s.vals.empty()) memcpy(paths->vals.data() + total, s.vals.data(), s.vals.size() * sizeof(int64_t));
+				total += s.vals.size();
+			}
 	}
 	PGQ_TRY(small_flush(c));
-	if (c->opt.stats)
-		c->stats.algo_bytes += (c->stats.levels - levels_before) * 4ull * (uint64_t)g->V * (uint64_t)(W / 8);
 	return PGQ_OK;
 }
 
@@ -738,7 +1251,6 @@ struct PartBufs {
 
 template <int W>
 int launch_part_level(Ctx *c, Csr *g, const PartBufs &b, int cur, int iter) {
-	using C = LaneCfg<W>;
 	cudaStream_t st = c->stream;
 	const int G = c->part_world, r = c->part_rank;
 	const size_t fwords = b.fwords_per_slice * G;
@@ -765,19 +1277,13 @@ int launch_part_level(Ctx *c, Csr *g, const PartBufs &b, int cur, int iter) {
 		a.peer_next = b.peer_tab + (size_t)(cur ^ 1) * (G - 1);
 		a.npeers = (uint32_t)(G - 1);
 	}
-	launch_tiny<W>(c, a, g, true);
-	launch_class<W, 2>(c, a, g->d_small, g->n_small, true);
-	launch_warp<W>(c, a, g->d_med, g->n_med, true);
-	launch_warp<W>(c, a, g->d_mid, g->n_mid, true);
-	if (g->n_hub) {
-		a.list = g->d_hub.as<uint32_t>();
-		a.nlist = g->n_hub;
-		a.chunks = g->d_hubchunks.as<HubChunk>();
-		a.nchunks = g->n_hubchunks;
-		pull_hub_kernel<W><<<g->n_hubchunks, 256, 0, st>>>(a);
-		hub_finalize_kernel<W><<<div_up((uint64_t)g->n_hub * C::TPV, 256), 256, 0, st>>>(a);
-		count_launch(c, 2);
-	}
+	uint32_t nk = 0;
+	launch_tiny<W>(a, g, true, st, &nk);
+	launch_class<W, 2>(a, g->d_small, g->n_small, true, st, &nk);
+	launch_warp<W>(a, g->d_med, g->n_med, true, st, &nk);
+	launch_warp<W>(a, g->d_mid, g->n_mid, true, st, &nk);
+	launch_hubs<W>(a, g, st, &nk);
+	count_launch(c, nk);
 	alive_fold_kernel<<<1, 1024, 0, st>>>(b.alive_slots, b.alive_local);
 	count_launch(c);
 	return PGQ_OK;
@@ -970,18 +1476,28 @@ int msbfs_run_device(Ctx *c, Csr *g, int64_t n, const int64_t *d_srcs, const int
 	lanes_from_rows_kernel<<<div_up(nslots, 256), 256, 0, st>>>(d_srcs, d_dsts, n, nslots, (uint64_t)g->V, d_src,
 	                                                            d_dst, d_err);
 	count_launch(c);
-	const uint64_t levels_before = c->stats.levels;
-	PGQ_TRY(run_batches(c, g, b, W, nbatch, false, [&](Ctx *w, const BatchBufs &bw, int64_t bi) {
-		return run_batch(w, g, bw, W, false, d_src + bi * W, d_dst + bi * W, d_found + bi * W);
+	std::vector<Worker> ws;
+	PGQ_TRY(make_workers(c, g, b, W, nbatch, false, d_src, d_dst, d_found, nslots, &ws));
+	const bool host_loop = !c->opt.loop || c->opt.stats || c->opt.timing || c->opt.trace || c->loop_unsupported;
+	bool multi_dev = false;
+	for (const Worker &wk : ws) multi_dev |= wk.w->device != c->device;
+	int32_t *stage = nullptr;
+	if (multi_dev) PGQ_TRY(pinned_found(c, (size_t)nslots * 4, &stage));
+	PGQ_TRY(run_batches(c, ws, nbatch, host_loop && ws.size() > 1, [&](Worker &wk, int64_t bi) {
+		PGQ_TRY(run_batch(wk.w, wk.g, wk.b, W, false, wk.d_src + bi * W, wk.d_dst + bi * W, wk.d_found + bi * W));
+		if (multi_dev) // results of every device meet in pinned host memory, then return to the primary
+			PGQ_CUDA(cudaMemcpyAsync(stage + bi * W, wk.d_found + bi * W, (size_t)W * 4, cudaMemcpyDeviceToHost,
+			                         wk.w->stream));
+		return (int)PGQ_OK;
 	}));
+	if (multi_dev) PGQ_CUDA(cudaMemcpyAsync(d_found, stage, (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
+	// helper streams of this device are complete (run_batches waited); order the result kernel after them
 	rows_from_lanes_kernel<<<div_up(n, 256), 256, 0, st>>>(d_srcs, d_dsts, n, d_found, d_out, d_out_valid);
 	count_launch(c);
 	uint32_t h_err = 0;
 	PGQ_CUDA(cudaMemcpyAsync(&h_err, d_err, 4, cudaMemcpyDeviceToHost, st));
 	PGQ_CUDA(cudaStreamSynchronize(st));
 	PGQ_TRY(small_flush(c));
-	if (c->opt.stats)
-		c->stats.algo_bytes += (c->stats.levels - levels_before) * 4ull * (uint64_t)g->V * (uint64_t)(W / 8);
 	if (h_err) {
 		set_error("iterativelength: src/dst id outside [0, v_size)");
 		return PGQ_ERR_INVALID;

@@ -21,6 +21,53 @@
 
 namespace pgq {
 
+// Device-side level loop.  After every level the check kernel rotates the frontier
+// views and decides the direction of the next level; the level kernels read their frontier pointers
+// from here, so the same kernel nodes serve every level of a CUDA-graph WHILE loop and the host is
+// not needed between the init kernel and the result copy.  The host-driven loop (options "stats",
+// "timing", "trace", "loop"=0) reads `mode` back after every level and launches the same bodies.
+enum LoopMode : uint32_t {
+	MODE_STOP = 0,
+	MODE_PUSH = 1,         // top-down over the work queue
+	MODE_PULL = 2,         // bottom-up, frontier-bitmap filter off (the frontier owns most edges)
+	MODE_PULL_F_EARLY = 3, // bottom-up, filter on, few vertices discovered so far (edge-parallel medium class)
+	MODE_PULL_F_LATE = 4,  // bottom-up, filter on, tail levels
+	MODE_COUNT = 5
+};
+
+struct LoopState {
+	// this worker's buffers (constant over the batch)
+	uint32_t *visit[2];
+	uint32_t *fbit[3];
+	uint2 *queue[2];
+	uint32_t *const *hist; // shortestpath: table of per-level frontier buffers, else nullptr
+	uint32_t hist_cap;     // entries of hist
+	uint32_t pad0;
+	// views of the level about to run
+	const uint32_t *cur_visit;
+	uint32_t *cur_next;
+	const uint32_t *cur_fbit; // bitmap of cur_visit
+	uint32_t *nxt_fbit;       // built for cur_next
+	uint32_t *old_fbit;       // describes what cur_next still holds (frontier of two levels ago)
+	const uint2 *cur_queue;
+	uint2 *nxt_queue;
+	uint32_t cur, fb[3], q, have_queue;
+	uint32_t iter;        // level about to run (1-based)
+	uint32_t mode;        // LoopMode of that level
+	uint32_t stop_reason; // 1 finished (no lane active / nothing changed / level cap), 2 hist table full
+	uint32_t level_cap;
+	unsigned long long cum_verts; // frontier vertices of all levels so far
+	// direction heuristic (Options)
+	uint32_t direction, push_beta, push_vbeta, filter_gamma;
+	unsigned long long E, V, n_listed;
+	uint32_t levels_run, push_levels;
+	// this batch's lanes (destination check)
+	const uint32_t *lane_dst;
+	int32_t *found;
+	uint32_t nk[MODE_COUNT]; // kernels one level of each mode launches (launch statistics without a host in the loop)
+	uint32_t pad1;
+};
+
 struct BfsCtrl {
 	uint32_t active[32]; // lane mask, W/32 words used (W <= 1024); first so slices are 16 B aligned
 	uint32_t alive[32];  // lanes that gained a frontier bit in the running level (others are exhausted)
@@ -45,7 +92,27 @@ struct BfsCtrl {
 	uint32_t small_overflow; // ran out of level buffers (shortestpath history): host falls back
 	uint32_t pad3;
 	uint32_t small_slots[3][20]; // per level (mod 3): alive lanes [0..15], change flag [16]
+	// what the level kernels actually touched (instrumented instantiations only, option "stats"=1):
+	// the roofline model of DESIGN.md section 4 is computed from these
+	unsigned long long k_listed;   // class-list entries visited (list entry + two offsets + done bit)
+	unsigned long long k_open;     // vertices whose `seen` word was read
+	unsigned long long k_new;      // vertices that stored a `next` word and rewrote `seen`
+	unsigned long long k_scanned;  // in-edges (pull) / out-edges (push) whose endpoint id was read
+	unsigned long long k_gathered; // frontier words gathered
+	unsigned long long kp_items;   // push: work items (queue entry + frontier word + two offsets)
+	unsigned long long kp_edges;   // push: out-edges whose target id was read
+	unsigned long long kp_seen;    // push: 4-byte atomicOr on `seen`
+	unsigned long long kp_next;    // push: 4-byte atomicOr on `next`
+	// running totals of this worker (never reset on the device; the host folds the deltas into pgq_stats_t)
+	unsigned long long tot_levels, tot_push_levels, tot_launches;
+	LoopState L;
 };
+
+// Instrumented kernels: per-thread counts -> one atomicAdd per warp and counter (untimed pass only).
+__device__ __forceinline__ void stat_add(unsigned long long *dst, uint32_t mine) {
+	const uint32_t tot = __reduce_add_sync(0xffffffffu, mine);
+	if ((threadIdx.x & 31) == 0 && tot) atomicAdd(dst, (unsigned long long)tot);
+}
 
 // Lanes that gained a frontier bit in the running level ("alive").  A lane with an empty frontier
 // can never reach anything new; the check kernel retires it so it stops blocking the pull
@@ -95,6 +162,18 @@ struct PullArgs {
 	const uint32_t *fcur; // 1 bit per vertex: visit word non-empty (may over-approximate, never under)
 	uint32_t *fnext;      // same for `next`, produced by this level
 	uint32_t *alive_slots;   // [ALIVE_SLOTS][16] per-block-slot OR of the words produced this level
+	// 1 bit per vertex: seen[n] already holds every lane that is still active.  `active` only ever shrinks,
+	// so a done vertex stays done for the rest of the batch and costs neither its 64-byte `seen` read nor
+	// anything else.  nullptr = not tracked (partitioned path).
+	uint32_t *done;
+	// 1 = visit / next / fcur / fnext come from ctrl->L (the level loop's rotating views), 0 = from the
+	// fields above (partitioned path)
+	uint32_t dyn;
+	// dense = 1: every listed vertex stores its `next` word, zero or not (unfiltered levels, where most
+	// vertices gain bits anyway and one streaming store beats a scrub pass plus scattered stores);
+	// dense = 0: `next` is all-zero on entry and only words that gained bits are written.
+	uint32_t dense;
+	uint32_t use_done; // test the done bitmap (tail levels); it is maintained on every level
 	// 1-D partition, fused exchange: the other ranks' `next` replicas (peer memory over NVLink), each
 	// already offset to THIS rank's slice.  A vertex that gained bits is stored to every replica by
 	// the thread that produced it, so the frontier words never go through a separate collective.
@@ -202,6 +281,11 @@ __device__ __forceinline__ bool fbit_test(const uint32_t *f, uint32_t v) {
 	return (__ldg(f + (v >> 5)) >> (v & 31)) & 1u;
 }
 
+// done bit of vertex n (plain load: other vertices' bits of the same word may be set by this launch)
+__device__ __forceinline__ bool done_test(const uint32_t *done, uint32_t n) {
+	return done && ((done[n >> 5] >> (n & 31)) & 1u);
+}
+
 template <int TPV>
 __device__ __forceinline__ bool group_any(bool x) {
 	unsigned b = x ? 1u : 0u;
@@ -219,8 +303,12 @@ __device__ __forceinline__ bool group_any(bool x) {
 // frontier bit is clear before their word is touched (pays off unless the frontier holds most
 // edges).  Loops are warp-uniform (trip count = the slowest vertex of the warp) because the
 // reductions use full-mask shuffles.
-template <int W, int GPV, bool FILTER>
+template <int W, int GPV, bool FILTER, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
+	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
 	static_assert(GPV >= 1 && GPV <= G, "groups per vertex");
@@ -233,8 +321,9 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
 	const uint32_t vslot = g / GPV, sg = g % GPV;
 	const uint64_t idx = (uint64_t)wid * VPW + vslot;
-	const bool valid = idx < a.nlist;
-	const uint32_t n = valid ? a.list[idx] : 0u;
+	const bool listed = idx < a.nlist;
+	const uint32_t n = listed ? a.list[idx] : 0u;
+	const bool valid = listed && !(a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
 	uint32_t lo = 0, hi = 0;
 	if (valid) {
 		lo = a.ioff[n];
@@ -242,6 +331,7 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	}
 	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
 	Slice<SW> s = slice_zero<SW>(), unseen = slice_zero<SW>();
+	uint32_t c_scan = 0, c_gath = 0; // STATS
 	// Software pipeline, three rounds deep: sources of round r+2 are being loaded and the frontier
 	// bits of round r+1 tested while the gathers of round r are in flight.  The first two rounds'
 	// sources do not depend on `seen`: issue them before it.
@@ -251,11 +341,13 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	for (int u = 0; u < U; u++) {
 		const uint32_t jj = j + u * GPV;
 		vs[u] = jj < hi ? a.isrc[jj] : INV;
+		if (STATS && t == 0 && jj < hi) c_scan++;
 	}
 #pragma unroll
 	for (int u = 0; u < U; u++) {
 		const uint32_t jj = j + GPV * U + u * GPV;
 		v1[u] = jj < hi ? a.isrc[jj] : INV;
+		if (STATS && t == 0 && jj < hi) c_scan++;
 	}
 	if (valid) {
 		s = ld_slice<SW>(a.seen + wo);
@@ -270,26 +362,29 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 #pragma unroll
 	for (int u = 0; u < U; u++) {
 		bool f = vs[u] != INV;
-		if (FILTER && f) f = fbit_test(a.fcur, vs[u]);
+		if (FILTER && f) f = fbit_test(fcur_p, vs[u]);
 		fm |= (f ? 1u : 0u) << u;
 	}
 	while (__any_sync(FULL, open && j < hi)) {
 		Slice<SW> w[U];
 #pragma unroll
-		for (int u = 0; u < U; u++)
-			w[u] = (open && ((fm >> u) & 1u)) ? ldg_slice<SW>(a.visit + (size_t)vs[u] * WPV + t * SW) : slice_zero<SW>();
+		for (int u = 0; u < U; u++) {
+			w[u] = (open && ((fm >> u) & 1u)) ? ldg_slice<SW>(visit_p + (size_t)vs[u] * WPV + t * SW) : slice_zero<SW>();
+			if (STATS && t == 0 && open && ((fm >> u) & 1u)) c_gath++;
+		}
 		const uint32_t jn = j + GPV * U;
 		uint32_t v2[U];
 #pragma unroll
 		for (int u = 0; u < U; u++) {
 			const uint32_t jj = jn + GPV * U + u * GPV;
 			v2[u] = (open && jj < hi) ? a.isrc[jj] : INV;
+			if (STATS && t == 0 && open && jj < hi) c_scan++;
 		}
 		uint32_t fn = 0;
 #pragma unroll
 		for (int u = 0; u < U; u++) {
 			bool f = v1[u] != INV;
-			if (FILTER && f) f = fbit_test(a.fcur, v1[u]);
+			if (FILTER && f) f = fbit_test(fcur_p, v1[u]);
 			fn |= (f ? 1u : 0u) << u;
 		}
 #pragma unroll
@@ -315,9 +410,20 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	Slice<SW> news;
 #pragma unroll
 	for (int i = 0; i < SW; i++) news.w[i] = tot.w[i] & unseen.w[i];
+	// `next` is all-zero on entry (the level's clear pass scrubbed what the frontier of two levels ago
+	// left there), so only words that gained bits are written: a vertex without news costs no store.
 	const bool writer = valid && sg == 0;
-	if (writer) {
-		st_slice<SW>(a.next + wo, news);
+	bool rest = false; // some active lane of my slice is still unseen after this level
+#pragma unroll
+	for (int i = 0; i < SW; i++) rest |= (unseen.w[i] & ~news.w[i]) != 0u;
+	const unsigned bal = __ballot_sync(FULL, writer && slice_any<SW>(news));
+	const unsigned rbal = __ballot_sync(FULL, writer && rest);
+	const unsigned gmask = ((1u << TPV) - 1u) << (vslot * (GPV * TPV));
+	const bool vnew = (bal & gmask) != 0;
+	if (writer && (vnew || a.dense)) {
+		// the WHOLE word is written when any slice gained bits: a reader that passed the frontier-bit test
+		// reads all of it
+		st_slice<SW>(next_p + wo, news);
 		if (slice_any<SW>(news)) {
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
@@ -325,20 +431,30 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 		}
 	}
-	const unsigned bal = __ballot_sync(FULL, writer && slice_any<SW>(news));
-	const bool vnew = ((bal >> (vslot * (GPV * TPV))) & ((1u << TPV) - 1u)) != 0;
-	const bool leader = writer && t == 0 && vnew;
-	if (leader) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+	const bool leader = writer && t == 0;
+	if (leader && vnew) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
+	if (leader && a.done && !(rbal & gmask)) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (a.npeers && writer && vnew) st_peers<SW>(a, wo, news); // whole word, zero slices included
 	// no global counters here: frontier_stats_kernel derives them from fnext afterwards
+	if (STATS) {
+		stat_add(&a.ctrl->k_listed, (listed && sg == 0 && t == 0) ? 1u : 0u);
+		stat_add(&a.ctrl->k_open, (leader) ? 1u : 0u);
+		stat_add(&a.ctrl->k_new, (leader && vnew) ? 1u : 0u);
+		stat_add(&a.ctrl->k_scanned, c_scan);
+		stat_add(&a.ctrl->k_gathered, c_gath);
+	}
 }
 
 // ---- K4 tiny: in-degree 1..4, straight-line ------------------------------------------------------
 // Same result as pull_list_kernel<W, 1, FILTER> for vertices with at most 4 in-edges, without the
 // round loop, the prefetch pipeline and the cross-group shuffles: this class is 25 % of an R-MAT's
 // vertices and 3 % of its edges, so its cost is instructions and dependent loads per VERTEX.
-template <int W, bool FILTER>
+template <int W, bool FILTER, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
+	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
 	constexpr uint32_t INV = 0xFFFFFFFFu, FULL = 0xffffffffu;
@@ -348,16 +464,21 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 	if ((uint64_t)wid * G >= a.nlist) return; // warp-uniform
 	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
 	const uint64_t idx = (uint64_t)wid * G + g;
-	const bool listed = idx < a.nlist;
-	const uint32_t n = listed ? a.list[idx] : 0u;
+	const bool inlist = idx < a.nlist;
+	const uint32_t n = inlist ? a.list[idx] : 0u;
+	const bool listed = inlist && !(a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
 	uint32_t lo = 0, hi = 0;
 	if (listed) {
 		lo = a.ioff[n];
 		hi = a.ioff[n + 1];
 	}
 	uint32_t vs[U];
+	uint32_t c_scan = 0, c_gath = 0; // STATS
 #pragma unroll
-	for (int u = 0; u < U; u++) vs[u] = lo + u < hi ? a.isrc[lo + u] : INV;
+	for (int u = 0; u < U; u++) {
+		vs[u] = lo + u < hi ? a.isrc[lo + u] : INV;
+		if (STATS && t == 0 && lo + u < hi) c_scan++;
+	}
 	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
 	Slice<SW> s = slice_zero<SW>(), unseen = slice_zero<SW>();
 	if (listed) {
@@ -372,8 +493,9 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 #pragma unroll
 		for (int u = 0; u < U; u++) {
 			bool f = vs[u] != INV;
-			if (FILTER && f) f = fbit_test(a.fcur, vs[u]);
-			w[u] = f ? ldg_slice<SW>(a.visit + (size_t)vs[u] * WPV + t * SW) : slice_zero<SW>();
+			if (FILTER && f) f = fbit_test(fcur_p, vs[u]);
+			w[u] = f ? ldg_slice<SW>(visit_p + (size_t)vs[u] * WPV + t * SW) : slice_zero<SW>();
+			if (STATS && t == 0 && f) c_gath++;
 		}
 #pragma unroll
 		for (int u = 0; u < U; u++) {
@@ -385,8 +507,15 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 #pragma unroll
 	for (int i = 0; i < SW; i++) news.w[i] = acc.w[i] & unseen.w[i];
 	const bool mine = slice_any<SW>(news);
-	if (listed) {
-		st_slice<SW>(a.next + wo, news);
+	bool rest = false; // some active lane of my slice is still unseen after this level
+#pragma unroll
+	for (int i = 0; i < SW; i++) rest |= (unseen.w[i] & ~news.w[i]) != 0u;
+	const unsigned bal = __ballot_sync(FULL, mine);
+	const unsigned rbal = __ballot_sync(FULL, listed && rest);
+	const unsigned gmask = ((1u << TPV) - 1u) << (g * TPV);
+	const bool vnew = (bal & gmask) != 0;
+	if (listed && (vnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
+		st_slice<SW>(next_p + wo, news);
 		if (mine) {
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
@@ -394,11 +523,17 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 		}
 	}
-	const unsigned bal = __ballot_sync(FULL, mine);
-	const bool vnew = ((bal >> (g * TPV)) & ((1u << TPV) - 1u)) != 0;
 	if (listed && vnew) {
-		if (t == 0) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+		if (t == 0) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
 		if (a.npeers) st_peers<SW>(a, wo, news);
+	}
+	if (listed && t == 0 && a.done && !(rbal & gmask)) atomicOr(&a.done[n >> 5], 1u << (n & 31));
+	if (STATS) {
+		stat_add(&a.ctrl->k_listed, (inlist && t == 0) ? 1u : 0u);
+		stat_add(&a.ctrl->k_open, (listed && t == 0) ? 1u : 0u);
+		stat_add(&a.ctrl->k_new, (listed && t == 0 && vnew) ? 1u : 0u);
+		stat_add(&a.ctrl->k_scanned, c_scan);
+		stat_add(&a.ctrl->k_gathered, c_gath);
 	}
 }
 
@@ -407,8 +542,12 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 // test per edge (instead of once per thread of the group), a ballot, and then the G groups gather
 // only the words whose test passed (source ids handed over by shuffle).  Rounds are pipelined two
 // deep like pull_list_kernel.  Early exit once every unseen lane of the vertex is covered.
-template <int W, bool FILTER>
+template <int W, bool FILTER, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
+	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G;
 	constexpr int STEPS = 32 / G;
@@ -419,9 +558,15 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 	if (wid >= a.nlist) return; // warp-uniform
 	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
 	const uint32_t n = a.list[wid];
+	if (a.use_done && done_test(a.done, n)) { // warp-uniform: the vertex is skipped altogether
+		if (STATS && lane == 0) atomicAdd(&a.ctrl->k_listed, 1ull);
+		return;
+	}
 	const uint32_t lo = a.ioff[n], hi = a.ioff[n + 1];
 	uint32_t v0 = lo + lane < hi ? a.isrc[lo + lane] : INV;
 	uint32_t v1 = lo + 32 + lane < hi ? a.isrc[lo + 32 + lane] : INV;
+	uint32_t c_scan = 0, c_gath = 0; // STATS
+	if (STATS) c_scan = (v0 != INV ? 1u : 0u) + (v1 != INV ? 1u : 0u);
 	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
 	Slice<SW> s = ld_slice<SW>(a.seen + wo);
 	const Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
@@ -431,7 +576,7 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 	Slice<SW> acc = slice_zero<SW>();
 	if (__any_sync(FULL, slice_any<SW>(unseen))) {
 		bool p0 = v0 != INV;
-		if (FILTER && p0) p0 = fbit_test(a.fcur, v0);
+		if (FILTER && p0) p0 = fbit_test(fcur_p, v0);
 		for (uint32_t base = lo; base < hi; base += 32) {
 			const unsigned mask = __ballot_sync(FULL, p0);
 			Slice<SW> w[STEPS];
@@ -439,12 +584,14 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 			for (int u = 0; u < STEPS; u++) {
 				const int sl = u * G + g;
 				const uint32_t src = STEPS == 1 ? v0 : __shfl_sync(FULL, v0, sl);
-				w[u] = ((mask >> sl) & 1u) ? ldg_slice<SW>(a.visit + (size_t)src * WPV + t * SW) : slice_zero<SW>();
+				w[u] = ((mask >> sl) & 1u) ? ldg_slice<SW>(visit_p + (size_t)src * WPV + t * SW) : slice_zero<SW>();
+				if (STATS && t == 0 && ((mask >> sl) & 1u)) c_gath++;
 			}
 			const uint32_t j2 = base + 64 + lane;
 			const uint32_t v2 = j2 < hi ? a.isrc[j2] : INV;
+			if (STATS && j2 < hi) c_scan++;
 			bool p1 = v1 != INV;
-			if (FILTER && p1) p1 = fbit_test(a.fcur, v1);
+			if (FILTER && p1) p1 = fbit_test(fcur_p, v1);
 #pragma unroll
 			for (int u = 0; u < STEPS; u++) {
 #pragma unroll
@@ -463,8 +610,13 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 	Slice<SW> news;
 #pragma unroll
 	for (int i = 0; i < SW; i++) news.w[i] = tot.w[i] & unseen.w[i];
-	if (g == 0) {
-		st_slice<SW>(a.next + wo, news);
+	const bool wany = __any_sync(FULL, slice_any<SW>(news));
+	bool rest = false; // some active lane of my slice is still unseen after this level
+#pragma unroll
+	for (int i = 0; i < SW; i++) rest |= (unseen.w[i] & ~news.w[i]) != 0u;
+	const bool wrest = __any_sync(FULL, rest);
+	if (g == 0 && (wany || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
+		st_slice<SW>(next_p + wo, news);
 		if (slice_any<SW>(news)) {
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
@@ -472,9 +624,18 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 		}
 	}
-	const bool wany = __any_sync(FULL, slice_any<SW>(news));
-	if (wany && lane == 0) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+	if (wany && lane == 0) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
+	if (!wrest && lane == 0 && a.done) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (a.npeers && wany && g == 0) st_peers<SW>(a, wo, news);
+	if (STATS) {
+		if (lane == 0) {
+			atomicAdd(&a.ctrl->k_listed, 1ull);
+			atomicAdd(&a.ctrl->k_open, 1ull);
+			if (wany) atomicAdd(&a.ctrl->k_new, 1ull);
+		}
+		stat_add(&a.ctrl->k_scanned, c_scan);
+		stat_add(&a.ctrl->k_gathered, c_gath);
+	}
 }
 
 // ---- K4 small class, filtered levels: SEG lanes per vertex, edge-parallel frontier test ----------------
@@ -485,8 +646,12 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 // ballot collects the hits of every segment, and the segment's SEG/TPV word groups gather only those,
 // source ids handed over by shuffle.  pull_warp_kernel is the SEG = 32 case of the same idea; this one
 // packs 32/SEG vertices into a warp for in-degrees far below 32.  Rounds are pipelined two deep.
-template <int W, int SEG>
+template <int W, int SEG, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
+	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
 	constexpr int VPW = 32 / SEG;  // vertices per warp
@@ -501,8 +666,9 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 	const uint32_t lane = threadIdx.x & 31, seg = lane / SEG, sl = lane % SEG;
 	const uint32_t g = sl / TPV, t = sl % TPV; // word group inside the segment, slice inside the word
 	const uint64_t idx = (uint64_t)wid * VPW + seg;
-	const bool valid = idx < a.nlist;
-	const uint32_t n = valid ? a.list[idx] : 0u;
+	const bool listed = idx < a.nlist;
+	const uint32_t n = listed ? a.list[idx] : 0u;
+	const bool valid = listed && !(a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
 	uint32_t lo = 0, hi = 0;
 	if (valid) {
 		lo = a.ioff[n];
@@ -510,6 +676,8 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 	}
 	uint32_t v0 = lo + sl < hi ? a.isrc[lo + sl] : INV;
 	uint32_t v1 = lo + SEG + sl < hi ? a.isrc[lo + SEG + sl] : INV;
+	uint32_t c_scan = 0, c_gath = 0; // STATS
+	if (STATS) c_scan = (v0 != INV ? 1u : 0u) + (v1 != INV ? 1u : 0u);
 	const size_t wo = (size_t)n * WPV + (size_t)t * SW;
 	Slice<SW> s = slice_zero<SW>(), unseen = slice_zero<SW>();
 	if (valid) {
@@ -523,14 +691,15 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 	bool mine_open = slice_any<SW>(unseen);
 	bool vopen = (__ballot_sync(FULL, mine_open) >> (seg * SEG)) & SEGMASK;
 	Slice<SW> acc = slice_zero<SW>();
-	bool p0 = vopen && v0 != INV && fbit_test(a.fcur, v0);
+	bool p0 = vopen && v0 != INV && fbit_test(fcur_p, v0);
 	uint32_t base = lo;
 	while (__any_sync(FULL, vopen && base < hi)) {
 		const unsigned bal = __ballot_sync(FULL, p0);
 		// sources of the round after next, frontier bits of the next round: in flight during the gathers
 		const uint32_t j2 = base + 2 * SEG + sl;
 		const uint32_t v2 = (vopen && j2 < hi) ? a.isrc[j2] : INV;
-		const bool p1 = vopen && v1 != INV && fbit_test(a.fcur, v1);
+		if (STATS && vopen && j2 < hi) c_scan++;
+		const bool p1 = vopen && v1 != INV && fbit_test(fcur_p, v1);
 		unsigned m = (bal >> (seg * SEG)) & SEGMASK; // hits of my vertex in this round
 		while (__any_sync(FULL, m != 0u)) {
 			unsigned mm = m; // my group takes the g-th lowest hit
@@ -539,7 +708,8 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 				if (k < (int)g) mm &= mm - 1u;
 			const uint32_t src = __shfl_sync(FULL, v0, (int)(seg * SEG) + (mm ? __ffs((int)mm) - 1 : 0));
 			if (mm && mine_open) {
-				const Slice<SW> w = ldg_slice<SW>(a.visit + (size_t)src * WPV + t * SW);
+				if (STATS) c_gath++; // per 16-byte slice here (a covered slice stops gathering): / TPV below
+				const Slice<SW> w = ldg_slice<SW>(visit_p + (size_t)src * WPV + t * SW);
 #pragma unroll
 				for (int i = 0; i < SW; i++) acc.w[i] |= w.w[i];
 			}
@@ -571,8 +741,15 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 #pragma unroll
 	for (int i = 0; i < SW; i++) news.w[i] = tot.w[i] & unseen.w[i];
 	const bool writer = valid && g == 0;
-	if (writer) {
-		st_slice<SW>(a.next + wo, news);
+	bool rest = false; // some active lane of my slice is still unseen after this level
+#pragma unroll
+	for (int i = 0; i < SW; i++) rest |= (unseen.w[i] & ~news.w[i]) != 0u;
+	const unsigned nb = __ballot_sync(FULL, writer && slice_any<SW>(news));
+	const unsigned rb = __ballot_sync(FULL, writer && rest);
+	const bool vnew = ((nb >> (seg * SEG)) & SEGMASK) != 0u;
+	const bool vrest = ((rb >> (seg * SEG)) & SEGMASK) != 0u;
+	if (writer && (vnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
+		st_slice<SW>(next_p + wo, news);
 		if (slice_any<SW>(news)) {
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
@@ -580,15 +757,26 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 		}
 	}
-	const unsigned nb = __ballot_sync(FULL, writer && slice_any<SW>(news));
-	const bool vnew = ((nb >> (seg * SEG)) & SEGMASK) != 0u;
-	if (writer && t == 0 && vnew) atomicOr(&a.fnext[n >> 5], 1u << (n & 31));
+	if (writer && t == 0 && vnew) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
+	if (writer && t == 0 && a.done && !vrest) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (a.npeers && writer && vnew) st_peers<SW>(a, wo, news); // whole word, zero slices included
+	if (STATS) {
+		stat_add(&a.ctrl->k_listed, (listed && sl == 0) ? 1u : 0u);
+		stat_add(&a.ctrl->k_open, (valid && sl == 0) ? 1u : 0u);
+		stat_add(&a.ctrl->k_new, (valid && sl == 0 && vnew) ? 1u : 0u);
+		stat_add(&a.ctrl->k_scanned, c_scan);
+		const uint32_t gsl = __reduce_add_sync(FULL, c_gath); // 16-byte slices -> words (rounded up)
+		if (lane == 0 && gsl) atomicAdd(&a.ctrl->k_gathered, (unsigned long long)((gsl + TPV - 1) / TPV));
+	}
 }
 
 // ---- K4 hubs: one block per chunk of a hub's in-list, partial ORs merged with atomicOr ---------
-template <int W>
+template <int W, bool STATS = false>
 __global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
+	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
 	const HubChunk hc = a.chunks[blockIdx.x];
@@ -601,23 +789,30 @@ __global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
 	Slice<SW> unseen;
 #pragma unroll
 	for (int i = 0; i < SW; i++) unseen.w[i] = ~s.w[i] & act.w[i];
+	if (STATS && threadIdx.x == 0) { // every chunk block reads the hub's `seen` word
+		atomicAdd(&a.ctrl->k_listed, 1ull);
+		atomicAdd(&a.ctrl->k_open, 1ull);
+	}
 	if (!__any_sync(0xffffffffu, slice_any<SW>(unseen))) return; // same decision in every warp
 	Slice<SW> acc = slice_zero<SW>();
 	Slice<SW> tot = slice_zero<SW>();
+	uint32_t c_scan = 0, c_gath = 0; // STATS
 	for (uint32_t j0 = hc.begin + warp * (G * U); j0 < hc.end; j0 += nwarps * G * U) {
 		uint32_t vs[U];
 #pragma unroll
 		for (int u = 0; u < U; u++) {
 			uint32_t j = j0 + u * G + g;
 			vs[u] = j < hc.end ? a.isrc[j] : 0xFFFFFFFFu;
+			if (STATS && t == 0 && j < hc.end) c_scan++;
 		}
 #pragma unroll
 		for (int u = 0; u < U; u++)
-			if (vs[u] != 0xFFFFFFFFu && !fbit_test(a.fcur, vs[u])) vs[u] = 0xFFFFFFFFu;
+			if (vs[u] != 0xFFFFFFFFu && !fbit_test(fcur_p, vs[u])) vs[u] = 0xFFFFFFFFu;
 #pragma unroll
 		for (int u = 0; u < U; u++) {
 			if (vs[u] != 0xFFFFFFFFu) {
-				Slice<SW> w = ldg_slice<SW>(a.visit + (size_t)vs[u] * WPV + t * SW);
+				if (STATS && t == 0) c_gath++;
+				Slice<SW> w = ldg_slice<SW>(visit_p + (size_t)vs[u] * WPV + t * SW);
 #pragma unroll
 				for (int i = 0; i < SW; i++) acc.w[i] |= w.w[i];
 			}
@@ -634,11 +829,19 @@ __global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
 			if (x) atomicOr(dst + i, x);
 		}
 	}
+	if (STATS) {
+		stat_add(&a.ctrl->k_scanned, c_scan);
+		stat_add(&a.ctrl->k_gathered, c_gath);
+	}
 }
 
 // one TPV-thread group per hub: next = hubacc & ~seen & active; seen |= next; hubacc = 0
 template <int W>
 __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
+	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
 	__shared__ uint32_t salive[16];
@@ -656,28 +859,33 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 		Slice<SW> act = ld_slice<SW>(a.ctrl->active + t * SW);
 #pragma unroll
 		for (int i = 0; i < SW; i++) news.w[i] = acc.w[i] & ~s.w[i] & act.w[i];
-		st_slice<SW>(a.next + wo, news);
-		if (slice_any<SW>(news)) {
+	}
+	const bool anyn = slice_any<SW>(news);
+	const bool gnew = group_any<TPV>(anyn);
+	if (h < a.nlist && (gnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
+		const uint32_t n = a.list[h];
+		const size_t wo = (size_t)n * WPV + (size_t)t * SW;
+		st_slice<SW>(next_p + wo, news);
+		if (anyn) {
+			Slice<SW> s = ld_slice<SW>(a.seen + wo);
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
 			st_slice<SW>(a.seen + wo, s);
 		}
 	}
-	const bool anyn = slice_any<SW>(news);
-	const bool gnew = group_any<TPV>(anyn);
 	const bool leader = gnew && t == 0 && h < a.nlist;
 	const uint32_t hn = h < a.nlist ? a.list[h] : 0u;
-	if (leader) atomicOr(&a.fnext[hn >> 5], 1u << (hn & 31));
+	if (leader) atomicOr(&fnext_p[hn >> 5], 1u << (hn & 31));
 	if (anyn) alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 	if (a.npeers && gnew && h < a.nlist) st_peers<SW>(a, (size_t)hn * WPV + (size_t)t * SW, news);
 }
 
 // After a pull level: vertices in the new frontier and the sum of their out-degrees (the inputs of
 // the direction switch), plus the `change` flag, from the frontier bitmap.  One atomic per block.
-__global__ void __launch_bounds__(256) frontier_stats_kernel(const uint32_t *__restrict__ fbit, uint32_t nwords,
-                                                             uint32_t V, const int64_t *__restrict__ off,
-                                                             BfsCtrl *ctrl) {
+__global__ void __launch_bounds__(256) frontier_stats_kernel(uint32_t nwords, uint32_t V,
+                                                             const int64_t *__restrict__ off, BfsCtrl *ctrl) {
 	constexpr uint32_t FULL = 0xffffffffu;
+	const uint32_t *const fbit = ctrl->L.nxt_fbit; // the frontier this level produced
 	__shared__ unsigned long long sdeg[8];
 	__shared__ uint32_t scnt[8];
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -735,19 +943,67 @@ __device__ __forceinline__ void enqueue_vertex(uint32_t n, const int64_t *off, u
 	atomicAdd(&ctrl->next_verts, 1u);
 }
 
+// Direction of the level about to run from the statistics of its input frontier (out_edges, out_verts)
+// -- the host loop of round 1, evaluated on the device by the init and check kernels.
+__device__ __forceinline__ uint32_t loop_pick_mode(const BfsCtrl *ctrl, const LoopState &L) {
+	const unsigned long long oe = ctrl->out_edges, ov = ctrl->out_verts;
+	// top-down while the frontier's out-edges are few
+	const bool push = L.direction == 0 && oe * L.push_beta <= L.E && ov * L.push_vbeta <= L.V + (unsigned long long)L.push_vbeta * 1024ull;
+	if (push) return MODE_PUSH;
+	// the bitmap test is dead weight once the frontier holds most of the edges
+	const bool filter = oe * L.filter_gamma <= L.E;
+	if (!filter) return MODE_PULL;
+	// "early": fewer vertex discoveries so far than vertices that can be discovered at all
+	return L.cum_verts < L.n_listed ? MODE_PULL_F_EARLY : MODE_PULL_F_LATE;
+}
+
+// rotating views of the level L.iter from cur / fb / q (and the level-buffer table of shortestpath)
+__device__ __forceinline__ void loop_set_views(LoopState &L) {
+	if (L.hist) {
+		L.cur_visit = L.hist[L.iter - 1];
+		L.cur_next = L.hist[L.iter];
+	} else {
+		L.cur_visit = L.visit[L.cur];
+		L.cur_next = L.visit[L.cur ^ 1];
+	}
+	L.cur_fbit = L.fbit[L.fb[0]];
+	L.nxt_fbit = L.fbit[L.fb[1]];
+	L.old_fbit = L.fbit[L.fb[2]];
+	L.cur_queue = L.queue[L.q];
+	L.nxt_queue = L.queue[L.q ^ 1];
+}
+
+// Per-batch parameters of the level loop (host -> init kernel, by value).
+struct LoopInit {
+	uint32_t *visit[2];
+	uint32_t *fbit[3];
+	uint2 *queue[2];
+	uint32_t *const *hist;
+	uint32_t hist_cap;
+	uint32_t level_cap;
+	uint32_t direction, push_beta, push_vbeta, filter_gamma;
+	unsigned long long E, V, n_listed;
+	const uint32_t *lane_dst;
+	uint32_t nk[MODE_COUNT];
+};
+
 // One block of W threads.  Sets the source bits (R4: visit only, seen untouched), the active mask,
-// found = -1, and the level-1 push queue (the distinct sources).  lane_src == 0xFFFFFFFF marks an
-// unused lane slot.  inq must be zero on entry.
-__global__ void bfs_init_kernel(const uint32_t *__restrict__ lane_src, int W, uint32_t *__restrict__ visit,
-                                int32_t *__restrict__ found, BfsCtrl *ctrl, const int64_t *__restrict__ off,
-                                uint2 *__restrict__ queue, uint32_t *__restrict__ inq) {
+// found = -1, the level-1 push queue (the distinct sources) and the loop state of level 1.
+// lane_src == 0xFFFFFFFF marks an unused lane slot.  The frontier bitmaps must be zero on entry.
+__global__ void bfs_init_kernel(const uint32_t *__restrict__ lane_src, int W, int32_t *__restrict__ found,
+                                BfsCtrl *ctrl, const int64_t *__restrict__ off, LoopInit li) {
 	__shared__ uint32_t cnt;
 	const int lane = threadIdx.x;
+	uint32_t *const visit = li.hist ? li.hist[0] : li.visit[0];
+	uint2 *const queue = li.queue[0];
+	uint32_t *const inq = li.fbit[0];
 	if (lane == 0) {
 		cnt = 0;
 		ctrl->change = 0; ctrl->change_out = 0;
 		ctrl->edges_lane = 0; ctrl->edges_unique = 0; ctrl->verts_active = 0;
 		ctrl->next_edges = 0; ctrl->next_verts = 0; ctrl->next_items = 0;
+		ctrl->k_listed = 0; ctrl->k_open = 0; ctrl->k_new = 0; ctrl->k_scanned = 0; ctrl->k_gathered = 0;
+		ctrl->kp_items = 0; ctrl->kp_edges = 0; ctrl->kp_seen = 0; ctrl->kp_next = 0;
 	}
 	__syncthreads();
 	const uint32_t s = lane_src[lane];
@@ -769,14 +1025,44 @@ __global__ void bfs_init_kernel(const uint32_t *__restrict__ lane_src, int W, ui
 		ctrl->n_active = cnt;
 		__threadfence();
 		snapshot_frontier(ctrl);
+		LoopState &L = ctrl->L;
+		for (int i = 0; i < 2; i++) { L.visit[i] = li.visit[i]; L.queue[i] = li.queue[i]; }
+		for (int i = 0; i < 3; i++) { L.fbit[i] = li.fbit[i]; L.fb[i] = (uint32_t)i; }
+		L.hist = li.hist;
+		L.hist_cap = li.hist_cap;
+		L.cur = 0; L.q = 0; L.have_queue = 1;
+		L.iter = 1;
+		L.level_cap = li.level_cap;
+		L.cum_verts = ctrl->out_verts;
+		L.direction = li.direction; L.push_beta = li.push_beta; L.push_vbeta = li.push_vbeta;
+		L.filter_gamma = li.filter_gamma;
+		L.E = li.E; L.V = li.V; L.n_listed = li.n_listed;
+		L.levels_run = 0; L.push_levels = 0;
+		L.stop_reason = 0;
+		L.lane_dst = li.lane_dst;
+		L.found = found;
+		for (int i = 0; i < (int)MODE_COUNT; i++) L.nk[i] = li.nk[i];
+		loop_set_views(L);
+		if (cnt == 0 || L.level_cap == 0) {
+			L.mode = MODE_STOP;
+			L.stop_reason = 1;
+		} else if (L.hist && L.hist_cap < 2) {
+			L.mode = MODE_STOP;
+			L.stop_reason = 2;
+		} else {
+			L.mode = loop_pick_mode(ctrl, L);
+		}
 	}
 }
 
 // After a level: lanes whose destination has been seen get found=iter and leave the active mask;
 // the frontier statistics of the level are snapshotted for the host's direction decision.
-__global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, const uint32_t *__restrict__ lane_dst, int W,
-                                 int32_t *__restrict__ found, BfsCtrl *ctrl, int iter,
-                                 uint32_t *__restrict__ alive_slots) {
+__global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, int W, BfsCtrl *ctrl,
+                                 uint32_t *__restrict__ alive_slots, int use_handles,
+                                 cudaGraphConditionalHandle h_while, cudaGraphConditionalHandle h_switch) {
+	const int iter = (int)ctrl->L.iter; // the level that just ran
+	const uint32_t *const lane_dst = ctrl->L.lane_dst;
+	int32_t *const found = ctrl->L.found;
 	__shared__ uint32_t cnt;
 	__shared__ uint32_t salive[16];
 	const int lane = threadIdx.x;
@@ -811,9 +1097,64 @@ __global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, const uint32
 	__syncthreads();
 	if (lane == 0) {
 		ctrl->n_active = cnt;
-		ctrl->change_out = ctrl->change;
+		const uint32_t changed = ctrl->change;
+		ctrl->change_out = changed;
 		ctrl->change = 0;
 		snapshot_frontier(ctrl);
+		// ---- the level loop's bookkeeping: the output of the level becomes the current frontier ----
+		LoopState &L = ctrl->L;
+		L.levels_run++;
+		ctrl->tot_levels++;
+		ctrl->tot_launches += L.nk[L.mode] + 1u; // + this kernel
+		if (L.mode == MODE_PUSH) { // the queue it built describes the new frontier
+			L.push_levels++;
+			ctrl->tot_push_levels++;
+			L.q ^= 1u;
+			L.have_queue = 1;
+		} else {
+			L.have_queue = 0;
+		}
+		L.cur ^= 1u;
+		const uint32_t t = L.fb[0];
+		L.fb[0] = L.fb[1];
+		L.fb[1] = L.fb[2];
+		L.fb[2] = t;
+		L.cum_verts += ctrl->out_verts;
+		L.iter = (uint32_t)iter + 1u;
+		if (!changed || cnt == 0 || (uint32_t)iter >= L.level_cap) {
+			L.mode = MODE_STOP;
+			L.stop_reason = 1;
+		} else if (L.hist && L.iter >= L.hist_cap) { // no buffer for the next level's output: the host extends the table
+			L.mode = MODE_STOP;
+			L.stop_reason = 2;
+		} else {
+			L.mode = loop_pick_mode(ctrl, L);
+		}
+		if (L.mode != MODE_STOP) loop_set_views(L); // a stopped loop keeps the views of its last level
+		if (use_handles) {
+			cudaGraphSetConditional(h_while, L.mode != MODE_STOP ? 1u : 0u);
+			cudaGraphSetConditional(h_switch, L.mode - 1u); // body index; MODE_STOP selects none
+		}
+	}
+}
+
+// First node of the loop graph: the conditional handles from the mode the init kernel (or the check
+// kernel of an interrupted loop) left behind.
+__global__ void loop_begin_kernel(BfsCtrl *ctrl, cudaGraphConditionalHandle h_while,
+                                  cudaGraphConditionalHandle h_switch) {
+	cudaGraphSetConditional(h_while, ctrl->L.mode != MODE_STOP ? 1u : 0u);
+	cudaGraphSetConditional(h_switch, ctrl->L.mode - 1u);
+}
+
+// The host extended the level-buffer table of an interrupted shortestpath batch: resume.
+__global__ void loop_resume_kernel(BfsCtrl *ctrl, uint32_t *const *hist, uint32_t hist_cap) {
+	LoopState &L = ctrl->L;
+	L.hist = hist;
+	L.hist_cap = hist_cap;
+	if (L.stop_reason == 2 && L.iter < hist_cap) {
+		L.stop_reason = 0;
+		L.mode = loop_pick_mode(ctrl, L);
+		loop_set_views(L);
 	}
 }
 
@@ -825,31 +1166,35 @@ __global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, const uint32
 struct PushArgs {
 	const int64_t *off;
 	const uint32_t *tgt;
-	const uint32_t *visit;
-	uint32_t *next;
 	uint32_t *seen;
-	BfsCtrl *ctrl;
-	const uint2 *queue;  // items of this level (count = ctrl->out_items)
-	uint2 *queue_next;   // items for the next level
-	uint32_t *fnext;     // frontier bitmap of `next` (doubles as the dedupe bitmap of queue_next)
+	BfsCtrl *ctrl; // frontier words, work queues and the next frontier's bitmap (= dedupe bitmap of the next
+	               // queue) are the level loop's rotating views in ctrl->L; item count = ctrl->out_items
 	uint32_t *alive_slots;
 };
 
-template <int W>
+template <int W, bool STATS = false>
 __global__ void __launch_bounds__(256) push_kernel(PushArgs a) {
 	constexpr int WPV = W / 32;
+	uint32_t c_scan = 0, c_gath = 0, c_items = 0, c_new = 0; // STATS
 	__shared__ uint32_t salive[16];
 	alive_init(salive, a.alive_slots);
+	const LoopState &L = a.ctrl->L;
+	const uint32_t *const visit_p = L.cur_visit;
+	uint32_t *const next_p = L.cur_next;
+	uint32_t *const fnext_p = L.nxt_fbit;
+	const uint2 *const queue_p = L.cur_queue;
+	uint2 *const queue_next_p = L.nxt_queue;
 	const uint32_t nitems = a.ctrl->out_items;
 	const uint32_t lane = threadIdx.x & 31;
 	const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
 	bool anynew = false;
 	for (uint32_t it = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; it < nitems; it += nwarps) {
-		const uint2 item = a.queue[it];
+		const uint2 item = queue_p[it];
 		const uint32_t v = item.x;
 		uint32_t word = 0;
-		if (lane < WPV) word = a.visit[(size_t)v * WPV + lane] & a.ctrl->active[lane];
+		if (lane < WPV) word = visit_p[(size_t)v * WPV + lane] & a.ctrl->active[lane];
 		const unsigned nz = __ballot_sync(0xffffffffu, word != 0);
+		if (STATS && lane == 0) c_items++;
 		if (nz == 0) continue;
 		const int64_t e0 = a.off[v] + (int64_t)item.y * PUSH_CHUNK;
 		int64_t e1 = a.off[v + 1];
@@ -858,6 +1203,7 @@ __global__ void __launch_bounds__(256) push_kernel(PushArgs a) {
 			const int64_t j = j0 + lane;
 			const bool have = j < e1;
 			const uint32_t n = have ? a.tgt[j] : 0u;
+			if (STATS && have) c_scan++;
 			bool mynew = false;
 			unsigned rem = nz;
 			while (rem) { // warp-uniform loop over the non-empty words of visit[v]
@@ -867,8 +1213,10 @@ __global__ void __launch_bounds__(256) push_kernel(PushArgs a) {
 				if (have) {
 					const uint32_t old = atomicOr(&a.seen[(size_t)n * WPV + w], bits);
 					const uint32_t nb = bits & ~old;
+					if (STATS) c_gath++;
 					if (nb) {
-						atomicOr(&a.next[(size_t)n * WPV + w], nb);
+						if (STATS) c_new++;
+						atomicOr(&next_p[(size_t)n * WPV + w], nb);
 						alive_note<1>(salive, a.alive_slots, (uint32_t)w, &nb);
 						mynew = true;
 					}
@@ -878,7 +1226,7 @@ __global__ void __launch_bounds__(256) push_kernel(PushArgs a) {
 			if (mynew) {
 				anynew = true;
 				const uint32_t bit = 1u << (n & 31);
-				enq = !(atomicOr(&a.fnext[n >> 5], bit) & bit);
+				enq = !(atomicOr(&fnext_p[n >> 5], bit) & bit);
 			}
 			// Warp-aggregated enqueue: the three queue counters are single addresses, and a level-1 push
 			// discovers tens of thousands of vertices -- one atomic per warp step instead of three per vertex.
@@ -908,18 +1256,24 @@ __global__ void __launch_bounds__(256) push_kernel(PushArgs a) {
 					atomicAdd(&a.ctrl->next_verts, (uint32_t)__popc(em));
 				}
 				base = __shfl_sync(0xffffffffu, base, 0) + inc - k;
-				for (uint32_t ch = 0; ch < k; ch++) a.queue_next[base + ch] = make_uint2(n, ch);
+				for (uint32_t ch = 0; ch < k; ch++) queue_next_p[base + ch] = make_uint2(n, ch);
 			}
 		}
 	}
 	if (__any_sync(0xffffffffu, anynew) && lane == 0) a.ctrl->change = 1u;
+	if (STATS) {
+		stat_add(&a.ctrl->kp_items, c_items);
+		stat_add(&a.ctrl->kp_edges, c_scan);
+		stat_add(&a.ctrl->kp_seen, c_gath);
+		stat_add(&a.ctrl->kp_next, c_new);
+	}
 }
 
 // Before a push level: the `next` buffer still holds the frontier of two levels ago, described by
 // its bitmap.  Zero exactly those words, then the bitmap (cost ~ that frontier, not V).
 template <int W>
-__global__ void __launch_bounds__(256) clear_by_bitmap_kernel(uint32_t *__restrict__ fbit, uint32_t nwords,
-                                                              uint32_t *__restrict__ visit) {
+__device__ __forceinline__ void clear_by_bitmap_body(uint32_t *__restrict__ fbit, uint32_t nwords,
+                                                     uint32_t *__restrict__ visit) {
 	// One warp per 32 bitmap words (1024 vertices).  The words a stale frontier leaves behind are 16-64 bytes
 	// each and often neighbours: the warp walks the set bits of one bitmap word at a time and zeroes 32 / Q
 	// vertices per store instruction, Q = 16-byte quarters per vertex word handled by Q adjacent lanes
@@ -956,12 +1310,54 @@ __global__ void __launch_bounds__(256) clear_by_bitmap_kernel(uint32_t *__restri
 	}
 }
 
+template <int W>
+__global__ void __launch_bounds__(256) clear_by_bitmap_kernel(uint32_t *__restrict__ fbit, uint32_t nwords,
+                                                              uint32_t *__restrict__ visit) {
+	clear_by_bitmap_body<W>(fbit, nwords, visit);
+}
+
+// Start of every level of the loop: the buffer that becomes `next` still holds the frontier of two
+// levels ago, named by old_fbit.  Zero exactly those words and that bitmap (which is the one the level
+// after this builds); afterwards `next` is all-zero, so the level kernels store only words that gained
+// bits.  words == 0 (shortestpath: `next` is a fresh level buffer): only the bitmap is zeroed.
+template <int W>
+__global__ void __launch_bounds__(256) level_clear_kernel(BfsCtrl *ctrl, uint32_t nwords, int words) {
+	const LoopState &L = ctrl->L;
+	// words == 2 (dense-store level: every listed vertex rewrites its word): only level 2 scrubs, because
+	// `next` then still holds the source words, some at in-degree-0 vertices that no class list names
+	if (words == 1 || (words == 2 && L.iter == 2)) {
+		clear_by_bitmap_body<W>(L.old_fbit, nwords, L.cur_next);
+	} else {
+		const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i < nwords) L.old_fbit[i] = 0;
+	}
+}
+
+// Start of a batch that reuses the frontier buffers of the previous batch of this worker: their only
+// non-zero words are the ones the bitmaps of its last two frontiers name (ctrl->L as that batch left
+// it).  which = 0: the last `visit` buffer / its bitmap, 1: the last `next` buffer / the bitmap before.
+template <int W>
+__global__ void __launch_bounds__(256) scrub_kernel(BfsCtrl *ctrl, uint32_t nwords, int which) {
+	const LoopState &L = ctrl->L;
+	if (which == 0) clear_by_bitmap_body<W>(L.fbit[L.fb[0]], nwords, L.visit[L.cur]);
+	else clear_by_bitmap_body<W>(L.fbit[L.fb[2]], nwords, L.visit[L.cur ^ 1]);
+}
+
+// shortestpath: zero the level buffer the level about to run writes (16 bytes per thread and step)
+__global__ void __launch_bounds__(256) zero_next_kernel(BfsCtrl *ctrl, size_t n16) {
+	uint4 *p = reinterpret_cast<uint4 *>(ctrl->L.cur_next);
+	const size_t stride = (size_t)gridDim.x * blockDim.x;
+	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) p[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
 // pull -> push transition: rebuild the work queue from the frontier bitmap.  One thread per bitmap
 // word, two passes (count items, warp-scan, one atomic per warp, write).  The vertex / edge totals
 // of this frontier were already published by frontier_stats_kernel; only the item count is new.
-__global__ void __launch_bounds__(256) compact_bitmap_kernel(const uint32_t *__restrict__ fbit, uint32_t nwords,
-                                                             uint32_t V, const int64_t *__restrict__ off,
-                                                             uint2 *__restrict__ queue, BfsCtrl *ctrl) {
+__global__ void __launch_bounds__(256) compact_bitmap_kernel(uint32_t nwords, uint32_t V,
+                                                             const int64_t *__restrict__ off, BfsCtrl *ctrl) {
+	if (ctrl->L.have_queue) return; // the previous level was top-down too: its output queue is the input
+	const uint32_t *const fbit = ctrl->L.cur_fbit;
+	uint2 *const queue = const_cast<uint2 *>(ctrl->L.cur_queue);
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	const uint32_t lane = threadIdx.x & 31;
 	const uint32_t m = i < nwords ? fbit[i] : 0u;
@@ -997,6 +1393,7 @@ __global__ void __launch_bounds__(256) compact_bitmap_kernel(const uint32_t *__r
 
 // publish the rebuilt queue's item count
 __global__ void bfs_snapshot_items_kernel(BfsCtrl *ctrl) {
+	if (ctrl->L.have_queue) return;
 	ctrl->out_items = ctrl->next_items;
 	ctrl->next_items = 0;
 }

@@ -58,16 +58,40 @@ typedef struct {
 	uint64_t d2h_bytes;
 	uint64_t coll_bytes;      /* bytes this rank contributed to per-level collectives (partitioned path) */
 	double coll_ms;           /* CUDA-event time of those collectives ("timing"=1) */
+	/* what the level kernels of THIS implementation touched ("stats"=1, instrumented instantiations;
+	 * DESIGN.md section 4 turns these into model_bytes, the numerator of bench.py's roofline.frac) */
+	uint64_t model_bytes;     /* bytes this algorithm must move for the levels it ran (no cache credit) */
+	uint64_t k_listed;        /* pull: class-list entries visited */
+	uint64_t k_open;          /* pull: vertices whose `seen` word was read (not yet done) */
+	uint64_t k_new;           /* pull: vertices that stored a `next` word and rewrote `seen` */
+	uint64_t k_scanned;       /* pull: in-edges whose source id was read */
+	uint64_t k_gathered;      /* pull: frontier words gathered */
+	uint64_t kp_items;        /* push: work items */
+	uint64_t kp_edges;        /* push: out-edges whose target id was read */
+	uint64_t kp_seen;         /* push: 4-byte atomicOr on `seen` */
+	uint64_t kp_next;         /* push: 4-byte atomicOr on `next` */
+	uint64_t host_syncs;      /* stream synchronisations issued inside MS-BFS batches (level loop) */
 } pgq_stats_t;
 
 /* ---- context ------------------------------------------------------------------------- */
 int pgq_init(int device, pgq_ctx_t **out_ctx);
+/* Multi-GPU context for a single-process host (DuckDB is one process with worker threads:
+ * /root/reference/src/parallel/task_scheduler.cpp:163-195).  devices[0] is the primary: CSRs are built
+ * there; the first query that has enough batches copies the query-side arrays to the other devices over
+ * NVLink (peer copies) and from then on every iterativelength / reachability / shortestpath call deals
+ * its 512-lane batches round-robin over all devices (source-batch sharding, no data-path collective).
+ * Same entry points, same results as a one-device context. */
+int pgq_init_devices(const int *devices, int n, pgq_ctx_t **out_ctx);
+int pgq_device_count(pgq_ctx_t *ctx, int *out_n);
 int pgq_shutdown(pgq_ctx_t *ctx);
 const char *pgq_last_error(void); /* thread-local message of the last failing call */
 
 /* options: "lanes" (0=auto, 64,128,256,512), "stats" (0/1), "timing" (0/1),
  *          "small_max", "hub_min" (in-degree bin thresholds), "direction" (0 auto, 1 pull only),
- *          "push_beta" (top-down when frontier out-edges * beta <= E) */
+ *          "push_beta" (top-down when frontier out-edges * beta <= E),
+ *          "loop" (1 = level loop on the device as a CUDA graph with WHILE/SWITCH nodes, 0 = host loop),
+ *          "streams" (batches of one call in flight per device), "devices_used" (multi-GPU contexts),
+ *          "done_bitmap", "l2_persist" (measurement switches), "hist_budget_mb" (shortestpath level history) */
 int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value);
 int pgq_get_stats(pgq_ctx_t *ctx, pgq_stats_t *out);
 int pgq_reset_stats(pgq_ctx_t *ctx);

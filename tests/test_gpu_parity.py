@@ -676,3 +676,141 @@ def test_batches_in_flight(ctx, streams):
     assert_paths_equal(got, exp, "streams %d" % streams)
     assert st["batches"] >= 16
     ctx.csr_delete(1)
+
+
+# ---- round 2: device-side level loop, done bitmap, level-history budget, multi-GPU context ----------------
+def _rmat_case(ctx, scale, n, seed=21):
+    V = 1 << scale
+    src, dst = orc.gen_rmat(0x5eed0000 + scale, scale)
+    v, e, eids = _build_both(ctx, V, src, dst)
+    ps, pd = orc.gen_pairs(seed, V, v, n)
+    return V, v, e, eids, ps, pd
+
+
+def test_device_loop_has_no_host_sync_and_equals_host_loop(ctx):
+    """The level loop runs as one CUDA graph (WHILE + SWITCH nodes) per batch: between the init kernel and
+    the result copy the host never waits (stats.host_syncs == 0), and the answers equal the host-driven
+    loop's and the oracle's."""
+    V, v, e, eids, ps, pd = _rmat_case(ctx, 14, 1500)
+    eo, ev = orc.iterativelength(V, v, e, ps, pd)
+    res = {}
+    try:
+        ctx.set_option("small_path", 0)
+        for loop in (1, 0):
+            ctx.set_option("loop", loop)
+            ctx.reset_stats()
+            out, ov = ctx.iterativelength(1, ps, pd)
+            st = ctx.stats()
+            _cmp_arr("valid loop=%d" % loop, ov, ev)
+            _cmp_arr("length loop=%d" % loop, out, eo)
+            res[loop] = st
+    finally:
+        ctx.set_option("loop", 1)
+    assert res[1]["host_syncs"] == 0, "device loop fell back to the host loop: %s" % res[1]
+    assert res[0]["host_syncs"] >= res[0]["levels"] > 0
+    assert res[1]["levels"] == res[0]["levels"] and res[1]["push_levels"] == res[0]["push_levels"]
+    assert res[1]["batches"] == res[0]["batches"] == 3
+    ctx.csr_delete(1)
+
+
+@pytest.mark.parametrize("done,l2p", [(0, 0), (1, 1)])
+def test_done_bitmap_and_l2_window_do_not_change_results(ctx, done, l2p):
+    V, v, e, eids, ps, pd = _rmat_case(ctx, 13, 700, seed=5)
+    ctx.set_option("done_bitmap", done)
+    ctx.set_option("l2_persist", l2p)
+    try:
+        out, ov = ctx.iterativelength(1, ps, pd)
+        got = ctx.shortestpath(1, ps[:300], pd[:300], mode=1)
+    finally:
+        ctx.set_option("done_bitmap", 1)
+        ctx.set_option("l2_persist", 0)
+    eo, ev = orc.iterativelength(V, v, e, ps, pd)
+    _cmp_arr("valid", ov, ev)
+    _cmp_arr("length", out, eo)
+    assert_paths_equal(got, orc.shortestpath(V, v, e, eids, ps[:300], pd[:300], mode=1), "done=%d" % done)
+    ctx.csr_delete(1)
+
+
+def test_level_history_budget(ctx):
+    """shortestpath keeps one frontier buffer per level.  When a batch's history would exceed its budget the
+    batch is redone with 64-lane words (8x fewer bytes per level), beyond that the call fails with a message
+    naming the option -- never a raw allocation error; results are unchanged by the narrowing."""
+    import pgq_b200
+    n = 8000
+    src = np.arange(n - 1, dtype=np.int64)
+    dst = src + 1
+    v, e, eids = _build_both(ctx, n, src, dst)
+    rng = np.random.default_rng(9)
+    qs = rng.integers(0, 200, 300).astype(np.int64)
+    qd = (qs + rng.integers(1, 120, 300)).astype(np.int64)  # up to 120 levels
+    qs[7] = qd[7]
+    exp = orc.shortestpath(n, v, e, eids, qs, qd, mode=1)
+    ctx.set_option("lanes", 512)
+    try:
+        ctx.set_option("hist_budget_mb", 16)  # 512 lanes: 512 KB per level -> 32 levels; 64 lanes: 256 levels
+        got = ctx.shortestpath(1, qs, qd, mode=1)
+        assert_paths_equal(got, exp, "narrowed history")
+        ctx.set_option("hist_budget_mb", 1)  # 64 lanes: 16 levels -- not enough for 120
+        with pytest.raises(pgq_b200.PgqError, match="hist_budget_mb"):
+            ctx.shortestpath(1, qs, qd, mode=1)
+        ctx.set_option("hist_budget_mb", 0)
+        got = ctx.shortestpath(1, qs, qd, mode=0)
+        assert_paths_equal(got, orc.shortestpath(n, v, e, eids, qs, qd, mode=0), "default budget")
+    finally:
+        ctx.set_option("hist_budget_mb", 0)
+        ctx.set_option("lanes", 0)
+    ctx.csr_delete(1)
+
+
+def test_model_byte_counters(ctx):
+    """Instrumented pass (stats=1): what the level kernels touched, the numerator of bench.py's roofline."""
+    V, v, e, eids, ps, pd = _rmat_case(ctx, 14, 512, seed=2)
+    ctx.set_option("small_path", 0)
+    ctx.set_option("stats", 1)
+    try:
+        ctx.reset_stats()
+        out, ov = ctx.iterativelength(1, ps, pd)
+        st = ctx.stats()
+    finally:
+        ctx.set_option("stats", 0)
+    eo, ev, est = orc.iterativelength(V, v, e, ps, pd, stats=True)
+    _cmp_arr("length", out, eo)
+    assert st["edges_lane"] == est["edges_lane"]
+    assert st["k_listed"] > 0 and st["k_open"] > 0 and st["k_new"] > 0
+    assert st["k_scanned"] >= st["k_gathered"] > 0
+    assert st["k_open"] <= st["k_listed"]
+    E = len(e)
+    assert st["k_scanned"] <= E * st["levels"]
+    lower = st["k_gathered"] * 64 + st["k_scanned"] * 4
+    assert lower < st["model_bytes"] < st["algo_bytes"] * 4
+    ctx.csr_delete(1)
+
+
+def test_multi_gpu_context_one_process(ctx):
+    """pgq_init_devices: ONE process, the batches of one call dealt over several GPUs (CSR replicated over
+    NVLink on first use): same answers as one device, for lengths, reachability and paths."""
+    import pgq_b200
+    from conftest import gpu_count
+    ng = gpu_count()
+    if ng < 2:
+        pytest.skip("needs >= 2 GPUs")
+    V, v, e, eids, ps, pd = _rmat_case(ctx, 14, 4096, seed=8)
+    ctx.csr_delete(1)
+    src, dst = orc.gen_rmat(0x5eed0000 + 14, 14)
+    m = pgq_b200.Context(devices=list(range(min(ng, 4))))
+    try:
+        m.set_option("small_path", 0)
+        m.set_option("lanes", 64)  # 64 batches
+        m.csr_build(3, V, src, dst, rowids=True)
+        out, ov = m.iterativelength(3, ps, pd)
+        r, rv = m.reachability(3, ps, pd)
+        got = m.shortestpath(3, ps[:1000], pd[:1000], mode=1)
+        st = m.stats()
+    finally:
+        m.close()
+    eo, ev = orc.iterativelength(V, v, e, ps, pd)
+    _cmp_arr("valid", ov, ev)
+    _cmp_arr("length", out, eo)
+    assert r.tolist() == [int(x) for x in ev]
+    assert_paths_equal(got, orc.shortestpath(V, v, e, eids, ps[:1000], pd[:1000], mode=1), "multi-gpu paths")
+    assert st["batches"] >= 64
