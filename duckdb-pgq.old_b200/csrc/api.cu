@@ -91,7 +91,8 @@ static int finalize(Ctx *c, Csr *g) {
 		set_error("create_csr_edge: got %lld rows, num_edges said %lld", (long long)g->uploaded, (long long)g->E);
 		return PGQ_ERR_MISMATCH;
 	}
-	PGQ_TRY(csr_device_build(c, g));
+	const int rc = csr_device_build(c, g);
+	// the 16-24 B/edge staging copies go whether the build worked or not
 	g->d_src64.release();
 	g->d_dst64.release();
 	g->d_eid64.release();
@@ -100,6 +101,11 @@ static int finalize(Ctx *c, Csr *g) {
 	pinned_release(g->h_eid, g->h_bytes);
 	g->h_src = g->h_dst = g->h_eid = nullptr;
 	g->staged_cap = 0;
+	if (rc != PGQ_OK) { // back to "vertices only": the edge rows can be sent again after pgq_csr_begin_edges
+		g->state = Csr::CREATED;
+		g->uploaded = g->staged = 0;
+		return rc;
+	}
 	g->state = Csr::READY;
 	return PGQ_OK;
 }
@@ -469,7 +475,7 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "sort_wide_min")) c->opt.sort_wide_min = value < 0 ? 0 : value;
 	else if (!strcmp(key, "streams")) c->opt.streams = value < 1 ? 1 : value > 16 ? 16 : value;
 	else if (!strcmp(key, "loop")) c->opt.loop = value;
-	else if (!strcmp(key, "done_bitmap")) c->opt.done_bitmap = value < 0 ? 0 : value > 2 ? 2 : value;
+	else if (!strcmp(key, "done_bitmap")) c->opt.done_bitmap = value ? 1 : 0;
 	else if (!strcmp(key, "dense_store")) c->opt.dense_store = value ? 1 : 0;
 	else if (!strcmp(key, "l2_persist")) c->opt.l2_persist = value;
 	else if (!strcmp(key, "hist_budget_mb")) c->opt.hist_budget_mb = value < 0 ? 0 : value;
@@ -554,8 +560,15 @@ int pgq_csr_begin_edges(pgq_ctx_t *ctx, int32_t id, int64_t e_size) {
 	LOCK(ctx);
 	Csr *g = find_csr(c, id);
 	if (!g) return PGQ_ERR_INVALID;
+	if (g->state != Csr::CREATED || g->pending_begin) { // a built (or half-built) graph is never reopened silently
+		set_error("create_csr_edge: csr %d already has its edge array (delete it or re-create it first)", id);
+		return PGQ_ERR_STATE;
+	}
+	if (e_size < 0) {
+		set_error("negative edge count");
+		return PGQ_ERR_INVALID;
+	}
 	g->E = e_size;
-	g->state = Csr::CREATED;
 	g->pending_begin = true;
 	return PGQ_OK;
 }
@@ -587,7 +600,14 @@ int pgq_csr_add_edges(pgq_ctx_t *ctx, int32_t id, const int64_t *src, const int6
 		g->h_src = static_cast<int64_t *>(pinned_acquire(bytes, &g->h_bytes));
 		g->h_dst = static_cast<int64_t *>(pinned_acquire(bytes, &g->h_bytes));
 		if (g->have_eid) g->h_eid = static_cast<int64_t *>(pinned_acquire(bytes, &g->h_bytes));
-		if (!g->h_src || !g->h_dst || (g->have_eid && !g->h_eid)) return PGQ_ERR_OOM;
+		if (!g->h_src || !g->h_dst || (g->have_eid && !g->h_eid)) { // all or nothing: a retry allocates again
+			pinned_release(g->h_src, g->h_bytes);
+			pinned_release(g->h_dst, g->h_bytes);
+			pinned_release(g->h_eid, g->h_bytes);
+			g->h_src = g->h_dst = g->h_eid = nullptr;
+			g->staged_cap = 0;
+			return PGQ_ERR_OOM;
+		}
 	}
 	int64_t done = 0;
 	while (done < n) {
@@ -965,10 +985,10 @@ int pgq_reachability(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, 
 	return query_lengths(c, id, n, src, dst, src_valid, dst_valid, nullptr, out, out_valid);
 }
 
-int pgq_shortestpath(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
-                     const uint8_t *src_valid, const uint8_t *dst_valid, int mode, pgq_list_entry_t *entries,
-                     uint8_t *out_valid, int64_t **out_vals, uint64_t *out_total) {
-	LOCK(ctx);
+static int shortestpath_common(Ctx *c, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                               const uint8_t *src_valid, const uint8_t *dst_valid, int mode,
+                               pgq_list_entry_t *entries, uint8_t *out_valid, int64_t **out_vals,
+                               pgq_reserve_fn reserve, void *user, uint64_t *out_total) {
 	Csr *g = find_csr(c, id);
 	if (!g) return PGQ_ERR_INVALID;
 	if (g->state != Csr::READY) {
@@ -987,9 +1007,12 @@ int pgq_shortestpath(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, 
 		set_error("shortestpath mode 1 needs a csr built with edge ids");
 		return PGQ_ERR_STATE;
 	}
-	*out_vals = nullptr;
+	if (out_vals) *out_vals = nullptr;
 	*out_total = 0;
-	if (n <= 0) return PGQ_OK;
+	if (n <= 0) {
+		if (reserve) (void)reserve(user, 0);
+		return PGQ_OK;
+	}
 	LaneTable lt;
 	PGQ_TRY(build_lane_table(c, g, n, src, dst, src_valid, dst_valid, &lt));
 	std::vector<int32_t> found((size_t)lt.nbatch * lt.W, -1);
@@ -997,7 +1020,13 @@ int pgq_shortestpath(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, 
 	po.mode = mode;
 	po.entries = entries;
 	po.valid = out_valid;
+	po.sink = reserve;
+	po.sink_user = user;
 	PGQ_TRY(msbfs_run(c, g, lt, found.data(), &po, src, n));
+	if (reserve) {
+		*out_total = po.total;
+		return PGQ_OK;
+	}
 	int64_t *vals = (int64_t *)malloc((po.vals.size() ? po.vals.size() : 1) * sizeof(int64_t));
 	if (!vals) {
 		set_error("host allocation failed");
@@ -1007,6 +1036,24 @@ int pgq_shortestpath(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, 
 	*out_vals = vals;
 	*out_total = po.vals.size();
 	return PGQ_OK;
+}
+
+int pgq_shortestpath(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                     const uint8_t *src_valid, const uint8_t *dst_valid, int mode, pgq_list_entry_t *entries,
+                     uint8_t *out_valid, int64_t **out_vals, uint64_t *out_total) {
+	LOCK(ctx);
+	if (!out_vals || !out_total) return PGQ_ERR_INVALID;
+	return shortestpath_common(c, id, n, src, dst, src_valid, dst_valid, mode, entries, out_valid, out_vals, nullptr,
+	                           nullptr, out_total);
+}
+
+int pgq_shortestpath_sink(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                          const uint8_t *src_valid, const uint8_t *dst_valid, int mode, pgq_list_entry_t *entries,
+                          uint8_t *out_valid, pgq_reserve_fn reserve, void *user, uint64_t *out_total) {
+	LOCK(ctx);
+	if (!reserve || !out_total) return PGQ_ERR_INVALID;
+	return shortestpath_common(c, id, n, src, dst, src_valid, dst_valid, mode, entries, out_valid, nullptr, reserve,
+	                           user, out_total);
 }
 
 void pgq_free(void *p) {

@@ -326,6 +326,10 @@ struct PathOut {
 	pgq_list_entry_t *entries = nullptr; // per row
 	uint8_t *valid = nullptr;            // per row
 	std::vector<int64_t> vals;
+	// when set: asked once for the final buffer of `total` values (the caller's list child buffer); vals stays empty
+	int64_t *(*sink)(void *user, uint64_t total) = nullptr;
+	void *sink_user = nullptr;
+	uint64_t total = 0;
 };
 int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *paths,
               const int64_t *row_src /*host, for trivial rows in path mode*/, int64_t nrows);

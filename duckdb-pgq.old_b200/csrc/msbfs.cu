@@ -148,7 +148,10 @@ int launch_body(Ctx *c, Csr *g, const BatchBufs &b, uint32_t mode, bool keep_his
 		a.done = b.done;
 		a.dyn = 1;
 		a.dense = dense ? 1u : 0u;
-		a.use_done = (b.done && (mode == MODE_PULL_F_LATE || c->opt.done_bitmap == 2)) ? 1u : 0u;
+		// the done test only on sparse-store tail levels: a skipped vertex stores nothing, and a dense level relies
+		// on every listed vertex overwriting what `next` still holds (testing it everywhere left stale frontier
+		// words behind: measured wrong frontiers from level 2 of the NEXT batch on)
+		a.use_done = (b.done && mode == MODE_PULL_F_LATE) ? 1u : 0u;
 		launch_tiny<W, STATS>(a, g, filter, st, nk);
 		// measured on the filtered levels of R-MAT s24 (levels 2 / 6): pull_list 2.23 / 0.62 ms, 8 lanes per
 		// vertex 2.08 / 0.56 ms, 16 lanes 2.31 / 0.73 ms; the same kernel for the tiny class: no change
@@ -607,6 +610,9 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 		hist_cap = c->bfs_hist.size() >= 16 ? c->bfs_hist.size() : 16;
 		int rc = hist_reserve(c, hist_cap, bm);
 		if (rc == PGQ_HIST_OVER && hist_cap > 2) {
+			// what earlier calls left allocated no longer fits the budget: give it back, start from two levels
+			PGQ_CUDA(cudaStreamSynchronize(st));
+			hist_trim(c);
 			hist_cap = 2;
 			rc = hist_reserve(c, hist_cap, bm);
 		}
@@ -673,11 +679,14 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 			if (!keep_hist) break;
 			PGQ_TRY(read_ctrl(c, b, &h)); // shortestpath sizes its output on the host anyway
 			if (h.L.stop_reason != 2) break;
-			const size_t want = hist_cap * 2;
+			size_t want = hist_cap * 2;
 			int rc = hist_reserve(c, want, bm);
-			if (rc == PGQ_HIST_OVER) rc = hist_reserve(c, hist_cap + 1, bm) == PGQ_OK ? PGQ_OK : PGQ_HIST_OVER;
+			if (rc == PGQ_HIST_OVER) {
+				want = hist_cap + 1;
+				rc = hist_reserve(c, want, bm);
+			}
 			if (rc != PGQ_OK) return rc;
-			hist_cap = c->bfs_hist.size();
+			hist_cap = want;
 			loop_resume_kernel<<<1, 1, 0, st>>>(b.ctrl, c->bfs_hist_tab.as<uint32_t *const>(), (uint32_t)hist_cap);
 			count_launch(c);
 		}
@@ -690,10 +699,14 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 		PGQ_TRY(read_ctrl(c, b, &h));
 		while (h.L.mode != MODE_STOP || h.L.stop_reason == 2) {
 			if (h.L.stop_reason == 2) { // level history full
-				int rc = hist_reserve(c, hist_cap * 2, bm);
-				if (rc == PGQ_HIST_OVER) rc = hist_reserve(c, hist_cap + 1, bm) == PGQ_OK ? PGQ_OK : PGQ_HIST_OVER;
+				size_t want = hist_cap * 2;
+				int rc = hist_reserve(c, want, bm);
+				if (rc == PGQ_HIST_OVER) {
+					want = hist_cap + 1;
+					rc = hist_reserve(c, want, bm);
+				}
 				if (rc != PGQ_OK) return rc;
-				hist_cap = c->bfs_hist.size();
+				hist_cap = want;
 				loop_resume_kernel<<<1, 1, 0, st>>>(b.ctrl, c->bfs_hist_tab.as<uint32_t *const>(), (uint32_t)hist_cap);
 				count_launch(c);
 				PGQ_TRY(read_ctrl(c, b, &h));
@@ -1221,12 +1234,24 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 		uint64_t total = 0; // running list offset over all rows
 		for (auto &bs : segs)
 			for (PathSeg &s : bs) total += s.vals.size();
-		paths->vals.resize(total);
+		int64_t *dstp = nullptr;
+		if (paths->sink) { // straight into the caller's buffer (the DuckDB shim: the LIST child vector)
+			dstp = paths->sink(paths->sink_user, total);
+			if (!dstp && total) {
+				set_error("shortestpath: the caller's reserve callback returned no buffer for %llu values",
+				          (unsigned long long)total);
+				return PGQ_ERR_OOM;
+			}
+		} else {
+			paths->vals.resize(total);
+			dstp = paths->vals.data();
+		}
+		paths->total = total;
 		total = 0;
 		for (auto &bs : segs)
 			for (PathSeg &s : bs) {
 				for (int64_t r = s.r0; r < s.r1; r++) paths->entries[r].offset += total;
-				if (!s.vals.empty()) memcpy(paths->vals.data() + total, s.vals.data(), s.vals.size() * sizeof(int64_t));
+				if (!s.vals.empty()) memcpy(dstp + total, s.vals.data(), s.vals.size() * sizeof(int64_t));
 				total += s.vals.size();
 			}
 	}

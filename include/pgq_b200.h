@@ -145,6 +145,15 @@ int pgq_shortestpath(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, 
                      pgq_list_entry_t *entries, uint8_t *out_valid, int64_t **out_vals,
                      uint64_t *out_total);
 void pgq_free(void *p);
+/* The same, with the values written straight into a buffer of the caller: once the total number of values is
+ * known `reserve(user, total)` is called exactly once (also for total == 0) and returns where the `total`
+ * int64 values go -- the DuckDB shim answers with ListVector::Reserve + the child vector's data pointer
+ * (/root/reference/src/function/scalar/list/range.cpp:118-149), so no intermediate malloc / memcpy. */
+typedef int64_t *(*pgq_reserve_fn)(void *user, uint64_t total);
+int pgq_shortestpath_sink(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
+                          const uint8_t *src_valid, const uint8_t *dst_valid, int mode,
+                          pgq_list_entry_t *entries, uint8_t *out_valid, pgq_reserve_fn reserve, void *user,
+                          uint64_t *out_total);
 
 /* ---- weighted next row ------------------------------------------------------
  * Replaces the 7-argument create_csr_edge(csr_id, v_size, num_edges, src, dst, edge_rowid, weight)
