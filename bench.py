@@ -43,6 +43,10 @@ def parse():
     ap.add_argument("--no-csr", action="store_true")
     ap.add_argument("--no-paths", action="store_true")
     ap.add_argument("--cpu-threads", type=int, default=0)
+    ap.add_argument("--ref-seconds", type=float, default=240.0,
+                    help="--impl reference: wall-clock box for the timed CPU passes")
+    ap.add_argument("--loop", type=int, default=1,
+                    help="1 = device-side level loop (CUDA graph), 0 = host-driven loop (one sync per level)")
     ap.add_argument("--streams", type=int, default=0,
                     help="batches of one call in flight at once (0 = library default)")
     return ap.parse_args()
@@ -107,6 +111,56 @@ def make_pairs(V, v_off, n, seed):
     same = src == dst
     dst[same] = cand[(np.searchsorted(cand, dst[same]) + 1) % len(cand)]
     return src, dst
+
+
+def lib_hash():
+    """sha256 (16 hex digits) of the built CUDA library: measured-traffic profiles are tied to it."""
+    import hashlib
+    import pgq_b200
+    try:
+        return hashlib.sha256(open(pgq_b200.LIB_PATH, "rb").read()).hexdigest()[:16]
+    except Exception:
+        return None
+
+
+def src_hash():
+    """sha256 (16 hex digits) over the kernel sources: survives a rebuild of the same code on another box."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "duckdb-pgq.old_b200", "csrc", "*.cu*"))):
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
+
+
+def load_traffic(name, want):
+    """Measured DRAM bytes from a committed ncu summary (profiles/<name>), or (None, why).  The summary
+    must have been taken on the same kernel sources and the same workload keys (`want`), else it is stale and
+    NOT applied (a constant file silently going stale)."""
+    path = os.path.join(ROOT, "profiles", name)
+    try:
+        prof = json.load(open(path))
+    except Exception:
+        return None, "no profiles/%s" % name
+    if prof.get("src_hash") != src_hash():
+        return None, "profiles/%s was taken on other kernel sources (src_hash %s != %s)" % (
+            name, prof.get("src_hash"), src_hash())
+    for k, v in want.items():
+        if prof.get(k) != v:
+            return None, "profiles/%s was taken at %s=%s, this run has %s" % (name, k, prof.get(k), v)
+    return prof, "profiles/%s (%s)" % (name, prof.get("command", ""))
+
+
+def csr_parity(ctx, csr_id, V, E, ov, oe):
+    """memcmp of the GPU-built CSR (reference layout, int64) with the oracle's arrays built on the host from
+    host-generated rows.  Downloads `e` in slices of the host array to bound memory."""
+    import pgq_b200
+    gv = np.empty(V + 2, dtype=np.int64)
+    ge = np.empty(max(E, 1), dtype=np.int64)
+    ctx._chk(ctx.lib.pgq_csr_download(ctx._ctx, csr_id, gv.ctypes.data_as(pgq_b200.I64P),
+                                      ge.ctypes.data_as(pgq_b200.I64P), None))
+    same = bool(np.array_equal(gv, ov) and np.array_equal(ge[:E], oe))
+    return "identical" if same else "MISMATCH"
 
 
 def host_cores():
@@ -198,12 +252,25 @@ def barrier_sum(dist, local, value):
     return float(t.item())
 
 
-def bench_csr(ctx, scale, ef, steps, warmup, peak_gbs):
+def bench_csr(ctx, scale, ef, steps, warmup, peak_gbs, with_parity=True):
     """BASELINE config 2: CSR build from the edge table, R-MAT scale 22 ef16."""
     import pgq_b200
     V, E = 1 << scale, ef << scale
     d_src, d_dst = ctx.dev_alloc(E * 8), ctx.dev_alloc(E * 8)
     ctx.gen_rmat_device(SEED_BASE + scale, scale, E, d_src, d_dst)
+    parity = None
+    if with_parity:
+        # config-size parity (untimed): the oracle builds the CSR on the host from HOST-generated rows (its own
+        # generator, bit-identical stream) and the GPU's arrays must memcmp-equal it
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import orc
+        hs, hd = orc.gen_rmat(SEED_BASE + scale, scale, E=E, nthreads=min(host_cores(), 64))
+        ov, oe, _ = orc.csr_build(V, hs, hd, want_eids=False)
+        del hs, hd
+        ctx.csr_build_device(100, V, E, d_src, d_dst)
+        parity = csr_parity(ctx, 100, V, E, ov, oe)
+        ctx.csr_delete(100)
+        del ov, oe
     kern_ms = []
     for i in range(warmup + steps):
         ctx.flush_l2()
@@ -230,12 +297,18 @@ def bench_csr(ctx, scale, ef, steps, warmup, peak_gbs):
     pgq_b200.pinned_free(p2)
     ms = float(np.mean(kern_ms))
     algo = 32 * E + 24 * V
+    prof, prof_src = load_traffic("r02_csr_traffic.json", {"scale": scale, "edgefactor": ef})
+    traffic = float(prof["dram_bytes_per_build"]) if prof else None
     return {"workload": "csr_build rmat scale %d ef%d (V=%d E=%d)" % (scale, ef, V, E),
+            "parity": parity, "parity_what": "v[V+2] and e[E] memcmp-equal the oracle's CSR built on the host from "
+                                             "host-generated rows" if parity else None,
             "value": E / (ms * 1e-3) / 1e9, "unit": "GE/s", "ms": ms,
             "e2e": {"value": E / (float(np.mean(e2e_ms)) * 1e-3) / 1e9, "unit": "GE/s",
                     "ms": float(np.mean(e2e_ms)), "h2d_bytes_per_step": 16 * E, "d2h_bytes_per_step": 0},
             "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak_gbs, "unit": "GB/s",
-                         "frac": algo / (ms * 1e-3) / 1e9 / peak_gbs, "traffic": None,
+                         "frac": algo / (ms * 1e-3) / 1e9 / peak_gbs, "traffic": traffic,
+                         "traffic_source": prof_src,
+                         "dram_frac": traffic / (ms * 1e-3) / 1e9 / peak_gbs if traffic else None,
                          "algo_bytes": algo, "kernels": "stable radix sort by source: global bucket histogram + two 11-bit passes (tile-reordered scatter, decoupled look-back) + offsets from sorted keys (whole build)"}}
 
 
@@ -250,7 +323,28 @@ def knows_params(V):
     return m, 0x9E3779B9 % V
 
 
-def bench_paths(ctx, V, E, npairs, steps, warmup):
+def oracle_paths_mt(V, v, e, eids, src, dst, nthreads, rows_per_thread=512):
+    """orc.shortestpath on nthreads host threads, one <=512-row call each (ctypes releases the GIL).
+    -> list of (lo, hi, (off, len, valid, vals))."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import orc
+    orc.lib()
+    res = [None] * nthreads
+
+    def work(t):
+        lo = t * rows_per_thread
+        hi = min(len(src), lo + rows_per_thread)
+        res[t] = (lo, hi, orc.shortestpath(V, v, e, eids, src[lo:hi], dst[lo:hi], mode=0))
+
+    ths = [threading.Thread(target=work, args=(t,)) for t in range(nthreads)]
+    for th in ths:
+        th.start()
+    for th in ths:
+        th.join()
+    return res
+
+
+def bench_paths(ctx, V, E, npairs, steps, warmup, peak_gbs, with_parity=True):
     """BASELINE config 4: shortestpath with path reconstruction on an LDBC-SF100-shaped knows graph
     (V persons, E directed knows rows = both directions), npairs (src,dst) pairs, host buffers in and
     the LIST<BIGINT> child buffer out (the scalar function's own data flow)."""
@@ -266,24 +360,88 @@ def bench_paths(ctx, V, E, npairs, steps, warmup):
     ctx._chk(ctx.lib.pgq_csr_download(ctx._ctx, 200, v_off.ctypes.data_as(pgq_b200.I64P), None, None))
     src, dst = make_pairs(V, v_off, npairs, 4242)
     out = {}
-    for name, fn in (("shortestpath", lambda: ctx.shortestpath(200, src, dst, mode=0)),
-                     ("iterativelength", lambda: ctx.iterativelength(200, src, dst))):
+    full = {}
+    calls = (("shortestpath", lambda a, b: ctx.shortestpath(200, a, b, mode=0)),
+             ("iterativelength", lambda a, b: ctx.iterativelength(200, a, b)))
+    for name, fn in calls:
         for _ in range(min(warmup, 2)):
-            res = fn()
+            res = fn(src, dst)
         ctx.reset_stats()
         t0 = time.perf_counter()
         for _ in range(steps):
-            res = fn()
+            res = fn(src, dst)
         secs = (time.perf_counter() - t0) / steps
         st = ctx.stats()
+        full[name] = res
         out[name] = {"pairs_per_s": npairs / secs, "ms": secs * 1e3, "batches": int(st["batches"] // steps),
-                     "levels": int(st["levels"] // steps),
+                     "levels": int(st["levels"] // steps), "host_syncs": int(st["host_syncs"] // steps),
                      "h2d_bytes_per_step": int(st["h2d_bytes"] // steps),
                      "d2h_bytes_per_step": int(st["d2h_bytes"] // steps)}
         if name == "shortestpath":
             off, ln, valid, vals = res
             out[name]["found"] = int(np.sum(valid))
             out[name]["path_values"] = int(len(vals))
+        # the plugin's granularity: the same pair set through <=1024-row calls
+        # (/root/reference/src/include/duckdb/common/vector_size.hpp:16-18)
+        fn(src[:1024], dst[:1024])
+        t0 = time.perf_counter()
+        for lo in range(0, npairs, 1024):
+            fn(src[lo:lo + 1024], dst[lo:lo + 1024])
+        secs = time.perf_counter() - t0
+        out[name]["e2e_chunked"] = {"pairs_per_s": npairs / secs, "ms": secs * 1e3, "rows_per_call": 1024,
+                                    "calls": (npairs + 1023) // 1024}
+    # roofline of the lengths pass on this graph: bytes this implementation touched (instrumented, untimed)
+    try:
+        ctx.set_option("stats", 1)
+        ctx.reset_stats()
+        ctx.iterativelength(200, src, dst)
+        st = ctx.stats()
+        ms = out["iterativelength"]["ms"]
+        out["iterativelength"]["roofline"] = {
+            "bound": "hbm", "achieved": st["model_bytes"] / (ms * 1e-3) / 1e9, "peak": peak_gbs, "unit": "GB/s",
+            "frac": st["model_bytes"] / (ms * 1e-3) / 1e9 / peak_gbs, "traffic": None,
+            "model_bytes": int(st["model_bytes"]),
+            "note": "86 MB of bitmaps per batch live in the 126 MB L2: the bytes are touched, mostly not in DRAM; "
+                    "the step is the whole call incl. H2D/D2H and host lane filling"}
+    except Exception as ex:
+        out["iterativelength"]["roofline"] = {"error": str(ex)[:200]}
+    finally:
+        ctx.set_option("stats", 0)
+    # ---- parity at config size (untimed): oracle CSR from host-generated rows; oracle paths, byte for byte ----
+    if with_parity:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import orc
+        hs, hd = orc.gen_knows(SEED_BASE + 100, V, E, nthreads=min(host_cores(), 32))
+        ov, oe, oeid = orc.csr_build(V, hs, hd)
+        del hs, hd
+        par = {"csr": csr_parity(ctx, 200, V, E, ov, oe)}
+        try:
+            avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
+        except Exception:
+            avail = 32 << 30
+        per = V * 512 * 8 * 2 + (256 << 20)  # the oracle's parent arrays
+        T = max(1, min(host_cores(), 32, (npairs + 511) // 512, int(avail * 0.6 // per)))
+        t0 = time.perf_counter()
+        chunks = oracle_paths_mt(V, ov, oe, oeid, src, dst, T)
+        cpu_secs = time.perf_counter() - t0
+        off, ln, valid, vals = full["shortestpath"]
+        glen, gval = full["iterativelength"]
+        same = True
+        rows = 0
+        for lo, hi, (ooff, oln, ovalid, ovals) in chunks:
+            rows += hi - lo
+            base = int(off[lo])
+            end = int(off[hi - 1] + ln[hi - 1])
+            same &= bool(np.array_equal(valid[lo:hi], ovalid) and np.array_equal(ln[lo:hi], oln) and
+                         np.array_equal(off[lo:hi] - np.uint64(base), ooff) and np.array_equal(vals[base:end], ovals))
+            # the lengths call must agree with the paths' lengths too
+            same &= bool(np.array_equal(gval[lo:hi], ovalid) and
+                         np.array_equal(np.where(ovalid == 1, glen[lo:hi] + 1, 0), oln.astype(np.int64)))
+        par["paths"] = "identical" if same else "MISMATCH"
+        par["paths_what"] = ("%d of %d pairs (offsets, lengths, validity and values byte for byte against the oracle's "
+                             "parent-array shortestpath on %d host threads, %.1f s)" % (rows, npairs, T, cpu_secs))
+        out["parity"] = par
+        out["cpu_oracle"] = {"shortestpath_pairs_per_s": rows / cpu_secs, "cores": T, "kind": "port"}
     # next row f4 on the same graph: cheapest_path_length, BIGINT weights 1..100 per knows row
     try:
         w = np.random.default_rng(4243).integers(1, 101, size=E).astype(np.int64)
@@ -305,7 +463,7 @@ def bench_paths(ctx, V, E, npairs, steps, warmup):
                         "(e2e through the C ABI)" % (V, E, npairs), **out}
 
 
-def bench_c1(ctx, steps, warmup, with_cpu):
+def bench_c1(ctx, steps, warmup, with_cpu, peak_gbs):
     """BASELINE configs[0]: LDBC SNB SF1-shaped Person-knows-Person graph (10 k vertices, 180 k directed
     edges): CSR build + iterativelength for 2048 pairs, everything from HOST buffers through the same
     calls the DuckDB functions make.  This is the one config the CPU side can run in full, so the
@@ -351,6 +509,28 @@ def bench_c1(ctx, steps, warmup, with_cpu):
                        "chunks + iterativelength for %d pairs in 1024-row calls, host buffers" % (V, E, npairs),
            "gpu": {"csr_build_ms": float(np.mean(tb)) * 1e3, "iterativelength_ms": float(np.mean(tq)) * 1e3,
                    "pairs_per_s": npairs / float(np.mean(tq))}}
+    # roofline of the whole-batch kernel: every level sweeps every vertex (seen read, next written) and gathers
+    # one frontier word per in-edge of the still-open vertices; upper bound = all in-edges
+    try:
+        ctx.create_csr_vertex(300, V, vid, deg)
+        ctx.create_csr_edge(300, V, E, src, dst)
+        ctx.csr_finalize(300)
+        ctx.reset_stats()
+        for lo in range(0, npairs, 1024):
+            ctx.iterativelength(300, ps[lo:lo + 1024], pd[lo:lo + 1024])
+        st = ctx.stats()
+        ctx.csr_delete(300)
+        lv = float(st["levels"])
+        algo = lv * (2.0 * V * 64 + E * 68.0)
+        ms = float(np.mean(tq)) * 1e3
+        res["gpu"]["roofline"] = {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak_gbs, "unit": "GB/s",
+                                  "frac": algo / (ms * 1e-3) / 1e9 / peak_gbs, "traffic": None,
+                                  "algo_bytes": int(algo), "levels": int(lv),
+                                  "note": "the graph's bitmaps (1.9 MB) and edges live in L2: the kernel is bound by "
+                                          "its per-level grid barrier (4.4 us) and the call's launch + copies, not "
+                                          "by HBM; algo bytes = levels * (2*V*64 + E*68), an upper bound"}
+    except Exception as ex:
+        res["gpu"]["roofline"] = {"error": str(ex)[:200]}
     if with_cpu:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import orc
@@ -373,6 +553,16 @@ def bench_c1(ctx, steps, warmup, with_cpu):
 W_BITS = 512  # lanes per vertex word on the timed path
 
 
+def time_steps(ctx, dist, local, fn, steps):
+    """K calls of fn bracketed by a barrier; CUDA-event time on the library's stream, max over ranks (ms)."""
+    ctx.sync()
+    barrier_max(dist, local, 0.0)
+    ctx.timer_start()
+    for _ in range(steps):
+        fn()
+    return barrier_max(dist, local, ctx.timer_stop_ms())
+
+
 def main_ours(a):
     import pgq_b200
     rank, world, local, dist = dist_setup(a.gpus)
@@ -386,6 +576,7 @@ def main_ours(a):
     ctx = pgq_b200.Context(local)
     scale, ef = a.scale, a.edgefactor
     V, E = 1 << scale, ef << scale
+    cpu_legs = rank == 0 and world == 1 and not a.no_cpu_baseline
     # ---- setup (untimed): synthetic graph in HBM, CSR + reverse CSR resident ----
     d_src, d_dst = ctx.dev_alloc(E * 8), ctx.dev_alloc(E * 8)
     ctx.gen_rmat_device(SEED_BASE + scale, scale, E, d_src, d_dst)
@@ -397,23 +588,38 @@ def main_ours(a):
     transpose_ms = ctx.stats()["transpose_ms"]
     v_off = np.empty(V + 2, dtype=np.int64)
     ctx._chk(ctx.lib.pgq_csr_download(ctx._ctx, 0, v_off.ctypes.data_as(pgq_b200.I64P), None, None))
+    # ---- config-size parity of THIS graph's CSR (untimed, rank 0 at N=1): the oracle builds it on the host from
+    # host-generated rows; the CPU legs below run on the ORACLE's arrays, never on a download of the GPU's ----
+    csr3_parity = None
+    o_v = o_e = None
+    if cpu_legs:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import orc
+        hs, hd = orc.gen_rmat(SEED_BASE + scale, scale, E=E, nthreads=min(host_cores(), 64))
+        o_v, o_e, _ = orc.csr_build(V, hs, hd, want_eids=False)
+        del hs, hd
+        csr3_parity = csr_parity(ctx, 0, V, E, o_v, o_e)
     n = a.pairs
     src, dst = make_pairs(V, v_off, n, 1000 + rank)
     d_ps, d_pd = ctx.dev_alloc(n * 8), ctx.dev_alloc(n * 8)
     d_out, d_ov = ctx.dev_alloc(n * 8), ctx.dev_alloc(n)
     ctx.h2d(d_ps, src)
     ctx.h2d(d_pd, dst)
-    # ---- instrumented pass (untimed): TEPS numerator + algorithmic bytes ----
+    # ---- instrumented pass (untimed): TEPS numerator, the reference algorithm's bytes and the bytes
+    # THIS implementation touched (DESIGN.md section 4 model) ----
     ctx.set_option("stats", 1)
     ctx.reset_stats()
     ctx.iterativelength_device(0, n, d_ps, d_pd, d_out, d_ov)
     st = ctx.stats()
     ctx.set_option("stats", 0)
     edges_lane, algo_bytes, levels, batches = st["edges_lane"], st["algo_bytes"], st["levels"], st["batches"]
+    model_bytes = st["model_bytes"]
+    model_parts = {k: int(st[k]) for k in ("k_listed", "k_open", "k_new", "k_scanned", "k_gathered", "kp_items",
+                                           "kp_edges", "kp_seen", "kp_next")}
     ref_out = np.empty(n, dtype=np.int64)
     ctx.d2h(ref_out, d_out)
-    # ---- level kernels timed alone (untimed pass): one batch at a time on one stream, CUDA events around
-    # each level's kernels; used for the kernels' share of a step ----
+    # ---- level kernels timed alone (untimed pass): one batch at a time on one stream, host-driven loop, CUDA
+    # events around each level's kernels; gives the kernels' share of a step ----
     ctx.set_option("timing", 1)
     ctx.iterativelength_device(0, n, d_ps, d_pd, d_out, d_ov)
     ctx.reset_stats()
@@ -423,10 +629,14 @@ def main_ours(a):
     st = ctx.stats()
     level_ms, level_launches = st["level_kernel_ms"], int(st["level_kernel_launches"])
     ctx.set_option("timing", 0)
-    # batches in flight per call: each has a host thread that spin-waits on its stream once per level, so
-    # keep ranks x streams within the host's cores
+    # (device-side level loop: one host thread enqueues every batch, so the host's core count no longer matters;
+    # the host-driven loop pins a spin-waiting thread per batch in flight)
     cores_per_rank = host_cores() // max(1, world)
-    streams = a.streams if a.streams else (8 if cores_per_rank >= 16 else max(1, min(4, cores_per_rank)))
+    if a.loop:
+        streams = a.streams if a.streams else 8
+    else:
+        streams = a.streams if a.streams else (8 if cores_per_rank >= 16 else max(1, min(4, cores_per_rank)))
+    ctx.set_option("loop", a.loop)
     ctx.set_option("streams", streams)
     # ---- device-resident timed region ----
     for _ in range(a.warmup):
@@ -435,43 +645,46 @@ def main_ours(a):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    barrier_max(dist, local, 0.0)
     ctx.reset_stats()
-    ctx.timer_start()
-    for _ in range(a.steps):
-        ctx.iterativelength_device(0, n, d_ps, d_pd, d_out, d_ov)
-    ms_total = ctx.timer_stop_ms()
-    ms_total = barrier_max(dist, local, ms_total)
+    local_t0 = time.perf_counter()
+    ms_total = time_steps(ctx, dist, local, lambda: ctx.iterativelength_device(0, n, d_ps, d_pd, d_out, d_ov), a.steps)
     st = ctx.stats()
     launches = int(st["kernel_launches"])
+    host_syncs = int(st["host_syncs"])
+    got = np.empty(n, dtype=np.int64)
+    ctx.d2h(got, d_out)
+    assert np.array_equal(got, ref_out), "timed run disagrees with the instrumented run"
     # ---- e2e: host buffers through the reference-facing C-ABI call ----
     out_h, ov_h = ctx.iterativelength(0, src, dst)  # warm
     assert np.array_equal(np.where(ov_h == 1, out_h, -1), ref_out), "host and device variants disagree"
-    barrier_max(dist, local, 0.0)
     ctx.reset_stats()
-    ctx.timer_start()
-    for _ in range(a.steps):
-        ctx.iterativelength(0, src, dst)
-    e2e_ms = barrier_max(dist, local, ctx.timer_stop_ms())
+    e2e_ms = time_steps(ctx, dist, local, lambda: ctx.iterativelength(0, src, dst), a.steps)
     st2 = ctx.stats()
+    # ---- the plugin's granularity: the same pair set through <= 1024-row calls (vector_size.hpp:16-18) ----
+    def chunked():
+        for lo in range(0, n, 1024):
+            ctx.iterativelength(0, src[lo:lo + 1024], dst[lo:lo + 1024])
+    chunked_steps = max(1, min(a.steps, 2))
+    chunked_ms = time_steps(ctx, dist, local, chunked, chunked_steps) / chunked_steps
     clocks = sampler.stop() if rank == 0 else None
+    del local_t0
     total_edges = barrier_sum(dist, local, float(edges_lane))
     total_pairs = barrier_sum(dist, local, float(n))
     ms_per_step = ms_total / a.steps
     value = total_edges / (ms_per_step * 1e-3) / 1e9
     e2e_value = total_edges / (e2e_ms / a.steps * 1e-3) / 1e9
-    # roofline over the timed region: algorithmic bytes of a step / CUDA-event time of a step (batches overlap
-    # on several streams, so the whole step is the honest denominator; it includes memsets, checks and host gaps)
-    achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9 if ms_per_step > 0 else 0.0
-    # measured DRAM traffic of the level kernels (ncu pass committed under profiles/, per 512-lane batch)
-    traffic = dram_frac = traffic_src = None
-    try:
-        prof = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+    # ---- roofline of the dominant kernels (the per-level pull/push kernels) ----
+    # frac     = bytes THIS implementation must move for the levels it ran (what its kernels touched, counted by the
+    #            instrumented pass; a gathered word counts 64 B wherever it was served from) / time / peak.
+    # reference_model = the REFERENCE algorithm's bytes per level: what the CPU loop would move;
+    #            the frontier filter, the early exit and the done bitmap skip most of it, so that ratio exceeds 1.
+    model_achieved = model_bytes / (ms_per_step * 1e-3) / 1e9 if ms_per_step > 0 else 0.0
+    ref_achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9 if ms_per_step > 0 else 0.0
+    prof, traffic_src = load_traffic("r02_traffic.json", {"scale": scale, "edgefactor": ef, "lanes": W_BITS})
+    traffic = dram_frac = None
+    if prof and ms_per_step > 0:
         traffic = float(prof["level_kernel_dram_bytes_per_batch"]) * float(batches)
-        dram_frac = traffic / (ms_per_step * 1e-3) / 1e9 / peak_gbs if ms_per_step > 0 else None
-        traffic_src = "profiles/r01_traffic.json (%s)" % prof.get("command", "")
-    except Exception:
-        pass
+        dram_frac = traffic / (ms_per_step * 1e-3) / 1e9 / peak_gbs
     line = {
         "metric": "msbfs_gteps", "value": value, "unit": "GTEPS", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -481,28 +694,44 @@ def main_ours(a):
                    "V": V, "E": E, "pairs_per_gpu": n, "batches": int(batches), "levels": int(levels),
                    "l2": "inputs larger than L2 (3 bitmaps of V*64 B = %.1f GB)" % (3 * V * 64 / 1e9),
                    "parallelism": "source-batch sharding x%d" % world,
-                   "batches_in_flight": int(streams)},
+                   "batches_in_flight": int(streams),
+                   "level_loop": "device (CUDA graph WHILE/SWITCH)" if a.loop else "host"},
         "pairs_per_s": total_pairs / (ms_per_step * 1e-3),
         "e2e": {"value": e2e_value, "unit": "GTEPS", "pairs_per_s": total_pairs / (e2e_ms / a.steps * 1e-3),
                 "h2d_bytes_per_step": int(st2["h2d_bytes"] // a.steps),
                 "d2h_bytes_per_step": int(st2["d2h_bytes"] // a.steps)},
+        "e2e_chunked": {"value": total_edges / (chunked_ms * 1e-3) / 1e9, "unit": "GTEPS",
+                        "pairs_per_s": total_pairs / (chunked_ms * 1e-3), "rows_per_call": 1024,
+                        "calls_per_step": (n + 1023) // 1024,
+                        "what": "the same pair set through <= 1024-row pgq_iterativelength calls, one after the other "
+                                "(the plugin's call granularity with one worker thread); the DuckDB shim's batcher "
+                                "merges the calls of concurrent workers, see sql"},
         "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
-                     "frac": achieved / peak_gbs, "traffic": traffic, "dram_frac": dram_frac,
+        "host_syncs_in_level_loops": host_syncs,
+        "roofline": {"bound": "hbm", "achieved": model_achieved, "peak": peak_gbs, "unit": "GB/s",
+                     "frac": model_achieved / peak_gbs, "traffic": traffic, "dram_frac": dram_frac,
                      "traffic_source": traffic_src, "peak_source": peak_src,
-                     "kernel": "MS-BFS level step = pull_list/pull_warp/pull_hub (+push, bitmap) kernels",
-                     "note": "achieved = the REFERENCE algorithm's bytes per level (SURVEY.md 8(d)) / time; the "
-                             "frontier filter, early exit and L2 hits move fewer DRAM bytes (traffic, dram_frac), "
-                             "so frac can exceed 1",
+                     "kernel": "MS-BFS level step = pull_tiny/pull_list/pull_seg/pull_warp/pull_hub (+push, bitmap) kernels",
+                     "model": "bytes this implementation touches (DESIGN.md section 4): per listed vertex 12 B (list "
+                              "entry, two in-offsets), per open vertex its 64-B seen word, per vertex that gained "
+                              "bits 128 B (next + seen stores), 4 B per scanned in-edge, 64 B per gathered frontier "
+                              "word; push: 88 B per work item, 4 B per out-edge, 8 B per 32-lane atomic; per level "
+                              "3 bitmap passes; per batch the seen memset and the frontier scrub",
+                     "model_bytes_per_step": int(model_bytes), "model_parts": model_parts,
+                     "reference_model": {"achieved": ref_achieved, "frac": ref_achieved / peak_gbs,
+                                         "algo_bytes_per_step": int(algo_bytes),
+                                         "what": "SURVEY.md 8(d): 4*V*W/8 per level + E_act*(4+W/8) + 8*V_act, the bytes "
+                                                 "of the reference's loop; > 1 means work the kernels skip"},
                      "launches": level_launches,
-                     "algo_bytes_per_step": int(algo_bytes),
                      "level_kernel_ms_per_step_alone": level_ms,
-                     "alone": "level kernels of one step timed with one batch in flight (streams=1, CUDA events "
-                              "around each level): achieved %.0f GB/s" % (algo_bytes / (level_ms * 1e-3) / 1e9
-                                                                         if level_ms > 0 else 0.0),
+                     "alone": "level kernels of one step timed with one batch in flight (host loop, CUDA events around "
+                              "each level): %.0f GB/s of model bytes" % (model_bytes / (level_ms * 1e-3) / 1e9
+                                                                        if level_ms > 0 else 0.0),
                      "step_ms_alone": step_alone_ms,
                      "share_of_step": level_ms / step_alone_ms if step_alone_ms else None},
-        "setup": {"csr_build_ms": build_ms, "reverse_csr_ms": transpose_ms},
+        "setup": {"csr_build_ms": build_ms, "reverse_csr_ms": transpose_ms,
+                  "csr_build_GEps": E / (build_ms * 1e-3) / 1e9 if build_ms else None},
+        "parity": {"csr_config3": csr3_parity},
         "clocks": clocks,
     }
     if rank == 0 and W_BITS == 512:
@@ -516,35 +745,211 @@ def main_ours(a):
                 "what": "measured live: random 64-byte gathers, 4 threads x 16 B per word, 4 in flight per "
                         "thread, indices streamed; GB/s counts 68 B per gather"}
         except Exception as ex:  # a probe must not cost the bench line
-            line["roofline"]["random_gather_gbs"] = {"error": str(ex)}
+            line["roofline"]["random_gather_gbs"] = {"error": str(ex)[:200]}
+    # ---- multi-GPU sections (N > 1): strong scaling of the stated pair set, ONE process driving all GPUs through a
+    # single C-ABI call, and BASELINE configs[4] (1-D vertex partition) ----
+    if world > 1:
+        multi_gpu_sections(a, ctx, dist, rank, world, local, line, V, E, v_off, ms_per_step, edges_lane, streams)
     if rank == 0 and world == 1 and not a.no_csr:
-        line["csr_build"] = bench_csr(ctx, a.csr_scale, ef, a.steps, a.warmup, peak_gbs)
+        line["csr_build"] = bench_csr(ctx, a.csr_scale, ef, a.steps, a.warmup, peak_gbs, not a.no_cpu_baseline)
+        line["parity"]["csr_config2"] = line["csr_build"]["parity"]
     if rank == 0 and world == 1 and not a.no_paths:
-        line["config1"] = bench_c1(ctx, a.steps, a.warmup, not a.no_cpu_baseline)
+        line["config1"] = bench_c1(ctx, a.steps, a.warmup, not a.no_cpu_baseline, peak_gbs)
+        line["parity"]["config1"] = line["config1"].get("cpu_oracle_1thread", {}).get("parity")
     if rank == 0 and world == 1 and not a.no_paths:
-        line["paths"] = bench_paths(ctx, 450000, 40000000, 16384, max(1, a.steps // 2), a.warmup)
-    if rank == 0 and world == 1 and not a.no_cpu_baseline:
-        e_h = np.empty(E, dtype=np.int64)
-        ctx._chk(ctx.lib.pgq_csr_download(ctx._ctx, 0, None, e_h.ctypes.data_as(pgq_b200.I64P), None))
+        line["paths"] = bench_paths(ctx, 450000, 40000000, 16384, max(1, a.steps // 2), a.warmup, peak_gbs,
+                                    not a.no_cpu_baseline)
+        line["parity"]["paths_config4"] = line["paths"].get("parity", {}).get("paths")
+        line["parity"]["csr_config4"] = line["paths"].get("parity", {}).get("csr")
+    if cpu_legs:
         T, cores = cpu_sample_threads(V, a.cpu_threads)
         rows_pt = min(512, n)
         T = max(1, min(T, n // rows_pt))
-        secs, rows, edges, res = run_cpu_sample(V, v_off, e_h, src, dst, T, rows_pt)
-        # the CPU sample doubles as a parity check at full size
+        # the ORACLE's own CSR (host-built from host-generated rows), not a download of the GPU's
+        secs, rows, edges, res = run_cpu_sample(V, o_v, o_e, src, dst, T, rows_pt)
+        same = True
         for t in range(T):
             lo = t * rows_pt
             eo, ev, _ = res[t]
-            assert np.array_equal(np.where(ev == 1, eo, -1), ref_out[lo:lo + rows_pt]), "GPU != oracle at full size"
+            same &= bool(np.array_equal(np.where(ev == 1, eo, -1), ref_out[lo:lo + rows_pt]))
+        line["parity"]["lengths_config3"] = "identical" if same else "MISMATCH"
+        line["parity"]["lengths_config3_what"] = "%d of %d pairs against the oracle on the oracle's own CSR" % (rows, n)
         line["cpu_baseline"] = {"value": edges / secs / 1e9, "unit": "GTEPS", "cores": T, "host_cores": cores,
                                 "kind": "port", "pairs_per_s": rows / secs,
                                 "sample": "%d pairs (%d threads x one %d-row call) of the same pair set, %.1f s"
-                                          % (rows, T, rows_pt, secs),
-                                "parity": "sample results identical to the GPU's"}
+                                          % (rows, T, rows_pt, secs)}
     if rank == 0:
+        bad = [k for k, v in line["parity"].items() if v == "MISMATCH"]
+        if bad:
+            line["parity"]["FAILED"] = bad
         print(json.dumps(line))
     ctx.close()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def multi_gpu_sections(a, ctx, dist, rank, world, local, line, V, E, v_off, ms_weak, edges_lane_rank, streams):
+    """N > 1 only.  (1) strong scaling: the stated 65 536-pair set split N ways (shard_rows), no collective;
+    (2) ONE process, ONE pgq_iterativelength call, all N GPUs (pgq_init_devices; rank 0, the other ranks idle);
+    (3) BASELINE configs[4]: 1-D vertex partition + per-level exchange, both exchange modes, with parity against the
+    single-GPU path at the bench graph's scale."""
+    import pgq_b200
+    n = a.pairs
+    steps = max(1, a.steps)
+    src0, dst0 = make_pairs(V, v_off, n, 1000)  # rank 0's set, identical on every rank
+    set_edges = barrier_sum(dist, local, float(edges_lane_rank) if rank == 0 else 0.0)
+    # ---- (1) strong scaling ----
+    lo, hi = pgq_b200.shard_rows(n, world, rank)
+    m = hi - lo
+    d = [ctx.dev_alloc(max(m, 1) * 8) for _ in range(3)] + [ctx.dev_alloc(max(m, 1))]
+    ctx.h2d(d[0], src0[lo:hi])
+    ctx.h2d(d[1], dst0[lo:hi])
+    run = (lambda: ctx.iterativelength_device(0, m, d[0], d[1], d[2], d[3])) if m else (lambda: None)
+    for _ in range(2):
+        run()
+    strong_ms = time_steps(ctx, dist, local, run, steps) / steps
+    for p in d:
+        ctx.dev_free(p)
+    line["strong"] = {"pairs_total": n, "pairs_per_gpu": [pgq_b200.shard_rows(n, world, r)[1] -
+                                                          pgq_b200.shard_rows(n, world, r)[0] for r in range(world)],
+                      "ms": strong_ms, "value": set_edges / (strong_ms * 1e-3) / 1e9, "unit": "GTEPS",
+                      "pairs_per_s": n / (strong_ms * 1e-3), "one_gpu_ms": ms_weak,
+                      "speedup_vs_1": ms_weak / strong_ms if strong_ms > 0 else None,
+                      "what": "BASELINE configs[2] as stated: ONE 65 536-pair set sharded by source batch over the "
+                              "GPUs (device-resident, max over ranks); one_gpu_ms = the weak-scaling step, where "
+                              "every GPU answers a whole 65 536-pair set"}
+    # ---- (2) one process, all GPUs, one call ----
+    barrier_max(dist, local, 0.0)
+    if rank == 0:
+        try:
+            mc = pgq_b200.Context(devices=list(range(world)))
+            mc.set_option("streams", streams)
+            scale = a.scale
+            ds, dd = mc.dev_alloc(E * 8), mc.dev_alloc(E * 8)
+            mc.gen_rmat_device(SEED_BASE + scale, scale, E, ds, dd)
+            mc.csr_build_device(0, V, E, ds, dd)
+            mc.dev_free(ds)
+            mc.dev_free(dd)
+            out1, ov1 = mc.iterativelength(0, src0, dst0)  # warm: replicates the CSR over NVLink
+            ref, rv = ctx.iterativelength(0, src0, dst0)
+            same = bool(np.array_equal(ov1, rv) and np.array_equal(out1, ref))
+            mc.iterativelength(0, src0, dst0)
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                mc.iterativelength(0, src0, dst0)
+            ms = (time.perf_counter() - t0) / steps * 1e3
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                ctx.iterativelength(0, src0, dst0)
+            ms1 = (time.perf_counter() - t0) / steps * 1e3
+            line["one_process"] = {"devices": world, "ms": ms, "value": set_edges / (ms * 1e-3) / 1e9, "unit": "GTEPS",
+                                   "pairs_per_s": n / (ms * 1e-3), "one_device_ms": ms1,
+                                   "speedup_vs_1_device": ms1 / ms if ms > 0 else None,
+                                   "parity_vs_one_device": "identical" if same else "MISMATCH",
+                                   "what": "pgq_init_devices: ONE process, ONE pgq_iterativelength call with host "
+                                           "buffers, batches dealt over all GPUs (CSR replicated by peer copies at "
+                                           "the first call); wall clock incl. H2D / D2H; the other ranks idle"}
+            mc.close()
+        except Exception as ex:
+            line["one_process"] = {"error": str(ex)[:300]}
+    barrier_max(dist, local, 0.0)
+    # ---- (3) configs[4]: 1-D vertex partition ----
+    try:
+        line_part = part_section(a, ctx, dist, rank, world, local, V, v_off, src0, dst0)
+        if rank == 0:
+            line["part"] = line_part
+            line["parity"]["part_vs_single_gpu"] = line_part.get("parity_vs_single_gpu")
+    except Exception as ex:
+        if rank == 0:
+            line["part"] = {"error": str(ex)[:300]}
+    barrier_max(dist, local, 0.0)
+
+
+def part_build(pc, scale, ef, csr_id, chunk=1 << 26):
+    import pgq_b200
+    C = pgq_b200.C
+    V, E = 1 << scale, ef << scale
+    pc.part_csr_create(csr_id, V)
+    chunk = min(chunk, E)
+    d_src, d_dst = pc.dev_alloc(chunk * 8), pc.dev_alloc(chunk * 8)
+    t0 = time.perf_counter()
+    for row0 in range(0, E, chunk):
+        k = min(chunk, E - row0)
+        pc._chk(pc.lib.pgq_gen_rmat_rows_device(pc._ctx, C.c_uint64(SEED_BASE + scale), C.c_int(scale),
+                                                C.c_int64(row0), C.c_int64(k), C.c_void_p(d_src), C.c_void_p(d_dst)))
+        pc.part_csr_add_edges_device(csr_id, d_src, d_dst, k)
+    pc.part_csr_finalize(csr_id)
+    pc.sync()
+    secs = time.perf_counter() - t0
+    pc.dev_free(d_src)
+    pc.dev_free(d_dst)
+    return V, E, secs
+
+
+def part_section(a, ctx, dist, rank, world, local, V0, v_off, src0, dst0):
+    """BASELINE configs[4]: R-MAT ef16 1-D vertex-partitioned over the N GPUs: scale 28 at N=8 (27 at 4, 26 at 2),
+    every rank generates the stream and keeps the rows whose target it owns; 256 pairs in 64-lane words, all ranks
+    answer collectively.  Exchange per level: ncclAllGather of the word slices (the stated baseline) and the fused
+    peer-store variant (the product)."""
+    import pgq_b200
+    box = [pgq_b200.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    pc = pgq_b200.Context(local)
+    pc.part_init(rank, world, box[0])
+    out = {}
+    # parity first, at the bench graph's own scale: the partitioned answers against the single-GPU path's
+    pV, pE, _ = part_build(pc, a.scale, a.edgefactor, 1)
+    k = min(1024, len(src0))
+    pc.set_option("lanes", 256)
+    po, pv = pc.part_iterativelength(1, src0[:k], dst0[:k])
+    if rank == 0:
+        so, sv = ctx.iterativelength(0, src0[:k], dst0[:k])
+        same = bool(np.array_equal(sv, pv) and np.array_equal(np.where(sv == 1, so, -1), np.where(pv == 1, po, -1)))
+        out["parity_vs_single_gpu"] = "identical" if same else "MISMATCH"
+        out["parity_what"] = "scale %d, %d pairs, %d ranks, ncclAllGather exchange, 256 lanes" % (a.scale, k, world)
+    pc.csr_delete(1)
+    scale = {2: 26, 4: 27, 8: 28}.get(world, 25)
+    lanes, pairs, steps = 64, 256, 2
+    V, E, build_s = part_build(pc, scale, a.edgefactor, 0)
+    rng = np.random.RandomState(1234)
+    ps = rng.randint(0, V, size=pairs).astype(np.int64)
+    pd = rng.randint(0, V, size=pairs).astype(np.int64)
+    pc.set_option("lanes", lanes)
+    res = {}
+    for mode in ("allgather", "fused"):
+        if mode == "fused":
+            pc.part_p2p_setup(dist, 0, lanes, world)
+        o, ov = pc.part_iterativelength(0, ps, pd)  # warm
+        res[mode] = (o, ov)
+        # instrumented pass: TEPS numerator of this pair set (same definition as the single-GPU path)
+        pc.set_option("stats", 1)
+        pc.reset_stats()
+        pc.part_iterativelength(0, ps, pd)
+        edges = barrier_sum(dist, local, float(pc.stats()["edges_lane"]))
+        pc.set_option("stats", 0)
+        pc.set_option("timing", 1)
+        pc.reset_stats()
+        pc.sync()
+        barrier_max(dist, local, 0.0)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            pc.part_iterativelength(0, ps, pd)
+        ms = barrier_max(dist, local, (time.perf_counter() - t0) / steps * 1e3)
+        st = pc.stats()
+        pc.set_option("timing", 0)
+        out[mode] = {"ms_per_step": ms, "pairs_per_s": pairs / (ms * 1e-3),
+                     "value": edges / (ms * 1e-3) / 1e9, "unit": "GTEPS", "edges_lane": edges,
+                     "levels": int(st["levels"] // steps), "pull_ms": st["level_kernel_ms"] / steps,
+                     "exchange_ms": st["coll_ms"] / steps, "coll_bytes_per_step_per_rank": int(st["coll_bytes"] // steps)}
+    same = bool(np.array_equal(res["allgather"][0], res["fused"][0]) and np.array_equal(res["allgather"][1], res["fused"][1]))
+    out.update({"workload": "BASELINE configs[4]: R-MAT scale %d ef%d (V=%d E=%d) 1-D vertex-partitioned over %d B200, "
+                            "%d pairs, %d-lane words" % (scale, a.edgefactor, V, E, world, pairs, lanes),
+                "slice_build_s": build_s, "found": int(res["fused"][1].sum()),
+                "fused_equals_allgather": "identical" if same else "MISMATCH",
+                "timing": "wall clock of the collective call (host buffers in and out), max over ranks; pull_ms / "
+                          "exchange_ms = CUDA-event sums over the levels on rank 0"})
+    pc.close()
+    return out
 
 
 def main_reference(a):
@@ -566,25 +971,34 @@ def main_reference(a):
     rows_pt = min(512, a.pairs)
     T = max(1, min(T, a.pairs // rows_pt))
     src, dst = make_pairs(V, v, a.pairs, 1000)
+    # Time-boxed: one pass over the sample is tens of seconds, so the requested K steps would run for a quarter of an
+    # hour (round 1: the scaling runs hit their limit four times).  The loop is deterministic CPU work: after the
+    # time box the passes timed so far are reported, `steps` says how many, `config.steps_requested` what was asked.
+    box_s = float(a.ref_seconds)
+    t_start = time.perf_counter()
     times, edges_l, rows_l = [], [], []
-    for i in range(a.warmup + a.steps):
-        if i < a.warmup and i > 0:
-            continue  # one warm-up pass is enough to fault the pages in; each pass is tens of seconds
+    if a.warmup > 0:
+        run_cpu_sample(V, v, e, src, dst, T, rows_pt)  # one warm-up pass faults the pages in
+    for i in range(max(1, a.steps)):
         secs, rows, edges, _ = run_cpu_sample(V, v, e, src, dst, T, rows_pt)
-        if i >= a.warmup:
-            times.append(secs)
-            edges_l.append(edges)
-            rows_l.append(rows)
+        times.append(secs)
+        edges_l.append(edges)
+        rows_l.append(rows)
+        if time.perf_counter() - t_start + secs > box_s:
+            break
+    steps_timed = len(times)
     secs = float(np.mean(times))
     value = float(np.mean(edges_l)) / secs / 1e9
     sample = "%d pairs per step (%d threads x one %d-row call) of the %d-pair set" % (rows_l[0], T, rows_pt, a.pairs)
     line = {"impl": "reference", "metric": "msbfs_gteps", "value": value, "unit": "GTEPS", "n_gpus": a.gpus,
-            "steps": a.steps, "warmup": a.warmup, "ms_per_step": secs * 1e3, "higher_is_better": True,
+            "steps": steps_timed, "warmup": min(a.warmup, 1), "ms_per_step": secs * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u64 bitset (512 lanes/vertex), int64 ids",
             "data": "synthetic",
             "config": {"workload": "BASELINE configs[2]: MS-BFS iterativelength, R-MAT scale %d ef%d; CPU oracle "
                                    "(port of the reference algorithm), bounded sample" % (scale, ef),
-                       "V": V, "E": E, "pairs_per_step": rows_l[0]},
+                       "V": V, "E": E, "pairs_per_step": rows_l[0], "steps_requested": a.steps,
+                       "steps_timed": steps_timed, "time_box_s": box_s,
+                       "note": "time-boxed: deterministic CPU passes, %d of %d requested steps timed" % (steps_timed, a.steps)},
             "pairs_per_s": rows_l[0] / secs,
             "cpu_baseline": {"value": value, "unit": "GTEPS", "cores": T, "host_cores": cores, "kind": "port",
                              "sample": sample, "csr_build_GEps_1thread": E / csr_secs / 1e9},

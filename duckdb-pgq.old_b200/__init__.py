@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpgq_b200.so")
+LIB_PATH = os.environ.get("PGQ_B200_LIB") or os.path.join(_HERE, "libpgq_b200.so")  # (override: A/B builds)
 
 I64P = C.POINTER(C.c_int64)
 U8P = C.POINTER(C.c_uint8)

@@ -2,6 +2,7 @@
 // Thread-safety: every entry point takes the context mutex (DuckDB may enter a scalar function
 // from several worker threads at once: /root/reference/src/parallel/pipeline.cpp:79-123).
 #include <execinfo.h>
+#include <fcntl.h>
 #include <signal.h>
 #include <stdarg.h>
 #include <stdlib.h>
@@ -324,21 +325,43 @@ const char *pgq_last_error(void) {
 
 // PGQ_B200_BACKTRACE=1: frames of a crashing thread on stderr (addresses resolve with addr2line -e libpgq_b200.so)
 static void crash_handler(int sig) {
+	const char msg[] = "[pgq_b200] fatal signal, backtrace:\n";
+	const int fd = open("/tmp/pgq_b200_crash.txt", O_WRONLY | O_CREAT | O_APPEND, 0644);
+	if (fd >= 0 && write(fd, msg, sizeof(msg) - 1) < 0) {
+	}
+	if (write(2, msg, sizeof(msg) - 1) < 0) {
+	}
 	void *frames[64];
 	const int n = backtrace(frames, 64);
-	const char msg[] = "[pgq_b200] fatal signal, backtrace:\n";
-	if (write(2, msg, sizeof(msg) - 1) < 0) {
+	if (fd >= 0) {
+		backtrace_symbols_fd(frames, n, fd);
+		close(fd);
 	}
 	backtrace_symbols_fd(frames, n, 2);
 	signal(sig, SIG_DFL);
 	raise(sig);
 }
 
+static void install_crash_handler() {
+	void *warm[4];
+	(void)backtrace(warm, 4); // the first call loads libgcc: not something to do inside a signal handler
+	static char altstack[1 << 16];
+	stack_t ss;
+	ss.ss_sp = altstack;
+	ss.ss_size = sizeof(altstack);
+	ss.ss_flags = 0;
+	sigaltstack(&ss, nullptr); // (the installing thread only: enough to tell a stack overflow apart)
+	struct sigaction sa;
+	memset(&sa, 0, sizeof(sa));
+	sa.sa_handler = crash_handler;
+	sa.sa_flags = SA_ONSTACK;
+	sigaction(SIGSEGV, &sa, nullptr);
+	sigaction(SIGBUS, &sa, nullptr);
+	sigaction(SIGABRT, &sa, nullptr);
+}
+
 static int init_one(int device, pgq_ctx_t **out_ctx) {
-	if (getenv("PGQ_B200_BACKTRACE")) {
-		signal(SIGSEGV, crash_handler);
-		signal(SIGABRT, crash_handler);
-	}
+	if (getenv("PGQ_B200_BACKTRACE")) install_crash_handler();
 	if (!out_ctx) return PGQ_ERR_INVALID;
 	*out_ctx = nullptr;
 	int ndev = 0;
@@ -477,6 +500,7 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "loop")) c->opt.loop = value;
 	else if (!strcmp(key, "done_bitmap")) c->opt.done_bitmap = value ? 1 : 0;
 	else if (!strcmp(key, "dense_store")) c->opt.dense_store = value ? 1 : 0;
+	else if (!strcmp(key, "dyn")) c->opt.dyn = value ? 1 : 0;
 	else if (!strcmp(key, "l2_persist")) c->opt.l2_persist = value;
 	else if (!strcmp(key, "hist_budget_mb")) c->opt.hist_budget_mb = value < 0 ? 0 : value;
 	else if (!strcmp(key, "devices_used")) { // at most this many devices of a multi-GPU context take batches

@@ -34,10 +34,45 @@ struct BatchBufs {
 	BfsCtrl *ctrl;
 };
 
-// ---- launchers of the in-degree class kernels.  *nk counts the kernels issued (a capture counts the
-// nodes of the body it records); STATS picks the instrumented instantiation of the untimed pass. ----
+// ---- launchers.  A kernel of a level body is either launched on a stream (host-driven loop) or added as an
+// explicit kernel node, chained after the previous one, to a body graph of the loop graph (device-side loop).
+// (Explicit nodes, not stream capture: graphs whose conditional bodies were filled by capture crashed inside
+// cuGraphDestroy on driver 580.159.)  nk counts the kernels issued. ----
+template <class T>
+struct ident {
+	using type = T;
+};
+
+struct Launch {
+	cudaStream_t st = nullptr;
+	cudaGraph_t graph = nullptr; // graph mode when set
+	cudaGraphNode_t last = nullptr;
+	uint32_t nk = 0;
+	cudaError_t err = cudaSuccess;
+	template <class... P>
+	void run(void (*k)(P...), dim3 grid, dim3 block, typename ident<P>::type... args) {
+		nk++;
+		if (!graph) {
+			k<<<grid, block, 0, st>>>(args...);
+			return;
+		}
+		void *ptrs[] = {(void *)&args...};
+		cudaKernelNodeParams kp{};
+		kp.func = (void *)k;
+		kp.gridDim = grid;
+		kp.blockDim = block;
+		kp.sharedMemBytes = 0;
+		kp.kernelParams = ptrs;
+		cudaGraphNode_t node = nullptr;
+		const cudaError_t e = cudaGraphAddKernelNode(&node, graph, last ? &last : nullptr, last ? 1 : 0, &kp);
+		if (e != cudaSuccess && err == cudaSuccess) err = e;
+		last = node;
+	}
+};
+
+// STATS picks the instrumented instantiation of the untimed pass.
 template <int W, int GPV, bool STATS = false>
-void launch_class(PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter, cudaStream_t st, uint32_t *nk) {
+void launch_class(PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter, Launch &L) {
 	if (!nlist) return;
 	using C = LaneCfg<W>;
 	constexpr int VPW = C::G / GPV;
@@ -45,95 +80,85 @@ void launch_class(PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter, 
 	a.nlist = nlist;
 	const uint32_t warps = div_up(nlist, VPW);
 	const uint32_t grid = div_up((uint64_t)warps * 32, 128);
-	if (filter) pull_list_kernel<W, GPV, true, STATS><<<grid, 128, 0, st>>>(a);
-	else pull_list_kernel<W, GPV, false, STATS><<<grid, 128, 0, st>>>(a);
-	++*nk;
+	if (filter) L.run(pull_list_kernel<W, GPV, true, STATS>, grid, 128, a);
+	else L.run(pull_list_kernel<W, GPV, false, STATS>, grid, 128, a);
 }
 
 // filtered levels, small in-degrees: SEG lanes per vertex, edge-parallel frontier test
 template <int W, int SEG, bool STATS = false>
-void launch_seg(PullArgs &a, const DevBuf &list, uint32_t nlist, cudaStream_t st, uint32_t *nk) {
+void launch_seg(PullArgs &a, const DevBuf &list, uint32_t nlist, Launch &L) {
 	if (!nlist) return;
 	a.list = list.as<uint32_t>();
 	a.nlist = nlist;
 	const uint32_t warps = div_up(nlist, 32 / SEG);
-	pull_seg_kernel<W, SEG, STATS><<<div_up((uint64_t)warps * 32, 128), 128, 0, st>>>(a);
-	++*nk;
+	L.run(pull_seg_kernel<W, SEG, STATS>, div_up((uint64_t)warps * 32, 128), 128, a);
 }
 
 template <int W, bool STATS = false>
-void launch_warp(PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter, cudaStream_t st, uint32_t *nk) {
+void launch_warp(PullArgs &a, const DevBuf &list, uint32_t nlist, bool filter, Launch &L) {
 	if (!nlist) return;
 	a.list = list.as<uint32_t>();
 	a.nlist = nlist;
 	const uint32_t grid = div_up((uint64_t)nlist * 32, 128);
-	if (filter) pull_warp_kernel<W, true, STATS><<<grid, 128, 0, st>>>(a);
-	else pull_warp_kernel<W, false, STATS><<<grid, 128, 0, st>>>(a);
-	++*nk;
+	if (filter) L.run(pull_warp_kernel<W, true, STATS>, grid, 128, a);
+	else L.run(pull_warp_kernel<W, false, STATS>, grid, 128, a);
 }
 
 // tiny class: straight-line kernel when the class really is <= 4 in-edges, else the generic one
 template <int W, bool STATS = false>
-void launch_tiny(PullArgs &a, Csr *g, bool filter, cudaStream_t st, uint32_t *nk) {
+void launch_tiny(PullArgs &a, Csr *g, bool filter, Launch &L) {
 	if (!g->n_tiny) return;
 	if (g->bins_tiny_max > 4) {
-		launch_class<W, 1, STATS>(a, g->d_tiny, g->n_tiny, filter, st, nk);
+		launch_class<W, 1, STATS>(a, g->d_tiny, g->n_tiny, filter, L);
 		return;
 	}
 	using C = LaneCfg<W>;
 	a.list = g->d_tiny.as<uint32_t>();
 	a.nlist = g->n_tiny;
 	const uint32_t grid = div_up((uint64_t)div_up(g->n_tiny, C::G) * 32, 128);
-	if (filter) pull_tiny_kernel<W, true, STATS><<<grid, 128, 0, st>>>(a);
-	else pull_tiny_kernel<W, false, STATS><<<grid, 128, 0, st>>>(a);
-	++*nk;
+	if (filter) L.run(pull_tiny_kernel<W, true, STATS>, grid, 128, a);
+	else L.run(pull_tiny_kernel<W, false, STATS>, grid, 128, a);
 }
 
 template <int W, bool STATS = false>
-void launch_hubs(PullArgs &a, Csr *g, cudaStream_t st, uint32_t *nk) {
+void launch_hubs(PullArgs &a, Csr *g, Launch &L) {
 	if (!g->n_hub) return;
 	using C = LaneCfg<W>;
 	a.list = g->d_hub.as<uint32_t>();
 	a.nlist = g->n_hub;
 	a.chunks = g->d_hubchunks.as<HubChunk>();
 	a.nchunks = g->n_hubchunks;
-	pull_hub_kernel<W, STATS><<<g->n_hubchunks, 256, 0, st>>>(a);
-	hub_finalize_kernel<W><<<div_up((uint64_t)g->n_hub * C::TPV, 256), 256, 0, st>>>(a);
-	*nk += 2;
+	L.run(pull_hub_kernel<W, STATS>, g->n_hubchunks, 256, a);
+	L.run(hub_finalize_kernel<W>, div_up((uint64_t)g->n_hub * C::TPV, 256), 256, a);
 }
 
-// One level of `mode` on stream st: the body of one SWITCH case of the loop graph (recorded by a stream
-// capture) and, identically, what the host loop launches.  Everything that changes from level to level
-// (frontier buffers, bitmaps, queues) is read from ctrl->L by the kernels.
+// One level of `mode`: the body of one SWITCH case of the loop graph and, identically, what the host loop
+// launches.  Everything that changes from level to level (frontier buffers, bitmaps, queues) is read from
+// ctrl->L by the kernels.
 template <int W, bool STATS>
-int launch_body(Ctx *c, Csr *g, const BatchBufs &b, uint32_t mode, bool keep_hist, cudaStream_t st, uint32_t *nk) {
+int launch_body(Ctx *c, Csr *g, const BatchBufs &b, uint32_t mode, bool keep_hist, Launch &L,
+                const LoopState *hl = nullptr) {
 	const uint32_t cgrid = div_up(b.fbit_words, 256);
 	const size_t bm = (size_t)g->V * (W / 8);
 	// `next` becomes all-zero: scrub the words its bitmap names (ping-pong pair) or zero the fresh level
 	// buffer (shortestpath); either way the bitmap two levels old is zeroed -- it is the one the level after
-	// this builds
-	// unfiltered bottom-up levels store densely (most vertices gain bits there: measured 3.1 vs 3.7 ms on the
-	// dense level of an s24 batch), every other level sparsely after a scrub of what `next` still holds
+	// this builds.  Unfiltered bottom-up levels store densely (most vertices gain bits there), every other level
+	// sparsely after the scrub.
 	const bool dense = mode == MODE_PULL && c->opt.dense_store;
-	level_clear_kernel<W><<<cgrid, 256, 0, st>>>(b.ctrl, b.fbit_words, keep_hist ? 0 : dense ? 2 : 1);
-	++*nk;
-	if (keep_hist && bm) {
-		zero_next_kernel<<<(uint32_t)c->sm_count * 4, 256, 0, st>>>(b.ctrl, bm / 16);
-		++*nk;
-	}
+	L.run(level_clear_kernel<W>, cgrid, 256, b.ctrl, b.fbit_words, keep_hist ? 0 : dense ? 2 : 1);
+	if (keep_hist && bm) L.run(zero_next_kernel, (uint32_t)c->sm_count * 4, 256, b.ctrl, bm / 16);
 	if (mode == MODE_PUSH) {
 		// pull -> push transition: the queue is rebuilt from the frontier bitmap (both kernels return at once
 		// when the previous level left a queue)
-		compact_bitmap_kernel<<<cgrid, 256, 0, st>>>(b.fbit_words, (uint32_t)g->V, g->d_off.as<int64_t>(), b.ctrl);
-		bfs_snapshot_items_kernel<<<1, 1, 0, st>>>(b.ctrl);
+		L.run(compact_bitmap_kernel, cgrid, 256, b.fbit_words, (uint32_t)g->V, g->d_off.as<int64_t>(), b.ctrl);
+		L.run(bfs_snapshot_items_kernel, 1, 1, b.ctrl);
 		PushArgs pa{};
 		pa.off = g->d_off.as<int64_t>();
 		pa.tgt = g->d_tgt.as<uint32_t>();
 		pa.seen = b.seen;
 		pa.ctrl = b.ctrl;
 		pa.alive_slots = b.alive_slots;
-		push_kernel<W, STATS><<<(uint32_t)c->sm_count * 8, 256, 0, st>>>(pa);
-		*nk += 3;
+		L.run(push_kernel<W, STATS>, (uint32_t)c->sm_count * 8, 256, pa);
 	} else {
 		const bool filter = mode != MODE_PULL, early = mode == MODE_PULL_F_EARLY;
 		PullArgs a{};
@@ -147,45 +172,58 @@ int launch_body(Ctx *c, Csr *g, const BatchBufs &b, uint32_t mode, bool keep_his
 		a.alive_slots = b.alive_slots;
 		a.done = b.done;
 		a.dyn = 1;
+		if (hl && !c->opt.dyn) { // host-driven loop, A/B switch: the level's views as kernel arguments
+			a.dyn = 0;
+			a.visit = hl->cur_visit;
+			a.next = hl->cur_next;
+			a.fcur = hl->cur_fbit;
+			a.fnext = hl->nxt_fbit;
+		}
 		a.dense = dense ? 1u : 0u;
 		// the done test only on sparse-store tail levels: a skipped vertex stores nothing, and a dense level relies
 		// on every listed vertex overwriting what `next` still holds (testing it everywhere left stale frontier
 		// words behind: measured wrong frontiers from level 2 of the NEXT batch on)
 		a.use_done = (b.done && mode == MODE_PULL_F_LATE) ? 1u : 0u;
-		launch_tiny<W, STATS>(a, g, filter, st, nk);
+		launch_tiny<W, STATS>(a, g, filter, L);
 		// measured on the filtered levels of R-MAT s24 (levels 2 / 6): pull_list 2.23 / 0.62 ms, 8 lanes per
 		// vertex 2.08 / 0.56 ms, 16 lanes 2.31 / 0.73 ms; the same kernel for the tiny class: no change
-		if (filter && c->opt.seg_small) launch_seg<W, 8, STATS>(a, g->d_small, g->n_small, st, nk);
-		else launch_class<W, 2, STATS>(a, g->d_small, g->n_small, filter, st, nk);
+		if (filter && c->opt.seg_small) launch_seg<W, 8, STATS>(a, g->d_small, g->n_small, L);
+		else launch_class<W, 2, STATS>(a, g->d_small, g->n_small, filter, L);
 		// medium in-degrees: the edge-parallel warp scan wins while most vertices still scan their whole
 		// in-list against a sparse frontier (early levels); two thread groups per vertex win when every
 		// word is gathered anyway (dense levels) or most vertices have nothing left to find (tail)
-		if (filter && early) launch_warp<W, STATS>(a, g->d_med, g->n_med, true, st, nk);
-		else launch_class<W, 2, STATS>(a, g->d_med, g->n_med, filter, st, nk);
-		launch_warp<W, STATS>(a, g->d_mid, g->n_mid, filter, st, nk);
-		launch_hubs<W, STATS>(a, g, st, nk);
-		frontier_stats_kernel<<<cgrid, 256, 0, st>>>(b.fbit_words, (uint32_t)g->V, g->d_off.as<int64_t>(), b.ctrl);
-		++*nk;
+		if (filter && early) launch_warp<W, STATS>(a, g->d_med, g->n_med, true, L);
+		else launch_class<W, 2, STATS>(a, g->d_med, g->n_med, filter, L);
+		launch_warp<W, STATS>(a, g->d_mid, g->n_mid, filter, L);
+		launch_hubs<W, STATS>(a, g, L);
+		L.run(frontier_stats_kernel, cgrid, 256, b.fbit_words, (uint32_t)g->V, g->d_off.as<int64_t>(), b.ctrl);
 	}
-	PGQ_CUDA(cudaGetLastError());
+	if (L.graph) {
+		if (L.err != cudaSuccess) {
+			set_error("loop graph: cudaGraphAddKernelNode -> %s", cudaGetErrorString(L.err));
+			return PGQ_ERR_CUDA;
+		}
+	} else {
+		PGQ_CUDA(cudaGetLastError());
+	}
 	return PGQ_OK;
 }
 
-int launch_body_w(Ctx *c, Csr *g, const BatchBufs &b, int W, bool stats, uint32_t mode, bool keep_hist,
-                  cudaStream_t st, uint32_t *nk) {
+int launch_body_w(Ctx *c, Csr *g, const BatchBufs &b, int W, bool stats, uint32_t mode, bool keep_hist, Launch &L,
+                  const LoopState *hl = nullptr) {
 	if (stats) {
 		switch (W) {
-		case 64: return launch_body<64, true>(c, g, b, mode, keep_hist, st, nk);
-		case 128: return launch_body<128, true>(c, g, b, mode, keep_hist, st, nk);
-		case 256: return launch_body<256, true>(c, g, b, mode, keep_hist, st, nk);
-		case 512: return launch_body<512, true>(c, g, b, mode, keep_hist, st, nk);
+		case 64: return launch_body<64, true>(c, g, b, mode, keep_hist, L, hl);
+		case 128: return launch_body<128, true>(c, g, b, mode, keep_hist, L, hl);
+		case 256: return launch_body<256, true>(c, g, b, mode, keep_hist, L, hl);
+		case 512: return launch_body<512, true>(c, g, b, mode, keep_hist, L, hl);
 		}
 	} else {
 		switch (W) {
-		case 64: return launch_body<64, false>(c, g, b, mode, keep_hist, st, nk);
-		case 128: return launch_body<128, false>(c, g, b, mode, keep_hist, st, nk);
-		case 256: return launch_body<256, false>(c, g, b, mode, keep_hist, st, nk);
-		case 512: return launch_body<512, false>(c, g, b, mode, keep_hist, st, nk);
+		case 64: return launch_body<64, false>(c, g, b, mode, keep_hist, L, hl);
+		case 128: return launch_body<128, false>(c, g, b, mode, keep_hist, L, hl);
+		case 256: return launch_body<256, false>(c, g, b, mode, keep_hist, L, hl);
+		case 512: return launch_body<512, false>(c, g, b, mode, keep_hist, L, hl);
 		}
 	}
 	set_error("unsupported lane width %d", W);
@@ -510,15 +548,10 @@ int loop_graph_build(Ctx *c, Csr *g, const BatchBufs &b, int W, bool keep_hist, 
 	sp.conditional.size = MODE_COUNT - 1;
 	PGQ_CUDA(cudaGraphAddNode(&n_switch, body, nullptr, 0, &sp));
 	for (uint32_t m = MODE_PUSH; m < MODE_COUNT; m++) {
-		cudaGraph_t bg = sp.conditional.phGraph_out[m - 1];
-		PGQ_CUDA(cudaStreamBeginCaptureToGraph(c->stream, bg, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
-		uint32_t nk = 0;
-		const int rc = launch_body_w(c, g, b, W, false, m, keep_hist, c->stream, &nk);
-		cudaGraph_t got = nullptr;
-		const cudaError_t e = cudaStreamEndCapture(c->stream, &got);
-		if (rc != PGQ_OK) return rc;
-		PGQ_CUDA(e);
-		nk_out[m] = nk;
+		Launch L;
+		L.graph = sp.conditional.phGraph_out[m - 1];
+		PGQ_TRY(launch_body_w(c, g, b, W, false, m, keep_hist, L));
+		nk_out[m] = L.nk;
 	}
 	nk_out[MODE_STOP] = 0;
 	{
@@ -535,6 +568,19 @@ int loop_graph_build(Ctx *c, Csr *g, const BatchBufs &b, int W, bool keep_hist, 
 		PGQ_CUDA(cudaGraphAddKernelNode(&n_check, body, &n_switch, 1, &kp));
 	}
 	PGQ_CUDA(cudaGraphInstantiate(&lg->exec, G, 0));
+	// The template is not needed once the executable graph exists.  It is destroyed HERE, before the first
+	// launch: destroying it later (at rebuild time, after launches) crashed inside cuGraphDestroy on driver
+	// 580.159 while it walked the nested WHILE -> SWITCH body graphs.  PGQ_B200_GRAPH_TEMPLATE=late restores that
+	// order, =leak never destroys templates (diagnostics).
+	{
+		static const char *mode = getenv("PGQ_B200_GRAPH_TEMPLATE");
+		if (!mode || !strcmp(mode, "early")) {
+			PGQ_CUDA(cudaGraphDestroy(G));
+			lg->graph = nullptr;
+		} else if (!strcmp(mode, "leak")) {
+			lg->graph = nullptr;
+		}
+	}
 	lg->g = g;
 	lg->gen = g->gen;
 	lg->W = W;
@@ -714,9 +760,11 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 			}
 			if (c->opt.stats) launch_count(c, g, b, W, h.L.cur_visit);
 			if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
-			uint32_t nk = 0;
+			Launch L;
+			L.st = st;
 			const uint32_t mode = h.L.mode;
-			PGQ_TRY(launch_body_w(c, g, b, W, c->opt.stats != 0, mode, keep_hist, st, &nk));
+			PGQ_TRY(launch_body_w(c, g, b, W, c->opt.stats != 0, mode, keep_hist, L, &h.L));
+			const uint32_t nk = L.nk;
 			count_launch(c, nk);
 			if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_b, st));
 			launch_check(b, W, st, 0, 0, 0);
@@ -1298,17 +1346,19 @@ int launch_part_level(Ctx *c, Csr *g, const PartBufs &b, int cur, int iter) {
 	a.fcur = b.fbit[cur];
 	a.fnext = b.fbit[cur ^ 1] + b.fwords_per_slice * r;
 	a.alive_slots = b.alive_slots;
+	a.dense = 1; // every owned vertex stores its word (the allgather ships the whole slice)
 	if (b.peer_tab) { // fused exchange: kernels store new words into every peer's replica
 		a.peer_next = b.peer_tab + (size_t)(cur ^ 1) * (G - 1);
 		a.npeers = (uint32_t)(G - 1);
 	}
-	uint32_t nk = 0;
-	launch_tiny<W>(a, g, true, st, &nk);
-	launch_class<W, 2>(a, g->d_small, g->n_small, true, st, &nk);
-	launch_warp<W>(a, g->d_med, g->n_med, true, st, &nk);
-	launch_warp<W>(a, g->d_mid, g->n_mid, true, st, &nk);
-	launch_hubs<W>(a, g, st, &nk);
-	count_launch(c, nk);
+	Launch L;
+	L.st = st;
+	launch_tiny<W>(a, g, true, L);
+	launch_class<W, 2>(a, g->d_small, g->n_small, true, L);
+	launch_warp<W>(a, g->d_med, g->n_med, true, L);
+	launch_warp<W>(a, g->d_mid, g->n_mid, true, L);
+	launch_hubs<W>(a, g, L);
+	count_launch(c, L.nk);
 	alive_fold_kernel<<<1, 1024, 0, st>>>(b.alive_slots, b.alive_local);
 	count_launch(c);
 	return PGQ_OK;
@@ -1409,6 +1459,17 @@ int msbfs_part_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found) {
 		uint32_t active = h.n_active;
 		int cur = 0;
 		for (int iter = 1; active; iter++) {
+			if (c->opt.stats && g->E > 0) { // TEPS numerator of this level (untimed instrumented pass)
+				const uint32_t ne = (uint32_t)g->E, grid = div_up(ne, 256);
+				const uint32_t *isrc = g->d_isrc.as<uint32_t>();
+				switch (W) {
+				case 64: part_count_kernel<64><<<grid, 256, 0, st>>>(isrc, ne, b.visit[cur], b.fbit[cur], b.ctrl); break;
+				case 128: part_count_kernel<128><<<grid, 256, 0, st>>>(isrc, ne, b.visit[cur], b.fbit[cur], b.ctrl); break;
+				case 256: part_count_kernel<256><<<grid, 256, 0, st>>>(isrc, ne, b.visit[cur], b.fbit[cur], b.ctrl); break;
+				default: part_count_kernel<512><<<grid, 256, 0, st>>>(isrc, ne, b.visit[cur], b.fbit[cur], b.ctrl); break;
+				}
+				count_launch(c);
+			}
 			if (c->opt.timing) PGQ_CUDA(cudaEventRecord(c->ev_a, st));
 			uint64_t before = c->stats.kernel_launches;
 			PGQ_TRY(launch_part_level_w(c, g, b, W, cur, iter));
@@ -1437,6 +1498,7 @@ int msbfs_part_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found) {
 			if (!h.change_out) break;
 			active = h.n_active;
 		}
+		if (c->opt.stats) c->stats.edges_lane += h.edges_lane; // accumulated in the control block over the batch
 	}
 	PGQ_CUDA(cudaMemcpyAsync(h_found, d_found, (size_t)nslots * 4, cudaMemcpyDeviceToHost, st));
 	PGQ_CUDA(cudaStreamSynchronize(st));

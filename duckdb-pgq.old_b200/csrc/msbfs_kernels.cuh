@@ -281,6 +281,23 @@ __device__ __forceinline__ bool fbit_test(const uint32_t *f, uint32_t v) {
 	return (__ldg(f + (v >> 5)) >> (v & 31)) & 1u;
 }
 
+// A/B switches for bisecting kernel cost (tools/r02_ab.sh builds library variants with -DPGQ_AB_...)
+#ifdef PGQ_AB_NODONE
+static constexpr bool kDone = false;
+#else
+static constexpr bool kDone = true;
+#endif
+#ifdef PGQ_AB_NODYN
+static constexpr bool kDyn = false;
+#else
+static constexpr bool kDyn = true;
+#endif
+#ifdef PGQ_AB_DENSE
+static constexpr bool kSparse = false;
+#else
+static constexpr bool kSparse = true;
+#endif
+
 // done bit of vertex n (plain load: other vertices' bits of the same word may be set by this launch)
 __device__ __forceinline__ bool done_test(const uint32_t *done, uint32_t n) {
 	return done && ((done[n >> 5] >> (n & 31)) & 1u);
@@ -305,10 +322,10 @@ __device__ __forceinline__ bool group_any(bool x) {
 // reductions use full-mask shuffles.
 template <int W, int GPV, bool FILTER, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
-	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
+	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
 	static_assert(GPV >= 1 && GPV <= G, "groups per vertex");
@@ -323,7 +340,7 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	const uint64_t idx = (uint64_t)wid * VPW + vslot;
 	const bool listed = idx < a.nlist;
 	const uint32_t n = listed ? a.list[idx] : 0u;
-	const bool valid = listed && !(a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
+	const bool valid = listed && !(kDone && a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
 	uint32_t lo = 0, hi = 0;
 	if (valid) {
 		lo = a.ioff[n];
@@ -420,7 +437,7 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	const unsigned rbal = __ballot_sync(FULL, writer && rest);
 	const unsigned gmask = ((1u << TPV) - 1u) << (vslot * (GPV * TPV));
 	const bool vnew = (bal & gmask) != 0;
-	if (writer && (vnew || a.dense)) {
+	if (writer && (!kSparse || vnew || a.dense)) {
 		// the WHOLE word is written when any slice gained bits: a reader that passed the frontier-bit test
 		// reads all of it
 		st_slice<SW>(next_p + wo, news);
@@ -433,7 +450,7 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	}
 	const bool leader = writer && t == 0;
 	if (leader && vnew) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
-	if (leader && a.done && !(rbal & gmask)) atomicOr(&a.done[n >> 5], 1u << (n & 31));
+	if (kDone && leader && a.done && !(rbal & gmask)) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (a.npeers && writer && vnew) st_peers<SW>(a, wo, news); // whole word, zero slices included
 	// no global counters here: frontier_stats_kernel derives them from fnext afterwards
 	if (STATS) {
@@ -451,10 +468,10 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 // vertices and 3 % of its edges, so its cost is instructions and dependent loads per VERTEX.
 template <int W, bool FILTER, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
-	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
+	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
 	constexpr uint32_t INV = 0xFFFFFFFFu, FULL = 0xffffffffu;
@@ -466,7 +483,7 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 	const uint64_t idx = (uint64_t)wid * G + g;
 	const bool inlist = idx < a.nlist;
 	const uint32_t n = inlist ? a.list[idx] : 0u;
-	const bool listed = inlist && !(a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
+	const bool listed = inlist && !(kDone && a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
 	uint32_t lo = 0, hi = 0;
 	if (listed) {
 		lo = a.ioff[n];
@@ -514,7 +531,7 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 	const unsigned rbal = __ballot_sync(FULL, listed && rest);
 	const unsigned gmask = ((1u << TPV) - 1u) << (g * TPV);
 	const bool vnew = (bal & gmask) != 0;
-	if (listed && (vnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
+	if (listed && (!kSparse || vnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
 		st_slice<SW>(next_p + wo, news);
 		if (mine) {
 #pragma unroll
@@ -527,7 +544,7 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 		if (t == 0) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
 		if (a.npeers) st_peers<SW>(a, wo, news);
 	}
-	if (listed && t == 0 && a.done && !(rbal & gmask)) atomicOr(&a.done[n >> 5], 1u << (n & 31));
+	if (kDone && listed && t == 0 && a.done && !(rbal & gmask)) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (STATS) {
 		stat_add(&a.ctrl->k_listed, (inlist && t == 0) ? 1u : 0u);
 		stat_add(&a.ctrl->k_open, (listed && t == 0) ? 1u : 0u);
@@ -544,10 +561,10 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 // deep like pull_list_kernel.  Early exit once every unseen lane of the vertex is covered.
 template <int W, bool FILTER, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
-	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
+	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G;
 	constexpr int STEPS = 32 / G;
@@ -558,7 +575,7 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 	if (wid >= a.nlist) return; // warp-uniform
 	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
 	const uint32_t n = a.list[wid];
-	if (a.use_done && done_test(a.done, n)) { // warp-uniform: the vertex is skipped altogether
+	if (kDone && a.use_done && done_test(a.done, n)) { // warp-uniform: the vertex is skipped altogether
 		if (STATS && lane == 0) atomicAdd(&a.ctrl->k_listed, 1ull);
 		return;
 	}
@@ -615,7 +632,7 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 #pragma unroll
 	for (int i = 0; i < SW; i++) rest |= (unseen.w[i] & ~news.w[i]) != 0u;
 	const bool wrest = __any_sync(FULL, rest);
-	if (g == 0 && (wany || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
+	if (g == 0 && (!kSparse || wany || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
 		st_slice<SW>(next_p + wo, news);
 		if (slice_any<SW>(news)) {
 #pragma unroll
@@ -625,7 +642,7 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 		}
 	}
 	if (wany && lane == 0) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
-	if (!wrest && lane == 0 && a.done) atomicOr(&a.done[n >> 5], 1u << (n & 31));
+	if (kDone && !wrest && lane == 0 && a.done) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (a.npeers && wany && g == 0) st_peers<SW>(a, wo, news);
 	if (STATS) {
 		if (lane == 0) {
@@ -648,10 +665,10 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 // packs 32/SEG vertices into a warp for in-degrees far below 32.  Rounds are pipelined two deep.
 template <int W, int SEG, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
-	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
+	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
 	constexpr int VPW = 32 / SEG;  // vertices per warp
@@ -668,7 +685,7 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 	const uint64_t idx = (uint64_t)wid * VPW + seg;
 	const bool listed = idx < a.nlist;
 	const uint32_t n = listed ? a.list[idx] : 0u;
-	const bool valid = listed && !(a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
+	const bool valid = listed && !(kDone && a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
 	uint32_t lo = 0, hi = 0;
 	if (valid) {
 		lo = a.ioff[n];
@@ -748,7 +765,7 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 	const unsigned rb = __ballot_sync(FULL, writer && rest);
 	const bool vnew = ((nb >> (seg * SEG)) & SEGMASK) != 0u;
 	const bool vrest = ((rb >> (seg * SEG)) & SEGMASK) != 0u;
-	if (writer && (vnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
+	if (writer && (!kSparse || vnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
 		st_slice<SW>(next_p + wo, news);
 		if (slice_any<SW>(news)) {
 #pragma unroll
@@ -758,7 +775,7 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 		}
 	}
 	if (writer && t == 0 && vnew) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
-	if (writer && t == 0 && a.done && !vrest) atomicOr(&a.done[n >> 5], 1u << (n & 31));
+	if (kDone && writer && t == 0 && a.done && !vrest) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (a.npeers && writer && vnew) st_peers<SW>(a, wo, news); // whole word, zero slices included
 	if (STATS) {
 		stat_add(&a.ctrl->k_listed, (listed && sl == 0) ? 1u : 0u);
@@ -773,10 +790,10 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 // ---- K4 hubs: one block per chunk of a hub's in-list, partial ORs merged with atomicOr ---------
 template <int W, bool STATS = false>
 __global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
-	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
+	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
 	const HubChunk hc = a.chunks[blockIdx.x];
@@ -838,10 +855,10 @@ __global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
 // one TPV-thread group per hub: next = hubacc & ~seen & active; seen |= next; hubacc = 0
 template <int W>
 __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
-	const uint32_t *const visit_p = a.dyn ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = a.dyn ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = a.dyn ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = a.dyn ? a.ctrl->L.nxt_fbit : a.fnext;
+	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
+	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
+	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
+	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
 	__shared__ uint32_t salive[16];
@@ -862,7 +879,7 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 	}
 	const bool anyn = slice_any<SW>(news);
 	const bool gnew = group_any<TPV>(anyn);
-	if (h < a.nlist && (gnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
+	if (h < a.nlist && (!kSparse || gnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
 		const uint32_t n = a.list[h];
 		const size_t wo = (size_t)n * WPV + (size_t)t * SW;
 		st_slice<SW>(next_p + wo, news);
@@ -882,7 +899,7 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 
 // After a pull level: vertices in the new frontier and the sum of their out-degrees (the inputs of
 // the direction switch), plus the `change` flag, from the frontier bitmap.  One atomic per block.
-__global__ void __launch_bounds__(256) frontier_stats_kernel(uint32_t nwords, uint32_t V,
+static __global__ void __launch_bounds__(256) frontier_stats_kernel(uint32_t nwords, uint32_t V,
                                                              const int64_t *__restrict__ off, BfsCtrl *ctrl) {
 	constexpr uint32_t FULL = 0xffffffffu;
 	const uint32_t *const fbit = ctrl->L.nxt_fbit; // the frontier this level produced
@@ -990,7 +1007,7 @@ struct LoopInit {
 // One block of W threads.  Sets the source bits (R4: visit only, seen untouched), the active mask,
 // found = -1, the level-1 push queue (the distinct sources) and the loop state of level 1.
 // lane_src == 0xFFFFFFFF marks an unused lane slot.  The frontier bitmaps must be zero on entry.
-__global__ void bfs_init_kernel(const uint32_t *__restrict__ lane_src, int W, int32_t *__restrict__ found,
+static __global__ void bfs_init_kernel(const uint32_t *__restrict__ lane_src, int W, int32_t *__restrict__ found,
                                 BfsCtrl *ctrl, const int64_t *__restrict__ off, LoopInit li) {
 	__shared__ uint32_t cnt;
 	const int lane = threadIdx.x;
@@ -1057,7 +1074,7 @@ __global__ void bfs_init_kernel(const uint32_t *__restrict__ lane_src, int W, in
 
 // After a level: lanes whose destination has been seen get found=iter and leave the active mask;
 // the frontier statistics of the level are snapshotted for the host's direction decision.
-__global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, int W, BfsCtrl *ctrl,
+static __global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, int W, BfsCtrl *ctrl,
                                  uint32_t *__restrict__ alive_slots, int use_handles,
                                  cudaGraphConditionalHandle h_while, cudaGraphConditionalHandle h_switch) {
 	const int iter = (int)ctrl->L.iter; // the level that just ran
@@ -1140,14 +1157,14 @@ __global__ void bfs_check_kernel(const uint32_t *__restrict__ seen, int W, BfsCt
 
 // First node of the loop graph: the conditional handles from the mode the init kernel (or the check
 // kernel of an interrupted loop) left behind.
-__global__ void loop_begin_kernel(BfsCtrl *ctrl, cudaGraphConditionalHandle h_while,
+static __global__ void loop_begin_kernel(BfsCtrl *ctrl, cudaGraphConditionalHandle h_while,
                                   cudaGraphConditionalHandle h_switch) {
 	cudaGraphSetConditional(h_while, ctrl->L.mode != MODE_STOP ? 1u : 0u);
 	cudaGraphSetConditional(h_switch, ctrl->L.mode - 1u);
 }
 
 // The host extended the level-buffer table of an interrupted shortestpath batch: resume.
-__global__ void loop_resume_kernel(BfsCtrl *ctrl, uint32_t *const *hist, uint32_t hist_cap) {
+static __global__ void loop_resume_kernel(BfsCtrl *ctrl, uint32_t *const *hist, uint32_t hist_cap) {
 	LoopState &L = ctrl->L;
 	L.hist = hist;
 	L.hist_cap = hist_cap;
@@ -1344,7 +1361,7 @@ __global__ void __launch_bounds__(256) scrub_kernel(BfsCtrl *ctrl, uint32_t nwor
 }
 
 // shortestpath: zero the level buffer the level about to run writes (16 bytes per thread and step)
-__global__ void __launch_bounds__(256) zero_next_kernel(BfsCtrl *ctrl, size_t n16) {
+static __global__ void __launch_bounds__(256) zero_next_kernel(BfsCtrl *ctrl, size_t n16) {
 	uint4 *p = reinterpret_cast<uint4 *>(ctrl->L.cur_next);
 	const size_t stride = (size_t)gridDim.x * blockDim.x;
 	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) p[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -1353,7 +1370,7 @@ __global__ void __launch_bounds__(256) zero_next_kernel(BfsCtrl *ctrl, size_t n1
 // pull -> push transition: rebuild the work queue from the frontier bitmap.  One thread per bitmap
 // word, two passes (count items, warp-scan, one atomic per warp, write).  The vertex / edge totals
 // of this frontier were already published by frontier_stats_kernel; only the item count is new.
-__global__ void __launch_bounds__(256) compact_bitmap_kernel(uint32_t nwords, uint32_t V,
+static __global__ void __launch_bounds__(256) compact_bitmap_kernel(uint32_t nwords, uint32_t V,
                                                              const int64_t *__restrict__ off, BfsCtrl *ctrl) {
 	if (ctrl->L.have_queue) return; // the previous level was top-down too: its output queue is the input
 	const uint32_t *const fbit = ctrl->L.cur_fbit;
@@ -1392,7 +1409,7 @@ __global__ void __launch_bounds__(256) compact_bitmap_kernel(uint32_t nwords, ui
 }
 
 // publish the rebuilt queue's item count
-__global__ void bfs_snapshot_items_kernel(BfsCtrl *ctrl) {
+static __global__ void bfs_snapshot_items_kernel(BfsCtrl *ctrl) {
 	if (ctrl->L.have_queue) return;
 	ctrl->out_items = ctrl->next_items;
 	ctrl->next_items = 0;
@@ -1432,7 +1449,7 @@ __global__ void __launch_bounds__(256) bfs_count_kernel(const uint32_t *__restri
 // Every rank runs these on its own replica of the full frontier structures, with identical inputs.
 
 // source bits + frontier bitmap + active mask (no push queue: this path is bottom-up only)
-__global__ void bfs_init_part_kernel(const uint32_t *__restrict__ lane_src, int W, uint32_t *__restrict__ visit,
+static __global__ void bfs_init_part_kernel(const uint32_t *__restrict__ lane_src, int W, uint32_t *__restrict__ visit,
                                      int32_t *__restrict__ found, BfsCtrl *ctrl, uint32_t *__restrict__ fbit0) {
 	__shared__ uint32_t cnt;
 	const int lane = threadIdx.x;
@@ -1465,8 +1482,33 @@ __global__ void bfs_init_part_kernel(const uint32_t *__restrict__ lane_src, int 
 	if (lane == 0) ctrl->n_active = cnt;
 }
 
+// Instrumented pass of the partitioned path: TEPS numerator of the level about to run, same definition as
+// bfs_count_kernel (sum over lanes of the out-degrees of the lane's frontier vertices).  A rank holds no
+// out-degrees, but every edge v -> n is an in-edge of exactly one rank's slice: each rank counts, over its own
+// in-edges, the lanes that have the edge's source in their frontier; the ranks' sums add up to the numerator.
+template <int W>
+__global__ void __launch_bounds__(256) part_count_kernel(const uint32_t *__restrict__ isrc, uint32_t nedges,
+                                                         const uint32_t *__restrict__ visit,
+                                                         const uint32_t *__restrict__ fbit, BfsCtrl *ctrl) {
+	constexpr int WPV = W / 32;
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned long long el = 0;
+	if (j < nedges) {
+		const uint32_t v = isrc[j];
+		if (fbit_test(fbit, v)) {
+			uint32_t pc = 0;
+#pragma unroll
+			for (int i = 0; i < WPV; i++) pc += __popc(visit[(size_t)v * WPV + i] & ctrl->active[i]);
+			el = pc;
+		}
+	}
+#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) el += __shfl_xor_sync(0xffffffffu, el, d);
+	if ((threadIdx.x & 31) == 0 && el) atomicAdd(&ctrl->edges_lane, el);
+}
+
 // fold (and re-zero) this rank's alive slots into 16 words for the allgather
-__global__ void alive_fold_kernel(uint32_t *__restrict__ alive_slots, uint32_t *__restrict__ out16) {
+static __global__ void alive_fold_kernel(uint32_t *__restrict__ alive_slots, uint32_t *__restrict__ out16) {
 	__shared__ uint32_t salive[16];
 	if (threadIdx.x < 16) salive[threadIdx.x] = 0;
 	__syncthreads();
@@ -1484,7 +1526,7 @@ __global__ void alive_fold_kernel(uint32_t *__restrict__ alive_slots, uint32_t *
 // After the allgather every rank holds the complete new frontier: a lane is found at this level iff
 // next[dst] carries its bit (seen[dst] gains a bit exactly when next[dst] does), and a lane is
 // alive iff some rank produced a bit for it.  Identical on all ranks, no further exchange.
-__global__ void bfs_check_part_kernel(const uint32_t *__restrict__ next, const uint32_t *__restrict__ lane_dst, int W,
+static __global__ void bfs_check_part_kernel(const uint32_t *__restrict__ next, const uint32_t *__restrict__ lane_dst, int W,
                                       int32_t *__restrict__ found, BfsCtrl *ctrl, int iter,
                                       const uint32_t *__restrict__ alive_all, int world,
                                       const uint32_t *__restrict__ fnext) {
@@ -1531,7 +1573,7 @@ __global__ void bfs_check_part_kernel(const uint32_t *__restrict__ next, const u
 // 10^5 entries long before the first hit).  Level 0's frontier is the source itself, found by
 // binary search in the id-sorted in-list.
 // mode 0: [src,..,dst] (len L+1); mode 1: [src,e0,v1,..,dst] (len 2L+1).
-__global__ void __launch_bounds__(256) bfs_paths_hist_kernel(const uint32_t *const *__restrict__ hist,
+static __global__ void __launch_bounds__(256) bfs_paths_hist_kernel(const uint32_t *const *__restrict__ hist,
                                                              const uint32_t *__restrict__ ioff,
                                                              const uint32_t *__restrict__ isrc,
                                                              const uint32_t *__restrict__ ipos,

@@ -558,3 +558,107 @@ SELECT p.i, CASE WHEN p.s = p.d THEN NULL WHEN fs.h >= 3 THEN fs.h ELSE NULL END
     assert r[-2] == ("result", ["True"])
     cp_sql = [row.split(",", 1)[1] for row in r[-1][1]]
     assert ext_cp == cp_sql
+
+
+# ---- round 2: the shim under concurrent entry, restartable builds, edge-less graphs, constant inputs ---------
+def _knows_setup_sql(tmp_path, V, src, dst, ps, pd, threads):
+    _write_csv(tmp_path / "person.csv", [np.arange(V)])
+    _write_csv(tmp_path / "knows.csv", [src, dst])
+    _write_csv(tmp_path / "pairs.csv", [np.arange(len(ps)), ps, pd])
+    return """LOAD '%s';
+PRAGMA threads=%d;
+CREATE TABLE person(id BIGINT);
+CREATE TABLE knows(p1 BIGINT, p2 BIGINT);
+CREATE TABLE pairs(i BIGINT, s BIGINT, d BIGINT);
+COPY person FROM '%s';
+COPY knows FROM '%s';
+COPY pairs FROM '%s';
+""" % (EXT, threads, tmp_path / "person.csv", tmp_path / "knows.csv", tmp_path / "pairs.csv")
+
+
+@pytest.mark.gpu
+@needs_host
+@pytest.mark.parametrize("verify", [False, True])
+def test_sql_concurrent_entry(tmp_path, verify):
+    """PRAGMA threads=4 (and the reference CI's PRAGMA verify_parallelism, src/function/pragma/pragma_functions.cpp:
+    305,311): the query functions are entered by several workers at once, their rows meet in the slot's batcher and
+    every row still gets its own answer.  The CSR is built with threads=1 first (its neighbour order is the row
+    arrival order), and lengths / reachability do not depend on that order anyway; paths are compared for
+    threads=4 too because the CSR was built single-threaded."""
+    V, E = 3000, 60000
+    src, dst = orc.gen_knows(4711, V, E)
+    v, e, eids = orc.csr_build(V, src, dst)
+    n = 20000  # ~20 chunks of 1024 rows
+    ps, pd = orc.gen_pairs(13, V, v, n)
+    ps[::53] = pd[::53]
+    vs = "CAST(%d AS BIGINT)" % V
+    sql = _knows_setup_sql(tmp_path, V, src, dst, ps, pd, 1)
+    sql += "SELECT sum(create_csr_edge(0, %s, CAST(%d AS BIGINT), p1, p2, rowid)) FROM knows;\n" % (vs, E)
+    sql += "PRAGMA threads=4;\n"
+    if verify:
+        sql += "PRAGMA verify_parallelism;\n"
+    sql += "SELECT i, iterativelength(0, %s, s, d) FROM pairs ORDER BY i;\n" % vs
+    sql += "SELECT i, reachability(0, %s, s, d) FROM pairs ORDER BY i;\n" % vs
+    sql += "SELECT i, shortestpath_with_edges(0, %s, s, d) FROM pairs WHERE i < 6000 ORDER BY i;\n" % vs
+    sql += "SELECT sum(iterativelength(0, %s, s, d)), count(*) FROM pairs;\n" % vs
+    sql += "SELECT pgq_batcher_stats(0);\n"
+    r = run_sql(sql)
+    assert all(k == "result" for k, _ in r), [x for x in r if x[0] != "result"][:2]
+    res = [rows for k, rows in r if rows and rows[0].count(",") >= 1]
+    eo, ev = orc.iterativelength(V, v, e, ps, pd)
+    got = [row.split(",", 1)[1] for row in res[0]]
+    assert got == ["NULL" if not ev[i] else str(int(eo[i])) for i in range(n)]
+    got = [row.split(",", 1)[1] for row in res[1]]
+    assert got == ["True" if ev[i] else "False" for i in range(n)]
+    off, ln, pv, vals = orc.shortestpath(V, v, e, eids, ps[:6000], pd[:6000], mode=1)
+    got = [_parse_list(row.split(",", 1)[1]) for row in res[2]]
+    exp = [None if not pv[i] else [int(x) for x in vals[int(off[i]):int(off[i]) + int(ln[i])]] for i in range(6000)]
+    assert got == exp
+    assert res[3] == ["%d,%d" % (int(eo[ev == 1].sum()), n)]
+    stats = r[-1][1][0]
+    calls, gpu_calls = (int(x.split("=")[1]) for x in stats.split())
+    assert calls >= 3 * (n // 1024) and gpu_calls <= calls
+
+
+@pytest.mark.gpu
+@needs_host
+def test_sql_build_is_restartable_and_edgeless_graphs_answer(tmp_path):
+    """(1) a create_csr_edge statement that aborts part-way (NULL row) must not wedge the slot -- the
+    normal build statements simply run again; (2) a graph with vertices and ZERO edge rows finalizes (queries
+    give NULL / false, not an internal error); (3) all-constant arguments give a constant result."""
+    V = 50
+    src = np.arange(V - 1)
+    dst = src + 1
+    _write_csv(tmp_path / "person.csv", [np.arange(V)])
+    _write_csv(tmp_path / "knows.csv", [src, dst])
+    bad_src = src.astype(object)
+    bad_src[30] = None
+    _write_csv(tmp_path / "bad.csv", [bad_src, dst])
+    vs = "CAST(%d AS BIGINT)" % V
+    build = ("SELECT sum(create_csr_edge(1, (SELECT count(*) FROM person), "
+             "CAST((SELECT sum(create_csr_vertex(1, (SELECT count(*) FROM person), sub.dense_id, sub.cnt)) "
+             "FROM (SELECT p.rowid AS dense_id, count(k.p1) AS cnt FROM person p LEFT JOIN %s k ON k.p1 = p.id "
+             "GROUP BY p.rowid) sub) AS BIGINT), k.p1, k.p2)) FROM %s k;\n")
+    sql = "LOAD '%s';\nPRAGMA threads=1;\n" % EXT
+    sql += "CREATE TABLE person(id BIGINT);\nCOPY person FROM '%s';\n" % (tmp_path / "person.csv")
+    sql += "CREATE TABLE knows(p1 BIGINT, p2 BIGINT);\nCOPY knows FROM '%s';\n" % (tmp_path / "knows.csv")
+    sql += "CREATE TABLE bad(p1 BIGINT, p2 BIGINT);\nCOPY bad FROM '%s';\n" % (tmp_path / "bad.csv")
+    sql += "CREATE TABLE nobody(p1 BIGINT, p2 BIGINT);\n"
+    sql += build % ("bad", "bad")          # 9: aborts on the NULL row
+    sql += build % ("knows", "knows")      # 9: the same statement on good rows just works
+    sql += "SELECT iterativelength(1, %s, CAST(0 AS BIGINT), CAST(49 AS BIGINT));\n" % vs  # 10: constant args
+    sql += build % ("knows", "knows")      # 11: rebuilding a finished CSR works too
+    sql += "SELECT shortestpath(1, %s, CAST(3 AS BIGINT), CAST(6 AS BIGINT));\n" % vs  # 12
+    # an edge-less graph: create_csr_vertex rows only (the edge query returns no row, so create_csr_edge never runs)
+    sql += ("SELECT sum(create_csr_vertex(2, (SELECT count(*) FROM person), sub.dense_id, sub.cnt)) FROM "
+            "(SELECT p.rowid AS dense_id, count(k.p1) AS cnt FROM person p LEFT JOIN nobody k ON k.p1 = p.id "
+            "GROUP BY p.rowid) sub;\n")    # 13
+    sql += "SELECT iterativelength(2, %s, id, id + 1), reachability(2, %s, id, id + 1), iterativelength(2, %s, id, id) FROM person WHERE id < 3 ORDER BY id;\n" % (vs, vs, vs)  # 14
+    r = run_sql(sql)
+    assert r[9][0] == "error" and "NULL" in r[9][1], r[9]
+    assert r[10] == ("result", [str(V - 1)]), r[10]
+    assert r[11] == ("result", ["49"]), r[11]
+    assert r[12] == ("result", [str(V - 1)]), r[12]
+    assert r[13] == ("result", ["[3, 4, 5, 6]"]), r[13]
+    assert r[14] == ("result", ["0"]), r[14]
+    assert r[15] == ("result", ["NULL,False,0"] * 3), r[15]
