@@ -374,6 +374,12 @@ class Context:
                                                       C.c_void_p(d_src), C.c_void_p(d_dst), C.c_void_p(d_out),
                                                       C.c_void_p(d_out_valid)))
 
+    def iterativelength_device_noalloc(self, csr_id, n, d_src, d_dst, d_out, d_out_valid):
+        """Allocation-free variant (static 8 MiB device scratch; small graphs, n <= 4096): include/pgq_b200.h."""
+        self._chk(self.lib.pgq_iterativelength_device_noalloc(self._ctx, C.c_int32(csr_id), C.c_int64(n),
+                                                              C.c_void_p(d_src), C.c_void_p(d_dst), C.c_void_p(d_out),
+                                                              C.c_void_p(d_out_valid)))
+
     # ---- helpers ----
     def dev_alloc(self, nbytes):
         p = C.c_void_p()

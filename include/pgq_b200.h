@@ -178,6 +178,19 @@ int pgq_cheapest_path_length(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_
 int pgq_iterativelength_device(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *d_src,
                                const int64_t *d_dst, int64_t *d_out, uint8_t *d_out_valid);
 
+/* Allocation-free variant of pgq_iterativelength_device.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments and results as pgq_iterativelength_device, but every byte of
+ * scratch (control block, lane tables, `seen`, both frontier buffers) lives in one file-scope static __device__
+ * array of 8 MiB (csrc/noalloc.cu) that every GPU loading the library holds until exit; the call performs no
+ * cudaMalloc / cudaFree / cudaHostAlloc.  Limits, rejected with an error naming them: n <= 4096 rows;
+ * 64 KiB + 3 * roundup256(V * lanes/8) <= 8 MiB (lanes = 64..512 by n, or option "lanes"): V <= ~43 000 at 512
+ * lanes, ~348 000 at 64; the csr must have been prepared before (pgq_csr_prepare or any earlier query -- that
+ * step allocates).  The array is shared by all calls on a device and keeps the last call's contents (what must
+ * be zero is cleared per batch); calls that overlap on the GPU (two contexts on one device) race on it. */
+int pgq_iterativelength_device_noalloc(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *d_src,
+                                       const int64_t *d_dst, int64_t *d_out, uint8_t *d_out_valid);
+
 /* ---- 1-D vertex partition across GPUs (BASELINE.json configs[4]) -------------------------------
  * One process per GPU.  32-vertex blocks are dealt to the ranks by a scrambling bijection of the
  * block index (plain ranges or plain block-cyclic dealing leave R-MAT ranks 3:1 unbalanced); a rank
