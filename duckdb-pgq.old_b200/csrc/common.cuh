@@ -166,9 +166,9 @@ struct Options {
 	int64_t sort_wide_min = 32768; // ... from this many keys on
 	int64_t level_cap = 0x7fffffff; // per call, not user-settable: iterativelength's upper bound (R11)
 	int64_t loop = 1;          // 1: device-side level loop (CUDA graph WHILE/SWITCH nodes), 0: host loop, one sync per level
-	int64_t done_bitmap = 1;   // skip vertices whose `seen` already holds every active lane: 1 = tested on tail levels, 2 = on every level
+	int64_t done_bitmap = 0;   // with dense_store=0: tail levels skip vertices whose `seen` already holds every active lane
 	int64_t dyn = 1;           // host-driven loop only: 0 = frontier views as kernel arguments instead of from the control block
-	int64_t dense_store = 1;   // unfiltered levels write every listed vertex's `next` word (0: sparse stores + scrub everywhere)
+	int64_t dense_store = 1;   // filtered bottom-up levels write every listed vertex's `next` word too (0: sparse stores after a scrub)
 	int64_t l2_persist = 0;    // access-policy window (persisting L2) on `seen` for the batch streams
 	int64_t hist_budget_mb = 0; // shortestpath level history per worker: 0 = a quarter of the free HBM
 };

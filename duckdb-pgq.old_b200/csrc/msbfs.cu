@@ -144,7 +144,11 @@ int launch_body(Ctx *c, Csr *g, const BatchBufs &b, uint32_t mode, bool keep_his
 	// buffer (shortestpath); either way the bitmap two levels old is zeroed -- it is the one the level after
 	// this builds.  Unfiltered bottom-up levels store densely (most vertices gain bits there), every other level
 	// sparsely after the scrub.
-	const bool dense = mode == MODE_PULL && c->opt.dense_store;
+	// Stores of a bottom-up level: dense = every listed vertex writes its `next` word (round 1's form).  The
+	// unfiltered instantiations always store densely (compile-time); on filtered levels it is option dense_store
+	// (default 1: measured 2.09 / 0.56 ms dense against 2.16 / 0.74 ms sparse on levels 2 / 6 of an s24 batch,
+	// profiles/r02_ab_views.md).  Top-down levels scrub `next` by bitmap first, as before.
+	const bool dense = mode == MODE_PULL || (mode != MODE_PUSH && c->opt.dense_store);
 	L.run(level_clear_kernel<W>, cgrid, 256, b.ctrl, b.fbit_words, keep_hist ? 0 : dense ? 2 : 1);
 	if (keep_hist && bm) L.run(zero_next_kernel, (uint32_t)c->sm_count * 4, 256, b.ctrl, bm / 16);
 	if (mode == MODE_PUSH) {
@@ -183,7 +187,7 @@ int launch_body(Ctx *c, Csr *g, const BatchBufs &b, uint32_t mode, bool keep_his
 		// the done test only on sparse-store tail levels: a skipped vertex stores nothing, and a dense level relies
 		// on every listed vertex overwriting what `next` still holds (testing it everywhere left stale frontier
 		// words behind: measured wrong frontiers from level 2 of the NEXT batch on)
-		a.use_done = (b.done && mode == MODE_PULL_F_LATE) ? 1u : 0u;
+		a.use_done = (b.done && mode == MODE_PULL_F_LATE && !dense) ? 1u : 0u;
 		launch_tiny<W, STATS>(a, g, filter, L);
 		// measured on the filtered levels of R-MAT s24 (levels 2 / 6): pull_list 2.23 / 0.62 ms, 8 lanes per
 		// vertex 2.08 / 0.56 ms, 16 lanes 2.31 / 0.73 ms; the same kernel for the tiny class: no change

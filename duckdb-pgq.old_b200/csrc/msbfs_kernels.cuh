@@ -298,6 +298,23 @@ static constexpr bool kSparse = false;
 static constexpr bool kSparse = true;
 #endif
 
+// The level's frontier views.  With the device-side level loop they rotate from level to level and are read
+// from the control block.  Only `visit` (and `fcur` on filtered levels) is looked up before the gather loop;
+// `next` / `fnext` are looked up where the results are stored, AFTER the loop: keeping all four pointers live
+// across the loop cost 10 % of a batch (measured: 8.84 ms -> 7.9 ms per s24 batch, profiles/r02_ab_views.md).
+__device__ __forceinline__ const uint32_t *view_visit(const PullArgs &a) {
+	return (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
+}
+__device__ __forceinline__ const uint32_t *view_fcur(const PullArgs &a) {
+	return (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
+}
+__device__ __forceinline__ uint32_t *view_next(const PullArgs &a) {
+	return (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
+}
+__device__ __forceinline__ uint32_t *view_fnext(const PullArgs &a) {
+	return (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
+}
+
 // done bit of vertex n (plain load: other vertices' bits of the same word may be set by this launch)
 __device__ __forceinline__ bool done_test(const uint32_t *done, uint32_t n) {
 	return done && ((done[n >> 5] >> (n & 31)) & 1u);
@@ -322,10 +339,11 @@ __device__ __forceinline__ bool group_any(bool x) {
 // reductions use full-mask shuffles.
 template <int W, int GPV, bool FILTER, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
-	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
+	// unfiltered (dense) levels: every listed vertex stores its word and no done-bitmap code at all (the code shape
+	// of round 1: measured 3.11 vs 3.40 ms on the dense level of an s24 batch); filtered levels: sparse stores + done
+	constexpr bool SP = FILTER;
+	const uint32_t *const visit_p = view_visit(a);
+	const uint32_t *const fcur_p = view_fcur(a);
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
 	static_assert(GPV >= 1 && GPV <= G, "groups per vertex");
@@ -340,7 +358,7 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	const uint64_t idx = (uint64_t)wid * VPW + vslot;
 	const bool listed = idx < a.nlist;
 	const uint32_t n = listed ? a.list[idx] : 0u;
-	const bool valid = listed && !(kDone && a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
+	const bool valid = listed && !(SP && kDone && a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
 	uint32_t lo = 0, hi = 0;
 	if (valid) {
 		lo = a.ioff[n];
@@ -437,10 +455,10 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 	const unsigned rbal = __ballot_sync(FULL, writer && rest);
 	const unsigned gmask = ((1u << TPV) - 1u) << (vslot * (GPV * TPV));
 	const bool vnew = (bal & gmask) != 0;
-	if (writer && (!kSparse || vnew || a.dense)) {
+	if (writer && (!SP || !kSparse || vnew || a.dense)) {
 		// the WHOLE word is written when any slice gained bits: a reader that passed the frontier-bit test
 		// reads all of it
-		st_slice<SW>(next_p + wo, news);
+		st_slice<SW>(view_next(a) + wo, news);
 		if (slice_any<SW>(news)) {
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
@@ -449,8 +467,8 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 		}
 	}
 	const bool leader = writer && t == 0;
-	if (leader && vnew) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
-	if (kDone && leader && a.done && !(rbal & gmask)) atomicOr(&a.done[n >> 5], 1u << (n & 31));
+	if (leader && vnew) atomicOr(&view_fnext(a)[n >> 5], 1u << (n & 31));
+	if (SP && kDone && leader && a.done && !(rbal & gmask)) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (a.npeers && writer && vnew) st_peers<SW>(a, wo, news); // whole word, zero slices included
 	// no global counters here: frontier_stats_kernel derives them from fnext afterwards
 	if (STATS) {
@@ -468,10 +486,11 @@ __global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
 // vertices and 3 % of its edges, so its cost is instructions and dependent loads per VERTEX.
 template <int W, bool FILTER, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
-	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
+	// unfiltered (dense) levels: every listed vertex stores its word and no done-bitmap code at all (the code shape
+	// of round 1: measured 3.11 vs 3.40 ms on the dense level of an s24 batch); filtered levels: sparse stores + done
+	constexpr bool SP = FILTER;
+	const uint32_t *const visit_p = view_visit(a);
+	const uint32_t *const fcur_p = view_fcur(a);
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
 	constexpr uint32_t INV = 0xFFFFFFFFu, FULL = 0xffffffffu;
@@ -483,7 +502,7 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 	const uint64_t idx = (uint64_t)wid * G + g;
 	const bool inlist = idx < a.nlist;
 	const uint32_t n = inlist ? a.list[idx] : 0u;
-	const bool listed = inlist && !(kDone && a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
+	const bool listed = inlist && !(SP && kDone && a.use_done && done_test(a.done, n)); // a done vertex is skipped altogether
 	uint32_t lo = 0, hi = 0;
 	if (listed) {
 		lo = a.ioff[n];
@@ -531,8 +550,8 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 	const unsigned rbal = __ballot_sync(FULL, listed && rest);
 	const unsigned gmask = ((1u << TPV) - 1u) << (g * TPV);
 	const bool vnew = (bal & gmask) != 0;
-	if (listed && (!kSparse || vnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
-		st_slice<SW>(next_p + wo, news);
+	if (listed && (!SP || !kSparse || vnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
+		st_slice<SW>(view_next(a) + wo, news);
 		if (mine) {
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
@@ -541,10 +560,10 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 		}
 	}
 	if (listed && vnew) {
-		if (t == 0) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
+		if (t == 0) atomicOr(&view_fnext(a)[n >> 5], 1u << (n & 31));
 		if (a.npeers) st_peers<SW>(a, wo, news);
 	}
-	if (kDone && listed && t == 0 && a.done && !(rbal & gmask)) atomicOr(&a.done[n >> 5], 1u << (n & 31));
+	if (SP && kDone && listed && t == 0 && a.done && !(rbal & gmask)) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (STATS) {
 		stat_add(&a.ctrl->k_listed, (inlist && t == 0) ? 1u : 0u);
 		stat_add(&a.ctrl->k_open, (listed && t == 0) ? 1u : 0u);
@@ -561,10 +580,11 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 // deep like pull_list_kernel.  Early exit once every unseen lane of the vertex is covered.
 template <int W, bool FILTER, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
-	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
+	// unfiltered (dense) levels: every listed vertex stores its word and no done-bitmap code at all (the code shape
+	// of round 1: measured 3.11 vs 3.40 ms on the dense level of an s24 batch); filtered levels: sparse stores + done
+	constexpr bool SP = FILTER;
+	const uint32_t *const visit_p = view_visit(a);
+	const uint32_t *const fcur_p = view_fcur(a);
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G;
 	constexpr int STEPS = 32 / G;
@@ -575,7 +595,7 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 	if (wid >= a.nlist) return; // warp-uniform
 	const uint32_t lane = threadIdx.x & 31, g = lane / TPV, t = lane % TPV;
 	const uint32_t n = a.list[wid];
-	if (kDone && a.use_done && done_test(a.done, n)) { // warp-uniform: the vertex is skipped altogether
+	if (SP && kDone && a.use_done && done_test(a.done, n)) { // warp-uniform: the vertex is skipped altogether
 		if (STATS && lane == 0) atomicAdd(&a.ctrl->k_listed, 1ull);
 		return;
 	}
@@ -632,8 +652,8 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 #pragma unroll
 	for (int i = 0; i < SW; i++) rest |= (unseen.w[i] & ~news.w[i]) != 0u;
 	const bool wrest = __any_sync(FULL, rest);
-	if (g == 0 && (!kSparse || wany || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
-		st_slice<SW>(next_p + wo, news);
+	if (g == 0 && (!SP || !kSparse || wany || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
+		st_slice<SW>(view_next(a) + wo, news);
 		if (slice_any<SW>(news)) {
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
@@ -641,8 +661,8 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 		}
 	}
-	if (wany && lane == 0) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
-	if (kDone && !wrest && lane == 0 && a.done) atomicOr(&a.done[n >> 5], 1u << (n & 31));
+	if (wany && lane == 0) atomicOr(&view_fnext(a)[n >> 5], 1u << (n & 31));
+	if (SP && kDone && !wrest && lane == 0 && a.done) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (a.npeers && wany && g == 0) st_peers<SW>(a, wo, news);
 	if (STATS) {
 		if (lane == 0) {
@@ -665,10 +685,8 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 // packs 32/SEG vertices into a warp for in-degrees far below 32.  Rounds are pipelined two deep.
 template <int W, int SEG, bool STATS = false>
 __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
-	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
+	const uint32_t *const visit_p = view_visit(a);
+	const uint32_t *const fcur_p = view_fcur(a);
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
 	constexpr int VPW = 32 / SEG;  // vertices per warp
@@ -766,7 +784,7 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 	const bool vnew = ((nb >> (seg * SEG)) & SEGMASK) != 0u;
 	const bool vrest = ((rb >> (seg * SEG)) & SEGMASK) != 0u;
 	if (writer && (!kSparse || vnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
-		st_slice<SW>(next_p + wo, news);
+		st_slice<SW>(view_next(a) + wo, news);
 		if (slice_any<SW>(news)) {
 #pragma unroll
 			for (int i = 0; i < SW; i++) s.w[i] |= news.w[i];
@@ -774,7 +792,7 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 			alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 		}
 	}
-	if (writer && t == 0 && vnew) atomicOr(&fnext_p[n >> 5], 1u << (n & 31));
+	if (writer && t == 0 && vnew) atomicOr(&view_fnext(a)[n >> 5], 1u << (n & 31));
 	if (kDone && writer && t == 0 && a.done && !vrest) atomicOr(&a.done[n >> 5], 1u << (n & 31));
 	if (a.npeers && writer && vnew) st_peers<SW>(a, wo, news); // whole word, zero slices included
 	if (STATS) {
@@ -790,10 +808,8 @@ __global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
 // ---- K4 hubs: one block per chunk of a hub's in-list, partial ORs merged with atomicOr ---------
 template <int W, bool STATS = false>
 __global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
-	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
+	const uint32_t *const visit_p = view_visit(a);
+	const uint32_t *const fcur_p = view_fcur(a);
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV, G = C::G, U = 4;
 	const HubChunk hc = a.chunks[blockIdx.x];
@@ -855,10 +871,8 @@ __global__ void __launch_bounds__(256) pull_hub_kernel(PullArgs a) {
 // one TPV-thread group per hub: next = hubacc & ~seen & active; seen |= next; hubacc = 0
 template <int W>
 __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
-	const uint32_t *const visit_p = (kDyn && a.dyn) ? a.ctrl->L.cur_visit : a.visit;
-	uint32_t *const next_p = (kDyn && a.dyn) ? a.ctrl->L.cur_next : a.next;
-	const uint32_t *const fcur_p = (kDyn && a.dyn) ? a.ctrl->L.cur_fbit : a.fcur;
-	uint32_t *const fnext_p = (kDyn && a.dyn) ? a.ctrl->L.nxt_fbit : a.fnext;
+	const uint32_t *const visit_p = view_visit(a);
+	const uint32_t *const fcur_p = view_fcur(a);
 	using C = LaneCfg<W>;
 	constexpr int SW = C::SW, TPV = C::TPV, WPV = C::WPV;
 	__shared__ uint32_t salive[16];
@@ -882,7 +896,7 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 	if (h < a.nlist && (!kSparse || gnew || a.dense)) { // sparse: `next` is all-zero on entry, only words that gained bits are written (whole word)
 		const uint32_t n = a.list[h];
 		const size_t wo = (size_t)n * WPV + (size_t)t * SW;
-		st_slice<SW>(next_p + wo, news);
+		st_slice<SW>(view_next(a) + wo, news);
 		if (anyn) {
 			Slice<SW> s = ld_slice<SW>(a.seen + wo);
 #pragma unroll
@@ -892,7 +906,7 @@ __global__ void __launch_bounds__(256) hub_finalize_kernel(PullArgs a) {
 	}
 	const bool leader = gnew && t == 0 && h < a.nlist;
 	const uint32_t hn = h < a.nlist ? a.list[h] : 0u;
-	if (leader) atomicOr(&fnext_p[hn >> 5], 1u << (hn & 31));
+	if (leader) atomicOr(&view_fnext(a)[hn >> 5], 1u << (hn & 31));
 	if (anyn) alive_note<SW>(salive, a.alive_slots, t * SW, news.w);
 	if (a.npeers && gnew && h < a.nlist) st_peers<SW>(a, (size_t)hn * WPV + (size_t)t * SW, news);
 }

@@ -6,7 +6,11 @@ from bench import SEED_BASE
 scale = int(sys.argv[1]) if len(sys.argv) > 1 else 22
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 ctx = pgq_b200.Context(0)
-for kv in sys.argv[3:]:  # option=value ...
+prep = True
+for kv in sys.argv[3:]:  # option=value ... | noprep (forward build only)
+    if kv == "noprep":
+        prep = False
+        continue
     k, val = kv.split("=")
     ctx.set_option(k, int(val))
 V, E = 1 << scale, 16 << scale
@@ -15,6 +19,7 @@ ctx.gen_rmat_device(SEED_BASE + scale, scale, E, d_src, d_dst)
 for _ in range(reps):
     ctx.csr_build_device(0, V, E, d_src, d_dst)
     print("csr_build_ms", ctx.stats()["csr_build_ms"])
-    ctx.csr_prepare(0)
-    print("transpose_ms", ctx.stats()["transpose_ms"])
+    if prep:
+        ctx.csr_prepare(0)
+        print("transpose_ms", ctx.stats()["transpose_ms"])
     ctx.csr_delete(0)

@@ -1,7 +1,10 @@
 """Summarise an `ncu --csv` launch list of bench.py into profiles/: per-kernel time share and the
 DRAM bytes the MS-BFS level kernels move per 512-lane batch (bench.py's roofline.traffic).
 
-usage: python tools/ncu_traffic.py gpurun_out/launches.csv profiles/r01_traffic.json "<command that was profiled>"
+usage: python tools/ncu_traffic.py gpurun_out/launches.csv profiles/r02_traffic.json "<command that was profiled>" \
+           [scale edgefactor lanes]
+The summary records the hash of the kernel sources and the workload keys it was taken at; bench.py refuses to apply
+it to any other build or workload (roofline.traffic: null + the reason).
 """
 import collections
 import csv
@@ -9,11 +12,18 @@ import json
 import sys
 
 LEVEL = ("pull_list_kernel", "pull_seg_kernel", "pull_tiny_kernel", "pull_warp_kernel", "pull_hub_kernel", "hub_finalize_kernel", "push_kernel",
-         "clear_by_bitmap_kernel", "compact_bitmap_kernel", "frontier_stats_kernel")
+         "clear_by_bitmap_kernel", "level_clear_kernel", "scrub_kernel", "zero_next_kernel", "compact_bitmap_kernel",
+         "frontier_stats_kernel", "bfs_snapshot_items_kernel")
+CSR = ("rw_global_hist_kernel", "rw_gdig_scan_kernel", "rw_scatter_kernel", "rw_hist_kernel", "rs_hist_kernel", "rs_scatter_kernel",
+       "offsets_from_sorted_kernel", "scan_")
 
 
 def main():
     path, out, cmd = sys.argv[1], sys.argv[2], sys.argv[3]
+    keys = [int(x) for x in sys.argv[4:7]]
+    import os
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from bench import src_hash
     rows = collections.OrderedDict()
     for x in csv.DictReader(l for l in open(path) if not l.startswith("==")):
         r = rows.setdefault(int(x["ID"]), {"name": x["Kernel Name"]})
@@ -25,8 +35,11 @@ def main():
             v *= {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1.0)
         r[m] = v
     agg = collections.OrderedDict()
-    batches = 0
-    lvl_bytes = lvl_ms = tot_ms = 0.0
+    tot_ms = 0.0
+    # walk the launches in order: a batch starts at bfs_init_kernel; batches of the instrumented pass (they contain
+    # bfs_count_kernel and the STATS instantiations of the level kernels) do not count
+    batches_all = []
+    cur = None
     for r in rows.values():
         name = r["name"].replace("void ", "").replace("pgq::", "").split("(")[0]
         base = name.split("<")[0]
@@ -38,18 +51,35 @@ def main():
         a[2] += by
         tot_ms += ms
         if base == "bfs_init_kernel":
-            batches += 1
+            cur = {"bytes": 0.0, "ms": 0.0, "stats": False, "levels": 0}
+            batches_all.append(cur)
+        if cur is None:
+            continue
+        if base == "bfs_count_kernel":
+            cur["stats"] = True
+        if base == "bfs_check_kernel":
+            cur["levels"] += 1
         if base in LEVEL:
-            lvl_bytes += by
-            lvl_ms += ms
+            cur["bytes"] += by
+            cur["ms"] += ms
+    good = [b for b in batches_all if not b["stats"] and b["levels"] > 0]
+    batches = len(good)
+    lvl_bytes = sum(b["bytes"] for b in good)
+    lvl_ms = sum(b["ms"] for b in good)
     summary = {
         "command": cmd,
+        "src_hash": src_hash(),
+        "scale": keys[0] if len(keys) > 0 else None, "edgefactor": keys[1] if len(keys) > 1 else None,
+        "lanes": keys[2] if len(keys) > 2 else None,
         "note": "ncu --clock-control none launch list; per-launch times are cold-cache and serialised, "
                 "shares (not absolutes) are comparable with bench.py's CUDA-event numbers",
-        "batches_profiled": batches,
+        "batches_profiled": batches, "batches_skipped_instrumented_or_graph_launched": len(batches_all) - batches,
+        "levels_per_batch": sum(b["levels"] for b in good) / max(batches, 1),
         "level_kernel_dram_bytes_per_batch": lvl_bytes / max(batches, 1),
         "level_kernel_ms_per_batch_under_ncu": lvl_ms / max(batches, 1),
         "level_kernel_share_of_all_kernel_time": lvl_ms / tot_ms if tot_ms else None,
+        "how": "the profiled command must run with --loop 0: ncu does not see kernels launched from conditional graph "
+               "nodes (the device-side level loop); the host-driven loop launches the same kernels",
         "kernels": [{"name": k, "launches": v[0], "ms": round(v[1], 3), "share": round(v[1] / tot_ms, 4),
                      "dram_GB": round(v[2] / 1e9, 3)}
                     for k, v in sorted(agg.items(), key=lambda t: -t[1][1])],

@@ -18,6 +18,8 @@ ctx._chk(ctx.lib.pgq_csr_download(ctx._ctx, 0, v_off.ctypes.data_as(pgq_b200.I64
 src, dst = make_pairs(V, v_off, npairs, 1000)
 for k, val in opts.items():
     ctx.set_option(k, int(val))
+if os.environ.get("PGQ_TRACE_HOSTLOOP"):
+    ctx.set_option("loop", 0)
 ctx.iterativelength(0, src, dst)  # warm
 ctx.set_option("timing", 1); ctx.set_option("trace", 1)
 ctx.reset_stats()
