@@ -909,18 +909,16 @@ def part_section(a, ctx, dist, rank, world, local, V0, v_off, src0, dst0):
         out["parity_what"] = "scale %d, %d pairs, %d ranks, ncclAllGather exchange, 256 lanes" % (a.scale, k, world)
     pc.csr_delete(1)
     scale = {2: 26, 4: 27, 8: 28}.get(world, 25)
-    lanes, pairs, steps = 64, 256, 2
+    steps = 2
     V, E, build_s = part_build(pc, scale, a.edgefactor, 0)
-    rng = np.random.RandomState(1234)
-    ps = rng.randint(0, V, size=pairs).astype(np.int64)
-    pd = rng.randint(0, V, size=pairs).astype(np.int64)
-    pc.set_option("lanes", lanes)
-    res = {}
-    for mode in ("allgather", "fused"):
-        if mode == "fused":
-            pc.part_p2p_setup(dist, 0, lanes, world)
+    out.update({"workload": "BASELINE configs[4]: R-MAT scale %d ef%d (V=%d E=%d) 1-D vertex-partitioned over %d B200"
+                            % (scale, a.edgefactor, V, E, world),
+                "slice_build_s": build_s,
+                "timing": "wall clock of the collective call (host buffers in and out), max over ranks; pull_ms / "
+                          "exchange_ms = CUDA-event sums over the levels on rank 0"})
+
+    def measure(ps, pd):
         o, ov = pc.part_iterativelength(0, ps, pd)  # warm
-        res[mode] = (o, ov)
         # instrumented pass: TEPS numerator of this pair set (same definition as the single-GPU path)
         pc.set_option("stats", 1)
         pc.reset_stats()
@@ -937,17 +935,35 @@ def part_section(a, ctx, dist, rank, world, local, V0, v_off, src0, dst0):
         ms = barrier_max(dist, local, (time.perf_counter() - t0) / steps * 1e3)
         st = pc.stats()
         pc.set_option("timing", 0)
-        out[mode] = {"ms_per_step": ms, "pairs_per_s": pairs / (ms * 1e-3),
-                     "value": edges / (ms * 1e-3) / 1e9, "unit": "GTEPS", "edges_lane": edges,
-                     "levels": int(st["levels"] // steps), "pull_ms": st["level_kernel_ms"] / steps,
-                     "exchange_ms": st["coll_ms"] / steps, "coll_bytes_per_step_per_rank": int(st["coll_bytes"] // steps)}
-    same = bool(np.array_equal(res["allgather"][0], res["fused"][0]) and np.array_equal(res["allgather"][1], res["fused"][1]))
-    out.update({"workload": "BASELINE configs[4]: R-MAT scale %d ef%d (V=%d E=%d) 1-D vertex-partitioned over %d B200, "
-                            "%d pairs, %d-lane words" % (scale, a.edgefactor, V, E, world, pairs, lanes),
-                "slice_build_s": build_s, "found": int(res["fused"][1].sum()),
-                "fused_equals_allgather": "identical" if same else "MISMATCH",
-                "timing": "wall clock of the collective call (host buffers in and out), max over ranks; pull_ms / "
-                          "exchange_ms = CUDA-event sums over the levels on rank 0"})
+        n = len(ps)
+        return (o, ov), {"pairs": n, "ms_per_step": ms, "pairs_per_s": n / (ms * 1e-3),
+                         "value": edges / (ms * 1e-3) / 1e9, "unit": "GTEPS", "edges_lane": edges,
+                         "batches": int(st["batches"] // steps), "levels": int(st["levels"] // steps),
+                         "pull_ms": st["level_kernel_ms"] / steps, "exchange_ms": st["coll_ms"] / steps,
+                         "coll_bytes_per_step_per_rank": int(st["coll_bytes"] // steps)}
+
+    rng = np.random.RandomState(1234)
+    ps = rng.randint(0, V, size=2048).astype(np.int64)
+    pd = rng.randint(0, V, size=2048).astype(np.int64)
+    # round 1's configuration: 256 pairs in 64-lane words, both exchange modes
+    pc.set_option("lanes", 64)
+    r_ag, out["allgather"] = measure(ps[:256], pd[:256])
+    out["allgather"]["lanes"] = 64
+    pc.part_p2p_setup(dist, 0, 64, world)
+    r_fu, out["fused"] = measure(ps[:256], pd[:256])
+    out["fused"]["lanes"] = 64
+    same = bool(np.array_equal(r_ag[0], r_fu[0]) and np.array_equal(r_ag[1], r_fu[1]))
+    out["fused_equals_allgather"] = "identical" if same else "MISMATCH"
+    # 512-lane words (2 x 17 GB of frontier replicas per rank at scale 28): every level's sweep serves 8x the lanes
+    try:
+        pc.set_option("lanes", 512)
+        pc.part_p2p_setup(dist, 0, 512, world)
+        r_w, out["fused_512"] = measure(ps, pd)
+        out["fused_512"]["lanes"] = 512
+        same = bool(np.array_equal(r_w[0][:256], r_fu[0]) and np.array_equal(r_w[1][:256], r_fu[1]))
+        out["fused_512"]["first_256_equal_64_lane_run"] = "identical" if same else "MISMATCH"
+    except Exception as ex:
+        out["fused_512"] = {"error": str(ex)[:300]}
     pc.close()
     return out
 

@@ -339,6 +339,8 @@ class Context:
     def part_p2p_setup(self, dist, csr_id, lanes, world):
         """Enable the fused exchange: export this rank's replica handles, all-gather them with the
         host plumbing (torch.distributed), map every peer's replicas (CUDA IPC over NVLink)."""
+        self._chk(self.lib.pgq_part_p2p_close(self._ctx))  # mappings of an earlier setup go first, on every rank
+        dist.barrier()
         mine = C.create_string_buffer(128)
         self._chk(self.lib.pgq_part_p2p_export(self._ctx, C.c_int32(csr_id), C.c_int(lanes), mine))
         box = [None] * world

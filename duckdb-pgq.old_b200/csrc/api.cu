@@ -1193,6 +1193,15 @@ int pgq_part_csr_finalize(pgq_ctx_t *ctx, int32_t id) {
 	return part_finalize(c, g);
 }
 
+int pgq_part_p2p_close(pgq_ctx_t *ctx) {
+	LOCK(ctx);
+	PGQ_CUDA(cudaStreamSynchronize(c->stream));
+	for (void *m : c->part_peer_open) cudaIpcCloseMemHandle(m);
+	c->part_peer_open.clear();
+	c->part_p2p = false;
+	return PGQ_OK;
+}
+
 int pgq_part_p2p_export(pgq_ctx_t *ctx, int32_t id, int lanes, void *out_handles128) {
 	LOCK(ctx);
 	Csr *g = find_csr(c, id);

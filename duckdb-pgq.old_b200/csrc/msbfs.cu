@@ -1256,7 +1256,12 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 	if (!want_paths) {
 		int32_t *stage = nullptr;
 		PGQ_TRY(pinned_found(c, (size_t)nslots * 4, &stage));
-		PGQ_TRY(run_batches(c, ws, lt.nbatch, host_loop && ws.size() > 1, [&](Worker &wk, int64_t bi) {
+		// one host thread deals all batches when they stay on one device; with several devices a thread per worker:
+		// a graph launch blocks while its stream's queue is full, and a single dealer stuck on one device's stream
+		// starved the other devices (measured: 0.90x on 2 GPUs with one dealer)
+		bool multi_dev = false;
+		for (const Worker &wk : ws) multi_dev |= wk.w->device != c->device;
+		PGQ_TRY(run_batches(c, ws, lt.nbatch, (host_loop || multi_dev) && ws.size() > 1, [&](Worker &wk, int64_t bi) {
 			PGQ_TRY(run_batch(wk.w, wk.g, wk.b, W, false, wk.d_src + bi * W, wk.d_dst + bi * W, wk.d_found + bi * W));
 			PGQ_CUDA(cudaMemcpyAsync(stage + bi * W, wk.d_found + bi * W, (size_t)W * 4, cudaMemcpyDeviceToHost,
 			                         wk.w->stream));
@@ -1574,7 +1579,7 @@ int msbfs_run_device(Ctx *c, Csr *g, int64_t n, const int64_t *d_srcs, const int
 	for (const Worker &wk : ws) multi_dev |= wk.w->device != c->device;
 	int32_t *stage = nullptr;
 	if (multi_dev) PGQ_TRY(pinned_found(c, (size_t)nslots * 4, &stage));
-	PGQ_TRY(run_batches(c, ws, nbatch, host_loop && ws.size() > 1, [&](Worker &wk, int64_t bi) {
+	PGQ_TRY(run_batches(c, ws, nbatch, (host_loop || multi_dev) && ws.size() > 1, [&](Worker &wk, int64_t bi) {
 		PGQ_TRY(run_batch(wk.w, wk.g, wk.b, W, false, wk.d_src + bi * W, wk.d_dst + bi * W, wk.d_found + bi * W));
 		if (multi_dev) // results of every device meet in pinned host memory, then return to the primary
 			PGQ_CUDA(cudaMemcpyAsync(stage + bi * W, wk.d_found + bi * W, (size_t)W * 4, cudaMemcpyDeviceToHost,

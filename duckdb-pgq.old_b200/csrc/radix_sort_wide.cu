@@ -20,8 +20,14 @@
 
 namespace pgq {
 
-static constexpr int RW_MAXBITS = 11;
+static constexpr int RW_MAXBITS = 11;          // keys of at most 22 bits: two passes of <= 11-bit digits
 static constexpr int RW_NB = 1 << RW_MAXBITS; // 2048 buckets
+// keys of 23 / 24 bits (R-MAT s24: C3's own graph) CAN take two passes of 12-bit digits: 4096 buckets, 512-thread
+// blocks (16 warps x 4096 x 2 B of counters = 128 KB + 64 KB staging + 16 KB bases = 208 KB, one block per SM, the
+// same 16 warps per SM as two 256-thread blocks of the 11-bit shape) instead of three 8-bit passes.  Measured slower
+// (10.4 vs 9.1 ms at s24), so it is opt-in (option sort_wide=3); the tests run it for bit-identity.
+static constexpr int RW_MAXBITS_BIG = 12;
+static constexpr int RW_NB_BIG = 1 << RW_MAXBITS_BIG;
 static constexpr int RW_THREADS = 256;
 static constexpr int RW_WARPS = RW_THREADS / 32;
 static constexpr int RW_ITEMS = 32;
@@ -45,6 +51,7 @@ struct RwArgs {
 	const uint32_t *gdig;  // [RW_NB] global start of every bucket of this pass
 	uint32_t n;
 	uint32_t ntiles;
+	uint32_t nb;           // bucket stride of status / gdig: RW_NB or RW_NB_BIG
 	int shift;
 	int nbits;
 	uint64_t vmax;
@@ -76,8 +83,8 @@ __device__ __forceinline__ uint2 rw_load_item(const RwArgs &a, uint32_t i, bool 
 // Tile digit counts (order-free: shared-memory atomics).
 template <int IN>
 __global__ void __launch_bounds__(RW_THREADS) rw_hist_kernel(RwArgs a) {
-	__shared__ uint32_t h[RW_NB];
-	for (int i = threadIdx.x; i < RW_NB; i += RW_THREADS) h[i] = 0;
+	__shared__ uint32_t h[RW_NB_BIG];
+	for (int i = threadIdx.x; i < RW_NB_BIG; i += RW_THREADS) h[i] = 0;
 	__syncthreads();
 	const uint32_t tbase = blockIdx.x * (uint32_t)RW_TILE;
 	const uint32_t mask = (1u << a.nbits) - 1u;
@@ -101,8 +108,9 @@ __global__ void __launch_bounds__(RW_THREADS) rw_hist_kernel(RwArgs a) {
 // ---- look-back variant: one read of the first-pass keys gives the GLOBAL bucket sizes of both passes ----
 template <int IN>
 __global__ void __launch_bounds__(RW_THREADS) rw_global_hist_kernel(RwArgs a, int bits0, int bits1, uint32_t *gh) {
-	__shared__ uint32_t h[2 * RW_NB];
-	for (int i = threadIdx.x; i < 2 * RW_NB; i += RW_THREADS) h[i] = 0;
+	__shared__ uint32_t h[2 * RW_NB_BIG];
+	for (int i = threadIdx.x; i < 2 * RW_NB_BIG; i += RW_THREADS) h[i] = 0;
+	const uint32_t NBS = a.nb;
 	__syncthreads();
 	const uint32_t m0 = (1u << bits0) - 1u, m1 = (1u << bits1) - 1u; // bits1 == 0: m1 = 0, everything in bucket 0
 	for (uint32_t tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
@@ -114,28 +122,36 @@ __global__ void __launch_bounds__(RW_THREADS) rw_global_hist_kernel(RwArgs a, in
 #pragma unroll
 			for (int r = 0; r < RW_ITEMS; r++) {
 				atomicAdd(&h[keys[r] & m0], 1u);
-				atomicAdd(&h[RW_NB + ((keys[r] >> bits0) & m1)], 1u);
+				atomicAdd(&h[NBS + ((keys[r] >> bits0) & m1)], 1u);
 			}
 		} else {
 			for (uint32_t idx = tbase + threadIdx.x; idx < a.n; idx += RW_THREADS) {
 				const uint32_t k = rw_load_key<IN>(a, idx);
 				atomicAdd(&h[k & m0], 1u);
-				atomicAdd(&h[RW_NB + ((k >> bits0) & m1)], 1u);
+				atomicAdd(&h[NBS + ((k >> bits0) & m1)], 1u);
 			}
 		}
 	}
 	__syncthreads();
-	for (int i = threadIdx.x; i < 2 * RW_NB; i += RW_THREADS)
+	for (uint32_t i = threadIdx.x; i < 2 * NBS; i += RW_THREADS)
 		if (h[i]) atomicAdd(&gh[i], h[i]);
 }
 
-// exclusive scan of each pass's RW_NB bucket sizes, in place (one 1024-thread block per pass)
+// exclusive scan of each pass's NB bucket sizes, in place (one 1024-thread block per pass)
+template <int NB>
 __global__ void __launch_bounds__(1024) rw_gdig_scan_kernel(uint32_t *gh) {
+	constexpr int PT = NB / 1024; // 2 or 4 consecutive buckets per thread
 	__shared__ uint32_t wsum[32];
-	uint32_t *g = gh + blockIdx.x * RW_NB;
+	uint32_t *g = gh + blockIdx.x * NB;
 	const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	const uint32_t x0 = g[2 * threadIdx.x], x1 = g[2 * threadIdx.x + 1];
-	uint32_t inc = x0 + x1;
+	uint32_t x[PT];
+	uint32_t inc = 0;
+#pragma unroll
+	for (int k = 0; k < PT; k++) {
+		x[k] = g[PT * threadIdx.x + k];
+		inc += x[k];
+	}
+	const uint32_t mine = inc;
 #pragma unroll
 	for (int o = 1; o < 32; o <<= 1) {
 		const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
@@ -143,10 +159,13 @@ __global__ void __launch_bounds__(1024) rw_gdig_scan_kernel(uint32_t *gh) {
 	}
 	if (lane == 31) wsum[warp] = inc;
 	__syncthreads();
-	uint32_t ex = inc - x0 - x1;
+	uint32_t ex = inc - mine;
 	for (int w = 0; w < (int)warp; w++) ex += wsum[w];
-	g[2 * threadIdx.x] = ex;
-	g[2 * threadIdx.x + 1] = ex + x0;
+#pragma unroll
+	for (int k = 0; k < PT; k++) {
+		g[PT * threadIdx.x + k] = ex;
+		ex += x[k];
+	}
 }
 
 static constexpr uint32_t RW_FLAG_A = 1u << 30, RW_FLAG_P = 2u << 30, RW_VMASK = (1u << 30) - 1u;
@@ -178,25 +197,27 @@ __device__ __forceinline__ void rw_status_store(uint32_t *p, const uint32_t (&w)
 // Scatter kernel configuration: THREADS x ITEMS = RW_TILE keys per block.
 //   <256, 32>: two blocks per SM (16 warps), long per-warp rank chains (default: 2.11 ms at R-MAT s22);
 //   <1024, 8>: one block per SM (32 warps), per-warp counters take 128 KB of shared memory (2.74 ms; option sort_wide=2).
-template <int THREADS>
+template <int THREADS, int NBITS>
 struct RwCfg {
+	static constexpr int NB = 1 << NBITS;
 	static constexpr int WARPS = THREADS / 32;
 	static constexpr int ITEMS = RW_TILE / THREADS;
-	static constexpr int DPT = RW_NB / THREADS; // digits per thread in the block scans (8 or 2)
+	static constexpr int DPT = NB / THREADS; // digits per thread in the block scans (8 or 2)
 	static constexpr size_t OFF_STAGE = 0;                                     // uint2[RW_TILE]
-	static constexpr size_t OFF_GBASE = OFF_STAGE + (size_t)RW_TILE * 8;       // uint32[RW_NB]
-	static constexpr size_t OFF_CNT = OFF_GBASE + (size_t)RW_NB * 4;           // uint16[WARPS][RW_NB]
-	static constexpr size_t OFF_WSUM = OFF_CNT + (size_t)WARPS * RW_NB * 2;    // uint32[WARPS]
+	static constexpr size_t OFF_GBASE = OFF_STAGE + (size_t)RW_TILE * 8;       // uint32[NB]
+	static constexpr size_t OFF_CNT = OFF_GBASE + (size_t)NB * 4;              // uint16[WARPS][NB]
+	static constexpr size_t OFF_WSUM = OFF_CNT + (size_t)WARPS * NB * 2;       // uint32[WARPS]
 	static constexpr size_t SMEM = OFF_WSUM + (size_t)WARPS * 4 + 32;
-	static_assert((size_t)WARPS * RW_NB * 2 >= (size_t)RW_TILE * 4, "payload1 staging reuses the counter area");
+	static_assert((size_t)WARPS * NB * 2 >= (size_t)RW_TILE * 4, "payload1 staging reuses the counter area");
 	static_assert(DPT == 8 || DPT == 2, "one 16-byte or one 4-byte row of 16-bit counters per thread");
 	static_assert(ITEMS % 4 == 0, "ballots are batched four rounds at a time");
+	static_assert(SMEM <= 227 * 1024, "shared memory per block");
 };
 
-template <int IN, int THREADS>
+template <int IN, int THREADS, int NBITS>
 __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_kernel(RwArgs a) {
-	using C = RwCfg<THREADS>;
-	constexpr int WARPS = C::WARPS, ITEMS = C::ITEMS, DPT = C::DPT;
+	using C = RwCfg<THREADS, NBITS>;
+	constexpr int WARPS = C::WARPS, ITEMS = C::ITEMS, DPT = C::DPT, NB = C::NB;
 	extern __shared__ __align__(16) unsigned char rw_smem[];
 	uint2 *stage = reinterpret_cast<uint2 *>(rw_smem + C::OFF_STAGE);
 	uint32_t *gbase = reinterpret_cast<uint32_t *>(rw_smem + C::OFF_GBASE); // global bucket base - local start
@@ -208,7 +229,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 	{
 		uint4 *z = reinterpret_cast<uint4 *>(cnt);
 #pragma unroll
-		for (int i = 0; i < WARPS * RW_NB * 2 / 16 / THREADS; i++) z[i * THREADS + threadIdx.x] = make_uint4(0u, 0u, 0u, 0u);
+		for (int i = 0; i < WARPS * NB * 2 / 16 / THREADS; i++) z[i * THREADS + threadIdx.x] = make_uint4(0u, 0u, 0u, 0u);
 	}
 	// Look-back variant: tiles are numbered in the order their blocks START, so every predecessor a tile
 	// waits for is already running (forward progress whatever order the hardware schedules blocks in).
@@ -241,7 +262,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 	// the reference would write out of bounds for such ids; the digits are masked, so nothing does here
 	if (IN == RW_IN_64 && a.err && bad) atomicOr(a.err, 1u);
 	__syncthreads();
-	uint16_t *mycnt = cnt + warp * RW_NB;
+	uint16_t *mycnt = cnt + warp * NB;
 	uint32_t lp[ITEMS / 2]; // two 16-bit values per register: rank inside (warp, digit), later the tile position
 #pragma unroll
 	for (int r0 = 0; r0 < ITEMS; r0 += 4) {
@@ -254,7 +275,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 			const uint32_t d = (keys[r0 + q] >> a.shift) & mask;
 			unsigned pm = __ballot_sync(0xffffffffu, wbase + (r0 + q) * 32 < a.n);
 #pragma unroll
-			for (int b = 0; b < RW_MAXBITS; b++) {
+			for (int b = 0; b < NBITS; b++) {
 				const bool bit = (d >> b) & 1u;
 				const unsigned m = __ballot_sync(0xffffffffu, bit);
 				pm &= bit ? m : ~m;
@@ -286,7 +307,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 #pragma unroll 8
 	for (int w = 0; w < WARPS; w++) {
 		if (DPT == 8) {
-			uint4 *row = reinterpret_cast<uint4 *>(cnt + w * RW_NB) + threadIdx.x;
+			uint4 *row = reinterpret_cast<uint4 *>(cnt + w * NB) + threadIdx.x;
 			const uint4 q = *row;
 			const uint32_t x[4] = {q.x, q.y, q.z, q.w};
 			uint32_t o[4];
@@ -298,7 +319,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 			}
 			*row = make_uint4(o[0], o[1], o[2], o[3]);
 		} else {
-			uint32_t *row = reinterpret_cast<uint32_t *>(cnt + w * RW_NB) + threadIdx.x;
+			uint32_t *row = reinterpret_cast<uint32_t *>(cnt + w * NB) + threadIdx.x;
 			const uint32_t x = *row;
 			*row = tot[0] | (tot[1 % DPT] << 16);
 			tot[0] += x & 0xFFFFu;
@@ -311,7 +332,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 #pragma unroll
 	for (int k = 0; k < DPT; k++) pre[k] = 0;
 	if (a.status) {
-		uint32_t *mine = a.status + (size_t)tile * RW_NB + threadIdx.x * DPT;
+		uint32_t *mine = a.status + (size_t)tile * NB + threadIdx.x * DPT;
 		uint32_t w[DPT];
 		if (tile != 0) {
 #pragma unroll
@@ -320,7 +341,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 			uint32_t open = (1u << DPT) - 1u; // buckets still looking back
 			uint32_t spins = 0;
 			for (uint32_t t = tile - 1; open;) {
-				rw_status_load<DPT>(a.status + (size_t)t * RW_NB + threadIdx.x * DPT, w);
+				rw_status_load<DPT>(a.status + (size_t)t * NB + threadIdx.x * DPT, w);
 				bool ready = true;
 #pragma unroll
 				for (int k = 0; k < DPT; k++) ready &= (w[k] >> 30) != 0u;
@@ -377,7 +398,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 #pragma unroll 8
 		for (int w = 0; w < WARPS; w++) {
 			if (DPT == 8) {
-				uint4 *row = reinterpret_cast<uint4 *>(cnt + w * RW_NB) + threadIdx.x;
+				uint4 *row = reinterpret_cast<uint4 *>(cnt + w * NB) + threadIdx.x;
 				uint4 q = *row;
 				q.x += ls[0] | (ls[1 % DPT] << 16);
 				q.y += ls[2 % DPT] | (ls[3 % DPT] << 16);
@@ -385,7 +406,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 				q.w += ls[6 % DPT] | (ls[7 % DPT] << 16);
 				*row = q;
 			} else {
-				uint32_t *row = reinterpret_cast<uint32_t *>(cnt + w * RW_NB) + threadIdx.x;
+				uint32_t *row = reinterpret_cast<uint32_t *>(cnt + w * NB) + threadIdx.x;
 				*row += ls[0] | (ls[1 % DPT] << 16);
 			}
 		}
@@ -447,15 +468,15 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 	}
 }
 
-template <int THREADS>
+template <int THREADS, int NBITS>
 static int rw_launch_scatter(Ctx *c, int form, const RwArgs &a) {
-	using C = RwCfg<THREADS>;
+	using C = RwCfg<THREADS, NBITS>;
 	// per device and cheap: set on every call rather than cached per process
 #define RW_LAUNCH(IN)                                                                                                  \
 	do {                                                                                                               \
-		PGQ_CUDA(cudaFuncSetAttribute(rw_scatter_kernel<IN, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
-		                              (int)C::SMEM));                                                                  \
-		rw_scatter_kernel<IN, THREADS><<<a.ntiles, THREADS, C::SMEM, c->stream>>>(a);                                  \
+		PGQ_CUDA(cudaFuncSetAttribute(rw_scatter_kernel<IN, THREADS, NBITS>,                                           \
+		                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));                     \
+		rw_scatter_kernel<IN, THREADS, NBITS><<<a.ntiles, THREADS, C::SMEM, c->stream>>>(a);                           \
 	} while (0)
 	if (form == RW_IN_64) RW_LAUNCH(RW_IN_64);
 	else if (form == RW_IN_32) RW_LAUNCH(RW_IN_32);
@@ -466,12 +487,17 @@ static int rw_launch_scatter(Ctx *c, int form, const RwArgs &a) {
 }
 
 bool radix_sort_wide_eligible(const Ctx *c, const SortIO &io) {
-	return c->opt.sort_wide != 0 && io.key_bits >= 1 && io.key_bits <= 2 * RW_MAXBITS &&
+	// 23 / 24-bit keys: the 12-bit shape only on request (sort_wide=3): measured 10.4 ms against 9.1 ms for the three
+	// 8-bit passes at R-MAT s24 (268 M keys) -- 16 warps of one 208 KB block rank slower than two 110 KB blocks
+	const int maxbits = c->opt.sort_wide == 3 ? 2 * RW_MAXBITS_BIG : 2 * RW_MAXBITS;
+	return c->opt.sort_wide != 0 && io.key_bits >= 1 && io.key_bits <= maxbits &&
 	       (int64_t)io.n >= c->opt.sort_wide_min && io.n < 0xFFFFFFFFu - 2u * (uint32_t)RW_TILE;
 }
 
 int radix_sort_wide(Ctx *c, const SortIO &io) {
 	if (io.n == 0) return PGQ_OK;
+	const bool big = io.key_bits > 2 * RW_MAXBITS; // 23 / 24-bit keys: 12-bit digits, 4096 buckets, 512-thread blocks
+	const uint32_t NBS = big ? RW_NB_BIG : RW_NB;
 	const int passes = io.key_bits <= RW_MAXBITS ? 1 : 2;
 	const int bits0 = passes == 1 ? io.key_bits : (io.key_bits + 1) / 2;
 	const int bits1 = io.key_bits - bits0;
@@ -491,22 +517,24 @@ int radix_sort_wide(Ctx *c, const SortIO &io) {
 	// look-back variant (option sort_lookback, counts must fit 30 bits): no per-tile histogram pre-pass and no
 	// device-wide scan; one extra read of the first-pass keys gives the global bucket sizes of both passes
 	const bool lookback = c->opt.sort_lookback != 0 && io.n < (1u << 30);
-	const size_t status_bytes = (size_t)ntiles * RW_NB * sizeof(uint32_t);
+	const size_t status_bytes = (size_t)ntiles * NBS * sizeof(uint32_t);
 	uint32_t *d_gdig = nullptr, *d_ticket = nullptr;
 	if (lookback) {
-		PGQ_TRY(c->sort_hist.reserve(status_bytes + 2 * RW_NB * sizeof(uint32_t) + 256));
+		PGQ_TRY(c->sort_hist.reserve(status_bytes + 2 * NBS * sizeof(uint32_t) + 256));
 		d_gdig = reinterpret_cast<uint32_t *>(static_cast<char *>(c->sort_hist.p) + status_bytes);
-		d_ticket = d_gdig + 2 * RW_NB;
-		PGQ_CUDA(cudaMemsetAsync(d_gdig, 0, 2 * RW_NB * sizeof(uint32_t) + 256, c->stream));
+		d_ticket = d_gdig + 2 * NBS;
+		PGQ_CUDA(cudaMemsetAsync(d_gdig, 0, 2 * NBS * sizeof(uint32_t) + 256, c->stream));
 		RwArgs a{};
 		a.k64 = io.k64;
 		a.k32 = io.k32;
 		a.n = io.n;
 		a.ntiles = ntiles;
+		a.nb = NBS;
 		const unsigned grid = ntiles < (unsigned)c->sm_count * 8u ? ntiles : (unsigned)c->sm_count * 8u;
 		if (io.k64) rw_global_hist_kernel<RW_IN_64><<<grid, RW_THREADS, 0, c->stream>>>(a, bits0, bits1, d_gdig);
 		else rw_global_hist_kernel<RW_IN_32><<<grid, RW_THREADS, 0, c->stream>>>(a, bits0, bits1, d_gdig);
-		rw_gdig_scan_kernel<<<2, 1024, 0, c->stream>>>(d_gdig);
+		if (big) rw_gdig_scan_kernel<RW_NB_BIG><<<2, 1024, 0, c->stream>>>(d_gdig);
+		else rw_gdig_scan_kernel<RW_NB><<<2, 1024, 0, c->stream>>>(d_gdig);
 		count_launch(c, 2);
 	} else {
 		PGQ_TRY(c->sort_hist.reserve(((size_t)ntiles << bits0) * sizeof(uint32_t)));
@@ -538,13 +566,14 @@ int radix_sort_wide(Ctx *c, const SortIO &io) {
 		a.hist = c->sort_hist.as<uint32_t>();
 		a.n = io.n;
 		a.ntiles = ntiles;
+		a.nb = NBS;
 		a.shift = first ? 0 : bits0;
 		a.nbits = first ? bits0 : bits1;
 		const int form = !first ? RW_IN_PACKED : io.k64 ? RW_IN_64 : RW_IN_32;
 		if (lookback) {
 			a.status = c->sort_hist.as<uint32_t>();
 			a.ticket = d_ticket + p;
-			a.gdig = d_gdig + p * RW_NB;
+			a.gdig = d_gdig + p * NBS;
 			PGQ_CUDA(cudaMemsetAsync(a.status, 0, status_bytes, c->stream));
 		} else {
 			if (form == RW_IN_64) rw_hist_kernel<RW_IN_64><<<ntiles, RW_THREADS, 0, c->stream>>>(a);
@@ -553,8 +582,9 @@ int radix_sort_wide(Ctx *c, const SortIO &io) {
 			count_launch(c);
 			PGQ_TRY(exclusive_scan_u32(c, a.hist, a.hist, (uint64_t)ntiles << a.nbits, nullptr));
 		}
-		if (c->opt.sort_wide == 2) PGQ_TRY(rw_launch_scatter<1024>(c, form, a));
-		else PGQ_TRY(rw_launch_scatter<256>(c, form, a));
+		if (big) PGQ_TRY((rw_launch_scatter<512, RW_MAXBITS_BIG>(c, form, a)));
+		else if (c->opt.sort_wide == 2) PGQ_TRY((rw_launch_scatter<1024, RW_MAXBITS>(c, form, a)));
+		else PGQ_TRY((rw_launch_scatter<256, RW_MAXBITS>(c, form, a)));
 		PGQ_CUDA(cudaGetLastError());
 	}
 	if (lookback && !io.err) {

@@ -217,6 +217,9 @@ int pgq_part_csr_finalize(pgq_ctx_t *ctx, int32_t id);
  * calls import with the world x 2 x 64 bytes. */
 #define PGQ_P2P_HANDLE_BYTES 128
 int pgq_part_p2p_export(pgq_ctx_t *ctx, int32_t id, int lanes, void *out_handles128);
+/* Before a SECOND export (another lane width / csr): every rank closes its mappings of the peers' old replicas, then
+ * the caller barriers, then everybody exports again (an exporter must not free memory a peer still maps). */
+int pgq_part_p2p_close(pgq_ctx_t *ctx);
 int pgq_part_p2p_import(pgq_ctx_t *ctx, const void *all_handles);
 int pgq_part_iterativelength(pgq_ctx_t *ctx, int32_t id, int64_t n, const int64_t *src, const int64_t *dst,
                              const uint8_t *src_valid, const uint8_t *dst_valid, int64_t *out,

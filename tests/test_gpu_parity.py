@@ -86,13 +86,15 @@ def test_csr_bit_identical_rmat(ctx, scale, ef):
     ctx.csr_delete(1)
 
 
-@pytest.mark.parametrize("wide,lookback", [(1, 1), (1, 0), (2, 1), (0, 0)])
+@pytest.mark.parametrize("wide,lookback", [(1, 1), (1, 0), (2, 1), (0, 0), (3, 1), (3, 0)])
 @pytest.mark.parametrize("V,E", [(2000, 40000), ((1 << 11) + 1, 50000), ((1 << 17) - 5, 300000),
-                                 ((1 << 22) - 3, 250000), ((1 << 22) + 9, 100000), (3, 70000)])
+                                 ((1 << 22) - 3, 250000), ((1 << 22) + 9, 100000), (3, 70000),
+                                 ((1 << 23) + 1, 150000), ((1 << 24) - 7, 200000), ((1 << 24) + 5, 120000)])
 def test_csr_both_sort_cores(ctx, V, E, wide, lookback):
     """The two-pass 11-bit sort (keys <= 22 bits; both block shapes; tile bases by decoupled look-back or by
     histogram pre-pass + scan) and the 8-bit sort give the same, oracle-identical CSR:
-    digit splits 6+5 / 6+6 / 9+8 / 11+11, one pass (<= 11 bits), > 22 bits (always the 8-bit core), ragged
+    digit splits 6+5 / 6+6 / 9+8 / 11+11, one pass (<= 11 bits), 23 / 24 bits (sort_wide=3: two 12-bit passes, 4096
+    buckets, 512-thread blocks; otherwise the 8-bit core), > 24 bits (always the 8-bit core), ragged
     last tiles, heavy duplicates (V = 3), forward arrays + edge ids and the reverse CSR (checked through
     a query)."""
     rng = np.random.default_rng(V + E)
