@@ -498,6 +498,8 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "sort_wide_min")) c->opt.sort_wide_min = value < 0 ? 0 : value;
 	else if (!strcmp(key, "streams")) c->opt.streams = value < 1 ? 1 : value > 16 ? 16 : value;
 	else if (!strcmp(key, "loop")) c->opt.loop = value;
+	else if (!strcmp(key, "loop_min_batches")) c->opt.loop_min_batches = value < 0 ? 0 : value;
+	else if (!strcmp(key, "loop_min_calls")) c->opt.loop_min_calls = value < 0 ? 0 : value;
 	else if (!strcmp(key, "done_bitmap")) c->opt.done_bitmap = value ? 1 : 0;
 	else if (!strcmp(key, "dense_store")) c->opt.dense_store = value ? 1 : 0;
 	else if (!strcmp(key, "dyn")) c->opt.dyn = value ? 1 : 0;

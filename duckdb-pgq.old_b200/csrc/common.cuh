@@ -131,6 +131,7 @@ struct Csr {
 	// identity of the device arrays: bumped whenever they are (re)built, so cached level-loop graphs
 	// (msbfs.cu) notice a CSR that was rebuilt under the same id / address
 	uint64_t gen = 0;
+	uint32_t query_calls = 0; // query calls served so far (device-loop heuristic)
 	int device = 0; // the GPU the arrays live on
 	// multi-GPU contexts (pgq_init_devices): read-only copies of the query-side arrays on the other
 	// devices, made on first use by a multi-device query (msbfs.cu csr_replica)
@@ -166,6 +167,9 @@ struct Options {
 	int64_t sort_wide_min = 32768; // ... from this many keys on
 	int64_t level_cap = 0x7fffffff; // per call, not user-settable: iterativelength's upper bound (R11)
 	int64_t loop = 1;          // 1: device-side level loop (CUDA graph WHILE/SWITCH nodes), 0: host loop, one sync per level
+	int64_t loop_now = 1;      // per call, not user-settable: this call uses the device loop (msbfs.cu use_device_loop)
+	int64_t loop_min_batches = 8; // calls with fewer batches on a CSR that has served < loop_min_calls calls take the host loop
+	int64_t loop_min_calls = 4;
 	int64_t done_bitmap = 0;   // with dense_store=0: tail levels skip vertices whose `seen` already holds every active lane
 	int64_t dyn = 1;           // host-driven loop only: 0 = frontier views as kernel arguments instead of from the control block
 	int64_t dense_store = 1;   // filtered bottom-up levels write every listed vertex's `next` word too (0: sparse stores after a scrub)

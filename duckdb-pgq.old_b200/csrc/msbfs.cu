@@ -653,7 +653,7 @@ int run_batch(Ctx *c, Csr *g, const BatchBufs &b_in, int W, bool keep_hist, cons
 		const int rc = run_batch_small(c, g, b, W, keep_hist, d_lane_src, d_lane_dst, d_found, out_levels);
 		if (rc != PGQ_SMALL_OVERFLOW) return rc;
 	}
-	const bool host_loop = !c->opt.loop || c->opt.stats || c->opt.timing || c->opt.trace || c->loop_unsupported;
+	const bool host_loop = !c->opt.loop_now || c->opt.stats || c->opt.timing || c->opt.trace || c->loop_unsupported;
 	apply_l2_window(c, b, bm);
 	size_t hist_cap = 0;
 	if (keep_hist) {
@@ -1115,6 +1115,18 @@ int run_batches(Ctx *c, std::vector<Worker> &ws, int64_t nbatch, bool threaded, 
 	return PGQ_OK;
 }
 
+// Device-side level loop for this call?  Building a worker's loop graph costs ~0.8 ms and pays back ~0.05 ms per
+// batch (gpurun check 14, tools/graph_build_cost.py: a fresh CSR's first 1024-row call 3.2 ms with the graph against
+// 1.65 ms with the host loop, later calls 1.50 against 1.59 ms).  DuckPGQ builds a CSR per query, so a small call on a
+// fresh CSR takes the host-driven loop; calls with many batches, and CSRs that keep being queried, take the graph.
+bool use_device_loop(Ctx *c, Csr *g, int64_t nbatch) {
+	const bool yes = c->opt.loop && !c->loop_unsupported &&
+	                 (nbatch >= c->opt.loop_min_batches || (int64_t)g->query_calls >= c->opt.loop_min_calls);
+	g->query_calls++;
+	c->opt.loop_now = yes ? 1 : 0; // the helper contexts copy the options per call (make_workers)
+	return yes;
+}
+
 int pinned_found(Ctx *c, size_t bytes, int32_t **out) {
 	if (bytes > c->h_found_cap) {
 		if (c->h_found) cudaFreeHost(c->h_found);
@@ -1250,9 +1262,10 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 	PGQ_CUDA(cudaMemcpyAsync(d_src, lt.src.data(), (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
 	PGQ_CUDA(cudaMemcpyAsync(d_dst, lt.dst.data(), (size_t)nslots * 4, cudaMemcpyHostToDevice, st));
 	c->stats.h2d_bytes += (uint64_t)nslots * 8;
+	const bool dev_loop = use_device_loop(c, g, lt.nbatch);
 	std::vector<Worker> ws;
 	PGQ_TRY(make_workers(c, g, b, W, lt.nbatch, want_paths, d_src, d_dst, d_found, nslots, &ws));
-	const bool host_loop = !c->opt.loop || c->opt.stats || c->opt.timing || c->opt.trace || c->loop_unsupported;
+	const bool host_loop = !dev_loop || c->opt.stats || c->opt.timing || c->opt.trace || c->loop_unsupported;
 	if (!want_paths) {
 		int32_t *stage = nullptr;
 		PGQ_TRY(pinned_found(c, (size_t)nslots * 4, &stage));
@@ -1265,6 +1278,9 @@ int msbfs_run(Ctx *c, Csr *g, const LaneTable &lt, int32_t *h_found, PathOut *pa
 			PGQ_TRY(run_batch(wk.w, wk.g, wk.b, W, false, wk.d_src + bi * W, wk.d_dst + bi * W, wk.d_found + bi * W));
 			PGQ_CUDA(cudaMemcpyAsync(stage + bi * W, wk.d_found + bi * W, (size_t)W * 4, cudaMemcpyDeviceToHost,
 			                         wk.w->stream));
+			// worker threads take batches dynamically; a batch is only ENQUEUED here, so without this wait the first
+			// thread to start would queue nearly every batch on its own stream (measured: 0.87x on 2 GPUs)
+			if (multi_dev && !host_loop) PGQ_CUDA(cudaStreamSynchronize(wk.w->stream));
 			return (int)PGQ_OK;
 		}));
 		PGQ_CUDA(cudaStreamSynchronize(st));
@@ -1572,18 +1588,21 @@ int msbfs_run_device(Ctx *c, Csr *g, int64_t n, const int64_t *d_srcs, const int
 	lanes_from_rows_kernel<<<div_up(nslots, 256), 256, 0, st>>>(d_srcs, d_dsts, n, nslots, (uint64_t)g->V, d_src,
 	                                                            d_dst, d_err);
 	count_launch(c);
+	const bool dev_loop = use_device_loop(c, g, nbatch);
 	std::vector<Worker> ws;
 	PGQ_TRY(make_workers(c, g, b, W, nbatch, false, d_src, d_dst, d_found, nslots, &ws));
-	const bool host_loop = !c->opt.loop || c->opt.stats || c->opt.timing || c->opt.trace || c->loop_unsupported;
+	const bool host_loop = !dev_loop || c->opt.stats || c->opt.timing || c->opt.trace || c->loop_unsupported;
 	bool multi_dev = false;
 	for (const Worker &wk : ws) multi_dev |= wk.w->device != c->device;
 	int32_t *stage = nullptr;
 	if (multi_dev) PGQ_TRY(pinned_found(c, (size_t)nslots * 4, &stage));
 	PGQ_TRY(run_batches(c, ws, nbatch, (host_loop || multi_dev) && ws.size() > 1, [&](Worker &wk, int64_t bi) {
 		PGQ_TRY(run_batch(wk.w, wk.g, wk.b, W, false, wk.d_src + bi * W, wk.d_dst + bi * W, wk.d_found + bi * W));
-		if (multi_dev) // results of every device meet in pinned host memory, then return to the primary
+		if (multi_dev) { // results of every device meet in pinned host memory, then return to the primary
 			PGQ_CUDA(cudaMemcpyAsync(stage + bi * W, wk.d_found + bi * W, (size_t)W * 4, cudaMemcpyDeviceToHost,
 			                         wk.w->stream));
+			if (!host_loop) PGQ_CUDA(cudaStreamSynchronize(wk.w->stream)); // dynamic hand-out: see msbfs_run
+		}
 		return (int)PGQ_OK;
 	}));
 	if (multi_dev) PGQ_CUDA(cudaMemcpyAsync(d_found, stage, (size_t)nslots * 4, cudaMemcpyHostToDevice, st));

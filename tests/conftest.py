@@ -23,6 +23,7 @@ def ctx(request):
     c = pgq_b200.Context(0)
     c.set_option("small_path", request.param[0])
     c.set_option("loop", request.param[1])
+    c.set_option("loop_min_batches", 0)  # the device loop for every call, however small (default: only when it pays)
     yield c
     c.close()
 

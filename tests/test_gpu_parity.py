@@ -715,6 +715,40 @@ def test_device_loop_has_no_host_sync_and_equals_host_loop(ctx):
     ctx.csr_delete(1)
 
 
+def test_loop_graph_is_built_only_where_it_pays():
+    """Default thresholds (own context): a small call on a fresh CSR takes the host-driven loop (building the loop
+    graph would cost more than the call), the fifth call on the same CSR and any call of >= 8 batches take the
+    device loop.  Same answers either way."""
+    import pgq_b200
+    c = pgq_b200.Context(0)
+    try:
+        c.set_option("small_path", 0)
+        scale = 13
+        V = 1 << scale
+        src, dst = orc.gen_rmat(0x5eed0000 + scale, scale)
+        c.csr_build(1, V, src, dst)
+        v, e, _ = orc.csr_build(V, src, dst, want_eids=False)
+        ps, pd = orc.gen_pairs(2, V, v, 600)
+        eo, ev = orc.iterativelength(V, v, e, ps, pd)
+        syncs = []
+        for _ in range(6):
+            c.reset_stats()
+            out, ov = c.iterativelength(1, ps, pd)
+            _cmp_arr("valid", ov, ev)
+            _cmp_arr("length", out, eo)
+            syncs.append(c.stats()["host_syncs"])
+        assert all(x > 0 for x in syncs[:4]) and syncs[4] == 0 and syncs[5] == 0, syncs
+        c.csr_build(2, V, src, dst)  # fresh CSR, 10 batches of 64 lanes in one call
+        c.set_option("lanes", 64)
+        c.reset_stats()
+        out, ov = c.iterativelength(2, ps, pd)
+        _cmp_arr("valid 64", ov, ev)
+        _cmp_arr("length 64", out, eo)
+        assert c.stats()["host_syncs"] == 0 and c.stats()["batches"] == 10
+    finally:
+        c.close()
+
+
 @pytest.mark.parametrize("done,l2p", [(0, 0), (1, 1)])
 def test_done_bitmap_and_l2_window_do_not_change_results(ctx, done, l2p):
     V, v, e, eids, ps, pd = _rmat_case(ctx, 13, 700, seed=5)
