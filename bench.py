@@ -344,6 +344,84 @@ def oracle_paths_mt(V, v, e, eids, src, dst, nthreads, rows_per_thread=512):
     return res
 
 
+def bench_cheapest(ctx, csr_id, V, E, src, dst, nw, peak_gbs, with_parity):
+    """SURVEY.md section 8(f) f4 on the C4 graph: cheapest_path_length over BIGINT weights 1..100 per knows row (and
+    the same values as DOUBLE), host buffers through the C ABI.  Reported: the default path (16-bit distance rows,
+    destination bound, 4 lane batches in flight), the same on 8-byte rows, round 1's shape (8-byte rows, no bound,
+    one batch at a time), and a byte model from the instrumented kernels."""
+    w = np.random.default_rng(4243).integers(1, 101, size=E).astype(np.int64)
+    ctx.csr_set_weights(csr_id, w)
+
+    def timed(reps=2):
+        ctx.cheapest_path_length(csr_id, src[:nw], dst[:nw])
+        ctx.reset_stats()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            res = ctx.cheapest_path_length(csr_id, src[:nw], dst[:nw])
+        secs = (time.perf_counter() - t0) / reps
+        st = ctx.stats()
+        return res, secs, {k: int(st[k] // reps) for k in ("batches", "levels", "sssp_narrow_batches",
+                                                           "sssp_redo_batches", "kernel_launches")}
+    res, secs, st = timed()
+    line = {"pairs": nw, "pairs_per_s": nw / secs, "ms": secs * 1e3, "batches": st["batches"],
+            "rounds": st["levels"], "narrow_batches": st["sssp_narrow_batches"], "redo_batches": st["sssp_redo_batches"],
+            "found": int(np.sum(res[1])), "weights": "int64 uniform 1..100",
+            "what": "16-bit distance rows relaxed with VIADDMNMX.U16x2, 8 threads per row (exact: non-negative int64 "
+                    "weights, a batch whose distances pass 0x3FFF is redone on 8-byte rows), destination bound, hub "
+                    "in-lists in 4096-edge chunks, 4 lane batches in flight, control block read every 4 rounds"}
+    # byte model from the instrumented instantiation (one extra pass, not timed)
+    ctx.set_option("stats", 1)
+    ctx.reset_stats()
+    ctx.cheapest_path_length(csr_id, src[:nw], dst[:nw])
+    ss = ctx.stats()
+    ctx.set_option("stats", 0)
+    hot, scanned, rounds = int(ss["k_gathered"]), int(ss["k_scanned"]), int(ss["levels"])
+    # per source row read: the 128-byte row + its 2-byte weight; per in-edge scanned: the 4-byte source id; per round:
+    # the in-degree offsets (4 B x V); per batch: the row fill (128 B x V).  The changed-bitmap tests hit L1/L2.
+    model = hot * (128 + 2) + scanned * 4 + rounds * 4 * V + st["batches"] * 128 * V
+    l2_peak = 6300 * 1.92  # GB/s: LTS cap of ~6300 B/clk (B300_MICROARCH.md, L2 table) at the 1.92 GHz boost clock
+    line["roofline"] = {"bound": "l2", "achieved": model / secs / 1e9, "peak": l2_peak, "unit": "GB/s",
+                        "frac": model / secs / 1e9 / l2_peak, "traffic": None,
+                        "hbm_peak": peak_gbs, "frac_of_hbm_peak": model / secs / 1e9 / peak_gbs if peak_gbs else None,
+                        "model_bytes_per_call": model, "source_rows_read": hot, "in_edges_scanned": scanned,
+                        "note": "whole-call wall time (4 streams overlap, so no per-kernel events); the 16-bit rows of "
+                                "this graph (V x 128 B = %.0f MB per batch in flight) largely sit in the 126 MB L2 "
+                                "(ncu: 86 %% L2 hit rate, 0.4 GB of DRAM reads against 5 GB of row reads in a dense "
+                                "round), so the bound is the L2-to-SM path, not HBM" % (V * 128 / 1e6)}
+    try:
+        ctx.set_option("sssp_narrow", 0)
+        r2, secs2, st2 = timed(1)
+        line["rows_8_byte"] = {"pairs_per_s": nw / secs2, "ms": secs2 * 1e3, "rounds": st2["levels"],
+                               "same_answers": bool(np.array_equal(r2[0], res[0]) and np.array_equal(r2[1], res[1]))}
+        ctx.set_option("sssp_prune", 0)
+        ctx.set_option("sssp_slots", 1)
+        r3, secs3, st3 = timed(1)
+        line["round1_shape"] = {"pairs_per_s": nw / secs3, "ms": secs3 * 1e3, "rounds": st3["levels"],
+                                "same_answers": bool(np.array_equal(r3[0], res[0]) and np.array_equal(r3[1], res[1])),
+                                "what": "8-byte rows, no destination bound, one lane batch at a time (round 1: 1830 "
+                                        "pairs/s with a host sync per round)"}
+    finally:
+        ctx.set_option("sssp_narrow", 1)
+        ctx.set_option("sssp_prune", 1)
+        ctx.set_option("sssp_slots", 4)
+    if with_parity:
+        import orc
+        k = min(8, nw)
+        v_off, tgt, _ = ctx.csr_download(csr_id)
+        wc = ctx.csr_download_weights(csr_id)
+        t0 = time.perf_counter()
+        eo, ev, _ = orc.cheapest_path_length(V, v_off, tgt, wc, src[:k], dst[:k])
+        line["parity"] = {"pairs": k, "vs_oracle": "identical" if (np.array_equal(eo, res[0][:k]) and
+                                                                 np.array_equal(ev, res[1][:k])) else "MISMATCH",
+                          "oracle_s": time.perf_counter() - t0}
+    ctx.csr_set_weights(csr_id, w.astype(np.float64))
+    rd, secsd, std_ = timed(1)
+    line["double_weights"] = {"pairs_per_s": nw / secsd, "ms": secsd * 1e3, "rounds": std_["levels"],
+                              "same_values_as_int64": bool(np.array_equal(rd[0], res[0].astype(np.float64)) and
+                                                           np.array_equal(rd[1], res[1]))}
+    return line
+
+
 def bench_paths(ctx, V, E, npairs, steps, warmup, peak_gbs, with_parity=True):
     """BASELINE config 4: shortestpath with path reconstruction on an LDBC-SF100-shaped knows graph
     (V persons, E directed knows rows = both directions), npairs (src,dst) pairs, host buffers in and
@@ -444,18 +522,7 @@ def bench_paths(ctx, V, E, npairs, steps, warmup, peak_gbs, with_parity=True):
         out["cpu_oracle"] = {"shortestpath_pairs_per_s": rows / cpu_secs, "cores": T, "kind": "port"}
     # next row f4 on the same graph: cheapest_path_length, BIGINT weights 1..100 per knows row
     try:
-        w = np.random.default_rng(4243).integers(1, 101, size=E).astype(np.int64)
-        ctx.csr_set_weights(200, w)
-        nw = min(npairs, 1024)
-        ctx.cheapest_path_length(200, src[:nw], dst[:nw])
-        ctx.reset_stats()
-        t0 = time.perf_counter()
-        res = ctx.cheapest_path_length(200, src[:nw], dst[:nw])
-        secs = time.perf_counter() - t0
-        st = ctx.stats()
-        out["cheapest_path_length"] = {"pairs": nw, "pairs_per_s": nw / secs, "ms": secs * 1e3,
-                                       "batches": int(st["batches"]), "rounds": int(st["levels"]),
-                                       "found": int(np.sum(res[1])), "weights": "int64 uniform 1..100"}
+        out["cheapest_path_length"] = bench_cheapest(ctx, 200, V, E, src, dst, min(npairs, 1024), peak_gbs, with_parity)
     except Exception as ex:  # reported, never fatal for the headline
         out["cheapest_path_length"] = {"error": str(ex)[:200]}
     ctx.csr_delete(200)
@@ -819,7 +886,14 @@ def multi_gpu_sections(a, ctx, dist, rank, world, local, line, V, E, v_off, ms_w
                               "GPUs (device-resident, max over ranks); one_gpu_ms = the weak-scaling step, where "
                               "every GPU answers a whole 65 536-pair set"}
     # ---- (2) one process, all GPUs, one call ----
+    # The other ranks wait on a HOST barrier (gloo): an NCCL barrier would park a spinning kernel of another process
+    # on every GPU rank 0 is about to use, and the driver would time-slice rank 0's kernels against it (measured:
+    # 1.44x on 2 GPUs with the NCCL wait, gpurun check 15).
     barrier_max(dist, local, 0.0)
+    import torch
+    torch.cuda.synchronize()
+    host_group = dist.new_group(backend="gloo")
+    dist.barrier(group=host_group)
     if rank == 0:
         try:
             mc = pgq_b200.Context(devices=list(range(world)))
@@ -852,6 +926,7 @@ def multi_gpu_sections(a, ctx, dist, rank, world, local, line, V, E, v_off, ms_w
             mc.close()
         except Exception as ex:
             line["one_process"] = {"error": str(ex)[:300]}
+    dist.barrier(group=host_group)
     barrier_max(dist, local, 0.0)
     # ---- (3) configs[4]: 1-D vertex partition ----
     try:

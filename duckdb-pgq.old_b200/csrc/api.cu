@@ -285,8 +285,11 @@ void ctx_release_resources(Ctx *c) {
 	DevBuf *bufs[] = {&c->scan_tmp, &c->sort_keys[0], &c->sort_keys[1], &c->sort_p0[0], &c->sort_p0[1],
 	                  &c->sort_p1[0], &c->sort_p1[1], &c->sort_hist, &c->sort_pack, &c->bfs_seen, &c->bfs_visit[0],
 	                  &c->bfs_visit[1], &c->bfs_hist_tab, &c->bfs_pathout, &c->bfs_hubacc, &c->bfs_queue[0], &c->bfs_queue[1], &c->bfs_inq[0],
-	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->part_visit[0], &c->part_visit[1], &c->part_peer_tab, &c->l2_flush, &c->sssp_dist, &c->sssp_chg};
+	                  &c->bfs_inq[1], &c->bfs_lane, &c->bfs_ctrl, &c->bfs_alive, &c->part_alive, &c->part_visit[0], &c->part_visit[1], &c->part_peer_tab, &c->l2_flush};
 	for (DevBuf *b : bufs) b->release();
+	for (SsspSlot &sl : c->sssp_slot) sl.destroy();
+	if (c->h_sssp) cudaFreeHost(c->h_sssp);
+	c->h_sssp = nullptr;
 	for (DevBuf &hb : c->bfs_hist) hb.release();
 	c->bfs_hist.clear();
 	if (c->h_ctrl) cudaFreeHost(c->h_ctrl);
@@ -498,6 +501,9 @@ int pgq_set_option(pgq_ctx_t *ctx, const char *key, int64_t value) {
 	else if (!strcmp(key, "sort_wide_min")) c->opt.sort_wide_min = value < 0 ? 0 : value;
 	else if (!strcmp(key, "streams")) c->opt.streams = value < 1 ? 1 : value > 16 ? 16 : value;
 	else if (!strcmp(key, "loop")) c->opt.loop = value;
+	else if (!strcmp(key, "sssp_narrow")) c->opt.sssp_narrow = value;
+	else if (!strcmp(key, "sssp_prune")) c->opt.sssp_prune = value;
+	else if (!strcmp(key, "sssp_slots")) c->opt.sssp_slots = value < 1 ? 1 : (value > 4 ? 4 : value);
 	else if (!strcmp(key, "loop_min_batches")) c->opt.loop_min_batches = value < 0 ? 0 : value;
 	else if (!strcmp(key, "loop_min_calls")) c->opt.loop_min_calls = value < 0 ? 0 : value;
 	else if (!strcmp(key, "done_bitmap")) c->opt.done_bitmap = value ? 1 : 0;

@@ -64,6 +64,23 @@ struct DevBuf {
 	}
 };
 
+// One in-flight cheapest_path_length batch (sssp.cu): its own stream, distance rows, changed bitmaps and control block.
+struct SsspSlot {
+	cudaStream_t st = nullptr;
+	cudaEvent_t ev = nullptr;
+	DevBuf dist, chg, ctl, acc; // acc: per hub vertex, the minima its in-list chunks found this round + a touched flag
+	void destroy() {
+		acc.release();
+		dist.release();
+		chg.release();
+		ctl.release();
+		if (ev) cudaEventDestroy(ev);
+		if (st) cudaStreamDestroy(st);
+		ev = nullptr;
+		st = nullptr;
+	}
+};
+
 // Scoped temporary device buffer.
 struct TmpBuf : DevBuf {
 	~TmpBuf() {
@@ -111,6 +128,9 @@ struct Csr {
 	DevBuf d_w_in;          // [E] input-row order while rows arrive
 	DevBuf d_w;             // [E] CSR slot order
 	DevBuf d_iw;            // [E] reverse-CSR order (lazy)
+	DevBuf d_iw16;          // uint16[E] reverse-CSR order, int64 weights clamped to 0x4000 (16-bit distance rows, lazy)
+	DevBuf d_wstat;         // device: weight statistics (sssp.cu WStat)
+	bool w_nonneg = false;  // every weight >= 0 (and no NaN): the destination's distance bounds the search
 	// reverse CSR (lazy)
 	bool prepared = false;
 	DevBuf d_ioff;  // uint32[V+1]
@@ -167,6 +187,9 @@ struct Options {
 	int64_t sort_wide_min = 32768; // ... from this many keys on
 	int64_t level_cap = 0x7fffffff; // per call, not user-settable: iterativelength's upper bound (R11)
 	int64_t loop = 1;          // 1: device-side level loop (CUDA graph WHILE/SWITCH nodes), 0: host loop, one sync per level
+	int64_t sssp_narrow = 1;   // cheapest_path_length: 16-bit distance rows for non-negative int64 weights (exact; falls back)
+	int64_t sssp_prune = 1;    // ... drop candidates that cannot beat the destination's distance (non-negative weights)
+	int64_t sssp_slots = 4;    // ... lane batches in flight
 	int64_t loop_now = 1;      // per call, not user-settable: this call uses the device loop (msbfs.cu use_device_loop)
 	int64_t loop_min_batches = 8; // calls with fewer batches on a CSR that has served < loop_min_calls calls take the host loop
 	int64_t loop_min_calls = 4;
@@ -237,7 +260,8 @@ struct Ctx {
 	int64_t part_p2p_Vp = 0;
 	DevBuf bfs_alive; // per-block-slot alive lane masks (msbfs_kernels.cuh)
 	DevBuf bfs_lane; // per-call lane tables
-	DevBuf sssp_dist, sssp_chg; // cheapest_path_length: dist[V][64], two changed-bitmaps + flag
+	SsspSlot sssp_slot[4]; // cheapest_path_length: up to four lane batches in flight (sssp.cu)
+	void *h_sssp = nullptr; // pinned: one SsspCtl mirror per slot
 	DevBuf bfs_ctrl; // device control block
 	DevBuf l2_flush;
 	void *h_ctrl = nullptr; // pinned host mirror of the control block (4 KiB; upper half: small-path level counts)

@@ -630,6 +630,75 @@ def test_cheapest_path_length_double_and_negative(ctx):
     ctx.csr_delete(1)
 
 
+@pytest.mark.parametrize("wcase", ["fits16", "overflow16", "huge", "zeros"])
+def test_cheapest_path_length_narrow_rows_and_bound(ctx, wcase):
+    """Non-negative int64 weights run on 16-bit distance rows with the destination's distance as a bound; a batch
+    whose distances do not fit is redone on 8-byte rows.  Same bytes as the oracle in every case, and the same as
+    with both shortcuts switched off."""
+    V = 2500
+    src, dst = orc.gen_knows(0x1dbc + 7, V, 30000)
+    rng = np.random.default_rng(21)
+    if wcase == "fits16":
+        w = rng.integers(1, 101, size=len(src))
+    elif wcase == "overflow16":
+        w = rng.integers(20000, 60000, size=len(src))  # two hops already pass 65535
+    elif wcase == "huge":
+        w = np.where(rng.random(len(src)) < 0.3, rng.integers(1 << 31, 1 << 40, size=len(src)),
+                     rng.integers(0, 50, size=len(src)))
+    else:
+        w = np.where(rng.random(len(src)) < 0.5, 0, rng.integers(0, 3, size=len(src)))
+    w = w.astype(np.int64)
+    v, e, wc, ps, pd, got, gv = _weighted_case(ctx, V, src, dst, w, 300, 9)
+    ctx.reset_stats()
+    ctx.cheapest_path_length(1, ps, pd)
+    st = ctx.stats()
+    if wcase in ("fits16", "zeros"):
+        assert st["sssp_narrow_batches"] == st["batches"] > 0 and st["sssp_redo_batches"] == 0, st
+    if wcase == "overflow16":
+        assert st["sssp_redo_batches"] > 0, st
+    try:
+        for narrow, prune, slots in ((0, 1, 4), (1, 0, 1), (0, 0, 2)):
+            ctx.set_option("sssp_narrow", narrow)
+            ctx.set_option("sssp_prune", prune)
+            ctx.set_option("sssp_slots", slots)
+            again, av = ctx.cheapest_path_length(1, ps, pd)
+            ref, rv, _ = orc.cheapest_path_length(V, v, e, wc, ps, pd)
+            assert av.tolist() == rv.tolist() and again.tobytes() == ref.tobytes(), (narrow, prune, slots)
+    finally:
+        ctx.set_option("sssp_narrow", 1)
+        ctx.set_option("sssp_prune", 1)
+        ctx.set_option("sssp_slots", 4)
+    ctx.csr_delete(1)
+
+
+@pytest.mark.parametrize("kind", ["narrow", "wide", "double", "negative"])
+def test_cheapest_path_length_hub_chunks(ctx, kind):
+    """In-lists above hub_min are relaxed chunk by chunk, the chunks' minima meeting through atomic minima (uint32,
+    int64, and compare-and-swap for double): force that path on a small graph."""
+    V = 1 << 11
+    src, dst = orc.gen_rmat(0x5eed0000 + 11, 11)
+    rng = np.random.default_rng(31)
+    if kind == "double":
+        w = rng.random(len(src)) * 7.0
+    elif kind == "negative":
+        lo, hi = np.minimum(src, dst), np.maximum(src, dst)
+        keep = lo != hi
+        src, dst = lo[keep], hi[keep]
+        w = rng.integers(-20, 60, size=len(src)).astype(np.int64)
+    else:
+        w = rng.integers(0, 200, size=len(src)).astype(np.int64)
+    ctx.set_option("hub_min", 8)
+    ctx.set_option("hub_chunk", 256)
+    ctx.set_option("sssp_narrow", 0 if kind == "wide" else 1)
+    try:
+        _weighted_case(ctx, V, src, dst, w, 260, 17)
+        ctx.csr_delete(1)
+    finally:
+        ctx.set_option("hub_min", 4096)
+        ctx.set_option("hub_chunk", 4096)
+        ctx.set_option("sssp_narrow", 1)
+
+
 def test_cheapest_path_length_errors(ctx):
     src = np.array([0, 1, 2], dtype=np.int64)
     dst = np.array([1, 2, 0], dtype=np.int64)
