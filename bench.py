@@ -123,13 +123,19 @@ def lib_hash():
         return None
 
 
-def src_hash():
-    """sha256 (16 hex digits) over the kernel sources: survives a rebuild of the same code on another box."""
-    import glob
+SRC_SETS = {  # the sources a profiled kernel family is compiled from
+    "msbfs": ("msbfs_kernels.cuh", "msbfs.cu", "common.cuh"),
+    "csr": ("csr_build.cu", "radix_sort.cu", "radix_sort_wide.cu", "scan.cu", "common.cuh"),
+}
+
+
+def src_hash(which="msbfs"):
+    """sha256 (16 hex digits) over the sources of one kernel family: survives a rebuild of the same code on another
+    box, and an edit to an unrelated kernel (say sssp.cu) does not make the MS-BFS traffic profile stale."""
     import hashlib
     h = hashlib.sha256()
-    for f in sorted(glob.glob(os.path.join(ROOT, "duckdb-pgq.old_b200", "csrc", "*.cu*"))):
-        h.update(open(f, "rb").read())
+    for f in SRC_SETS[which]:
+        h.update(open(os.path.join(ROOT, "duckdb-pgq.old_b200", "csrc", f), "rb").read())
     return h.hexdigest()[:16]
 
 
@@ -142,9 +148,10 @@ def load_traffic(name, want):
         prof = json.load(open(path))
     except Exception:
         return None, "no profiles/%s" % name
-    if prof.get("src_hash") != src_hash():
+    which = "csr" if "csr" in name else "msbfs"
+    if prof.get("src_hash") != src_hash(which):
         return None, "profiles/%s was taken on other kernel sources (src_hash %s != %s)" % (
-            name, prof.get("src_hash"), src_hash())
+            name, prof.get("src_hash"), src_hash(which))
     for k, v in want.items():
         if prof.get(k) != v:
             return None, "profiles/%s was taken at %s=%s, this run has %s" % (name, k, prof.get(k), v)

@@ -71,21 +71,26 @@ struct LoopState {
 struct BfsCtrl {
 	uint32_t active[32]; // lane mask, W/32 words used (W <= 1024); first so slices are 16 B aligned
 	uint32_t alive[32];  // lanes that gained a frontier bit in the running level (others are exhausted)
-	uint32_t change;     // set by level kernels when any new bit appeared
-	uint32_t change_out; // snapshot taken by the check kernel
+	uint32_t change_out; // snapshot of `change` taken by the check kernel
 	uint32_t n_active;   // lanes still searching
-	uint32_t pad;
+	uint32_t pad[2];
 	unsigned long long edges_lane;
 	unsigned long long edges_unique;
 	unsigned long long verts_active;
 	unsigned long long pad2;
-	// frontier being produced by the running level (accumulated), and its snapshot
-	unsigned long long next_edges; // sum of out-degrees of vertices with a non-empty next word
-	uint32_t next_verts;
-	uint32_t next_items;           // work items written to the next push queue
+	// snapshot of the frontier the running level consumes (written by the init / check kernels only)
 	unsigned long long out_edges;
 	uint32_t out_verts;
 	uint32_t out_items;
+	// The frontier being produced by the running level: the ONLY words of this block the level kernels write (one
+	// atomicAdd per warp or block), on a 128-byte line of their own -- every warp of a level kernel reads `active`,
+	// `out_items` and the views in `L`, and a load queues behind the atomics aimed at its line (the effect measured on
+	// cheapest_path_length's control block, profiles/r02_sssp_relax_before_ctl_fix.txt).
+	alignas(128) unsigned long long next_edges; // sum of out-degrees of vertices with a non-empty next word
+	uint32_t next_verts;
+	uint32_t next_items; // work items written to the next push queue
+	uint32_t change;     // set by level kernels when any new bit appeared
+	alignas(128) uint32_t line_end; // (the next field starts a new line)
 	// whole-batch kernel for small graphs (msbfs_small_kernel)
 	uint32_t small_bar;      // grid barrier counter (zeroed by the host before the launch)
 	uint32_t small_levels;   // levels run

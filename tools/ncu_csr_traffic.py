@@ -36,7 +36,7 @@ def main():
         kern.append({"name": name, "ms": round(ms, 4), "dram_GB": round(by / 1e9, 4)})
         tot_b += by
         tot_ms += ms
-    summary = {"command": cmd, "src_hash": src_hash(), "scale": scale, "edgefactor": ef,
+    summary = {"command": cmd, "src_hash": src_hash("csr"), "scale": scale, "edgefactor": ef,
                "dram_bytes_per_build": tot_b, "kernel_ms_under_ncu": tot_ms, "kernels": kern}
     json.dump(summary, open(out, "w"), indent=1)
     print(json.dumps({k: v for k, v in summary.items() if k != "kernels"}, indent=1))

@@ -68,7 +68,7 @@ def main():
     lvl_ms = sum(b["ms"] for b in good)
     summary = {
         "command": cmd,
-        "src_hash": src_hash(),
+        "src_hash": src_hash("msbfs"),
         "scale": keys[0] if len(keys) > 0 else None, "edgefactor": keys[1] if len(keys) > 1 else None,
         "lanes": keys[2] if len(keys) > 2 else None,
         "note": "ncu --clock-control none launch list; per-launch times are cold-cache and serialised, "
