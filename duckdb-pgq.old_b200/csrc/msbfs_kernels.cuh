@@ -68,6 +68,25 @@ struct LoopState {
 	uint32_t pad1;
 };
 
+// Launch bounds of the gather kernels.  A/B builds (tools/r02_ab_build.sh) add a minimum number of resident blocks
+// per SM; note that asking for a minimum of 1 is NOT neutral: ptxas then spends 62 registers on pull_list instead of
+// 48 and the level gets slower (gpurun check 20).
+#ifdef PGQ_LIST_MINB
+#define PGQ_LIST_BOUNDS __launch_bounds__(128, PGQ_LIST_MINB)
+#else
+#define PGQ_LIST_BOUNDS __launch_bounds__(128)
+#endif
+#ifdef PGQ_WARP_MINB
+#define PGQ_WARP_BOUNDS __launch_bounds__(128, PGQ_WARP_MINB)
+#else
+#define PGQ_WARP_BOUNDS __launch_bounds__(128)
+#endif
+#ifdef PGQ_SEG_MINB
+#define PGQ_SEG_BOUNDS __launch_bounds__(128, PGQ_SEG_MINB)
+#else
+#define PGQ_SEG_BOUNDS __launch_bounds__(128)
+#endif
+
 struct BfsCtrl {
 	uint32_t active[32]; // lane mask, W/32 words used (W <= 1024); first so slices are 16 B aligned
 	uint32_t alive[32];  // lanes that gained a frontier bit in the running level (others are exhausted)
@@ -343,7 +362,7 @@ __device__ __forceinline__ bool group_any(bool x) {
 // edges).  Loops are warp-uniform (trip count = the slowest vertex of the warp) because the
 // reductions use full-mask shuffles.
 template <int W, int GPV, bool FILTER, bool STATS = false>
-__global__ void __launch_bounds__(128) pull_list_kernel(PullArgs a) {
+__global__ void PGQ_LIST_BOUNDS pull_list_kernel(PullArgs a) {
 	// unfiltered (dense) levels: every listed vertex stores its word and no done-bitmap code at all (the code shape
 	// of round 1: measured 3.11 vs 3.40 ms on the dense level of an s24 batch); filtered levels: sparse stores + done
 	constexpr bool SP = FILTER;
@@ -584,7 +603,7 @@ __global__ void __launch_bounds__(128) pull_tiny_kernel(PullArgs a) {
 // only the words whose test passed (source ids handed over by shuffle).  Rounds are pipelined two
 // deep like pull_list_kernel.  Early exit once every unseen lane of the vertex is covered.
 template <int W, bool FILTER, bool STATS = false>
-__global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
+__global__ void PGQ_WARP_BOUNDS pull_warp_kernel(PullArgs a) {
 	// unfiltered (dense) levels: every listed vertex stores its word and no done-bitmap code at all (the code shape
 	// of round 1: measured 3.11 vs 3.40 ms on the dense level of an s24 batch); filtered levels: sparse stores + done
 	constexpr bool SP = FILTER;
@@ -689,7 +708,7 @@ __global__ void __launch_bounds__(128) pull_warp_kernel(PullArgs a) {
 // source ids handed over by shuffle.  pull_warp_kernel is the SEG = 32 case of the same idea; this one
 // packs 32/SEG vertices into a warp for in-degrees far below 32.  Rounds are pipelined two deep.
 template <int W, int SEG, bool STATS = false>
-__global__ void __launch_bounds__(128) pull_seg_kernel(PullArgs a) {
+__global__ void PGQ_SEG_BOUNDS pull_seg_kernel(PullArgs a) {
 	const uint32_t *const visit_p = view_visit(a);
 	const uint32_t *const fcur_p = view_fcur(a);
 	using C = LaneCfg<W>;
