@@ -133,9 +133,13 @@ def src_hash(which="msbfs"):
     """sha256 (16 hex digits) over the sources of one kernel family: survives a rebuild of the same code on another
     box, and an edit to an unrelated kernel (say sssp.cu) does not make the MS-BFS traffic profile stale."""
     import hashlib
+    import re
     h = hashlib.sha256()
     for f in SRC_SETS[which]:
-        h.update(open(os.path.join(ROOT, "duckdb-pgq.old_b200", "csrc", f), "rb").read())
+        text = open(os.path.join(ROOT, "duckdb-pgq.old_b200", "csrc", f), "r", errors="replace").read()
+        text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)  # comments and layout do not change the kernels
+        text = re.sub(r"//[^\n]*", " ", text)
+        h.update(" ".join(text.split()).encode())
     return h.hexdigest()[:16]
 
 
@@ -452,13 +456,17 @@ def bench_paths(ctx, V, E, npairs, steps, warmup, peak_gbs, with_parity=True):
         for _ in range(min(warmup, 2)):
             res = fn(src, dst)
         ctx.reset_stats()
-        t0 = time.perf_counter()
+        steps = max(steps, 5)  # ~20 ms calls: time each one, report the median and every sample
+        samples = []
         for _ in range(steps):
+            t0 = time.perf_counter()
             res = fn(src, dst)
-        secs = (time.perf_counter() - t0) / steps
+            samples.append(time.perf_counter() - t0)
+        secs = float(np.median(samples))
         st = ctx.stats()
         full[name] = res
-        out[name] = {"pairs_per_s": npairs / secs, "ms": secs * 1e3, "batches": int(st["batches"] // steps),
+        out[name] = {"pairs_per_s": npairs / secs, "ms": secs * 1e3,
+                     "ms_samples": [round(x * 1e3, 2) for x in samples], "batches": int(st["batches"] // steps),
                      "levels": int(st["levels"] // steps), "host_syncs": int(st["host_syncs"] // steps),
                      "h2d_bytes_per_step": int(st["h2d_bytes"] // steps),
                      "d2h_bytes_per_step": int(st["d2h_bytes"] // steps)}
