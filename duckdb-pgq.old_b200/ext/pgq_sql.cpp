@@ -4,18 +4,21 @@
 // and errors as "-- error N: <message>".  It links the same libduckdb.so as the extension, so the
 // plugin and the host share one copy of DuckDB (SURVEY.md §8(b) caveat about the static shell).
 #include "duckdb.hpp"
+#include "pgq_rewrite.hpp"
 
 #include <chrono>
 #include <cstdlib>
 #include <iostream>
 #include <sstream>
 #include <string>
+#include <vector>
 
 using namespace duckdb;
 
 int main(int argc, char **argv) {
 	DuckDB db(argc > 1 ? argv[1] : nullptr);
 	Connection con(db);
+	pgq_rewrite::Rewriter rewriter;
 	std::string line, stmt;
 	int n = 0, failed = 0;
 	const bool timing = std::getenv("PGQ_SQL_TIME") != nullptr;
@@ -24,9 +27,32 @@ int main(int argc, char **argv) {
 		stmt += "\n";
 		size_t end = line.find_last_not_of(" \t\r");
 		if (end == std::string::npos || line[end] != ';') continue;
+		// SQL/PGQ surface syntax (CREATE PROPERTY GRAPH, GRAPH_TABLE ... MATCH) becomes plain SQL over the path's
+		// scalar functions first (pgq_rewrite.hpp; PGQ_SQL_SHOW_REWRITE=1 prints what is run instead)
+		pgq_rewrite::Result rw = rewriter.rewrite(stmt);
+		std::vector<std::string> after;
+		if (rw.handled) {
+			n++;
+			stmt.clear();
+			if (!rw.error.empty()) {
+				std::cout << "-- error " << n << ": " << rw.error << "\n";
+				failed++;
+				continue;
+			}
+			if (rw.statements.empty()) {
+				std::cout << "-- result " << n << "\n";
+				continue;
+			}
+			if (std::getenv("PGQ_SQL_SHOW_REWRITE"))
+				for (auto &q : rw.statements) std::cout << "-- rewrite " << n << ": " << q << "\n";
+			stmt = rw.statements[rw.main_statement];
+			for (size_t k = rw.main_statement + 1; k < rw.statements.size(); k++) after.push_back(rw.statements[k]);
+			n--;
+		}
 		auto t0 = std::chrono::steady_clock::now();
 		auto res = con.Query(stmt);
 		auto t1 = std::chrono::steady_clock::now();
+		for (auto &q : after) con.Query(q); // delete_csr of the CSRs the statement built
 		stmt.clear();
 		n++;
 		if (timing) // PGQ_SQL_TIME=1: wall time of Connection::Query (parse + plan + execute + materialise)
