@@ -147,8 +147,11 @@ inline std::string Rewriter::graph_table(detail::Cur &c, std::vector<std::string
 	// ---- path function calls ----
 	// call expressions of quantified edge k (source side first)
 	struct Calls {
+		// |V|: a column of the one-row aggregate, not a scalar subquery — with a subquery inside a WHERE predicate this
+		// engine plans a blockwise nested-loop join and calls the function one row at a time (71 us per row, measured in
+		// round 1: profiles/r01_sql_path.md)
 		static std::string cnt(const PEdge &e) {
-			return "(SELECT count(*) FROM " + e.tbl->src_table + ")";
+			return "__pgq_x" + num(e.csr_id) + ".n";
 		}
 		static std::string sd(const PEdge &e, const PVertex &a, const PVertex &b) {
 			const PVertex &s = e.reversed ? b : a, &d = e.reversed ? a : b;
@@ -157,7 +160,7 @@ inline std::string Rewriter::graph_table(detail::Cur &c, std::vector<std::string
 		static std::string bounds(const PEdge &e) {
 			if (e.lower == 0 && e.upper < 0) return "";
 			return ", CAST(" + num(e.lower) + " AS BIGINT), " +
-			       (e.upper < 0 ? "CAST(" + cnt(e) + " AS BIGINT)" : "CAST(" + num(e.upper) + " AS BIGINT)");
+			       (e.upper < 0 ? cnt(e) : "CAST(" + num(e.upper) + " AS BIGINT)");
 		}
 		static std::string length(const PEdge &e, const PVertex &a, const PVertex &b) {
 			return "iterativelength(" + num(e.csr_id) + ", " + cnt(e) + ", " + sd(e, a, b) + bounds(e) + ")";
@@ -260,7 +263,8 @@ inline std::string Rewriter::graph_table(detail::Cur &c, std::vector<std::string
 	for (size_t k = 0; k < es.size(); k++)
 		if (es[k].quantified) {
 			const std::string id = num(es[k].csr_id);
-			from += (from.empty() ? "" : ", ") + std::string("(SELECT count(__pgq_csr") + id + ".temp) * 0 AS z FROM __pgq_csr" + id + ") __pgq_x" + id;
+			from += (from.empty() ? "" : ", ") + std::string("(SELECT count(__pgq_csr") + id + ".temp) * 0 AS z, (SELECT count(*) FROM " +
+			        es[k].tbl->src_table + ") AS n FROM __pgq_csr" + id + ") __pgq_x" + id;
 		}
 	for (size_t k = 0; k < vs.size(); k++) from += (from.empty() ? "" : ", ") + vs[k].tbl->table + " " + vs[k].var;
 	for (size_t k = 0; k < es.size(); k++)

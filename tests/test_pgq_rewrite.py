@@ -66,9 +66,12 @@ def test_any_shortest_becomes_the_csr_template():
                            "sum(create_csr_vertex(1000, (SELECT count(*) FROM person), sub.dense_id, sub.cnt))")
     assert "s.rowid, d.rowid, e.rowid) AS temp FROM knows e JOIN person s ON s.id = e.p1 JOIN person d ON d.id = e.p2)" in main
     # the path functions cannot run before the CSR is complete: their source argument depends on the aggregate
-    assert "iterativelength(1000, (SELECT count(*) FROM person), a.rowid + __pgq_x1000.z, b.rowid) AS len" in main
-    assert "shortestpath(1000, (SELECT count(*) FROM person), a.rowid + __pgq_x1000.z, b.rowid) AS vs" in main
-    assert "(SELECT count(__pgq_csr1000.temp) * 0 AS z FROM __pgq_csr1000) __pgq_x1000, person a, person b" in main
+    # (and |V| is a column of that one-row aggregate: a scalar subquery inside the predicate would make the engine call
+    # the function one row at a time)
+    assert "iterativelength(1000, __pgq_x1000.n, a.rowid + __pgq_x1000.z, b.rowid) AS len" in main
+    assert "shortestpath(1000, __pgq_x1000.n, a.rowid + __pgq_x1000.z, b.rowid) AS vs" in main
+    assert ("(SELECT count(__pgq_csr1000.temp) * 0 AS z, (SELECT count(*) FROM person) AS n FROM __pgq_csr1000) __pgq_x1000, "
+            "person a, person b") in main
     assert "IS NOT NULL AND (a.id = 3)) gt ORDER BY dst;" in main  # MATCH keeps the pairs that have a path
     assert st[1] == "SELECT delete_csr(1000);"
 
@@ -85,16 +88,16 @@ def test_quantifiers_directions_and_joins():
     assert one_hop == ["SELECT count(*) FROM (SELECT a.id, k.p2 FROM person a, person b, knows k WHERE k.p1 = a.id AND k.p2 = b.id "
                        "AND (a.id < b.id)) __pgq_gt0;"]  # a join, no CSR, no cleanup
     rev = r[2][1][0]  # <-[ ]- : the path runs from b to a; {1,3} is the bounded 6-argument form
-    assert "shortestpath_with_edges(1000, (SELECT count(*) FROM person), b.rowid + __pgq_x1000.z, a.rowid) AS pe" in rev
+    assert "shortestpath_with_edges(1000, __pgq_x1000.n, b.rowid + __pgq_x1000.z, a.rowid) AS pe" in rev
     assert "b.rowid + __pgq_x1000.z, a.rowid, CAST(1 AS BIGINT), CAST(3 AS BIGINT)) IS NOT NULL" in rev
     plus = r[3][1][0]
-    assert "CAST(1 AS BIGINT), CAST((SELECT count(*) FROM person) AS BIGINT)) IS NOT NULL" in plus
+    assert "CAST(1 AS BIGINT), __pgq_x1001.n) IS NOT NULL" in plus
     star = r[4][1][0]  # no path variable, no ANY SHORTEST: existence only
-    assert "WHERE reachability(1002, (SELECT count(*) FROM person), a.rowid + __pgq_x1002.z, b.rowid)) __pgq_gt0" in star
+    assert "WHERE reachability(1002, __pgq_x1002.n, a.rowid + __pgq_x1002.z, b.rowid)) __pgq_gt0" in star
     cheap = r[5][1][0]  # joins an existing WITH list; the weight column travels with the edge rows
     assert cheap.startswith("WITH __pgq_csr1003 AS (") and "),  x AS (SELECT 3 AS s) SELECT * FROM x, (" in cheap
     assert "e.rowid, CAST(e.w AS BIGINT)) AS temp" in cheap
-    assert "cheapest_path_length(1003, (SELECT count(*) FROM person), a.rowid + __pgq_x1003.z, b.rowid) AS c" in cheap
+    assert "cheapest_path_length(1003, __pgq_x1003.n, a.rowid + __pgq_x1003.z, b.rowid) AS c" in cheap
 
 
 def test_unsupported_syntax_is_reported_not_guessed():

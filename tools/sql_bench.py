@@ -54,6 +54,12 @@ def main():
     ctx.csr_build(900, V, src, dst)
     lo, lv = ctx.iterativelength(900, ps, pd)
     want_sum, want_cnt = int(lo[lv == 1].sum()), int((lv == 1).sum())
+    # SQL/PGQ form (pgq_rewrite.hpp): 16 sources x every person
+    nsrc = 16
+    gs = np.repeat(np.arange(nsrc, dtype=np.int64), V)
+    gd = np.tile(np.arange(V, dtype=np.int64), nsrc)
+    glo, glv = ctx.iterativelength(900, gs, gd)
+    gt_sum, gt_cnt = int(glo[glv == 1].sum()), int((glv == 1).sum())
     ctx.csr_delete(900)
     ctx.close()
     tmp = tempfile.mkdtemp(prefix="pgq_sql_")
@@ -73,7 +79,13 @@ def main():
              ("copy1", "COPY person FROM '%s';" % os.path.join(tmp, "person.csv")),
              ("copy2", "COPY knows FROM '%s';" % os.path.join(tmp, "knows.csv")),
              ("copy3", "COPY pairs FROM '%s';" % os.path.join(tmp, "pairs.csv"))]
+    stmts.append(("pg", "CREATE PROPERTY GRAPH snb VERTEX TABLES (person KEY (id) LABEL Person) EDGE TABLES (knows SOURCE KEY (p1) "
+                        "REFERENCES person (id) DESTINATION KEY (p2) REFERENCES person (id) LABEL knows);"))
     for r in range(a.reps):
+        # CREATE PROPERTY GRAPH + GRAPH_TABLE through the rewriter: CSR build (CTE), 16 x V path lengths, delete_csr
+        stmts.append(("graph_table_%d" % r,
+                      "SELECT sum(len), count(len) FROM GRAPH_TABLE (snb MATCH p = ANY SHORTEST (a:Person WHERE a.rowid < %d)"
+                      "-[k:knows]->*(b:Person) COLUMNS (path_length(p) AS len)) g;" % nsrc))
         stmts += [("csr_build_%d" % r, build),
                   ("iterativelength_%d" % r, "SELECT sum(iterativelength(0, %s, s, d)), count(iterativelength(0, %s, s, d)) FROM pairs;" % (vq, vq)),
                   ("reachability_%d" % r, "SELECT sum(CASE WHEN reachability(0, %s, s, d) THEN 1 ELSE 0 END) FROM pairs;" % vq),
@@ -107,11 +119,13 @@ def main():
     out = {"persons": V, "knows": E, "pairs": n, "threads": a.threads, "statements_ms": {}, "errors": errors,
            "expect": {"sum": want_sum, "count": want_cnt}, "got": {}}
     for i, (name, _) in enumerate(stmts, start=1):
-        if name.startswith(("csr_build", "iterativelength", "reachability", "shortestpath", "copy2")):
+        if name.startswith(("csr_build", "iterativelength", "reachability", "shortestpath", "copy2", "graph_table")):
             out["statements_ms"][name] = times.get(i)
-        if name.startswith(("iterativelength", "reachability", "shortestpath", "csr_build")):
+        if name.startswith(("iterativelength", "reachability", "shortestpath", "csr_build", "graph_table")):
             out["got"][name] = results.get(i)
     last = a.reps - 1
+    out["graph_table"] = {"pairs": nsrc * V, "expect": "%d,%d" % (gt_sum, gt_cnt),
+                          "parity_vs_c_abi": out["got"].get("graph_table_%d" % last) == ["%d,%d" % (gt_sum, gt_cnt)]}
     out["parity_vs_c_abi"] = bool(results and out["got"].get("iterativelength_%d" % last) == ["%d,%d" % (want_sum, want_cnt)])
     print(json.dumps(out))
     if p.returncode != 0 or errors:
