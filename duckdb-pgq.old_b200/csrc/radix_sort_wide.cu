@@ -273,10 +273,6 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 #pragma unroll
 		for (int q = 0; q < 4; q++) {
 			const uint32_t d = (keys[r0 + q] >> a.shift) & mask;
-#ifdef PGQ_RW_MATCH
-			// one MATCH.ANY instead of NBITS ballots (rows past the end share the key ~0, which no digit equals)
-			peers[q] = __match_any_sync(0xffffffffu, wbase + (r0 + q) * 32 < a.n ? d : 0xFFFFFFFFu);
-#else
 			unsigned pm = __ballot_sync(0xffffffffu, wbase + (r0 + q) * 32 < a.n);
 #pragma unroll
 			for (int b = 0; b < NBITS; b++) {
@@ -285,7 +281,6 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) rw_scatter_ke
 				pm &= bit ? m : ~m;
 			}
 			peers[q] = pm;
-#endif
 		}
 #pragma unroll
 		for (int q = 0; q < 4; q++) {
