@@ -545,6 +545,38 @@ def bench_paths(ctx, V, E, npairs, steps, warmup, peak_gbs, with_parity=True):
                         "(e2e through the C ABI)" % (V, E, npairs), **out}
 
 
+def bench_sql():
+    """The same functions through the reference engine: LOAD of the extension into the DuckDB built from the reference
+    (baseline/_ref/duckdb travels with the snapshot), C1-shaped tables, hand-written statements and one SQL/PGQ
+    GRAPH_TABLE statement through the rewriter (tools/sql_bench.py; wall time of Connection::Query per statement, third
+    repetition; checksums against the C ABI).  Reported, never fatal."""
+    import subprocess
+    need = [os.path.join(ROOT, "duckdb-pgq.old_b200", "ext", "pgq_b200.duckdb_extension"),
+            os.path.join(ROOT, "duckdb-pgq.old_b200", "ext", "pgq_sql"),
+            os.path.join(ROOT, "baseline", "_ref", "duckdb", "libduckdb.so")]
+    if not all(os.path.exists(f) for f in need):
+        return {"unavailable": "reference DuckDB host / extension not built in this snapshot"}
+    try:
+        p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sql_bench.py")], capture_output=True, text=True,
+                           timeout=600)
+        d = json.loads(p.stdout.strip().splitlines()[-1])
+        reps = [k.rsplit("_", 1) for k in d["statements_ms"] if "_" in k and k.rsplit("_", 1)[1].isdigit()]
+        last = max(int(r[1]) for r in reps)
+        ms = {k.rsplit("_", 1)[0]: round(v, 3) for k, v in d["statements_ms"].items()
+              if k.endswith("_%d" % last) and v is not None}
+        n = d["pairs"]
+        return {"workload": "reference DuckDB + pgq_b200.duckdb_extension, %d persons, %d knows rows, %d pairs, PRAGMA "
+                            "threads=%d" % (d["persons"], d["knows"], n, d["threads"]),
+                "statement_ms": ms,
+                "iterativelength_pairs_per_s": 2 * n / (ms["iterativelength"] * 1e-3) if ms.get("iterativelength") else None,
+                "graph_table": dict(d["graph_table"], ms=ms.get("graph_table"),
+                                    what="CREATE PROPERTY GRAPH + SELECT ... FROM GRAPH_TABLE (... ANY SHORTEST ...) through "
+                                         "ext/pgq_rewrite.hpp: CSR build CTE, 2 x pairs path lengths, delete_csr"),
+                "parity_vs_c_abi": d["parity_vs_c_abi"], "errors": d["errors"]}
+    except Exception as ex:
+        return {"error": str(ex)[:300]}
+
+
 def bench_c1(ctx, steps, warmup, with_cpu, peak_gbs):
     """BASELINE configs[0]: LDBC SNB SF1-shaped Person-knows-Person graph (10 k vertices, 180 k directed
     edges): CSR build + iterativelength for 2048 pairs, everything from HOST buffers through the same
@@ -843,6 +875,7 @@ def main_ours(a):
                                     not a.no_cpu_baseline)
         line["parity"]["paths_config4"] = line["paths"].get("parity", {}).get("paths")
         line["parity"]["csr_config4"] = line["paths"].get("parity", {}).get("csr")
+        line["sql"] = bench_sql()
     if cpu_legs:
         T, cores = cpu_sample_threads(V, a.cpu_threads)
         rows_pt = min(512, n)
