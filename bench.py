@@ -548,8 +548,8 @@ def bench_paths(ctx, V, E, npairs, steps, warmup, peak_gbs, with_parity=True):
 def bench_sql():
     """The same functions through the reference engine: LOAD of the extension into the DuckDB built from the reference
     (baseline/_ref/duckdb travels with the snapshot), C1-shaped tables, hand-written statements and one SQL/PGQ
-    GRAPH_TABLE statement through the rewriter (tools/sql_bench.py; wall time of Connection::Query per statement, third
-    repetition; checksums against the C ABI).  Reported, never fatal."""
+    GRAPH_TABLE statement through the rewriter (tools/sql_bench.py; wall time of Connection::Query per statement, median
+    of repetitions 1-3 of 4; checksums against the C ABI).  Reported, never fatal."""
     import subprocess
     need = [os.path.join(ROOT, "duckdb-pgq.old_b200", "ext", "pgq_b200.duckdb_extension"),
             os.path.join(ROOT, "duckdb-pgq.old_b200", "ext", "pgq_sql"),
@@ -557,13 +557,14 @@ def bench_sql():
     if not all(os.path.exists(f) for f in need):
         return {"unavailable": "reference DuckDB host / extension not built in this snapshot"}
     try:
-        p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sql_bench.py")], capture_output=True, text=True,
-                           timeout=600)
+        p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sql_bench.py"), "--reps", "4"],
+                           capture_output=True, text=True, timeout=600)
         d = json.loads(p.stdout.strip().splitlines()[-1])
-        reps = [k.rsplit("_", 1) for k in d["statements_ms"] if "_" in k and k.rsplit("_", 1)[1].isdigit()]
-        last = max(int(r[1]) for r in reps)
-        ms = {k.rsplit("_", 1)[0]: round(v, 3) for k, v in d["statements_ms"].items()
-              if k.endswith("_%d" % last) and v is not None}
+        samples = {}  # statement -> times of repetitions 1.. (repetition 0 pays module loading and first allocations)
+        for k, v in d["statements_ms"].items():
+            if "_" in k and k.rsplit("_", 1)[1].isdigit() and int(k.rsplit("_", 1)[1]) >= 1 and v is not None:
+                samples.setdefault(k.rsplit("_", 1)[0], []).append(v)
+        ms = {k: round(float(np.median(v)), 3) for k, v in samples.items()}
         n = d["pairs"]
         return {"workload": "reference DuckDB + pgq_b200.duckdb_extension, %d persons, %d knows rows, %d pairs, PRAGMA "
                             "threads=%d" % (d["persons"], d["knows"], n, d["threads"]),
