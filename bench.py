@@ -404,6 +404,12 @@ def bench_cheapest(ctx, csr_id, V, E, src, dst, nw, peak_gbs, with_parity):
         r2, secs2, st2 = timed(1)
         line["rows_8_byte"] = {"pairs_per_s": nw / secs2, "ms": secs2 * 1e3, "rounds": st2["levels"],
                                "same_answers": bool(np.array_equal(r2[0], res[0]) and np.array_equal(r2[1], res[1]))}
+        ctx.set_option("sssp_narrow", 2)
+        r4, secs4, st4 = timed(1)
+        line["rows_32_bit"] = {"pairs_per_s": nw / secs4, "ms": secs4 * 1e3, "rounds": st4["levels"],
+                               "same_answers": bool(np.array_equal(r4[0], res[0]) and np.array_equal(r4[1], res[1])),
+                               "what": "what a batch costs when its distances do not fit 14 bits (VIADDMNMX.U32)"}
+        ctx.set_option("sssp_narrow", 0)
         ctx.set_option("sssp_prune", 0)
         ctx.set_option("sssp_slots", 1)
         r3, secs3, st3 = timed(1)

@@ -37,7 +37,8 @@ class Stats(C.Structure):
                 ("model_bytes", C.c_uint64), ("k_listed", C.c_uint64), ("k_open", C.c_uint64), ("k_new", C.c_uint64),
                 ("k_scanned", C.c_uint64), ("k_gathered", C.c_uint64), ("kp_items", C.c_uint64),
                 ("kp_edges", C.c_uint64), ("kp_seen", C.c_uint64), ("kp_next", C.c_uint64),
-                ("host_syncs", C.c_uint64), ("sssp_narrow_batches", C.c_uint64), ("sssp_redo_batches", C.c_uint64)]
+                ("host_syncs", C.c_uint64), ("sssp_narrow_batches", C.c_uint64), ("sssp_redo_batches", C.c_uint64),
+                ("sssp_narrow32_batches", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -129,6 +129,7 @@ struct Csr {
 	DevBuf d_w;             // [E] CSR slot order
 	DevBuf d_iw;            // [E] reverse-CSR order (lazy)
 	DevBuf d_iw16;          // uint16[E] reverse-CSR order, int64 weights clamped to 0x4000 (16-bit distance rows, lazy)
+	DevBuf d_iw32n;         // uint32[E] reverse-CSR order, int64 weights clamped to 0x40000000 (32-bit distance rows, lazy)
 	DevBuf d_wstat;         // device: weight statistics (sssp.cu WStat)
 	bool w_nonneg = false;  // every weight >= 0 (and no NaN): the destination's distance bounds the search
 	// reverse CSR (lazy)
@@ -187,7 +188,7 @@ struct Options {
 	int64_t sort_wide_min = 32768; // ... from this many keys on
 	int64_t level_cap = 0x7fffffff; // per call, not user-settable: iterativelength's upper bound (R11)
 	int64_t loop = 1;          // 1: device-side level loop (CUDA graph WHILE/SWITCH nodes), 0: host loop, one sync per level
-	int64_t sssp_narrow = 1;   // cheapest_path_length: 16-bit distance rows for non-negative int64 weights (exact; falls back)
+	int64_t sssp_narrow = 1;   // cheapest_path_length, non-negative int64 weights: 1 = 16-bit then 32-bit distance rows, 2 = 32-bit only, 0 = 8-byte (all exact)
 	int64_t sssp_prune = 1;    // ... drop candidates that cannot beat the destination's distance (non-negative weights)
 	int64_t sssp_slots = 4;    // ... lane batches in flight
 	int64_t loop_now = 1;      // per call, not user-settable: this call uses the device loop (msbfs.cu use_device_loop)

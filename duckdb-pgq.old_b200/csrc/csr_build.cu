@@ -317,7 +317,7 @@ void Csr::free_all() {
 	h_src = h_dst = h_eid = nullptr;
 	d_src64.release(); d_dst64.release(); d_eid64.release();
 	d_off.release(); d_tgt.release(); d_row.release(); d_eid.release(); d_fsrc.release();
-	d_w_in.release(); d_w.release(); d_iw.release(); d_iw16.release(); d_wstat.release();
+	d_w_in.release(); d_w.release(); d_iw.release(); d_iw16.release(); d_iw32n.release(); d_wstat.release();
 	d_ioff.release(); d_isrc.release(); d_ipos.release();
 	d_tiny.release(); d_small.release(); d_med.release(); d_mid.release(); d_hub.release(); d_hubchunks.release();
 	d_ltgt.release(); d_lsrc.release();

@@ -13,8 +13,8 @@
 // Round 2 (all measured on the C4 graph, 1024 pairs, int64 weights 1..100: 559 ms -> 80 ms):
 //  - the control block no longer has the "changed" flag next to `done` (every warp's first load queued behind
 //    450 k stores to that line: 3.1 ms -> 0.55 ms per dense round); the round-end kernel counts the changed-bitmap;
-//  - non-negative int64 weights run on 16-bit rows (sssp16.cuh: one 128-byte line per vertex, VIADDMNMX.U16x2,
-//    exact, batches whose distances do not fit are redone on 8-byte rows);
+//  - non-negative int64 weights run on 16-bit rows (sssp_narrow.cuh: one 128-byte line per vertex, VIADDMNMX.U16x2,
+//    exact; batches whose distances do not fit are redone on 32-bit rows (VIADDMNMX.U32), then on 8-byte rows);
 //  - with non-negative weights the destination's current distance bounds what a row accepts;
 //  - hub in-lists are relaxed in 4096-edge chunks (one 59 k-edge in-list used to set the length of every round);
 //  - sparse rounds relax only the out-neighbours of the changed vertices (sssp_mark_kernel);
@@ -175,11 +175,22 @@ struct Row64 { // 64 lanes x 8 bytes, T = long long | double; thread t owns lane
 	}
 };
 
-// 64 lanes x 2 bytes (one 128-byte line per vertex), for non-negative int64 weights: its own kernels (sssp16.cuh)
+// Narrow rows for non-negative int64 weights (sssp_narrow.cuh has their kernels): 64 lanes x 2 bytes (one 128-byte
+// line per vertex), and 64 lanes x 4 bytes for the batches whose distances do not fit 14 bits
+struct N16;
+struct N32;
 struct Row16 {
 	using R = uint32_t; // hub accumulator element
 	using S = uint16_t;
 	using W = uint16_t;
+	using N = N16;
+	static constexpr bool narrow = true;
+};
+struct Row32 {
+	using R = uint32_t;
+	using S = uint32_t;
+	using W = uint32_t;
+	using N = N32;
 	static constexpr bool narrow = true;
 };
 
@@ -459,7 +470,7 @@ __global__ void sssp_result_kernel(const uint32_t *__restrict__ lane_src, const 
 }
 
 } // namespace pgq
-#include "sssp16.cuh"
+#include "sssp_narrow.cuh"
 namespace pgq {
 
 // ---- weights ---------------------------------------------------------------------------------
@@ -483,6 +494,7 @@ int csr_set_weights(Ctx *c, Csr *g, int wtype, const void *w, int64_t row0, int6
 		g->w_ready = false;
 		g->d_iw.release();
 		g->d_iw16.release();
+		g->d_iw32n.release();
 		PGQ_TRY(g->d_w_in.reserve((size_t)(g->E > 0 ? g->E : 1) * 8));
 	}
 	if (n) {
@@ -609,17 +621,18 @@ static int sssp_batches(Ctx *c, Csr *g, const LaneTable &lt, const std::vector<i
 			                                                                  g->d_tgt.as<uint32_t>(), mark, ctl);
 			// in-degree up to med_max: a warp per vertex; above: exactly the `mid` and `hub` class lists of csr_prepare
 			if constexpr (TR::narrow) {
-				(stats ? sssp16_relax_kernel<true> : sssp16_relax_kernel<false>)<<<g_warp, 256, 0, sl.st>>>(
+				using NW = typename TR::N;
+				(stats ? ssspn_relax_kernel<NW, true> : ssspn_relax_kernel<NW, false>)<<<g_warp, 256, 0, sl.st>>>(
 				    ioff, isrc, iw, dist, prev, nxt, ctl, mark, V, g->eff_med_max);
 				if (g->n_mid)
-					(stats ? sssp16_relax_big_kernel<true> : sssp16_relax_big_kernel<false>)<<<g->n_mid, 256, 0, sl.st>>>(
+					(stats ? ssspn_relax_big_kernel<NW, true> : ssspn_relax_big_kernel<NW, false>)<<<g->n_mid, 256, 0, sl.st>>>(
 					    mid, ioff, isrc, iw, dist, prev, nxt, ctl, mark);
 				if (g->n_hubchunks) {
-					(stats ? sssp16_hub_kernel<true> : sssp16_hub_kernel<false>)<<<g->n_hubchunks, 256, 0, sl.st>>>(
+					(stats ? ssspn_hub_kernel<NW, true> : ssspn_hub_kernel<NW, false>)<<<g->n_hubchunks, 256, 0, sl.st>>>(
 					    chunks, isrc, iw, dist, prev, acc, acc_touched, ctl);
-					sssp16_hub_commit_kernel<<<g_hubc, 256, 0, sl.st>>>(hub, g->n_hub, acc, acc_touched, dist, nxt, ctl);
+					ssspn_hub_commit_kernel<NW><<<g_hubc, 256, 0, sl.st>>>(hub, g->n_hub, acc, acc_touched, dist, nxt, ctl);
 				}
-				sssp16_round_end_kernel<<<1, 1024, 0, sl.st>>>(ls, ld, dist, nxt, cw, ctl, prune ? 1 : 0, mark_max);
+				ssspn_round_end_kernel<NW><<<1, 1024, 0, sl.st>>>(ls, ld, dist, nxt, cw, ctl, prune ? 1 : 0, mark_max);
 			} else {
 				(stats ? sssp_relax_kernel<TR, true> : sssp_relax_kernel<TR, false>)<<<g_warp, 256, 0, sl.st>>>(
 				    ioff, isrc, iw, dist, prev, nxt, ctl, mark, V, g->eff_med_max);
@@ -651,8 +664,9 @@ static int sssp_batches(Ctx *c, Csr *g, const LaneTable &lt, const std::vector<i
 		PGQ_CUDA(cudaStreamWaitEvent(sl.st, c->ev_fork, 0));
 		PGQ_CUDA(cudaMemsetAsync(sl.chg.p, 0, (size_t)cw * 4, sl.st));
 		if constexpr (TR::narrow) {
-			sssp16_fill_kernel<<<c->sm_count * 8, 256, 0, sl.st>>>(sl.dist.as<uint4>(), cells / 8);
-			sssp16_seed_kernel<<<1, L, 0, sl.st>>>(d_src + r.batch * L, sl.dist.as<S>(), sl.chg.as<uint32_t>(),
+			ssspn_fill_kernel<typename TR::N><<<c->sm_count * 8, 256, 0, sl.st>>>(sl.dist.as<uint4>(),
+			                                                                     cells * sizeof(S) / 16);
+			ssspn_seed_kernel<typename TR::N><<<1, L, 0, sl.st>>>(d_src + r.batch * L, sl.dist.as<S>(), sl.chg.as<uint32_t>(),
 			                                       sl.ctl.as<SsspCtl>(), mark_max);
 		} else {
 			sssp_fill_kernel<TR><<<c->sm_count * 8, 256, 0, sl.st>>>(sl.dist.as<S>(), cells);
@@ -662,7 +676,7 @@ static int sssp_batches(Ctx *c, Csr *g, const LaneTable &lt, const std::vector<i
 		count_launch(c, 2);
 		if (g->n_hub) { // the hub accumulators start at "not reached"
 			if constexpr (TR::narrow)
-				sssp16_acc_fill_kernel<<<div_up((uint64_t)acc_cells, 256), 256, 0, sl.st>>>(sl.acc.as<R>(),
+				ssspn_acc_fill_kernel<typename TR::N><<<div_up((uint64_t)acc_cells, 256), 256, 0, sl.st>>>(sl.acc.as<R>(),
 				                                                                        (uint32_t)acc_cells);
 			else
 				sssp_acc_fill_kernel<TR><<<div_up((uint64_t)acc_cells, 256), 256, 0, sl.st>>>(sl.acc.as<R>(),
@@ -709,12 +723,13 @@ static int sssp_batches(Ctx *c, Csr *g, const LaneTable &lt, const std::vector<i
 		c->stats.k_scanned += hc.scanned_seen; // stats mode: in-edges scanned
 		if (TR::narrow) {
 			if (hc.overflow_seen) c->stats.sssp_redo_batches++;
-			else c->stats.sssp_narrow_batches++;
+			else if (sizeof(S) == 2) c->stats.sssp_narrow_batches++;
+			else c->stats.sssp_narrow32_batches++;
 		}
 		if (TR::narrow && hc.overflow_seen) redo->push_back(r.batch);
 		else {
 			if constexpr (TR::narrow)
-				sssp16_result_kernel<<<1, L, 0, sl.st>>>(d_src + r.batch * L, d_dst + r.batch * L, sl.dist.as<S>(),
+				ssspn_result_kernel<typename TR::N><<<1, L, 0, sl.st>>>(d_src + r.batch * L, d_dst + r.batch * L, sl.dist.as<S>(),
 				                                         d_out + r.batch * L);
 			else
 				sssp_result_kernel<TR, T><<<1, L, 0, sl.st>>>(d_src + r.batch * L, d_dst + r.batch * L, sl.dist.as<S>(),
@@ -752,14 +767,27 @@ static int sssp_typed(Ctx *c, Csr *g, const LaneTable &lt, T *h_out) {
 	std::vector<int64_t> todo((size_t)lt.nbatch), redo;
 	for (int64_t b = 0; b < lt.nbatch; b++) todo[(size_t)b] = b;
 	if constexpr (std::is_same<T, long long>::value) {
-		if (g->w_nonneg && c->opt.sssp_narrow) {
+		// option sssp_narrow: 1 = 16-bit rows, then 32-bit rows for what did not fit; 2 = 32-bit rows only; 0 = neither
+		if (g->w_nonneg && c->opt.sssp_narrow == 1) {
 			if (!g->d_iw16.p && g->E > 0) {
 				PGQ_TRY(g->d_iw16.reserve((size_t)g->E * 2));
-				narrow_w_kernel<<<div_up(g->E, 256), 256, 0, st>>>(g->d_iw.as<long long>(), (uint32_t)g->E,
-				                                                   g->d_iw16.as<uint16_t>());
+				narrow_w_kernel<N16><<<div_up(g->E, 256), 256, 0, st>>>(g->d_iw.as<long long>(), (uint32_t)g->E,
+				                                                        g->d_iw16.as<uint16_t>());
 				count_launch(c);
 			}
 			PGQ_TRY((sssp_batches<Row16, T>(c, g, lt, todo, g->d_iw16.as<uint16_t>(), prune, d_out, d_src, d_dst,
+			                                &redo)));
+			todo.swap(redo);
+			redo.clear();
+		}
+		if (g->w_nonneg && c->opt.sssp_narrow && !todo.empty()) {
+			if (!g->d_iw32n.p && g->E > 0) {
+				PGQ_TRY(g->d_iw32n.reserve((size_t)g->E * 4));
+				narrow_w_kernel<N32><<<div_up(g->E, 256), 256, 0, st>>>(g->d_iw.as<long long>(), (uint32_t)g->E,
+				                                                        g->d_iw32n.as<uint32_t>());
+				count_launch(c);
+			}
+			PGQ_TRY((sssp_batches<Row32, T>(c, g, lt, todo, g->d_iw32n.as<uint32_t>(), prune, d_out, d_src, d_dst,
 			                                &redo)));
 			todo.swap(redo);
 			redo.clear();

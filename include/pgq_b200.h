@@ -74,7 +74,8 @@ typedef struct {
 	/* cheapest_path_length (levels = relaxation rounds; "stats"=1 also fills k_scanned / k_gathered with the
 	 * in-edges scanned and the source rows read) */
 	uint64_t sssp_narrow_batches; /* lane batches answered on 16-bit distance rows */
-	uint64_t sssp_redo_batches;   /* of the batches tried on 16-bit rows, those redone on 8-byte rows */
+	uint64_t sssp_redo_batches;   /* batches that did not fit their narrow rows and were redone on wider ones */
+	uint64_t sssp_narrow32_batches; /* lane batches answered on 32-bit distance rows */
 } pgq_stats_t;
 
 /* ---- context ------------------------------------------------------------------------- */
@@ -90,8 +91,8 @@ int pgq_device_count(pgq_ctx_t *ctx, int *out_n);
 int pgq_shutdown(pgq_ctx_t *ctx);
 const char *pgq_last_error(void); /* thread-local message of the last failing call */
 
-/* options (cheapest_path_length): "sssp_narrow" (1: 16-bit distance rows for non-negative int64 weights, exact,
- *          batches that do not fit are redone on 8-byte rows), "sssp_prune" (1: with non-negative weights, drop
+/* options (cheapest_path_length): "sssp_narrow" (non-negative int64 weights; 1: 16-bit distance rows, batches that do
+ *          not fit are redone on 32-bit rows, then on 8-byte rows; 2: 32-bit rows first; 0: 8-byte rows; all exact), "sssp_prune" (1: with non-negative weights, drop
  *          candidates that cannot beat the destination's distance), "sssp_slots" (1..4 lane batches in flight).
  * options: "lanes" (0=auto, 64,128,256,512), "stats" (0/1), "timing" (0/1),
  *          "small_max", "hub_min" (in-degree bin thresholds), "direction" (0 auto, 1 pull only),

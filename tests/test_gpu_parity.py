@@ -633,8 +633,8 @@ def test_cheapest_path_length_double_and_negative(ctx):
 @pytest.mark.parametrize("wcase", ["fits16", "overflow16", "huge", "zeros"])
 def test_cheapest_path_length_narrow_rows_and_bound(ctx, wcase):
     """Non-negative int64 weights run on 16-bit distance rows with the destination's distance as a bound; a batch
-    whose distances do not fit is redone on 8-byte rows.  Same bytes as the oracle in every case, and the same as
-    with both shortcuts switched off."""
+    whose distances do not fit is redone on 32-bit rows, and on 8-byte rows if they do not fit those either.  Same
+    bytes as the oracle in every case, and the same as with the shortcuts switched off."""
     V = 2500
     src, dst = orc.gen_knows(0x1dbc + 7, V, 30000)
     rng = np.random.default_rng(21)
@@ -654,10 +654,13 @@ def test_cheapest_path_length_narrow_rows_and_bound(ctx, wcase):
     st = ctx.stats()
     if wcase in ("fits16", "zeros"):
         assert st["sssp_narrow_batches"] == st["batches"] > 0 and st["sssp_redo_batches"] == 0, st
-    if wcase == "overflow16":
-        assert st["sssp_redo_batches"] > 0, st
+    if wcase == "overflow16":  # too long for 14 bits, fine for 30: redone once, on 32-bit rows
+        assert st["sssp_redo_batches"] == st["sssp_narrow32_batches"] > 0, st
+        assert st["sssp_narrow_batches"] + st["sssp_narrow32_batches"] == st["batches"] - st["sssp_redo_batches"], st
+    if wcase == "huge":  # weights past 2^30: some batches end on 8-byte rows after two redos
+        assert st["sssp_redo_batches"] > st["sssp_narrow32_batches"], st
     try:
-        for narrow, prune, slots in ((0, 1, 4), (1, 0, 1), (0, 0, 2)):
+        for narrow, prune, slots in ((0, 1, 4), (1, 0, 1), (0, 0, 2), (2, 1, 3)):
             ctx.set_option("sssp_narrow", narrow)
             ctx.set_option("sssp_prune", prune)
             ctx.set_option("sssp_slots", slots)
@@ -671,7 +674,7 @@ def test_cheapest_path_length_narrow_rows_and_bound(ctx, wcase):
     ctx.csr_delete(1)
 
 
-@pytest.mark.parametrize("kind", ["narrow", "wide", "double", "negative"])
+@pytest.mark.parametrize("kind", ["narrow", "narrow32", "wide", "double", "negative"])
 def test_cheapest_path_length_hub_chunks(ctx, kind):
     """In-lists above hub_min are relaxed chunk by chunk, the chunks' minima meeting through atomic minima (uint32,
     int64, and compare-and-swap for double): force that path on a small graph."""
@@ -689,7 +692,7 @@ def test_cheapest_path_length_hub_chunks(ctx, kind):
         w = rng.integers(0, 200, size=len(src)).astype(np.int64)
     ctx.set_option("hub_min", 8)
     ctx.set_option("hub_chunk", 256)
-    ctx.set_option("sssp_narrow", 0 if kind == "wide" else 1)
+    ctx.set_option("sssp_narrow", {"wide": 0, "narrow32": 2}.get(kind, 1))
     try:
         _weighted_case(ctx, V, src, dst, w, 260, 17)
         ctx.csr_delete(1)
