@@ -36,13 +36,8 @@ def main():
         r[m] = v
     agg = collections.OrderedDict()
     tot_ms = 0.0
-    # walk the launches in order: a batch starts at bfs_init_kernel; batches of the instrumented pass (they contain
-    # bfs_count_kernel and the STATS instantiations of the level kernels) do not count
-    batches_all = []
-    cur = None
     for r in rows.values():
         name = r["name"].replace("void ", "").replace("pgq::", "").split("(")[0]
-        base = name.split("<")[0]
         ms = r.get("gpu__time_duration.sum", 0.0)
         by = r.get("dram__bytes_read.sum", 0.0) + r.get("dram__bytes_write.sum", 0.0)
         a = agg.setdefault(name, [0, 0.0, 0.0])
@@ -50,22 +45,37 @@ def main():
         a[1] += ms
         a[2] += by
         tot_ms += ms
-        if base == "bfs_init_kernel":
-            cur = {"bytes": 0.0, "ms": 0.0, "stats": False, "levels": 0}
-            batches_all.append(cur)
-        if cur is None:
+    # Batches of several workers interleave in ncu's (serialised) launch order, so batches are NOT cut out of the list
+    # by position (round 2's first version did, and divided by too few batches: 31.7-41.5 GB per batch from the same
+    # per-kernel totals).  Instead: the instrumented pass launches the STATS=1 instantiations of the level kernels (last
+    # template argument), every other pass the STATS=0 ones, and every pass answers the same pairs, so
+    #   instrumented share = launches(STATS=1) / launches(STATS=0 or 1)   over the flagged kernels,
+    #   plain batches = bfs_init_kernel launches x (1 - share),
+    #   plain bytes = bytes of the STATS=0 instantiations + (1 - share) x bytes of the level kernels without the flag.
+    FLAGGED = ("pull_list_kernel", "pull_seg_kernel", "pull_tiny_kernel", "pull_warp_kernel", "pull_hub_kernel", "push_kernel")
+    n_init = agg.get("bfs_init_kernel", [0])[0]
+    l0 = l1 = 0
+    b0 = ms0 = bu = msu = 0.0
+    for name, (cnt, ms, by) in agg.items():
+        base = name.split("<")[0]
+        if base not in LEVEL:
             continue
-        if base == "bfs_count_kernel":
-            cur["stats"] = True
-        if base == "bfs_check_kernel":
-            cur["levels"] += 1
-        if base in LEVEL:
-            cur["bytes"] += by
-            cur["ms"] += ms
-    good = [b for b in batches_all if not b["stats"] and b["levels"] > 0]
-    batches = len(good)
-    lvl_bytes = sum(b["bytes"] for b in good)
-    lvl_ms = sum(b["ms"] for b in good)
+        if base in FLAGGED and "<" in name:
+            flag = name.rstrip(">").split(",")[-1].strip()
+            if flag == "1":
+                l1 += cnt
+            else:
+                l0 += cnt
+                b0 += by
+                ms0 += ms
+        else:
+            bu += by
+            msu += ms
+    share = l1 / (l0 + l1) if l0 + l1 else 0.0
+    batches = int(round(n_init * (1.0 - share)))
+    lvl_bytes = b0 + (1.0 - share) * bu
+    lvl_ms = ms0 + (1.0 - share) * msu
+    n_check = agg.get("bfs_check_kernel", [0])[0]
     summary = {
         "command": cmd,
         "src_hash": src_hash("msbfs"),
@@ -73,8 +83,8 @@ def main():
         "lanes": keys[2] if len(keys) > 2 else None,
         "note": "ncu --clock-control none launch list; per-launch times are cold-cache and serialised, "
                 "shares (not absolutes) are comparable with bench.py's CUDA-event numbers",
-        "batches_profiled": batches, "batches_skipped_instrumented_or_graph_launched": len(batches_all) - batches,
-        "levels_per_batch": sum(b["levels"] for b in good) / max(batches, 1),
+        "batches_profiled": batches, "batches_instrumented": n_init - batches,
+        "levels_per_batch": n_check / max(n_init, 1),
         "level_kernel_dram_bytes_per_batch": lvl_bytes / max(batches, 1),
         "level_kernel_ms_per_batch_under_ncu": lvl_ms / max(batches, 1),
         "level_kernel_share_of_all_kernel_time": lvl_ms / tot_ms if tot_ms else None,
