@@ -435,7 +435,24 @@ def bench_cheapest(ctx, csr_id, V, E, src, dst, nw, peak_gbs, with_parity):
     rd, secsd, std_ = timed(1)
     line["double_weights"] = {"pairs_per_s": nw / secsd, "ms": secsd * 1e3, "rounds": std_["levels"],
                               "same_values_as_int64": bool(np.array_equal(rd[0], res[0].astype(np.float64)) and
-                                                           np.array_equal(rd[1], res[1]))}
+                                                           np.array_equal(rd[1], res[1])),
+                              "what": "the same weights as DOUBLE: whole numbers, so the integer rows answer them with "
+                                      "the same bits (sums of whole-numbered doubles below 2^53 are exact)"}
+    wf = w.astype(np.float64) + 0.25
+    ctx.csr_set_weights(csr_id, wf)
+    rf, secsf, stf = timed(1)
+    line["double_weights_fractional"] = {"pairs_per_s": nw / secsf, "ms": secsf * 1e3, "rounds": stf["levels"],
+                                         "what": "weights + 0.25: 8-byte double rows (bound, chunks, sparse rounds, 4 in "
+                                                 "flight as for the integer rows)"}
+    if with_parity:
+        import orc
+        k = min(8, nw)
+        v_off, tgt, _ = ctx.csr_download(csr_id)
+        wcf = ctx.csr_download_weights(csr_id)
+        eo, ev, _ = orc.cheapest_path_length(V, v_off, tgt, wcf, src[:k], dst[:k])
+        line["double_weights_fractional"]["parity"] = {
+            "pairs": k, "vs_oracle": "identical" if (eo.tobytes() == rf[0][:k].tobytes() and
+                                                     np.array_equal(ev, rf[1][:k])) else "MISMATCH"}
     return line
 
 

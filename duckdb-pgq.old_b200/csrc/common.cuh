@@ -131,6 +131,9 @@ struct Csr {
 	DevBuf d_iw16;          // uint16[E] reverse-CSR order, int64 weights clamped to 0x4000 (16-bit distance rows, lazy)
 	DevBuf d_iw32n;         // uint32[E] reverse-CSR order, int64 weights clamped to 0x40000000 (32-bit distance rows, lazy)
 	DevBuf d_wstat;         // device: weight statistics (sssp.cu WStat)
+	TmpBuf d_iwi;           // int64[E] reverse-CSR order: DOUBLE weights that are all whole numbers, as integers (lazy;
+	                        // released with the object: every owner deletes the Csr right after free_all)
+	bool w_whole = false;   // DOUBLE weights, every one a non-negative whole number <= 2^20: integer rows give the same bits
 	bool w_nonneg = false;  // every weight >= 0 (and no NaN): the destination's distance bounds the search
 	// reverse CSR (lazy)
 	bool prepared = false;

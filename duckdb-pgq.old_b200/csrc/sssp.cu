@@ -202,16 +202,31 @@ __global__ void __launch_bounds__(256) gather_w_kernel(const unsigned long long 
 	if (i < n) out[i] = in[idx[i]];
 }
 
-// stat[0] = 1 when some weight is negative (or NaN)
+// Sums of whole-numbered doubles are exact while they stay below 2^53: with every weight a whole number of at most
+// 2^20 and fewer than 2^32 edges on a path, double weights can take the integer rows and give the same bits.
+static constexpr double SSSP_WHOLE_MAX = 1048576.0;
+
+// stat[0] bit 0: some weight is negative (or NaN); bit 1 (double weights): some weight is not a whole number <= 2^20
 __global__ void __launch_bounds__(256) wstat_kernel(const unsigned long long *__restrict__ w, uint32_t n, int f64,
                                                     uint32_t *__restrict__ stat) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	bool bad = false;
+	bool bad = false, frac = false;
 	if (i < n) {
-		if (f64) bad = !(__longlong_as_double((long long)w[i]) >= 0.0);
-		else bad = (long long)w[i] < 0;
+		if (f64) {
+			const double x = __longlong_as_double((long long)w[i]);
+			bad = !(x >= 0.0);
+			frac = !(x == floor(x) && x <= SSSP_WHOLE_MAX);
+		} else
+			bad = (long long)w[i] < 0;
 	}
-	if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(stat, 1u);
+	const uint32_t bits = (__any_sync(0xffffffffu, bad) ? 1u : 0u) | (__any_sync(0xffffffffu, frac) ? 2u : 0u);
+	if (bits && (threadIdx.x & 31) == 0) atomicOr(stat, bits);
+}
+
+// whole-numbered double weights as int64, and the int64 answers back as doubles (+inf = not reached)
+__global__ void __launch_bounds__(256) whole_w_kernel(const double *__restrict__ in, uint32_t n, long long *__restrict__ out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) out[i] = (long long)in[i];
 }
 
 template <class TR>
@@ -495,6 +510,7 @@ int csr_set_weights(Ctx *c, Csr *g, int wtype, const void *w, int64_t row0, int6
 		g->d_iw.release();
 		g->d_iw16.release();
 		g->d_iw32n.release();
+		g->d_iwi.release();
 		PGQ_TRY(g->d_w_in.reserve((size_t)(g->E > 0 ? g->E : 1) * 8));
 	}
 	if (n) {
@@ -525,7 +541,8 @@ int csr_set_weights(Ctx *c, Csr *g, int wtype, const void *w, int64_t row0, int6
 		uint32_t bad = 1;
 		PGQ_CUDA(cudaMemcpyAsync(&bad, g->d_wstat.p, 4, cudaMemcpyDeviceToHost, st));
 		PGQ_CUDA(cudaStreamSynchronize(st));
-		g->w_nonneg = bad == 0;
+		g->w_nonneg = (bad & 1u) == 0;
+		g->w_whole = wtype == PGQ_WEIGHT_F64 && bad == 0; // non-negative whole numbers stored as DOUBLE
 		g->w_ready = true;
 		g->w_rows = 0; // a later call starts a fresh set of weights
 	}
@@ -752,7 +769,7 @@ static int sssp_batches(Ctx *c, Csr *g, const LaneTable &lt, const std::vector<i
 
 // out8[slot] = distance of the lane slot (raw 8 bytes of T), +inf when the destination was not reached
 template <typename T>
-static int sssp_typed(Ctx *c, Csr *g, const LaneTable &lt, T *h_out) {
+static int sssp_typed(Ctx *c, Csr *g, const LaneTable &lt, T *h_out, const T *iw64) {
 	cudaStream_t st = c->stream;
 	const int L = SSSP_LANES;
 	const size_t nslots = (size_t)lt.nbatch * L;
@@ -771,7 +788,7 @@ static int sssp_typed(Ctx *c, Csr *g, const LaneTable &lt, T *h_out) {
 		if (g->w_nonneg && c->opt.sssp_narrow == 1) {
 			if (!g->d_iw16.p && g->E > 0) {
 				PGQ_TRY(g->d_iw16.reserve((size_t)g->E * 2));
-				narrow_w_kernel<N16><<<div_up(g->E, 256), 256, 0, st>>>(g->d_iw.as<long long>(), (uint32_t)g->E,
+				narrow_w_kernel<N16><<<div_up(g->E, 256), 256, 0, st>>>(iw64, (uint32_t)g->E,
 				                                                        g->d_iw16.as<uint16_t>());
 				count_launch(c);
 			}
@@ -783,7 +800,7 @@ static int sssp_typed(Ctx *c, Csr *g, const LaneTable &lt, T *h_out) {
 		if (g->w_nonneg && c->opt.sssp_narrow && !todo.empty()) {
 			if (!g->d_iw32n.p && g->E > 0) {
 				PGQ_TRY(g->d_iw32n.reserve((size_t)g->E * 4));
-				narrow_w_kernel<N32><<<div_up(g->E, 256), 256, 0, st>>>(g->d_iw.as<long long>(), (uint32_t)g->E,
+				narrow_w_kernel<N32><<<div_up(g->E, 256), 256, 0, st>>>(iw64, (uint32_t)g->E,
 				                                                        g->d_iw32n.as<uint32_t>());
 				count_launch(c);
 			}
@@ -794,7 +811,7 @@ static int sssp_typed(Ctx *c, Csr *g, const LaneTable &lt, T *h_out) {
 		}
 	}
 	if (!todo.empty())
-		PGQ_TRY((sssp_batches<Row64<T>, T>(c, g, lt, todo, g->d_iw.as<T>(), prune, d_out, d_src, d_dst, &redo)));
+		PGQ_TRY((sssp_batches<Row64<T>, T>(c, g, lt, todo, iw64, prune, d_out, d_src, d_dst, &redo)));
 	PGQ_CUDA(cudaMemcpyAsync(h_out, d_out, nslots * sizeof(T), cudaMemcpyDeviceToHost, st));
 	PGQ_CUDA(cudaStreamSynchronize(st));
 	c->stats.d2h_bytes += (uint64_t)nslots * sizeof(T);
@@ -816,8 +833,27 @@ int sssp_run(Ctx *c, Csr *g, const LaneTable &lt, void *h_out8) {
 		                                                          g->d_iw.as<unsigned long long>());
 		count_launch(c);
 	}
-	if (g->wtype == PGQ_WEIGHT_I64) return sssp_typed<long long>(c, g, lt, static_cast<long long *>(h_out8));
-	return sssp_typed<double>(c, g, lt, static_cast<double *>(h_out8));
+	if (g->wtype == PGQ_WEIGHT_I64)
+		return sssp_typed<long long>(c, g, lt, static_cast<long long *>(h_out8), g->d_iw.as<long long>());
+	if (g->w_whole && c->opt.sssp_narrow && g->E > 0) {
+		// DOUBLE weights that are all non-negative whole numbers: the integer rows give the same bits (see SSSP_WHOLE_MAX)
+		if (!g->d_iwi.p) {
+			PGQ_TRY(g->d_iwi.reserve((size_t)g->E * 8));
+			whole_w_kernel<<<div_up(g->E, 256), 256, 0, c->stream>>>(g->d_iw.as<double>(), (uint32_t)g->E,
+			                                                         g->d_iwi.as<long long>());
+			count_launch(c);
+		}
+		long long *hi = static_cast<long long *>(h_out8);
+		PGQ_TRY(sssp_typed<long long>(c, g, lt, hi, g->d_iwi.as<long long>()));
+		double *hd = static_cast<double *>(h_out8);
+		const size_t nslots = (size_t)lt.nbatch * SSSP_LANES;
+		for (size_t k = 0; k < nslots; k++) {
+			const long long v = hi[k]; // read before the same 8 bytes are rewritten
+			hd[k] = WInf<long long>::is_inf(v) ? WInf<double>::value() : (double)v;
+		}
+		return PGQ_OK;
+	}
+	return sssp_typed<double>(c, g, lt, static_cast<double *>(h_out8), g->d_iw.as<double>());
 }
 
 } // namespace pgq

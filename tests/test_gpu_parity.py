@@ -702,6 +702,35 @@ def test_cheapest_path_length_hub_chunks(ctx, kind):
         ctx.set_option("sssp_narrow", 1)
 
 
+def test_cheapest_path_length_whole_numbered_doubles(ctx):
+    """DOUBLE weights that are all non-negative whole numbers take the integer rows (sums of such doubles are exact, so
+    the bits are the oracle's); one fractional weight, and the same graph runs on 8-byte double rows."""
+    V = 2500
+    src, dst = orc.gen_knows(0x1dbc + 9, V, 30000)
+    w = np.random.default_rng(41).integers(0, 300, size=len(src)).astype(np.float64)
+    _weighted_case(ctx, V, src, dst, w, 300, 11)
+    ctx.reset_stats()
+    v, e, _ = orc.csr_build(V, src, dst, want_eids=False)
+    ps, pd = orc.gen_pairs(3, V, v, 128)
+    ctx.cheapest_path_length(1, ps, pd)
+    st = ctx.stats()
+    assert st["sssp_narrow_batches"] == st["batches"] == 2, st
+    ctx.csr_delete(1)
+    w[17] = 2.5
+    _weighted_case(ctx, V, src, dst, w, 300, 11)
+    ctx.reset_stats()
+    ctx.cheapest_path_length(1, ps, pd)
+    st = ctx.stats()
+    assert st["sssp_narrow_batches"] == 0 and st["sssp_narrow32_batches"] == 0, st
+    ctx.csr_delete(1)
+    w[17] = 3.0e6  # whole, but past the bound that keeps every sum exact: double rows again
+    _weighted_case(ctx, V, src, dst, w, 300, 11)
+    ctx.reset_stats()
+    ctx.cheapest_path_length(1, ps, pd)
+    assert ctx.stats()["sssp_narrow_batches"] == 0
+    ctx.csr_delete(1)
+
+
 def test_cheapest_path_length_errors(ctx):
     src = np.array([0, 1, 2], dtype=np.int64)
     dst = np.array([1, 2, 0], dtype=np.int64)
