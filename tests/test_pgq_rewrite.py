@@ -159,6 +159,26 @@ SELECT count(*) FROM GRAPH_TABLE (snb MATCH (a:Person)-[k:knows]->*(b:Person) CO
     assert r[-1][1] == ["10"]  # stand-in reachability: src rowid <= dst rowid, 4 + 3 + 2 + 1 pairs
 
 
+@needs_host
+def test_rewritten_sql_binds_against_the_real_functions():
+    """The extension LOADs without a GPU (calls fail loudly, binding works), so EXPLAIN of the rewritten statements
+    checks every generated call against the registered signatures: 4- and 6-argument iterativelength, reachability,
+    shortestpath, shortestpath_with_edges, cheapest_path_length / _double with the 7-argument create_csr_edge."""
+    qs = ["SELECT * FROM GRAPH_TABLE (snb MATCH p = ANY SHORTEST (a:Person WHERE a.id = 10)-[k:knows]->*(b:Person) "
+          "COLUMNS (a.id, b.id, path_length(p) AS len, vertices(p) AS vs, path_with_edges(p) AS pe))",
+          "SELECT * FROM GRAPH_TABLE (snb MATCH p = ANY SHORTEST (a:Person)-[k:knows]->{2,5}(b:Person) COLUMNS (path_length(p) AS len))",
+          "SELECT * FROM GRAPH_TABLE (snb MATCH (a:Person)<-[k:knows]-+(b:Person) COLUMNS (a.id, b.id))",
+          "SELECT * FROM GRAPH_TABLE (snb MATCH (a:Person)-[k:knows]->*(b:Person) COLUMNS (a.id, b.id))",
+          "SELECT * FROM GRAPH_TABLE (snb MATCH p = ANY SHORTEST (a:Person)-[k:knows]->*(b:Person) COLUMNS (cheapest_path_length(p, k.w) AS c))",
+          "SELECT * FROM GRAPH_TABLE (snb MATCH p = ANY SHORTEST (a:Person)-[k:knows]->*(b:Person) "
+          "COLUMNS (cheapest_path_length_double(p, k.wd) AS c))"]
+    sql = ("LOAD '%s';\nCREATE TABLE person(id BIGINT);\nCREATE TABLE knows(p1 BIGINT, p2 BIGINT, w BIGINT, wd DOUBLE);\n" % EXT
+           + GRAPH + "".join("EXPLAIN " + q + ";\n" for q in qs))
+    r = run_sql(sql)
+    assert [k for k, _ in r] == ["result"] * len(r), [x for x in r if x[0] != "result"]
+    assert all(len(rows) > 5 for _, rows in r[4:])  # a plan came back for every statement
+
+
 @pytest.mark.gpu
 @needs_host
 def test_graph_table_queries_match_the_oracle(tmp_path):
