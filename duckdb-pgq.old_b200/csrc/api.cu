@@ -263,6 +263,14 @@ int ctx_init_resources(Ctx *c) {
 	PGQ_CUDA(cudaEventCreate(&c->ev_timer2));
 	PGQ_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
 	PGQ_CUDA(cudaHostAlloc(&c->h_ctrl, 4096, cudaHostAllocDefault));
+	if (const char *fg = getenv("PGQ_B200_L2_FETCH")) { // A/B knob: cudaLimitMaxL2FetchGranularity (32, 64 or 128 bytes)
+		const int bytes = atoi(fg);
+		if (bytes == 32 || bytes == 64 || bytes == 128) (void)cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)bytes);
+		size_t got = 0;
+		if (cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity) == cudaSuccess && getenv("PGQ_B200_VERBOSE"))
+			fprintf(stderr, "[pgq] L2 fetch granularity %zu bytes\n", got);
+		(void)cudaGetLastError();
+	}
 	return PGQ_OK;
 }
 

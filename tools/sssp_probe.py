@@ -17,6 +17,8 @@ v_off = np.empty(V + 2, dtype=np.int64)
 ctx._chk(ctx.lib.pgq_csr_download(ctx._ctx, 5, v_off.ctypes.data_as(pgq_b200.I64P), None, None))
 src, dst = make_pairs(V, v_off, max(n, 1024), 7)
 w = np.random.default_rng(4243).integers(1, 101, size=E).astype(np.int64)
+if os.environ.get("PROBE_DOUBLE"):
+    w = w.astype(np.float64) + 0.25  # fractional: the 8-byte double rows
 ctx.csr_set_weights(5, w)
 for kv in sys.argv[2:]:
     k, v = kv.split("=")
