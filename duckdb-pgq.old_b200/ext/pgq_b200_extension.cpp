@@ -42,6 +42,7 @@
 #include <vector>
 
 #include "../../include/pgq_b200.h"
+#include "pgq_rewrite.hpp"
 
 namespace duckdb {
 
@@ -785,6 +786,45 @@ static void BatcherStatsFunction(DataChunk &args, ExpressionState &state, Vector
 	for (idx_t i = 0; i < count; i++) out[i] = StringVector::AddString(result, text);
 }
 
+// ---- pgq_rewrite(VARCHAR statement) -> VARCHAR: the SQL/PGQ rewriter (pgq_rewrite.hpp) for clients that cannot put it
+// in front of the parser: CREATE / DROP PROPERTY GRAPH register in a process-wide catalog and return '', a statement
+// with GRAPH_TABLE comes back as plain SQL (the query first, then one "SELECT delete_csr(id);" per CSR it builds, one
+// statement per line), anything else comes back unchanged.  The client runs what it gets.  Errors raise. -------------
+static void RewriteFunction(DataChunk &args, ExpressionState &state, Vector &result) {
+	static std::mutex mu;
+	static pgq_rewrite::Rewriter rewriter;
+	const idx_t count = args.size();
+	result.SetVectorType(VectorType::FLAT_VECTOR);
+	VectorData vd;
+	args.data[0].Orrify(count, vd);
+	auto in = (const string_t *)vd.data;
+	auto out = FlatVector::GetData<string_t>(result);
+	for (idx_t i = 0; i < count; i++) {
+		const idx_t k = vd.sel->get_index(i);
+		if (!vd.validity.RowIsValid(k)) {
+			FlatVector::Validity(result).SetInvalid(i);
+			continue;
+		}
+		const string text = in[k].GetString();
+		pgq_rewrite::Result r;
+		{
+			std::lock_guard<std::mutex> l(mu);
+			r = rewriter.rewrite(text);
+		}
+		if (!r.error.empty()) throw InvalidInputException(r.error);
+		string res;
+		if (!r.handled) res = text;
+		else
+			for (auto &q : r.statements) {
+				string one = q;
+				for (auto &ch : one)
+					if (ch == '\n') ch = ' ';
+				res += (res.empty() ? "" : "\n") + one;
+			}
+		out[i] = StringVector::AddString(result, res);
+	}
+}
+
 static void Register(ClientContext &context, Catalog &catalog, const string &name, vector<LogicalType> args,
                      LogicalType ret, scalar_function_t fn) {
 	ScalarFunction f(name, move(args), move(ret), move(fn), /*has_side_effects=*/true, PgqBind);
@@ -841,6 +881,7 @@ DUCKDB_EXTENSION_API void pgq_b200_init(duckdb::DatabaseInstance &db) {
 	         CheapestPathLengthFunction<true>);
 	Register(context, catalog, "delete_csr", {I}, BO, DeleteCsrFunction);
 	Register(context, catalog, "pgq_batcher_stats", {I}, LogicalType::VARCHAR, BatcherStatsFunction);
+	Register(context, catalog, "pgq_rewrite", {LogicalType::VARCHAR}, LogicalType::VARCHAR, RewriteFunction);
 	con.Commit();
 }
 

@@ -179,6 +179,26 @@ def test_rewritten_sql_binds_against_the_real_functions():
     assert all(len(rows) > 5 for _, rows in r[4:])  # a plan came back for every statement
 
 
+@needs_host
+def test_pgq_rewrite_scalar_function_of_the_extension():
+    """Clients that cannot hook the parser ask the extension: SELECT pgq_rewrite(statement) returns what to run."""
+    q = "SELECT * FROM GRAPH_TABLE (g MATCH p = ANY SHORTEST (a)-[k]->*(b) COLUMNS (path_length(p) AS len))"
+    sql = ("LOAD '%s';\n" % EXT +
+           "SELECT pgq_rewrite('CREATE PROPERTY GRAPH g VERTEX TABLES (person) EDGE TABLES (knows SOURCE KEY (p1) REFERENCES "
+           "person (id) DESTINATION KEY (p2) REFERENCES person (id))');\n"
+           "SELECT pgq_rewrite('%s');\nSELECT pgq_rewrite('SELECT 42');\nSELECT pgq_rewrite(NULL);\n"
+           "SELECT pgq_rewrite('SELECT * FROM GRAPH_TABLE (nope MATCH (a)-[k]->(b) COLUMNS (a.id))');\n" % q)
+    r = run_sql(sql)
+    assert r[1] == ("result", [""])
+    assert r[2][0] == "result" and len(r[2][1]) == 2
+    assert r[2][1][0].startswith("WITH __pgq_csr") and "iterativelength(" in r[2][1][0]
+    assert r[2][1][1].startswith("SELECT delete_csr(")
+    assert "person a, person b WHERE iterativelength(" in r[2][1][0]
+    assert r[3] == ("result", ["SELECT 42"])
+    assert r[4] == ("result", ["NULL"])
+    assert r[5][0] == "error" and "does not exist" in r[5][1]
+
+
 @pytest.mark.gpu
 @needs_host
 def test_graph_table_queries_match_the_oracle(tmp_path):
